@@ -1,0 +1,235 @@
+/*
+ * me_gpu.h - C-ABI of the B200 open-loop motion-estimation engine.
+ *
+ * Drop-in boundary for SVT-AV1-PSYEX's per-picture ME path.
+ * Plain C, host pointers and sizes only; no CUDA or torch types.
+ *
+ * What each entry point replaces in the reference (paths under Source/Lib/Codec):
+ *   me_gpu_register_picture  <- svt_aom_downsample_filtering_input_picture
+ *                               (pic_analysis_process.c:2139) + svt_aom_generate_padding
+ *                               (pic_operators.c:397) + the PA reference object planes
+ *                               (reference_object.c:249-295)
+ *   me_gpu_submit / _wait    <- the b64 loop of svt_aom_motion_estimation_kernel
+ *                               (me_process.c:174-290) calling
+ *                               svt_aom_motion_estimation_b64 (motion_estimation.c:3076)
+ *   me_gpu_release_picture   <- svt_aom_release_pa_reference_objects (reference_object.c:406)
+ *   MeGpuParams              <- the MeContext control fields written by
+ *                               svt_aom_sig_deriv_me (enc_mode_config.c:681-828) and
+ *                               me_process.c:195-262, plus the pcs/scs scalars that
+ *                               motion_estimation.c reads
+ *   MeGpuOutputs             <- pcs->pa_me_data->me_results[b64] (me_sb_results.h:28-51) and the
+ *                               per-b64 pcs arrays written by compute_distortion /
+ *                               perform_gm_detection (motion_estimation.c:2964,2838)
+ *
+ * There is no CPU fallback behind this interface: every call fails with
+ * ME_GPU_ERR_NO_DEVICE when no CUDA device is usable.
+ */
+#ifndef ME_GPU_H
+#define ME_GPU_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ME_GPU_MAX_LISTS 2 /* MAX_NUM_OF_REF_PIC_LIST, definitions.h:2337 */
+#define ME_GPU_MAX_REFS 4 /* MAX_REF_IDX / REF_LIST_MAX_DEPTH, definitions.h:2352 */
+#define ME_GPU_SQUARE_PU_COUNT 85 /* SQUARE_PU_COUNT, me_sb_results.h:23 */
+#define ME_GPU_SEARCH_REGIONS 2 /* SEARCH_REGION_COUNT, me_context.h:320 */
+
+#define ME_GPU_SUB_SAD_SEARCH 0 /* definitions.h:2071 */
+#define ME_GPU_FULL_SAD_SEARCH 1
+
+/* error codes (0 = ok); the host maps non-zero to EB_ErrorInsufficientResources / EB_ErrorUndefined */
+#define ME_GPU_OK 0
+#define ME_GPU_ERR_NO_DEVICE -1
+#define ME_GPU_ERR_BAD_ARG -2
+#define ME_GPU_ERR_NOT_FOUND -3
+#define ME_GPU_ERR_NO_MEMORY -4
+#define ME_GPU_ERR_UNSUPPORTED -5
+#define ME_GPU_ERR_CUDA -6
+#define ME_GPU_ERR_STATE -7
+
+typedef struct MeGpuSearchArea { /* SearchArea, me_context.h:321 */
+    uint16_t width;
+    uint16_t height;
+} MeGpuSearchArea;
+
+typedef struct MeGpuSearchAreaMinMax { /* SearchAreaMinMax, me_context.h:325 */
+    MeGpuSearchArea sa_min;
+    MeGpuSearchArea sa_max;
+} MeGpuSearchAreaMinMax;
+
+/* Flat copy of every input svt_aom_motion_estimation_b64 reads besides pixels. */
+typedef struct MeGpuParams {
+    /* ---- pcs / scs scalars ---- */
+    uint64_t picture_number; /* pcs->picture_number */
+    uint8_t  input_resolution; /* scs->input_resolution (EbInputResolution, definitions.h:2079) */
+    uint8_t  enable_me_8x8; /* pcs->enable_me_8x8 */
+    uint8_t  enable_me_16x16; /* pcs->enable_me_16x16 */
+    uint8_t  max_number_of_pus_per_sb; /* pcs->max_number_of_pus_per_sb (85) */
+    uint8_t  gm_enabled; /* pcs->gm_ctrls.enabled */
+    uint8_t  gm_use_distance_based_active_th; /* pcs->gm_ctrls.use_distance_based_active_th */
+    uint8_t  hierarchical_levels; /* pcs->hierarchical_levels */
+    uint8_t  pcs_temporal_layer_index; /* pcs->temporal_layer_index */
+    uint8_t  similar_brightness_refs; /* pcs->similar_brightness_refs */
+    uint8_t  only_l_bwd; /* scs->mrp_ctrls.only_l_bwd */
+    uint8_t  max_cand; /* pcs->pa_me_data->max_cand */
+    uint8_t  max_refs; /* pcs->pa_me_data->max_refs */
+    uint8_t  max_l0; /* pcs->pa_me_data->max_l0 */
+    /* ---- per-item MeContext fields, me_process.c:219-262 ---- */
+    uint8_t num_of_list_to_search;
+    uint8_t num_of_ref_pic_to_search[ME_GPU_MAX_LISTS];
+    uint8_t temporal_layer_index; /* me_ctx->temporal_layer_index */
+    uint8_t is_ref;
+    /* ---- controls written by svt_aom_sig_deriv_me ---- */
+    uint8_t  enable_hme_flag;
+    uint8_t  enable_hme_level0_flag;
+    uint8_t  enable_hme_level1_flag;
+    uint8_t  enable_hme_level2_flag;
+    uint8_t  hme_search_method; /* ME_GPU_SUB_SAD_SEARCH for TASK_PAME */
+    uint8_t  me_search_method;
+    uint8_t  use_best_unipred_cand_only;
+    uint8_t  reduce_hme_l0_sr_th_min;
+    uint8_t  reduce_hme_l0_sr_th_max;
+    uint16_t num_hme_sa_w; /* always 2 (get_worst_quadrant asserts it) */
+    uint16_t num_hme_sa_h;
+    MeGpuSearchAreaMinMax me_sa;
+    MeGpuSearchAreaMinMax hme_l0_sa;
+    MeGpuSearchArea       hme_l1_sa;
+    MeGpuSearchArea       hme_l2_sa;
+    /* MeHmeRefPruneCtrls, me_context.h:280 */
+    uint8_t  enable_me_hme_ref_pruning;
+    uint16_t prune_ref_if_hme_sad_dev_bigger_than_th;
+    uint16_t prune_ref_if_me_sad_dev_bigger_than_th;
+    uint32_t zz_sad_th;
+    uint16_t zz_sad_pct;
+    uint32_t phme_sad_th;
+    uint16_t phme_sad_pct;
+    /* MeSrCtrls, me_context.h:292 */
+    uint8_t  enable_me_sr_adjustment;
+    uint16_t reduce_me_sr_based_on_mv_length_th;
+    uint16_t stationary_hme_sad_abs_th;
+    uint16_t stationary_me_sr_divisor;
+    uint16_t reduce_me_sr_based_on_hme_sad_abs_th;
+    uint16_t me_sr_divisor_for_low_hme_sad;
+    uint8_t  distance_based_hme_resizing;
+    /* Me8x8VarCtrls, me_context.h:310 */
+    uint8_t  me_8x8_var_enabled;
+    uint32_t me_sr_div4_th;
+    uint32_t me_sr_div2_th;
+    uint32_t me_sr_mult2_th;
+    /* MvBasedSearchAdj, me_context.h:356 */
+    uint8_t  mv_sa_adj_enabled;
+    uint8_t  mv_sa_adj_nearest_ref_only;
+    uint16_t mv_sa_adj_mv_size_th;
+    uint16_t mv_sa_adj_sa_multiplier;
+    /* PreHmeCtrls, me_context.h:336 */
+    uint8_t               prehme_enable;
+    uint8_t               prehme_skip_search_line;
+    uint8_t               prehme_l1_early_exit;
+    MeGpuSearchAreaMinMax prehme_sa_cfg[ME_GPU_SEARCH_REGIONS];
+    /* remaining scalars */
+    int32_t  prune_me_candidates_th;
+    uint32_t me_early_exit_th;
+    uint32_t me_safe_limit_zz_th;
+    uint32_t prev_me_stage_based_exit_th;
+} MeGpuParams;
+
+/* What the encoder knows before svt_aom_sig_deriv_me runs; input of me_gpu_derive_params(). */
+typedef struct MeGpuEncoderConfig {
+    int8_t   enc_mode; /* ENC_MRS=-3, ENC_MRP=-2, ENC_MR=-1, ENC_M0=0 ... ENC_M13 (definitions.h EncMode) */
+    uint8_t  rtc_tune; /* pred_structure == SVT_AV1_PRED_LOW_DELAY_B */
+    uint8_t  sc_class1; /* screen-content class */
+    uint8_t  qp; /* static_config.qp (default 35) */
+    uint8_t  rate_control_vbr; /* static_config.rate_control_mode == VBR */
+    uint8_t  fast_decode; /* static_config.fast_decode */
+    uint8_t  hierarchical_levels; /* 4 for a 16-picture mini-GOP */
+    uint8_t  temporal_layer_index;
+    uint8_t  is_ref;
+    uint8_t  slice_type; /* 0 = B_SLICE, 1 = P_SLICE (definitions.h SliceType); I pictures are skipped */
+    uint8_t  similar_brightness_refs;
+    uint8_t  low_frame_rate; /* scs->frame_rate >> 16 != 0 */
+    int8_t   force_ref_l0; /* >0: override the mrp-level reference counts (BASELINE config labels) */
+    int8_t   force_ref_l1;
+    uint16_t width; /* luma size, multiple of 8 */
+    uint16_t height;
+    uint64_t picture_number;
+} MeGpuEncoderConfig;
+
+/* Per-picture results in caller-owned host memory. Array extents:
+ *   b64_count = ceil(w/64)*ceil(h/64); P = number of exported PUs (85 / 21 / 5, pcs.c:108-117). */
+typedef struct MeGpuOutputs {
+    uint32_t b64_count; /* in: capacity in b64s; out: b64s written */
+    uint32_t pu_count; /* out: P */
+    /* MeSbResults images, one contiguous slab per array (b64-major) */
+    uint8_t  *total_me_candidate_index; /* [b64][P] */
+    uint8_t  *me_candidate_array; /* [b64][P*max_cand], MeCandidate bitfield bytes */
+    uint32_t *me_mv_array; /* [b64][P*max_refs], MvCandidate.as_int */
+    /* per-b64 pcs arrays */
+    uint32_t *me_64x64_distortion;
+    uint32_t *me_32x32_distortion;
+    uint32_t *me_16x16_distortion;
+    uint32_t *me_8x8_distortion;
+    uint32_t *me_8x8_cost_variance;
+    uint32_t *rc_me_distortion;
+    uint8_t  *stationary_block_present_sb;
+    uint8_t  *rc_me_allow_gm;
+    /* optional parity/debug taps (may be NULL): MeContext state after the b64 finished */
+    uint32_t *p_sb_best_sad; /* [b64][2][4][85] */
+    uint32_t *p_sb_best_mv; /* [b64][2][4][85] */
+    int16_t  *hme_search_centre; /* [b64][2][4][2] (hme_sc_x, hme_sc_y) */
+    uint64_t *hme_sad; /* [b64][2][4] search_results.hme_sad at exit */
+    uint8_t  *do_ref; /* [b64][2][4] */
+    int16_t  *search_area; /* [b64][2][4][4] final (origin_x, origin_y, width, height) of the integer search */
+} MeGpuOutputs;
+
+/* library / device lifecycle ------------------------------------------------------------- */
+int me_gpu_init(int device_count, const int *device_ids, int max_width, int max_height, int max_refs_l0,
+                int max_refs_l1, int pictures_in_flight);
+void me_gpu_shutdown(void);
+const char *me_gpu_last_error(void);
+int me_gpu_device_count(void);
+
+/* pictures ------------------------------------------------------------------------------- */
+/* y8b_padded points at the first byte of the padded luma plane (buffer_y), stride bytes per row,
+ * picture origin at (org_x, org_y); the caller has already edge-replicated the padding
+ * (svt_aom_pad_input_pictures). The 1/4 and 1/16 planes are built and padded on the device. */
+int me_gpu_register_picture(uint64_t picture_number, const uint8_t *y8b_padded, int stride, int org_x, int org_y,
+                            int width, int height);
+/* same, source plane without padding (stride >= width): padding of 68 is generated on the device */
+int me_gpu_register_picture_unpadded(uint64_t picture_number, const uint8_t *y8b, int stride, int width,
+                                     int height);
+int  me_gpu_release_picture(uint64_t picture_number);
+/* copy the device pyramids back (parity tests): planes are full padded images; any pointer may be NULL */
+int me_gpu_read_pyramid(uint64_t picture_number, uint8_t *full, uint8_t *quarter, uint8_t *sixteenth);
+/* plane geometry helper: level 0 = full (pad 68), 1 = quarter (pad 32), 2 = sixteenth (pad 16) */
+int me_gpu_plane_geometry(int width, int height, int level, int *plane_w, int *plane_h, int *pad, int *stride,
+                          int *rows);
+
+/* motion estimation ----------------------------------------------------------------------- */
+int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
+                  const uint64_t ref_picture_numbers[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS]);
+int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out);
+
+/* host-side restatement of svt_aom_sig_deriv_me and the pcs/scs settings it depends on */
+int me_gpu_derive_params(const MeGpuEncoderConfig *cfg, MeGpuParams *params);
+
+/* measurement taps used by bench.py ------------------------------------------------------- */
+/* device-only timing of the last waited picture on its stream (ms), per stage */
+typedef struct MeGpuTimings {
+    float pyramid_ms;
+    float hme_ms;
+    float search_ms;
+    float epilogue_ms;
+    float total_ms;
+    uint64_t kernel_launches; /* cumulative launches of this library's kernels */
+    uint64_t byte_sad_ops; /* algorithmic byte-SAD count of the last waited picture */
+} MeGpuTimings;
+int me_gpu_get_timings(MeGpuTimings *t);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ME_GPU_H */

@@ -1,0 +1,400 @@
+/*
+ * ref_harness.c - thin driver around the UNMODIFIED reference sources (compiled in place from
+ * /root/reference by oracle/Makefile into oracle/_ref/libme_ref.so). TEST INFRASTRUCTURE ONLY.
+ *
+ * It builds the minimum PictureParentControlSet / SequenceControlSet / MeContext state that
+ * svt_aom_motion_estimation_b64 (Codec/motion_estimation.c:3076) reads, calls the reference function
+ * for every 64x64 block, and returns results in the MeGpuOutputs layout so that the restatement
+ * (me_oracle*.c) and the CUDA engine can be compared with it byte for byte.
+ *
+ * No reference source is copied: this file only includes the reference headers and calls its symbols.
+ */
+#include <stdlib.h>
+#include <string.h>
+
+#define RTCD_C
+#include "common_dsp_rtcd.h"
+#include "aom_dsp_rtcd.h"
+#include "pcs.h"
+#include "sequence_control_set.h"
+#include "motion_estimation.h"
+#include "me_context.h"
+#include "me_sad_calculation.h"
+#include "compute_sad_c.h"
+#include "pic_operators.h"
+#include "enc_mode_config.h"
+
+#include "me_oracle.h"
+
+#define REF_API __attribute__((visibility("default")))
+
+/* symbols the few reference translation units we link expect from the rest of the library */
+void svt_aom_downsample_filtering_input_picture(PictureParentControlSet *pcs, EbPictureBufferDesc *input_padded_pic,
+                                                EbPictureBufferDesc *quarter_picture_ptr,
+                                                EbPictureBufferDesc *sixteenth_picture_ptr);
+
+
+static int g_simd_level = -1;
+
+/* svt_memcpy is an RTCD pointer (Codec/common_dsp_rtcd.h:1071); plain memcpy has its semantics */
+static void harness_memcpy(void *dst, void const *src, size_t n) { memcpy(dst, src, n); }
+
+/* RTCD pointers on the ME path (Codec/aom_dsp_rtcd.c:501-515). level 0 = the _c specification. */
+static void set_rtcd(int level) {
+    if (g_simd_level == level)
+        return;
+    svt_sad_loop_kernel                       = svt_sad_loop_kernel_c;
+    svt_ext_all_sad_calculation_8x8_16x16     = svt_ext_all_sad_calculation_8x8_16x16_c;
+    svt_ext_eight_sad_calculation_32x32_64x64 = svt_ext_eight_sad_calculation_32x32_64x64_c;
+    svt_ext_sad_calculation_8x8_16x16         = svt_ext_sad_calculation_8x8_16x16_c;
+    svt_ext_sad_calculation_32x32_64x64       = svt_ext_sad_calculation_32x32_64x64_c;
+    svt_nxm_sad_kernel                        = svt_nxm_sad_kernel_helper_c;
+    svt_initialize_buffer_32bits              = svt_initialize_buffer_32bits_c;
+    downsample_2d                             = svt_aom_downsample_2d_c;
+    svt_memcpy                                = harness_memcpy;
+#ifdef REF_HAVE_SIMD
+    if (level >= 1) {
+        svt_sad_loop_kernel                       = svt_sad_loop_kernel_avx2_intrin;
+        svt_ext_all_sad_calculation_8x8_16x16     = svt_ext_all_sad_calculation_8x8_16x16_avx2;
+        svt_ext_eight_sad_calculation_32x32_64x64 = svt_ext_eight_sad_calculation_32x32_64x64_avx2;
+        svt_ext_sad_calculation_8x8_16x16         = svt_ext_sad_calculation_8x8_16x16_avx2_intrin;
+        svt_ext_sad_calculation_32x32_64x64       = svt_ext_sad_calculation_32x32_64x64_sse4_intrin;
+        svt_nxm_sad_kernel                        = svt_nxm_sad_kernel_helper_avx2;
+        svt_initialize_buffer_32bits              = svt_initialize_buffer_32bits_sse2_intrin;
+    }
+    if (level >= 2) {
+        svt_sad_loop_kernel = svt_sad_loop_kernel_avx512_intrin;
+        svt_nxm_sad_kernel  = svt_nxm_sad_kernel_helper_avx512;
+    }
+#endif
+    g_simd_level = level;
+}
+
+REF_API int ref_simd_available(void) {
+#ifdef REF_HAVE_SIMD
+    return 1;
+#else
+    return 0;
+#endif
+}
+
+static void desc_from_plane(EbPictureBufferDesc *d, const OraclePlane *p) {
+    memset(d, 0, sizeof *d);
+    d->buffer_y   = p->buf;
+    d->stride_y   = (uint16_t)p->stride;
+    d->org_x      = (uint16_t)p->org_x;
+    d->org_y      = (uint16_t)p->org_y;
+    d->width      = (uint16_t)p->width;
+    d->height     = (uint16_t)p->height;
+    d->max_width  = (uint16_t)p->width;
+    d->max_height = (uint16_t)p->height;
+    d->bit_depth  = EB_EIGHT_BIT;
+}
+
+/* leaf kernels of the reference, for the kernel-level tests --------------------------------- */
+REF_API void ref_downsample_2d(uint8_t *in, uint32_t in_stride, uint32_t w, uint32_t h, uint8_t *out, uint32_t out_stride,
+                       uint32_t step) {
+    svt_aom_downsample_2d_c(in, in_stride, w, h, out, out_stride, step);
+}
+REF_API void ref_sad_loop(uint8_t *src, uint32_t src_stride, uint8_t *ref, uint32_t ref_stride, uint32_t bh, uint32_t bw,
+                  uint64_t *best, int16_t *x, int16_t *y, uint32_t raw, uint8_t skip, int16_t sw, int16_t sh) {
+    svt_sad_loop_kernel_c(src, src_stride, ref, ref_stride, bh, bw, best, x, y, raw, skip, sw, sh);
+}
+
+/* svt_aom_downsample_filtering_input_picture + paddings on caller-provided planes */
+REF_API int ref_build_pyramid(OraclePicture *pic) {
+    set_rtcd(0);
+    PictureParentControlSet *pcs = calloc(1, sizeof *pcs);
+    if (!pcs)
+        return -1;
+    pcs->enable_hme_flag = pcs->enable_hme_level0_flag = pcs->enable_hme_level1_flag = 1;
+    EbPictureBufferDesc f, q, s;
+    desc_from_plane(&f, &pic->full);
+    desc_from_plane(&q, &pic->quarter);
+    desc_from_plane(&s, &pic->sixteenth);
+    svt_aom_downsample_filtering_input_picture(pcs, &f, &q, &s);
+    free(pcs);
+    return 0;
+}
+/* svt_aom_generate_padding on the full plane (what svt_aom_pad_input_pictures does for luma) */
+REF_API void ref_pad_full(OraclePicture *pic) {
+    svt_aom_generate_padding(pic->full.buf, pic->full.stride, pic->full.width, pic->full.height, pic->full.org_x,
+                             pic->full.org_y);
+}
+
+static void ctx_from_params(MeContext *m, const MeGpuParams *p) {
+    m->me_type                = ME_OPEN_LOOP;
+    m->num_of_list_to_search  = p->num_of_list_to_search;
+    m->num_of_ref_pic_to_search[0] = p->num_of_ref_pic_to_search[0];
+    m->num_of_ref_pic_to_search[1] = p->num_of_ref_pic_to_search[1];
+    m->temporal_layer_index   = p->temporal_layer_index;
+    m->is_ref                 = p->is_ref;
+    m->enable_hme_flag        = p->enable_hme_flag;
+    m->enable_hme_level0_flag = p->enable_hme_level0_flag;
+    m->enable_hme_level1_flag = p->enable_hme_level1_flag;
+    m->enable_hme_level2_flag = p->enable_hme_level2_flag;
+    m->hme_search_method      = p->hme_search_method;
+    m->me_search_method       = p->me_search_method;
+    m->use_best_unipred_cand_only = p->use_best_unipred_cand_only;
+    m->reduce_hme_l0_sr_th_min = p->reduce_hme_l0_sr_th_min;
+    m->reduce_hme_l0_sr_th_max = p->reduce_hme_l0_sr_th_max;
+    m->num_hme_sa_w = p->num_hme_sa_w;
+    m->num_hme_sa_h = p->num_hme_sa_h;
+    memcpy(&m->me_sa, &p->me_sa, sizeof m->me_sa);
+    memcpy(&m->hme_l0_sa, &p->hme_l0_sa, sizeof m->hme_l0_sa);
+    memcpy(&m->hme_l1_sa, &p->hme_l1_sa, sizeof m->hme_l1_sa);
+    memcpy(&m->hme_l2_sa, &p->hme_l2_sa, sizeof m->hme_l2_sa);
+    m->me_hme_prune_ctrls.enable_me_hme_ref_pruning               = p->enable_me_hme_ref_pruning;
+    m->me_hme_prune_ctrls.prune_ref_if_hme_sad_dev_bigger_than_th = p->prune_ref_if_hme_sad_dev_bigger_than_th;
+    m->me_hme_prune_ctrls.prune_ref_if_me_sad_dev_bigger_than_th  = p->prune_ref_if_me_sad_dev_bigger_than_th;
+    m->me_hme_prune_ctrls.zz_sad_th    = p->zz_sad_th;
+    m->me_hme_prune_ctrls.zz_sad_pct   = p->zz_sad_pct;
+    m->me_hme_prune_ctrls.phme_sad_th  = p->phme_sad_th;
+    m->me_hme_prune_ctrls.phme_sad_pct = p->phme_sad_pct;
+    m->me_sr_adjustment_ctrls.enable_me_sr_adjustment              = p->enable_me_sr_adjustment;
+    m->me_sr_adjustment_ctrls.reduce_me_sr_based_on_mv_length_th   = p->reduce_me_sr_based_on_mv_length_th;
+    m->me_sr_adjustment_ctrls.stationary_hme_sad_abs_th            = p->stationary_hme_sad_abs_th;
+    m->me_sr_adjustment_ctrls.stationary_me_sr_divisor             = p->stationary_me_sr_divisor;
+    m->me_sr_adjustment_ctrls.reduce_me_sr_based_on_hme_sad_abs_th = p->reduce_me_sr_based_on_hme_sad_abs_th;
+    m->me_sr_adjustment_ctrls.me_sr_divisor_for_low_hme_sad        = p->me_sr_divisor_for_low_hme_sad;
+    m->me_sr_adjustment_ctrls.distance_based_hme_resizing          = p->distance_based_hme_resizing;
+    m->me_8x8_var_ctrls.enabled        = p->me_8x8_var_enabled;
+    m->me_8x8_var_ctrls.me_sr_div4_th  = p->me_sr_div4_th;
+    m->me_8x8_var_ctrls.me_sr_div2_th  = p->me_sr_div2_th;
+    m->me_8x8_var_ctrls.me_sr_mult2_th = p->me_sr_mult2_th;
+    m->mv_based_sa_adj.enabled          = p->mv_sa_adj_enabled;
+    m->mv_based_sa_adj.nearest_ref_only = p->mv_sa_adj_nearest_ref_only;
+    m->mv_based_sa_adj.mv_size_th       = p->mv_sa_adj_mv_size_th;
+    m->mv_based_sa_adj.sa_multiplier    = p->mv_sa_adj_sa_multiplier;
+    m->prehme_ctrl.enable           = p->prehme_enable;
+    m->prehme_ctrl.skip_search_line = p->prehme_skip_search_line;
+    m->prehme_ctrl.l1_early_exit    = p->prehme_l1_early_exit;
+    memcpy(m->prehme_ctrl.prehme_sa_cfg, p->prehme_sa_cfg, sizeof m->prehme_ctrl.prehme_sa_cfg);
+    m->prune_me_candidates_th      = p->prune_me_candidates_th;
+    m->me_early_exit_th            = p->me_early_exit_th;
+    m->me_safe_limit_zz_th         = p->me_safe_limit_zz_th;
+    m->prev_me_stage_based_exit_th = p->prev_me_stage_based_exit_th;
+}
+
+static void params_from_ctx(MeGpuParams *p, const MeContext *m) {
+    p->enable_hme_flag        = m->enable_hme_flag;
+    p->enable_hme_level0_flag = m->enable_hme_level0_flag;
+    p->enable_hme_level1_flag = m->enable_hme_level1_flag;
+    p->enable_hme_level2_flag = m->enable_hme_level2_flag;
+    p->hme_search_method      = m->hme_search_method;
+    p->me_search_method       = m->me_search_method;
+    p->use_best_unipred_cand_only = m->use_best_unipred_cand_only;
+    p->reduce_hme_l0_sr_th_min = m->reduce_hme_l0_sr_th_min;
+    p->reduce_hme_l0_sr_th_max = m->reduce_hme_l0_sr_th_max;
+    p->num_hme_sa_w = m->num_hme_sa_w;
+    p->num_hme_sa_h = m->num_hme_sa_h;
+    memcpy(&p->me_sa, &m->me_sa, sizeof p->me_sa);
+    memcpy(&p->hme_l0_sa, &m->hme_l0_sa, sizeof p->hme_l0_sa);
+    memcpy(&p->hme_l1_sa, &m->hme_l1_sa, sizeof p->hme_l1_sa);
+    memcpy(&p->hme_l2_sa, &m->hme_l2_sa, sizeof p->hme_l2_sa);
+    p->enable_me_hme_ref_pruning               = m->me_hme_prune_ctrls.enable_me_hme_ref_pruning;
+    p->prune_ref_if_hme_sad_dev_bigger_than_th = m->me_hme_prune_ctrls.prune_ref_if_hme_sad_dev_bigger_than_th;
+    p->prune_ref_if_me_sad_dev_bigger_than_th  = m->me_hme_prune_ctrls.prune_ref_if_me_sad_dev_bigger_than_th;
+    p->zz_sad_th    = m->me_hme_prune_ctrls.zz_sad_th;
+    p->zz_sad_pct   = m->me_hme_prune_ctrls.zz_sad_pct;
+    p->phme_sad_th  = m->me_hme_prune_ctrls.phme_sad_th;
+    p->phme_sad_pct = m->me_hme_prune_ctrls.phme_sad_pct;
+    p->enable_me_sr_adjustment              = m->me_sr_adjustment_ctrls.enable_me_sr_adjustment;
+    p->reduce_me_sr_based_on_mv_length_th   = m->me_sr_adjustment_ctrls.reduce_me_sr_based_on_mv_length_th;
+    p->stationary_hme_sad_abs_th            = m->me_sr_adjustment_ctrls.stationary_hme_sad_abs_th;
+    p->stationary_me_sr_divisor             = m->me_sr_adjustment_ctrls.stationary_me_sr_divisor;
+    p->reduce_me_sr_based_on_hme_sad_abs_th = m->me_sr_adjustment_ctrls.reduce_me_sr_based_on_hme_sad_abs_th;
+    p->me_sr_divisor_for_low_hme_sad        = m->me_sr_adjustment_ctrls.me_sr_divisor_for_low_hme_sad;
+    p->distance_based_hme_resizing          = m->me_sr_adjustment_ctrls.distance_based_hme_resizing;
+    p->me_8x8_var_enabled = m->me_8x8_var_ctrls.enabled;
+    p->me_sr_div4_th      = m->me_8x8_var_ctrls.me_sr_div4_th;
+    p->me_sr_div2_th      = m->me_8x8_var_ctrls.me_sr_div2_th;
+    p->me_sr_mult2_th     = m->me_8x8_var_ctrls.me_sr_mult2_th;
+    p->mv_sa_adj_enabled          = m->mv_based_sa_adj.enabled;
+    p->mv_sa_adj_nearest_ref_only = m->mv_based_sa_adj.nearest_ref_only;
+    p->mv_sa_adj_mv_size_th       = m->mv_based_sa_adj.mv_size_th;
+    p->mv_sa_adj_sa_multiplier    = m->mv_based_sa_adj.sa_multiplier;
+    p->prehme_enable           = m->prehme_ctrl.enable;
+    p->prehme_skip_search_line = m->prehme_ctrl.skip_search_line;
+    p->prehme_l1_early_exit    = m->prehme_ctrl.l1_early_exit;
+    memcpy(p->prehme_sa_cfg, m->prehme_ctrl.prehme_sa_cfg, sizeof p->prehme_sa_cfg);
+    p->prune_me_candidates_th      = m->prune_me_candidates_th;
+    p->me_early_exit_th            = m->me_early_exit_th;
+    p->me_safe_limit_zz_th         = m->me_safe_limit_zz_th;
+    p->prev_me_stage_based_exit_th = m->prev_me_stage_based_exit_th;
+}
+
+/* Extra inputs of svt_aom_sig_deriv_me that come from enc_handle.c's static set_mrp_ctrl() and cannot be
+ * called from outside the reference: passed in by the caller (the host-side restatement computes them,
+ * and tests/test_derive_params.py pins them against enc_handle.c:3397-3670 by table). */
+typedef struct RefMrpInputs {
+    uint8_t  safe_limit_nref;
+    uint32_t safe_limit_zz_th;
+} RefMrpInputs;
+
+/* Runs the reference's svt_aom_sig_deriv_me (Codec/enc_mode_config.c:681) plus the exported helper
+ * functions that set the pcs-level inputs, and flattens the result into MeGpuParams. Fields that only
+ * enc_handle.c / pd_process.c know (reference counts, max_cand...) are left untouched in *out. */
+REF_API int ref_derive_params(const MeGpuEncoderConfig *cfg, const RefMrpInputs *mrp, MeGpuParams *out) {
+    PictureParentControlSet *pcs = calloc(1, sizeof *pcs);
+    SequenceControlSet      *scs = calloc(1, sizeof *scs);
+    MeContext               *m   = calloc(1, sizeof *m);
+    if (!pcs || !scs || !m)
+        return -1;
+    pcs->scs                         = scs;
+    pcs->enc_mode                    = (EncMode)cfg->enc_mode;
+    pcs->sc_class1                   = cfg->sc_class1;
+    pcs->temporal_layer_index        = cfg->temporal_layer_index;
+    pcs->hierarchical_levels         = cfg->hierarchical_levels;
+    pcs->slice_type                  = (SliceType)cfg->slice_type;
+    scs->static_config.pred_structure = cfg->rtc_tune ? SVT_AV1_PRED_LOW_DELAY_B : SVT_AV1_PRED_RANDOM_ACCESS;
+    scs->static_config.qp            = cfg->qp;
+    scs->static_config.enc_mode      = cfg->enc_mode;
+    scs->frame_rate                  = cfg->low_frame_rate ? (1u << 16) : 30;
+    scs->mrp_ctrls.safe_limit_nref   = mrp->safe_limit_nref;
+    scs->mrp_ctrls.safe_limit_zz_th  = mrp->safe_limit_zz_th;
+    svt_aom_derive_input_resolution(&scs->input_resolution, (uint32_t)cfg->width * cfg->height);
+    pcs->input_resolution = scs->input_resolution;
+    /* HME level flags: Codec/enc_mode_config.c:1633-1645 (inside svt_aom_sig_deriv_multi_processes, which
+     * needs a fully built encoder; the three assignments are restated here) */
+    pcs->enable_hme_flag        = 1;
+    pcs->enable_hme_level0_flag = 1;
+    pcs->enable_hme_level1_flag = 1;
+    pcs->enable_hme_level2_flag = (cfg->sc_class1 || cfg->enc_mode <= ENC_M6) ? 1 : 0;
+    /* Codec/enc_mode_config.c:1845-1848 */
+    pcs->use_best_me_unipred_cand_only = cfg->enc_mode <= ENC_M3 ? 0 : 1;
+    svt_aom_set_gm_controls(pcs, svt_aom_derive_gm_level(pcs, true));
+    svt_aom_sig_deriv_me(scs, pcs, m);
+
+    params_from_ctx(out, m);
+    out->picture_number                  = cfg->picture_number;
+    out->input_resolution                = (uint8_t)scs->input_resolution;
+    out->enable_me_8x8                   = svt_aom_get_enable_me_8x8(pcs->enc_mode, cfg->rtc_tune, scs->input_resolution);
+    out->enable_me_16x16                 = svt_aom_get_enable_me_16x16(pcs->enc_mode);
+    out->max_number_of_pus_per_sb        = SQUARE_PU_COUNT; /* resource_coordination_process.c:425 */
+    out->gm_enabled                      = pcs->gm_ctrls.enabled;
+    out->gm_use_distance_based_active_th = pcs->gm_ctrls.use_distance_based_active_th;
+    out->hierarchical_levels             = cfg->hierarchical_levels;
+    out->pcs_temporal_layer_index        = cfg->temporal_layer_index;
+    out->temporal_layer_index            = cfg->temporal_layer_index;
+    out->similar_brightness_refs         = cfg->similar_brightness_refs;
+    out->is_ref                          = cfg->is_ref;
+    free(m);
+    free(scs);
+    free(pcs);
+    return 0;
+}
+
+/* ME of b64s [first, first+count) with the reference's own svt_aom_motion_estimation_b64.
+ * simd: 0 = C kernels (the specification), 1 = AVX2, 2 = AVX-512 sad_loop on top of AVX2. */
+REF_API int ref_me_b64_range(const OraclePicture *src, const OraclePicture *const refs[2][4], const MeGpuParams *p,
+                     MeGpuOutputs *out, uint32_t first, uint32_t count, int simd) {
+    set_rtcd(simd);
+    const int pic_w = (src->full.width + 7) & ~7, pic_h = (src->full.height + 7) & ~7;
+    const uint32_t bw = (pic_w + 63) / 64, bh = (pic_h + 63) / 64, total = bw * bh;
+    if (out->b64_count < total)
+        return -2;
+    PictureParentControlSet *pcs = calloc(1, sizeof *pcs);
+    SequenceControlSet      *scs = calloc(1, sizeof *scs);
+    MeContext               *m   = calloc(1, sizeof *m);
+    MotionEstimationData    *md  = calloc(1, sizeof *md);
+    MeSbResults             *res = calloc(total, sizeof *res);
+    MeSbResults            **rp  = calloc(total, sizeof *rp);
+    B64Geom                 *geo = calloc(total, sizeof *geo);
+    if (!pcs || !scs || !m || !md || !res || !rp || !geo)
+        return -1;
+    const uint32_t P = p->enable_me_16x16 ? (p->enable_me_8x8 ? p->max_number_of_pus_per_sb : 21) : 5;
+
+    ctx_from_params(m, p);
+    pcs->scs                      = scs;
+    pcs->picture_number           = p->picture_number;
+    pcs->aligned_width            = (uint16_t)pic_w;
+    pcs->aligned_height           = (uint16_t)pic_h;
+    pcs->enable_me_8x8            = p->enable_me_8x8;
+    pcs->enable_me_16x16          = p->enable_me_16x16;
+    pcs->max_number_of_pus_per_sb = p->max_number_of_pus_per_sb;
+    pcs->gm_ctrls.enabled         = p->gm_enabled;
+    pcs->gm_ctrls.use_distance_based_active_th = p->gm_use_distance_based_active_th;
+    pcs->hierarchical_levels      = p->hierarchical_levels;
+    pcs->temporal_layer_index     = p->pcs_temporal_layer_index;
+    pcs->similar_brightness_refs  = p->similar_brightness_refs;
+    pcs->b64_geom                 = geo;
+    pcs->pa_me_data               = md;
+    pcs->me_64x64_distortion      = out->me_64x64_distortion;
+    pcs->me_32x32_distortion      = out->me_32x32_distortion;
+    pcs->me_16x16_distortion      = out->me_16x16_distortion;
+    pcs->me_8x8_distortion        = out->me_8x8_distortion;
+    pcs->me_8x8_cost_variance     = out->me_8x8_cost_variance;
+    pcs->rc_me_distortion         = out->rc_me_distortion;
+    pcs->stationary_block_present_sb = out->stationary_block_present_sb;
+    pcs->rc_me_allow_gm           = out->rc_me_allow_gm;
+    scs->mrp_ctrls.only_l_bwd     = p->only_l_bwd;
+    scs->input_resolution         = (EbInputResolution)p->input_resolution;
+    scs->b64_size                 = 64;
+    md->me_results                = rp;
+    md->max_cand                  = p->max_cand;
+    md->max_refs                  = p->max_refs;
+    md->max_l0                    = p->max_l0;
+    for (uint32_t b = 0; b < total; b++) {
+        rp[b]                        = &res[b];
+        res[b].total_me_candidate_index = out->total_me_candidate_index + (size_t)b * P;
+        res[b].me_candidate_array    = (MeCandidate *)(out->me_candidate_array + (size_t)b * P * p->max_cand);
+        res[b].me_mv_array           = (MvCandidate *)(out->me_mv_array + (size_t)b * P * p->max_refs);
+        geo[b].org_x                 = (uint16_t)((b % bw) * 64);
+        geo[b].org_y                 = (uint16_t)((b / bw) * 64);
+        geo[b].width                 = (uint8_t)((pic_w - geo[b].org_x) < 64 ? pic_w - geo[b].org_x : 64);
+        geo[b].height                = (uint8_t)((pic_h - geo[b].org_y) < 64 ? pic_h - geo[b].org_y : 64);
+    }
+    EbPictureBufferDesc sf, sq, ss, rf[2][4], rq[2][4], rs[2][4];
+    desc_from_plane(&sf, &src->full);
+    desc_from_plane(&sq, &src->quarter);
+    desc_from_plane(&ss, &src->sixteenth);
+    for (int li = 0; li < p->num_of_list_to_search; li++)
+        for (int ri = 0; ri < p->num_of_ref_pic_to_search[li]; ri++) {
+            desc_from_plane(&rf[li][ri], &refs[li][ri]->full);
+            desc_from_plane(&rq[li][ri], &refs[li][ri]->quarter);
+            desc_from_plane(&rs[li][ri], &refs[li][ri]->sixteenth);
+            m->me_ds_ref_array[li][ri].picture_ptr           = &rf[li][ri];
+            m->me_ds_ref_array[li][ri].quarter_picture_ptr   = &rq[li][ri];
+            m->me_ds_ref_array[li][ri].sixteenth_picture_ptr = &rs[li][ri];
+            m->me_ds_ref_array[li][ri].picture_number        = refs[li][ri]->picture_number;
+        }
+
+    for (uint32_t b = first; b < first + count && b < total; b++) {
+        const uint32_t ox = geo[b].org_x, oy = geo[b].org_y;
+        /* me_process.c:183-214 */
+        m->b64_src_ptr                 = &sf.buffer_y[(sf.org_y + oy) * sf.stride_y + sf.org_x + ox];
+        m->b64_src_stride              = sf.stride_y;
+        m->quarter_b64_buffer          = &sq.buffer_y[(sq.org_y + (oy >> 1)) * sq.stride_y + sq.org_x + (ox >> 1)];
+        m->quarter_b64_buffer_stride   = sq.stride_y;
+        m->sixteenth_b64_buffer        = &ss.buffer_y[(ss.org_y + (oy >> 2)) * ss.stride_y + ss.org_x + (ox >> 2)];
+        m->sixteenth_b64_buffer_stride = ss.stride_y;
+        m->me_type                     = ME_OPEN_LOOP;
+        /* canonical state for data the reference leaves stale between blocks (never read for an output) */
+        for (int li = 0; li < 2; li++)
+            for (int ri = 0; ri < 4; ri++)
+                for (int k = 0; k < SQUARE_PU_COUNT; k++) m->p_sb_best_sad[li][ri][k] = MAX_SAD_VALUE;
+        memset(m->prehme_data, 0, sizeof m->prehme_data);
+        for (int li = 0; li < 2; li++)
+            for (int ri = 0; ri < 4; ri++) m->search_results[li][ri].hme_sc_x = m->search_results[li][ri].hme_sc_y = 0;
+
+        svt_aom_motion_estimation_b64(pcs, b, ox, oy, m, &sf);
+
+        if (out->p_sb_best_sad) memcpy(out->p_sb_best_sad + (size_t)b * 2 * 4 * 85, m->p_sb_best_sad, sizeof m->p_sb_best_sad);
+        if (out->p_sb_best_mv) memcpy(out->p_sb_best_mv + (size_t)b * 2 * 4 * 85, m->p_sb_best_mv, sizeof m->p_sb_best_mv);
+        for (int li = 0; li < 2; li++)
+            for (int ri = 0; ri < 4; ri++) {
+                size_t k = ((size_t)b * 2 + li) * 4 + ri;
+                if (out->hme_search_centre) {
+                    out->hme_search_centre[2 * k]     = m->search_results[li][ri].hme_sc_x;
+                    out->hme_search_centre[2 * k + 1] = m->search_results[li][ri].hme_sc_y;
+                }
+                if (out->hme_sad) out->hme_sad[k] = m->search_results[li][ri].hme_sad;
+                if (out->do_ref) out->do_ref[k] = m->search_results[li][ri].do_ref;
+            }
+    }
+    out->b64_count = total;
+    out->pu_count  = P;
+    free(geo); free(rp); free(res); free(md); free(m); free(scs); free(pcs);
+    return 0;
+}

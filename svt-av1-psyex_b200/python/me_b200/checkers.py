@@ -1,0 +1,94 @@
+"""CPU checkers: the plain-C restatement (oracle/libme_oracle.so) and the reference's own sources
+(oracle/_ref/libme_ref.so). TEST INFRASTRUCTURE: only tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs import this module. The product (engine.py) never does."""
+import ctypes as C
+import os
+
+from . import abi
+from .planes import Outputs, Picture
+
+
+def _refs_array(refs):
+    """refs: [[Picture...], [Picture...]] -> (RefArray, keepalive list)"""
+    arr, keep = abi.RefArray(), []
+    for li, lst in enumerate(refs):
+        for ri, pic in enumerate(lst):
+            s = pic.c_struct()
+            keep.append(s)
+            arr[li][ri] = C.pointer(s)
+    return arr, keep
+
+
+class Oracle:
+    def __init__(self):
+        if not os.path.exists(abi.ORACLE_LIB):
+            raise RuntimeError(f"{abi.ORACLE_LIB} missing: run make -C oracle")
+        self.lib = C.CDLL(abi.ORACLE_LIB)
+        self.lib.oracle_me_b64_range.argtypes = [C.POINTER(abi.OraclePicture), C.POINTER(abi.RefArray),
+                                                 C.POINTER(abi.MeGpuParams), C.POINTER(abi.MeGpuOutputs),
+                                                 abi.u32, abi.u32, C.POINTER(abi.u64)]
+        self.lib.oracle_build_pyramid.argtypes = [C.POINTER(abi.OraclePicture)]
+        self.lib.oracle_sad_loop.argtypes = [C.c_void_p, abi.u32, C.c_void_p, abi.u32, abi.u32, abi.u32,
+                                             C.POINTER(abi.u64), C.POINTER(abi.i16), C.POINTER(abi.i16), abi.u32,
+                                             abi.u8, abi.i16, abi.i16]
+        self.lib.oracle_downsample_2d.argtypes = [C.c_void_p, abi.u32, abi.u32, abi.u32, C.c_void_p, abi.u32, abi.u32]
+
+    def build_pyramid(self, pic: Picture):
+        s = pic.c_struct()
+        self.lib.oracle_build_pyramid(C.byref(s))
+
+    def me_picture(self, src: Picture, refs, params, first=0, count=1 << 30, debug=True):
+        out = Outputs(src.width, src.height, params, debug=debug)
+        arr, keep = _refs_array(refs)
+        s = src.c_struct()
+        ops = abi.u64(0)
+        rc = self.lib.oracle_me_b64_range(C.byref(s), C.byref(arr), C.byref(params), C.byref(out.c), first, count,
+                                          C.byref(ops))
+        if rc != 0:
+            raise RuntimeError(f"oracle_me_b64_range failed: {rc}")
+        out.byte_sad_ops = ops.value
+        return out
+
+
+class Reference:
+    """The reference's own C (simd=0) or AVX2 / AVX-512 (simd=1/2) ME, via oracle/ref_harness.c."""
+
+    def __init__(self):
+        if not os.path.exists(abi.REF_LIB):
+            raise RuntimeError(f"{abi.REF_LIB} missing: run make -C oracle (needs /root/reference)")
+        self.lib = C.CDLL(abi.REF_LIB)
+        self.lib.ref_me_b64_range.argtypes = [C.POINTER(abi.OraclePicture), C.POINTER(abi.RefArray),
+                                              C.POINTER(abi.MeGpuParams), C.POINTER(abi.MeGpuOutputs), abi.u32,
+                                              abi.u32, C.c_int]
+        self.lib.ref_build_pyramid.argtypes = [C.POINTER(abi.OraclePicture)]
+        self.lib.ref_derive_params.argtypes = [C.POINTER(abi.MeGpuEncoderConfig), C.POINTER(abi.RefMrpInputs),
+                                               C.POINTER(abi.MeGpuParams)]
+        self.lib.ref_sad_loop.argtypes = [C.c_void_p, abi.u32, C.c_void_p, abi.u32, abi.u32, abi.u32,
+                                          C.POINTER(abi.u64), C.POINTER(abi.i16), C.POINTER(abi.i16), abi.u32,
+                                          abi.u8, abi.i16, abi.i16]
+        self.lib.ref_downsample_2d.argtypes = [C.c_void_p, abi.u32, abi.u32, abi.u32, C.c_void_p, abi.u32, abi.u32]
+
+    @staticmethod
+    def available():
+        return os.path.exists(abi.REF_LIB)
+
+    def build_pyramid(self, pic: Picture):
+        s = pic.c_struct()
+        self.lib.ref_build_pyramid(C.byref(s))
+
+    def me_picture(self, src: Picture, refs, params, first=0, count=1 << 30, simd=0, debug=True):
+        out = Outputs(src.width, src.height, params, debug=debug)
+        arr, keep = _refs_array(refs)
+        s = src.c_struct()
+        rc = self.lib.ref_me_b64_range(C.byref(s), C.byref(arr), C.byref(params), C.byref(out.c), first, count, simd)
+        if rc != 0:
+            raise RuntimeError(f"ref_me_b64_range failed: {rc}")
+        return out
+
+    def derive_params(self, cfg, safe_limit_nref, safe_limit_zz_th):
+        p = abi.MeGpuParams()
+        mrp = abi.RefMrpInputs(safe_limit_nref, safe_limit_zz_th)
+        rc = self.lib.ref_derive_params(C.byref(cfg), C.byref(mrp), C.byref(p))
+        if rc != 0:
+            raise RuntimeError("ref_derive_params failed")
+        return p
