@@ -78,8 +78,11 @@ class Sequence:
         rng = np.random.default_rng(seed)
         if kind == "motion":
             self.field = _box5(rng.integers(0, 256, size=(height + 512, width + 512), dtype=np.uint8))
-            self.rect_tex = [_box5(rng.integers(0, 256, size=(192, 256), dtype=np.uint8)) for _ in self.RECTS]
-            self.rect_pos = [(int(rng.integers(0, width - 256)), int(rng.integers(0, height - 192))) for _ in self.RECTS]
+            # rectangles are 256x192 at 1080p/4K; small test pictures shrink them to a third of the picture
+            self.rw, self.rh = min(256, (width // 3) & ~7), min(192, (height // 3) & ~7)
+            self.rect_tex = [_box5(rng.integers(0, 256, size=(self.rh, self.rw), dtype=np.uint8)) for _ in self.RECTS]
+            self.rect_pos = [(int(rng.integers(0, width - self.rw)), int(rng.integers(0, height - self.rh)))
+                             for _ in self.RECTS]
 
     def luma(self, poc):
         rng = np.random.default_rng([self.seed, poc])
@@ -91,8 +94,8 @@ class Sequence:
         ox, oy = (3 * poc) % 512, (1 * poc) % 512
         img = self.field[oy:oy + h, ox:ox + w].astype(np.int16)
         for (vx, vy), tex, (px, py) in zip(self.RECTS, self.rect_tex, self.rect_pos):
-            x = (px + vx * poc) % (w - 256)
-            y = (py + vy * poc) % (h - 192)
-            img[y:y + 192, x:x + 256] = tex
+            x = (px + vx * poc) % (w - self.rw)
+            y = (py + vy * poc) % (h - self.rh)
+            img[y:y + self.rh, x:x + self.rw] = tex
         img += rng.integers(-2, 3, size=(h, w), dtype=np.int16)
         return np.clip(img, 0, 255).astype(np.uint8)
