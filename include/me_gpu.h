@@ -185,7 +185,10 @@ typedef struct MeGpuOutputs {
     int16_t  *search_area; /* [b64][2][4][4] final (origin_x, origin_y, width, height) of the integer search */
 } MeGpuOutputs;
 
-/* library / device lifecycle ------------------------------------------------------------- */
+/* library / device lifecycle -------------------------------------------------------------
+ * pictures_in_flight = capacity of the device picture pool (registered and not yet released pictures,
+ * sources and references alike); up to min(pictures_in_flight, 16) pictures may be submitted and not yet
+ * waited for per device. device_count <= 0 selects the current CUDA device. */
 int me_gpu_init(int device_count, const int *device_ids, int max_width, int max_height, int max_refs_l0,
                 int max_refs_l1, int pictures_in_flight);
 void me_gpu_shutdown(void);
@@ -228,6 +231,9 @@ typedef struct MeGpuTimings {
     uint64_t byte_sad_ops; /* algorithmic byte-SAD count of the last waited picture */
 } MeGpuTimings;
 int me_gpu_get_timings(MeGpuTimings *t);
+/* measured VABSDIFF4 lane-operations per second of the engine's first device (x4 = byte-SADs / s): the
+ * denominator of the integer-SAD roofline; 0.0 when the engine is not initialised */
+double me_gpu_measure_sad_peak(void);
 
 #ifdef __cplusplus
 }

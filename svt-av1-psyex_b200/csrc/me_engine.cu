@@ -1,0 +1,653 @@
+/*
+ * me_engine.cu - host runtime behind the C-ABI of include/me_gpu.h.
+ *
+ * Owns, per device: the picture pool (padded full / quarter / sixteenth planes of every registered
+ * picture, resident in HBM from register to release), a ring of job contexts (one stream + the per-picture
+ * state, task, key and output buffers) and an upload stream. A job is the whole open-loop ME of one
+ * picture: ~15 kernel launches on the job's stream, no host round trip until me_gpu_wait copies the
+ * MeSbResults images back. Pictures of different jobs overlap on the device through their streams.
+ *
+ * With several devices in one process every registered pyramid is built once on its owner device and
+ * replicated to the others with cudaMemcpyPeerAsync (NVLink); jobs are dealt round-robin by picture.
+ * There is no collective on the search and no CPU fallback: without a usable device every call fails.
+ */
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "me_ctrl.h"
+#include "me_kernels.h"
+
+namespace {
+
+constexpr int kMaxJobs = 16;
+
+struct Slot {
+    bool        used = false;
+    uint64_t    picture_number = 0;
+    int         width = 0, height = 0;
+    int         refcount = 0; /* jobs in flight that read this slot */
+    bool        release_pending = false;
+    cudaEvent_t ready[8] = {}; /* per device: pyramid complete on that device */
+};
+
+struct JobCtx {
+    bool         busy = false;
+    uint64_t     picture_number = 0;
+    int          device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t  ev[5] = {}; /* start, hme done, search done, end, (spare) */
+    MeJob       *h_job = nullptr; /* pinned */
+    MeJob       *d_job = nullptr;
+    FsTileList  *d_list = nullptr;
+    FsTileList  *h_list = nullptr; /* pinned copy of the header for overflow checks */
+    unsigned long long *h_ops = nullptr; /* pinned */
+    std::vector<int> slots_used;
+    /* device buffers */
+    B64State *state = nullptr; SearchTask *tasks = nullptr; SearchResult *results = nullptr; FsTask *fs_tasks = nullptr;
+    unsigned long long *keys = nullptr; FsTile *tiles = nullptr;
+    uint8_t *total = nullptr, *cands = nullptr; uint32_t *mvs = nullptr, *dist = nullptr; uint8_t *flags = nullptr;
+    uint32_t *dbg_sad = nullptr, *dbg_mv = nullptr; int16_t *dbg_centre = nullptr; uint64_t *dbg_hme = nullptr;
+    uint8_t *dbg_do_ref = nullptr; int16_t *dbg_area = nullptr; unsigned long long *ops_total = nullptr;
+    size_t cap_cands = 0, cap_mvs = 0;
+    uint32_t tile_cap = 0;
+};
+
+struct Device {
+    int          id = 0;
+    uint8_t     *pool = nullptr;
+    cudaStream_t upload = nullptr;
+    int          sms = 148;
+    std::vector<JobCtx> jobs;
+};
+
+struct Engine {
+    bool                initialised = false;
+    std::vector<Device> dev;
+    MePicGeom           gmax{};
+    int                 nslots = 0;
+    std::vector<Slot>   slots;
+    std::map<uint64_t, int> by_number;
+    int                 max_l0 = 0, max_l1 = 0;
+    uint64_t            submit_counter = 0, register_counter = 0;
+    MeGpuTimings        last{};
+    std::mutex          mu;
+    std::string         err;
+};
+
+Engine g;
+
+int fail(int code, const std::string &msg) {
+    g.err = msg;
+    return code;
+}
+#define CU(x)                                                                                              \
+    do {                                                                                                   \
+        cudaError_t e_ = (x);                                                                              \
+        if (e_ != cudaSuccess)                                                                             \
+            return fail(ME_GPU_ERR_CUDA, std::string(#x) + ": " + cudaGetErrorString(e_));                \
+    } while (0)
+
+template <typename T>
+cudaError_t dalloc(T **p, size_t n) {
+    return cudaMalloc((void **)p, n * sizeof(T));
+}
+
+uint32_t max_tiles_per_task(const MeGpuParams *p) {
+    /* upper bound of the main search area: sa_max, x mv-based multiplier, x1.5 for high variance, rounded */
+    uint32_t w = p->me_sa.sa_max.width, h = p->me_sa.sa_max.height;
+    if (p->mv_sa_adj_enabled) {
+        w *= p->mv_sa_adj_sa_multiplier;
+        h *= p->mv_sa_adj_sa_multiplier;
+    }
+    if (p->me_sr_mult2_th != 0xFFFFFFFFu) {
+        w = w * 3 / 2;
+        h = h * 3 / 2;
+    }
+    w = (w + 7 + 8) & ~7u;
+    h = h < 3 ? 3 : h;
+    return ((w + FS_TW - 1) / FS_TW) * ((h + FS_TH - 1) / FS_TH);
+}
+
+int alloc_job(Device &d, JobCtx &jc, const MePicGeom &gm, int max_l0, int max_l1) {
+    const size_t nb = (size_t)gm.b64_count;
+    const size_t max_refs = (size_t)max_l0 + max_l1;
+    const size_t max_cand = (size_t)max_l0 + max_l1 + (size_t)max_l0 * max_l1 + (max_l0 ? max_l0 - 1 : 0) + (max_l1 == 3 ? 1 : 0);
+    jc.device    = d.id;
+    jc.cap_cands = nb * ME_NPU * (max_cand ? max_cand : 1);
+    jc.cap_mvs   = nb * ME_NPU * (max_refs ? max_refs : 1);
+    jc.tile_cap  = (uint32_t)(nb * ME_NREF * 64);
+    CU(cudaStreamCreateWithFlags(&jc.stream, cudaStreamNonBlocking));
+    for (auto &e : jc.ev) CU(cudaEventCreate(&e));
+    CU(cudaMallocHost((void **)&jc.h_job, sizeof(MeJob)));
+    CU(cudaMallocHost((void **)&jc.h_list, sizeof(FsTileList)));
+    CU(cudaMallocHost((void **)&jc.h_ops, sizeof(unsigned long long)));
+    CU(dalloc(&jc.d_job, 1));
+    CU(dalloc(&jc.d_list, 1));
+    CU(dalloc(&jc.state, nb));
+    CU(dalloc(&jc.tasks, nb * ME_SLOTS));
+    CU(dalloc(&jc.results, nb * ME_SLOTS));
+    CU(dalloc(&jc.fs_tasks, nb * ME_NREF));
+    CU(dalloc(&jc.keys, nb * ME_NREF * ME_NPU));
+    CU(dalloc(&jc.tiles, (size_t)jc.tile_cap));
+    CU(dalloc(&jc.total, nb * ME_NPU));
+    CU(dalloc(&jc.cands, jc.cap_cands));
+    CU(dalloc(&jc.mvs, jc.cap_mvs));
+    CU(dalloc(&jc.dist, nb * 6));
+    CU(dalloc(&jc.flags, nb * 2));
+    CU(dalloc(&jc.dbg_sad, nb * ME_NREF * ME_NPU));
+    CU(dalloc(&jc.dbg_mv, nb * ME_NREF * ME_NPU));
+    CU(dalloc(&jc.dbg_centre, nb * ME_NREF * 2));
+    CU(dalloc(&jc.dbg_hme, nb * ME_NREF));
+    CU(dalloc(&jc.dbg_do_ref, nb * ME_NREF));
+    CU(dalloc(&jc.dbg_area, nb * ME_NREF * 4));
+    CU(dalloc(&jc.ops_total, 1));
+    CU(cudaMemset(jc.tasks, 0, nb * ME_SLOTS * sizeof(SearchTask)));
+    CU(cudaMemset(jc.results, 0, nb * ME_SLOTS * sizeof(SearchResult)));
+    return ME_GPU_OK;
+}
+
+void free_job(JobCtx &jc) {
+    if (jc.stream) cudaStreamDestroy(jc.stream);
+    for (auto &e : jc.ev)
+        if (e) cudaEventDestroy(e);
+    cudaFreeHost(jc.h_job); cudaFreeHost(jc.h_list); cudaFreeHost(jc.h_ops);
+    void *ptrs[] = {jc.d_job, jc.d_list, jc.state, jc.tasks, jc.results, jc.fs_tasks, jc.keys, jc.tiles, jc.total, jc.cands,
+                    jc.mvs, jc.dist, jc.flags, jc.dbg_sad, jc.dbg_mv, jc.dbg_centre, jc.dbg_hme, jc.dbg_do_ref, jc.dbg_area,
+                    jc.ops_total};
+    for (void *p : ptrs) cudaFree(p);
+    jc = JobCtx();
+}
+
+void free_slot_if_idle(int s) {
+    Slot &sl = g.slots[s];
+    if (sl.used && sl.release_pending && sl.refcount == 0) {
+        g.by_number.erase(sl.picture_number);
+        sl.used = false;
+        sl.release_pending = false;
+    }
+}
+
+/* builds the pyramid of slot s on its owner device and replicates the slot to the other devices */
+int build_and_replicate(int s, int owner, const MePicGeom &gm, bool pad_full) {
+    Device      &d   = g.dev[owner];
+    const size_t off = (size_t)s * g.gmax.slot_bytes;
+    CU(cudaSetDevice(d.id));
+    if (pad_full)
+        me_launch_pad_full(d.pool, off, &gm.plane[0], d.upload);
+    me_launch_downsample(d.pool, off, &gm.plane[0], &gm.plane[1], d.upload);
+    me_launch_downsample(d.pool, off, &gm.plane[1], &gm.plane[2], d.upload);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(g.slots[s].ready[owner], d.upload));
+    for (size_t o = 0; o < g.dev.size(); o++) {
+        if ((int)o == owner)
+            continue;
+        Device &p = g.dev[o];
+        /* the copy runs on the destination's upload stream, after the owner finished the pyramid */
+        CU(cudaSetDevice(p.id));
+        CU(cudaStreamWaitEvent(p.upload, g.slots[s].ready[owner], 0));
+        CU(cudaMemcpyPeerAsync(p.pool + off, p.id, d.pool + off, d.id, g.gmax.slot_bytes, p.upload));
+        CU(cudaEventRecord(g.slots[s].ready[o], p.upload));
+    }
+    return ME_GPU_OK;
+}
+
+int register_common(uint64_t picture_number, const uint8_t *src, int stride, int org_x, int org_y, int width, int height,
+                    bool padded) {
+    if (!g.initialised)
+        return fail(ME_GPU_ERR_STATE, "me_gpu_init has not been called");
+    if (!src || width <= 0 || height <= 0 || (width & 7) || (height & 7) || width > g.gmax.width || height > g.gmax.height)
+        return fail(ME_GPU_ERR_BAD_ARG, "bad picture geometry (luma size must be a multiple of 8 and within the init maximum)");
+    if (padded && (org_x < ME_PAD_FULL || org_y < ME_PAD_FULL || stride < width + org_x + ME_PAD_FULL))
+        return fail(ME_GPU_ERR_BAD_ARG, "padded plane needs at least 68 pixels of border on every side");
+    if (g.by_number.count(picture_number))
+        return fail(ME_GPU_ERR_STATE, "picture already registered");
+    int s = -1;
+    for (int i = 0; i < g.nslots; i++)
+        if (!g.slots[i].used) {
+            s = i;
+            break;
+        }
+    if (s < 0)
+        return fail(ME_GPU_ERR_NO_MEMORY, "picture pool is full (raise pictures_in_flight or release pictures)");
+    MePicGeom gm;
+    me_make_geom(&gm, width, height);
+    const int    owner = (int)(g.register_counter++ % g.dev.size());
+    Device      &d     = g.dev[owner];
+    const size_t off   = (size_t)s * g.gmax.slot_bytes + gm.plane[0].offset;
+    CU(cudaSetDevice(d.id));
+    if (padded) {
+        const uint8_t *top_left = src + (size_t)(org_y - ME_PAD_FULL) * stride + (org_x - ME_PAD_FULL);
+        CU(cudaMemcpy2DAsync(d.pool + off, gm.plane[0].stride, top_left, stride, width + 2 * ME_PAD_FULL,
+                             height + 2 * ME_PAD_FULL, cudaMemcpyHostToDevice, d.upload));
+    } else {
+        CU(cudaMemcpy2DAsync(d.pool + off + (size_t)ME_PAD_FULL * gm.plane[0].stride + ME_PAD_FULL, gm.plane[0].stride, src,
+                             stride, width, height, cudaMemcpyHostToDevice, d.upload));
+    }
+    Slot &sl          = g.slots[s];
+    sl.used           = true;
+    sl.picture_number = picture_number;
+    sl.width          = width;
+    sl.height         = height;
+    sl.refcount       = 0;
+    sl.release_pending = false;
+    g.by_number[picture_number] = s;
+    return build_and_replicate(s, owner, gm, !padded);
+}
+
+} // namespace
+
+extern "C" {
+
+const char *me_gpu_last_error(void) { return g.err.c_str(); }
+
+int me_gpu_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess)
+        return 0;
+    return n;
+}
+
+void me_gpu_shutdown(void) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.initialised)
+        return;
+    for (auto &d : g.dev) {
+        cudaSetDevice(d.id);
+        cudaDeviceSynchronize();
+        for (auto &jc : d.jobs) free_job(jc);
+        if (d.upload) cudaStreamDestroy(d.upload);
+        cudaFree(d.pool);
+    }
+    for (auto &s : g.slots)
+        for (auto &e : s.ready)
+            if (e) cudaEventDestroy(e);
+    g.dev.clear();
+    g.slots.clear();
+    g.by_number.clear();
+    g.initialised = false;
+}
+
+int me_gpu_init(int device_count, const int *device_ids, int max_width, int max_height, int max_refs_l0, int max_refs_l1,
+                int pictures_in_flight) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (g.initialised)
+        return fail(ME_GPU_ERR_STATE, "already initialised");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(ME_GPU_ERR_NO_DEVICE, "no CUDA device (this engine has no CPU fallback)");
+    if (max_width <= 0 || max_height <= 0 || max_refs_l0 < 1 || max_refs_l0 > ME_NR || max_refs_l1 < 0 || max_refs_l1 > ME_NR ||
+        pictures_in_flight < 2 || device_count > 8)
+        return fail(ME_GPU_ERR_BAD_ARG, "bad init arguments");
+    std::vector<int> ids;
+    if (device_count <= 0) {
+        int cur = 0;
+        cudaGetDevice(&cur);
+        ids.push_back(cur);
+    } else
+        for (int i = 0; i < device_count; i++) ids.push_back(device_ids ? device_ids[i] : i);
+    for (int id : ids)
+        if (id < 0 || id >= ndev)
+            return fail(ME_GPU_ERR_BAD_ARG, "device id out of range");
+    me_make_geom(&g.gmax, (max_width + 7) & ~7, (max_height + 7) & ~7);
+    g.nslots = pictures_in_flight;
+    g.max_l0 = max_refs_l0;
+    g.max_l1 = max_refs_l1;
+    g.slots.assign((size_t)g.nslots, Slot());
+    g.dev.resize(ids.size());
+    const int njobs = pictures_in_flight < kMaxJobs ? pictures_in_flight : kMaxJobs;
+    for (size_t i = 0; i < ids.size(); i++) {
+        Device &d = g.dev[i];
+        d.id      = ids[i];
+        CU(cudaSetDevice(d.id));
+        cudaDeviceProp prop;
+        CU(cudaGetDeviceProperties(&prop, d.id));
+        if (prop.major < 10)
+            return fail(ME_GPU_ERR_UNSUPPORTED, "sm_100a device required");
+        d.sms = prop.multiProcessorCount;
+        CU(me_kernels_setup());
+        CU(cudaStreamCreateWithFlags(&d.upload, cudaStreamNonBlocking));
+        CU(cudaMalloc((void **)&d.pool, (size_t)g.nslots * g.gmax.slot_bytes + 65536));
+        CU(cudaMemset(d.pool, 0, (size_t)g.nslots * g.gmax.slot_bytes + 65536));
+        d.jobs.resize((size_t)njobs);
+        for (auto &jc : d.jobs) {
+            int rc = alloc_job(d, jc, g.gmax, max_refs_l0, max_refs_l1);
+            if (rc)
+                return rc;
+        }
+        for (size_t o = 0; o < ids.size(); o++)
+            if (o != i) {
+                int can = 0;
+                cudaDeviceCanAccessPeer(&can, d.id, ids[o]);
+                if (can) {
+                    cudaError_t e = cudaDeviceEnablePeerAccess(ids[o], 0);
+                    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+                        return fail(ME_GPU_ERR_CUDA, "cudaDeviceEnablePeerAccess failed");
+                    cudaGetLastError();
+                }
+            }
+        CU(cudaDeviceSynchronize());
+    }
+    for (auto &s : g.slots)
+        for (size_t i = 0; i < ids.size(); i++) {
+            CU(cudaSetDevice(ids[i]));
+            CU(cudaEventCreateWithFlags(&s.ready[i], cudaEventDisableTiming));
+        }
+    g.initialised = true;
+    return ME_GPU_OK;
+}
+
+int me_gpu_plane_geometry(int width, int height, int level, int *plane_w, int *plane_h, int *pad, int *stride, int *rows) {
+    if (level < 0 || level > 2 || width <= 0 || height <= 0 || (width & 7) || (height & 7))
+        return ME_GPU_ERR_BAD_ARG;
+    /* geometry of the planes as me_gpu_read_pyramid returns them: reference strides (width + 2 * pad) */
+    static const int pads[3] = {ME_PAD_FULL, ME_PAD_QUARTER, ME_PAD_SIXTEENTH};
+    if (plane_w) *plane_w = width >> level;
+    if (plane_h) *plane_h = height >> level;
+    if (pad) *pad = pads[level];
+    if (stride) *stride = (width >> level) + 2 * pads[level];
+    if (rows) *rows = (height >> level) + 2 * pads[level];
+    return ME_GPU_OK;
+}
+
+int me_gpu_register_picture(uint64_t picture_number, const uint8_t *y8b_padded, int stride, int org_x, int org_y, int width,
+                            int height) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!y8b_padded)
+        return fail(ME_GPU_ERR_BAD_ARG, "null plane");
+    /* y8b_padded points at the first byte of the padded buffer: the interior starts at (org_x, org_y) */
+    return register_common(picture_number, y8b_padded, stride, org_x, org_y, width, height, true);
+}
+
+int me_gpu_register_picture_unpadded(uint64_t picture_number, const uint8_t *y8b, int stride, int width, int height) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (stride < width)
+        return fail(ME_GPU_ERR_BAD_ARG, "stride < width");
+    return register_common(picture_number, y8b, stride, 0, 0, width, height, false);
+}
+
+int me_gpu_release_picture(uint64_t picture_number) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.initialised)
+        return fail(ME_GPU_ERR_STATE, "not initialised");
+    auto it = g.by_number.find(picture_number);
+    if (it == g.by_number.end())
+        return fail(ME_GPU_ERR_NOT_FOUND, "picture not registered");
+    const int s = it->second;
+    /* uploads / peer copies into this slot must finish before the slot can be handed out again */
+    for (size_t i = 0; i < g.dev.size(); i++) {
+        cudaSetDevice(g.dev[i].id);
+        cudaEventSynchronize(g.slots[s].ready[i]);
+    }
+    g.slots[s].release_pending = true;
+    free_slot_if_idle(s);
+    return ME_GPU_OK;
+}
+
+int me_gpu_read_pyramid(uint64_t picture_number, uint8_t *full, uint8_t *quarter, uint8_t *sixteenth) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.initialised)
+        return fail(ME_GPU_ERR_STATE, "not initialised");
+    auto it = g.by_number.find(picture_number);
+    if (it == g.by_number.end())
+        return fail(ME_GPU_ERR_NOT_FOUND, "picture not registered");
+    const int s = it->second;
+    MePicGeom gm;
+    me_make_geom(&gm, g.slots[s].width, g.slots[s].height);
+    /* read from the last device: proves the replication as well when there are several */
+    const size_t di = g.dev.size() - 1;
+    Device      &d  = g.dev[di];
+    CU(cudaSetDevice(d.id));
+    CU(cudaEventSynchronize(g.slots[s].ready[di]));
+    uint8_t *dst[3] = {full, quarter, sixteenth};
+    for (int l = 0; l < 3; l++) {
+        if (!dst[l])
+            continue;
+        const MePlaneGeom &pl = gm.plane[l];
+        const int          pw = pl.width + 2 * pl.pad;
+        CU(cudaMemcpy2D(dst[l], pw, d.pool + (size_t)s * g.gmax.slot_bytes + pl.offset, pl.stride, pw, pl.rows,
+                        cudaMemcpyDeviceToHost));
+    }
+    return ME_GPU_OK;
+}
+
+int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
+                  const uint64_t ref_picture_numbers[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS]) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.initialised)
+        return fail(ME_GPU_ERR_STATE, "not initialised");
+    if (!params || !ref_picture_numbers)
+        return fail(ME_GPU_ERR_BAD_ARG, "null argument");
+    const MeGpuParams &p = *params;
+    if (p.num_hme_sa_w != 2 || p.num_hme_sa_h != 2) /* get_worst_quadrant asserts it, motion_estimation.c:1875 */
+        return fail(ME_GPU_ERR_UNSUPPORTED, "num_hme_sa_w/h must be 2");
+    if (p.num_of_list_to_search < 1 || p.num_of_list_to_search > ME_NL || p.num_of_ref_pic_to_search[0] < 1 ||
+        p.num_of_ref_pic_to_search[0] > ME_NR || p.num_of_ref_pic_to_search[1] > ME_NR)
+        return fail(ME_GPU_ERR_BAD_ARG, "bad reference counts");
+    if (p.enable_me_sr_adjustment == 2)
+        return fail(ME_GPU_ERR_UNSUPPORTED,
+                    "me_sr_adjustment level 4/5 (screen content) makes later references depend on reference (0,0)'s "
+                    "search result; not implemented");
+    if (p.distance_based_hme_resizing && p.reduce_hme_l0_sr_th_min && p.reduce_hme_l0_sr_th_max)
+        return fail(ME_GPU_ERR_UNSUPPORTED, "low-delay HME-L0 resizing from reference (0,0)'s centre is not implemented");
+    if (p.max_number_of_pus_per_sb != ME_NPU)
+        return fail(ME_GPU_ERR_UNSUPPORTED, "max_number_of_pus_per_sb must be 85");
+    auto it = g.by_number.find(picture_number);
+    if (it == g.by_number.end())
+        return fail(ME_GPU_ERR_NOT_FOUND, "source picture not registered");
+    const int src_slot = it->second;
+    const Slot &src    = g.slots[src_slot];
+    /* device: pictures are dealt round-robin */
+    const size_t di = (size_t)(g.submit_counter % g.dev.size());
+    Device      &d  = g.dev[di];
+    JobCtx      *jc = nullptr;
+    for (auto &c : d.jobs)
+        if (!c.busy) {
+            jc = &c;
+            break;
+        }
+    if (!jc)
+        return fail(ME_GPU_ERR_STATE, "too many pictures in flight: call me_gpu_wait first");
+    for (auto &c : d.jobs)
+        if (c.busy && c.picture_number == picture_number)
+            return fail(ME_GPU_ERR_STATE, "picture already submitted");
+
+    MeJob &j = *jc->h_job;
+    memset(&j, 0, sizeof j);
+    j.p = p;
+    me_make_geom(&j.g, src.width, src.height);
+    j.g.slot_bytes = g.gmax.slot_bytes;
+    j.src_slot     = (uint16_t)src_slot;
+    jc->slots_used.clear();
+    jc->slots_used.push_back(src_slot);
+    for (int li = 0; li < p.num_of_list_to_search; li++)
+        for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ri++) {
+            auto r = g.by_number.find(ref_picture_numbers[li][ri]);
+            if (r == g.by_number.end())
+                return fail(ME_GPU_ERR_NOT_FOUND, "reference picture not registered");
+            const Slot &rs = g.slots[r->second];
+            if (rs.width != src.width || rs.height != src.height)
+                return fail(ME_GPU_ERR_BAD_ARG, "reference picture size differs from the source (get_me_reference warns and skips)");
+            j.ref_slot[li][ri]           = (uint16_t)r->second;
+            j.ref_picture_number[li][ri] = ref_picture_numbers[li][ri];
+            jc->slots_used.push_back(r->second);
+        }
+    j.pu_count = (uint32_t)me_exported_pu_count(&p);
+    const size_t nb = (size_t)j.g.b64_count;
+    if (nb * j.pu_count * p.max_cand > jc->cap_cands || nb * j.pu_count * p.max_refs > jc->cap_mvs || p.max_cand == 0 || p.max_refs == 0)
+        return fail(ME_GPU_ERR_BAD_ARG, "max_cand / max_refs exceed what me_gpu_init allocated");
+    if ((uint64_t)max_tiles_per_task(&p) * nb * ME_NREF > jc->tile_cap)
+        return fail(ME_GPU_ERR_UNSUPPORTED, "search area too large for the tile list");
+    j.state = jc->state; j.tasks = jc->tasks; j.results = jc->results; j.fs_tasks = jc->fs_tasks; j.keys = jc->keys;
+    j.total_me_candidate_index = jc->total; j.me_candidate_array = jc->cands; j.me_mv_array = jc->mvs;
+    j.dist = jc->dist; j.flags = jc->flags;
+    j.dbg_best_sad = jc->dbg_sad; j.dbg_best_mv = jc->dbg_mv; j.dbg_centre = jc->dbg_centre; j.dbg_hme_sad = jc->dbg_hme;
+    j.dbg_do_ref = jc->dbg_do_ref; j.dbg_area = jc->dbg_area; j.ops_total = jc->ops_total;
+
+    CU(cudaSetDevice(d.id));
+    cudaStream_t st = jc->stream;
+    for (int s : jc->slots_used) CU(cudaStreamWaitEvent(st, g.slots[s].ready[di], 0));
+    CU(cudaEventRecord(jc->ev[0], st));
+    CU(cudaMemcpyAsync(jc->d_job, jc->h_job, sizeof(MeJob), cudaMemcpyHostToDevice, st));
+    FsTileList hl;
+    hl.count = hl.next = hl.overflow = 0;
+    hl.cap   = jc->tile_cap;
+    hl.tiles = jc->tiles;
+    *jc->h_list = hl;
+    CU(cudaMemcpyAsync(jc->d_list, jc->h_list, sizeof(FsTileList), cudaMemcpyHostToDevice, st));
+    CU(cudaMemsetAsync(jc->total, 0, nb * j.pu_count, st));
+    CU(cudaMemsetAsync(jc->cands, 0, nb * j.pu_count * p.max_cand, st));
+    CU(cudaMemsetAsync(jc->mvs, 0, nb * j.pu_count * p.max_refs * sizeof(uint32_t), st));
+    CU(cudaMemsetAsync(jc->ops_total, 0, sizeof(unsigned long long), st));
+
+    const int  nbi  = (int)nb;
+    const bool zz   = p.me_early_exit_th || p.me_safe_limit_zz_th;
+    const bool phme = p.prehme_enable != 0;
+    const bool l1ee = phme && p.prehme_l1_early_exit && p.num_of_list_to_search == 2;
+    const bool l0 = p.enable_hme_flag && p.enable_hme_level0_flag, l1 = p.enable_hme_flag && p.enable_hme_level1_flag,
+               l2 = p.enable_hme_flag && p.enable_hme_level2_flag;
+    /* Each ctrl launch runs the stages between two search launches; a search launch is skipped when the
+     * stage before it cannot have emitted tasks. */
+    uint32_t mask = 1u << ST_INIT;
+    auto     flush = [&](int slots) {
+        me_launch_ctrl(jc->d_job, 1, nbi, mask, jc->d_list, st);
+        me_launch_search(jc->d_job, 1, nbi, slots, d.pool, st);
+        mask = 0;
+    };
+    if (zz) flush(ME_NREF);
+    mask |= 1u << ST_PREHME0;
+    if (phme) flush(ME_NREF * 2);
+    if (l1ee) {
+        mask |= 1u << ST_PREHME1;
+        flush(ME_NREF * 2);
+    }
+    mask |= 1u << ST_HME_L0;
+    if (l0) flush(ME_NREF * 4);
+    mask |= 1u << ST_HME_L1;
+    if (l1) flush(ME_NREF * 4);
+    mask |= 1u << ST_HME_L2;
+    if (l2) flush(ME_NREF * 4);
+    mask |= 1u << ST_CENTRE;
+    flush(ME_NREF * 2);
+    CU(cudaEventRecord(jc->ev[1], st));
+    const int fs_ctas = d.sms * 2;
+    me_launch_ctrl(jc->d_job, 1, nbi, 1u << ST_PROBE, jc->d_list, st);
+    me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, fs_ctas, st);
+    /* second round: main searches of the probed references */
+    CU(cudaMemsetAsync(jc->d_list, 0, 2 * sizeof(unsigned int), st)); /* count = next = 0 */
+    me_launch_ctrl(jc->d_job, 1, nbi, 1u << ST_MAIN, jc->d_list, st);
+    me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, fs_ctas, st);
+    CU(cudaEventRecord(jc->ev[2], st));
+    me_launch_epilogue(jc->d_job, 1, nbi, st);
+    CU(cudaEventRecord(jc->ev[3], st));
+    CU(cudaGetLastError());
+
+    jc->busy           = true;
+    jc->picture_number = picture_number;
+    for (int s : jc->slots_used) g.slots[s].refcount++;
+    g.submit_counter++;
+    return ME_GPU_OK;
+}
+
+int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out) {
+    std::unique_lock<std::mutex> lk(g.mu);
+    if (!g.initialised)
+        return fail(ME_GPU_ERR_STATE, "not initialised");
+    if (!out)
+        return fail(ME_GPU_ERR_BAD_ARG, "null outputs");
+    JobCtx *jc = nullptr;
+    Device *dv = nullptr;
+    for (auto &d : g.dev)
+        for (auto &c : d.jobs)
+            if (c.busy && c.picture_number == picture_number) {
+                jc = &c;
+                dv = &d;
+            }
+    if (!jc)
+        return fail(ME_GPU_ERR_NOT_FOUND, "picture was not submitted");
+    const MeJob   &j  = *jc->h_job;
+    const size_t   nb = (size_t)j.g.b64_count;
+    const uint32_t P  = j.pu_count;
+    if (out->b64_count < nb)
+        return fail(ME_GPU_ERR_BAD_ARG, "MeGpuOutputs.b64_count is smaller than the picture's b64 count");
+    CU(cudaSetDevice(dv->id));
+    cudaStream_t st = jc->stream;
+#define D2H(dst, src, bytes)                                                                \
+    do {                                                                                    \
+        if (dst)                                                                            \
+            CU(cudaMemcpyAsync((dst), (src), (bytes), cudaMemcpyDeviceToHost, st));         \
+    } while (0)
+    D2H(out->total_me_candidate_index, jc->total, nb * P);
+    D2H(out->me_candidate_array, jc->cands, nb * P * j.p.max_cand);
+    D2H(out->me_mv_array, jc->mvs, nb * P * j.p.max_refs * sizeof(uint32_t));
+    D2H(out->me_64x64_distortion, jc->dist + 0 * nb, nb * 4);
+    D2H(out->me_32x32_distortion, jc->dist + 1 * nb, nb * 4);
+    D2H(out->me_16x16_distortion, jc->dist + 2 * nb, nb * 4);
+    D2H(out->me_8x8_distortion, jc->dist + 3 * nb, nb * 4);
+    D2H(out->me_8x8_cost_variance, jc->dist + 4 * nb, nb * 4);
+    D2H(out->rc_me_distortion, jc->dist + 5 * nb, nb * 4);
+    D2H(out->stationary_block_present_sb, jc->flags + 0 * nb, nb);
+    D2H(out->rc_me_allow_gm, jc->flags + 1 * nb, nb);
+    D2H(out->p_sb_best_sad, jc->dbg_sad, nb * ME_NREF * ME_NPU * 4);
+    D2H(out->p_sb_best_mv, jc->dbg_mv, nb * ME_NREF * ME_NPU * 4);
+    D2H(out->hme_search_centre, jc->dbg_centre, nb * ME_NREF * 2 * sizeof(int16_t));
+    D2H(out->hme_sad, jc->dbg_hme, nb * ME_NREF * sizeof(uint64_t));
+    D2H(out->do_ref, jc->dbg_do_ref, nb * ME_NREF);
+    D2H(out->search_area, jc->dbg_area, nb * ME_NREF * 4 * sizeof(int16_t));
+#undef D2H
+    CU(cudaMemcpyAsync(jc->h_list, jc->d_list, sizeof(FsTileList), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(jc->h_ops, jc->ops_total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    CU(cudaEventRecord(jc->ev[4], st));
+    lk.unlock();
+    cudaError_t e = cudaStreamSynchronize(st);
+    lk.lock();
+    if (e != cudaSuccess)
+        return fail(ME_GPU_ERR_CUDA, std::string("job failed: ") + cudaGetErrorString(e));
+    const bool overflow = jc->h_list->overflow != 0;
+    MeGpuTimings t{};
+    cudaEventElapsedTime(&t.hme_ms, jc->ev[0], jc->ev[1]);
+    cudaEventElapsedTime(&t.search_ms, jc->ev[1], jc->ev[2]);
+    cudaEventElapsedTime(&t.epilogue_ms, jc->ev[2], jc->ev[3]);
+    cudaEventElapsedTime(&t.total_ms, jc->ev[0], jc->ev[4]);
+    t.pyramid_ms      = 0.f;
+    t.kernel_launches = me_launch_count();
+    t.byte_sad_ops    = *jc->h_ops;
+    g.last            = t;
+    out->b64_count    = (uint32_t)nb;
+    out->pu_count     = P;
+    jc->busy          = false;
+    for (int s : jc->slots_used) {
+        g.slots[s].refcount--;
+        free_slot_if_idle(s);
+    }
+    if (overflow)
+        return fail(ME_GPU_ERR_UNSUPPORTED, "full-search tile list overflowed");
+    return ME_GPU_OK;
+}
+
+int me_gpu_get_timings(MeGpuTimings *t) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!t)
+        return ME_GPU_ERR_BAD_ARG;
+    *t                 = g.last;
+    t->kernel_launches = me_launch_count();
+    return ME_GPU_OK;
+}
+
+/* VABSDIFF4 lane-operations per second of device 0 of the engine (x4 = byte-SADs per second): the measured
+ * denominator of the integer-SAD roofline */
+double me_gpu_measure_sad_peak(void) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.initialised)
+        return 0.0;
+    cudaSetDevice(g.dev[0].id);
+    return me_measure_sad_peak(g.dev[0].upload);
+}
+
+} /* extern "C" */

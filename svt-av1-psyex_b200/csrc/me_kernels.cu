@@ -1,0 +1,612 @@
+/*
+ * me_kernels.cu - hand-written sm_100a kernels of the open-loop ME engine.
+ *
+ *   k_downsample_pad   svt_aom_downsample_2d_c + svt_aom_generate_padding   (pic_analysis_process.c:130-160,
+ *                      pic_operators.c:397-443): one pass writes a whole padded plane of the pyramid
+ *   k_pad_full         edge replication of the full-resolution plane (svt_aom_pad_input_pictures)
+ *   k_ctrl             one thread per 64x64 block runs the integer control stages of me_ctrl.h and emits
+ *                      search tasks / full-search tiles
+ *   k_search           svt_sad_loop_kernel_c (C_DEFAULT/compute_sad_c.c:58-101) for every task of a stage:
+ *                      zero-MV SADs, pre-HME, HME level 0/1/2, check_00_center SADs
+ *   k_fullsearch       open_loop_me_fullpel_search_sblock (motion_estimation.c:781-817) with the 85 square
+ *                      PU SADs per position (motion_estimation.c:210-425): persistent CTAs pull 64x32-position
+ *                      tiles, stage the reference window into four byte-shifted shared-memory copies, keep 8
+ *                      positions per thread in registers, VABSDIFF4.ACC for the SADs, packed (sad, scan index)
+ *                      keys reduced with redux.sync + shared/global atomicMin so that the lowest scan index
+ *                      wins ties exactly as the reference's strict '<' does
+ *   k_epilogue         me_prune_ref, candidate arrays, compute_distortion, GM detection per b64
+ *
+ * All arithmetic is integer; results are bit-exact with the reference C code (tests/test_gpu_parity.py).
+ */
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "me_ctrl.h"
+#include "me_kernels.h"
+
+/* ------------------------------------------------------------------------------------------------
+ * small device helpers
+ * ---------------------------------------------------------------------------------------------- */
+__device__ __forceinline__ uint32_t vsad4(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+__device__ __forceinline__ const uint8_t *plane_ptr(const uint8_t *pool, const MePicGeom &g, uint32_t slot, int level) {
+    return pool + (size_t)slot * g.slot_bytes + g.plane[level].offset;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * pyramid
+ * ---------------------------------------------------------------------------------------------- */
+
+/* dst(px, py) over the whole padded plane = rounded 2x2 average of the source interior at the clamped
+ * interior coordinate, i.e. downsample (step 2) followed by edge replication. 4 output bytes per thread. */
+__global__ void __launch_bounds__(256) k_downsample_pad(uint8_t *pool, size_t slot_off, MePlaneGeom src, MePlaneGeom dst) {
+    const int wx = blockIdx.x * blockDim.x + threadIdx.x; /* word index in the row */
+    const int py = blockIdx.y;
+    if (wx * 4 >= dst.stride)
+        return;
+    const uint8_t *s  = pool + slot_off + src.offset;
+    uint8_t       *d  = pool + slot_off + dst.offset;
+    int            iy = py - dst.pad;
+    iy                = iy < 0 ? 0 : (iy > dst.height - 1 ? dst.height - 1 : iy);
+    const uint8_t *r0 = s + (size_t)(src.pad + 2 * iy) * src.stride + src.pad;
+    const uint8_t *r1 = r0 + src.stride;
+    uint32_t       out = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        int ix = wx * 4 + i - dst.pad;
+        ix     = ix < 0 ? 0 : (ix > dst.width - 1 ? dst.width - 1 : ix);
+        const uint32_t v = ((uint32_t)r0[2 * ix] + r0[2 * ix + 1] + r1[2 * ix] + r1[2 * ix + 1] + 2) >> 2;
+        out |= v << (8 * i);
+    }
+    *(uint32_t *)(d + (size_t)py * dst.stride + wx * 4) = out;
+}
+
+/* replicate the interior of the full plane into its 68-pixel border (rows and columns) */
+__global__ void __launch_bounds__(256) k_pad_full(uint8_t *pool, size_t slot_off, MePlaneGeom pl) {
+    const int wx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int py = blockIdx.y;
+    const int padded_w = pl.width + 2 * pl.pad;
+    if (wx * 4 >= padded_w)
+        return;
+    const int px = wx * 4;
+    const bool inside_y = py >= pl.pad && py < pl.pad + pl.height;
+    const bool inside_x = px >= pl.pad && px < pl.pad + pl.width;
+    if (inside_x && inside_y)
+        return; /* pad and width are multiples of 4: a word is never half interior */
+    uint8_t *base = pool + slot_off + pl.offset;
+    int      iy   = py - pl.pad;
+    iy            = iy < 0 ? 0 : (iy > pl.height - 1 ? pl.height - 1 : iy);
+    const uint8_t *row = base + (size_t)(pl.pad + iy) * pl.stride + pl.pad;
+    uint32_t       out = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        int ix = px + i - pl.pad;
+        ix     = ix < 0 ? 0 : (ix > pl.width - 1 ? pl.width - 1 : ix);
+        out |= (uint32_t)row[ix] << (8 * i);
+    }
+    *(uint32_t *)(base + (size_t)py * pl.stride + px) = out;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * control stages
+ * ---------------------------------------------------------------------------------------------- */
+__global__ void __launch_bounds__(64) k_ctrl(MeJob *jobs, uint32_t stage_mask, FsTileList *list) {
+    MeJob    *j = &jobs[blockIdx.y];
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= j->g.b64_count)
+        return;
+    CtrlCtx c;
+    c.j     = j;
+    c.p     = &j->p;
+    c.s     = &j->state[b];
+    c.t     = &j->tasks[(size_t)b * ME_SLOTS];
+    c.r     = &j->results[(size_t)b * ME_SLOTS];
+    c.f     = &j->fs_tasks[(size_t)b * ME_NREF];
+    c.keys  = &j->keys[(size_t)b * ME_NREF * ME_NPU];
+    c.org_x = (b % j->g.b64_cols) * 64;
+    c.org_y = (b / j->g.b64_cols) * 64;
+    c.b64_w = (uint32_t)min(64, j->g.width - c.org_x);
+    c.b64_h = (uint32_t)min(64, j->g.height - c.org_y);
+    c.pic_w = j->g.width;
+    c.pic_h = j->g.height;
+    for (int st = 0; st < ST_COUNT; st++)
+        if (stage_mask & (1u << st))
+            mc_run_stage(&c, st);
+    if (stage_mask & ((1u << ST_PROBE) | (1u << ST_MAIN))) {
+        /* cut every full-search task of this b64 into tiles and append them to the work list */
+        for (int k = 0; k < ME_NREF; k++) {
+            const FsTask f = c.f[k];
+            if (!f.valid)
+                continue;
+            const uint32_t ntx = (uint32_t)(f.w + FS_TW - 1) / FS_TW, nty = (uint32_t)(f.h + FS_TH - 1) / FS_TH;
+            const uint32_t n = ntx * nty;
+            const uint32_t base = atomicAdd(&list->count, n);
+            if (base + n > list->cap) {
+                atomicExch(&list->overflow, 1u);
+                continue;
+            }
+            FsTile *t = list->tiles + base;
+            for (uint32_t ty = 0; ty < nty; ty++)
+                for (uint32_t tx = 0; tx < ntx; tx++, t++) {
+                    t->task = (uint32_t)b * ME_NREF + (uint32_t)k;
+                    t->job  = (uint16_t)blockIdx.y;
+                    t->tx   = (uint16_t)(tx * FS_TW);
+                    t->ty   = (uint16_t)(ty * FS_TH);
+                    t->pad_ = 0;
+                }
+        }
+    }
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * k_search: one CTA per svt_sad_loop_kernel task
+ * ---------------------------------------------------------------------------------------------- */
+#define KS_THREADS 128
+#define KS_SMEM_WORDS (22 * 1024) /* 88 KB of dynamic shared memory */
+
+__global__ void __launch_bounds__(KS_THREADS) k_search(const MeJob *jobs, const uint8_t *pool) {
+    extern __shared__ uint32_t ks_smem[];
+    __shared__ unsigned long long ks_red[KS_THREADS / 32];
+    const MeJob     *j    = &jobs[blockIdx.z];
+    const uint32_t   b    = blockIdx.y;
+    const uint32_t   slot = blockIdx.x;
+    const SearchTask t    = j->tasks[(size_t)b * ME_SLOTS + slot];
+    if (!t.valid)
+        return;
+    const MePlaneGeom pl   = j->g.plane[t.level];
+    const uint8_t    *srcp = plane_ptr(pool, j->g, j->src_slot, t.level);
+    const uint8_t    *refp = plane_ptr(pool, j->g, t.ref_slot, t.level);
+    const int         tid  = threadIdx.x;
+    const int         nw   = (t.bw + 3) >> 2; /* words per block row */
+    const uint32_t    last_mask = (t.bw & 3) ? ((1u << (8 * (t.bw & 3))) - 1u) : 0xFFFFFFFFu;
+    const int         rows = t.rows, step = t.row_step;
+
+    /* source block -> shared memory words (bytes beyond the block width masked to 0) */
+    uint32_t *srcw = ks_smem;
+    for (int i = tid; i < rows * nw; i += KS_THREADS) {
+        const int      r = i / nw, cw = i % nw;
+        const uint8_t *g = srcp + (size_t)(pl.pad + t.sy + r * step) * pl.stride + pl.pad + t.sx + cw * 4;
+        uint32_t       v = 0;
+        for (int k = 0; k < 4; k++)
+            if (cw * 4 + k < t.bw)
+                v |= (uint32_t)g[k] << (8 * k);
+        srcw[i] = v;
+    }
+    uint32_t *win = ks_smem + ((rows * nw + 3) & ~3);
+
+    /* window geometry: search point (x, y) reads ref rows y + r*step, bytes [x, x + bw) */
+    const uint8_t *w00   = refp + (size_t)(pl.pad + t.ry) * pl.stride + pl.pad + t.rx; /* search point (0,0) */
+    const int      a     = (int)((uintptr_t)w00 & 3);
+    const int      pitch = ((a + t.sa_w - 1 + t.bw + 3) >> 2) + 1; /* words per window row (+1 for the funnel read) */
+    const bool     skip  = t.bw == 16 && t.rows <= 16 && t.skip_line;
+    const int      erows = skip ? (t.sa_h >> 1) : t.sa_h; /* search rows that are evaluated */
+    const int      span  = (rows - 1) * step; /* extra window rows below a search row */
+    const int      rows_avail = (KS_SMEM_WORDS - ((rows * nw + 3) & ~3)) / pitch;
+    int            band  = skip ? ((rows_avail - span - 1) / 2 + 1) : (rows_avail - span);
+    if (band < 1)
+        band = 1;
+
+    unsigned long long best = ((unsigned long long)ME_SAD_LOOP_INIT << 32) | 0xFFFFFFFFull;
+    for (int e0 = 0; e0 < erows; e0 += band) {
+        const int e1   = min(erows, e0 + band);
+        const int ymin = skip ? 2 * e0 + 1 : e0;
+        const int ymax = skip ? 2 * (e1 - 1) + 1 : e1 - 1;
+        const int wrows = ymax - ymin + span + 1;
+        __syncthreads();
+        /* stage the window with aligned 32-bit loads */
+        const uint32_t *g0 = (const uint32_t *)(w00 - a + (ptrdiff_t)ymin * pl.stride);
+        for (int i = tid; i < wrows * pitch; i += KS_THREADS) {
+            const int r = i / pitch, cw = i % pitch;
+            win[i]      = g0[(size_t)r * (pl.stride >> 2) + cw];
+        }
+        __syncthreads();
+        const int npos = (e1 - e0) * t.sa_w;
+        for (int p = tid; p < npos; p += KS_THREADS) {
+            const int ee = p / t.sa_w, x = p - ee * t.sa_w;
+            const int yl = skip ? 2 * ee : ee; /* row inside the band window */
+            const int o  = a + x;
+            const int sh = (o & 3) * 8;
+            const uint32_t *wp = win + yl * pitch + (o >> 2);
+            const uint32_t *sp = srcw;
+            uint32_t        sad = 0;
+            for (int r = 0; r < rows; r++) {
+                uint32_t prev = wp[0];
+                for (int cw = 0; cw < nw; cw++) {
+                    const uint32_t next = wp[cw + 1];
+                    uint32_t       v    = __funnelshift_r(prev, next, sh);
+                    prev                = next;
+                    if (cw == nw - 1)
+                        v &= last_mask;
+                    sad = vsad4(sp[cw], v, sad);
+                }
+                wp += pitch * step;
+                sp += nw;
+            }
+            const unsigned long long key = ((unsigned long long)sad << 32) | (uint32_t)((e0 + ee) * t.sa_w + x);
+            best                         = key < best ? key : best;
+        }
+    }
+    /* CTA minimum of (sad, scan index): the first minimum in scan order wins, as in the reference */
+    for (int off = 16; off; off >>= 1) {
+        const unsigned long long o = __shfl_xor_sync(0xffffffffu, best, off);
+        best                       = o < best ? o : best;
+    }
+    if ((tid & 31) == 0)
+        ks_red[tid >> 5] = best;
+    __syncthreads();
+    if (tid == 0) {
+        for (int i = 1; i < KS_THREADS / 32; i++) best = ks_red[i] < best ? ks_red[i] : best;
+        SearchResult r;
+        r.sad   = (uint32_t)(best >> 32);
+        r.found = r.sad < ME_SAD_LOOP_INIT;
+        r.x = r.y = 0;
+        r.pad_[0] = r.pad_[1] = r.pad_[2] = 0;
+        if (r.found) {
+            const uint32_t idx = (uint32_t)best;
+            const uint32_t ee  = idx / (uint32_t)t.sa_w;
+            r.x                = (int16_t)(idx - ee * (uint32_t)t.sa_w);
+            r.y                = (int16_t)(skip ? 2 * ee + 1 : ee);
+        }
+        j->results[(size_t)b * ME_SLOTS + slot] = r;
+    }
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * k_fullsearch: integer full search, all 85 square PUs per position
+ * ---------------------------------------------------------------------------------------------- */
+#define FS_THREADS 256
+#define FS_PW 36 /* words per window row and copy: 4 x odd, so that 8 rows hit 8 distinct 16-byte bank groups */
+#define FS_ROWS 96 /* FS_TH + 63 window rows (+1) */
+#define FS_KEY_SHIFT 11 /* 64 x 32 tile positions */
+#define FS_BIAS (1u << 17) /* added to the 8x8 SADs of positions outside the tile: they can never win */
+#define FS_SMEM_BYTES ((4 * FS_ROWS * FS_PW + 64 * 16 + 96) * 4)
+
+template <bool SUB>
+__device__ __forceinline__ void fs_compute(const uint32_t *__restrict__ wc, const uint32_t *__restrict__ srcw,
+                                           uint32_t *sbest, int xw0, int ly, int s, int wvalid, int hvalid, int lane) {
+    constexpr int RSTEP = SUB ? 2 : 1; /* window rows per summed block row */
+    constexpr int NR    = SUB ? 4 : 8; /* summed rows per 8x8 block */
+    uint32_t      bias[8], idx[8];
+    uint32_t      vmask = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const int  lx = xw0 + s + 4 * k;
+        const bool v  = lx < wvalid && ly < hvalid;
+        bias[k]       = v ? 0u : FS_BIAS;
+        idx[k]        = (uint32_t)(ly * FS_TW + lx);
+        vmask |= (v ? 1u : 0u) << k;
+    }
+    const int j0 = xw0 >> 2;
+    uint32_t  s64[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) s64[k] = 0;
+#pragma unroll 1
+    for (int q = 0; q < 4; q++) {
+        const int qx = q & 1, qy = q >> 1;
+        uint32_t  s32[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) s32[k] = 0;
+#pragma unroll 1
+        for (int h = 0; h < 2; h++) {
+            uint32_t s16[2][8];
+#pragma unroll
+            for (int k = 0; k < 8; k++) s16[0][k] = s16[1][k] = 0;
+#pragma unroll
+            for (int br = 0; br < 2; br++) {
+                uint32_t acc[4][8];
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+#pragma unroll
+                    for (int k = 0; k < 8; k++) acc[i][k] = bias[k];
+                const int brow = 32 * qy + 16 * h + 8 * br; /* first pixel row of this 8x8 block row */
+#pragma unroll
+                for (int r = 0; r < NR; r++) {
+                    const uint4 *rp = (const uint4 *)(wc + (ly + brow + r * RSTEP) * FS_PW + j0 + 8 * qx);
+                    const uint4 *sp = (const uint4 *)(srcw + (brow / RSTEP + r) * 16 + 8 * qx);
+                    uint32_t     rw[16], sw[8];
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        const uint4 v = rp[i];
+                        rw[4 * i] = v.x; rw[4 * i + 1] = v.y; rw[4 * i + 2] = v.z; rw[4 * i + 3] = v.w;
+                    }
+#pragma unroll
+                    for (int i = 0; i < 2; i++) {
+                        const uint4 v = sp[i];
+                        sw[4 * i] = v.x; sw[4 * i + 1] = v.y; sw[4 * i + 2] = v.z; sw[4 * i + 3] = v.w;
+                    }
+#pragma unroll
+                    for (int cw = 0; cw < 8; cw++)
+#pragma unroll
+                        for (int k = 0; k < 8; k++) acc[cw >> 1][k] = vsad4(sw[cw], rw[cw + k], acc[cw >> 1][k]);
+                }
+                /* four 8x8 PUs done for 8 positions: z-order index 21 + 16q + 8h + 4(i>>1) + 2br + (i&1) */
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    uint32_t m = 0xFFFFFFFFu;
+#pragma unroll
+                    for (int k = 0; k < 8; k++) m = min(m, (acc[i][k] << FS_KEY_SHIFT) + idx[k]);
+                    m = __reduce_min_sync(0xffffffffu, m);
+                    if (lane == 0)
+                        atomicMin(&sbest[21 + 16 * q + 8 * h + 4 * (i >> 1) + 2 * br + (i & 1)], m);
+#pragma unroll
+                    for (int k = 0; k < 8; k++) s16[i >> 1][k] += acc[i][k];
+                }
+            }
+            /* two 16x16 PUs: 5 + 4q + 2h + {0,1} */
+#pragma unroll
+            for (int i = 0; i < 2; i++) {
+                uint32_t m = 0xFFFFFFFFu;
+#pragma unroll
+                for (int k = 0; k < 8; k++) m = min(m, (s16[i][k] << FS_KEY_SHIFT) + idx[k]);
+                m = __reduce_min_sync(0xffffffffu, m);
+                if (lane == 0)
+                    atomicMin(&sbest[5 + 4 * q + 2 * h + i], m);
+#pragma unroll
+                for (int k = 0; k < 8; k++) s32[k] += s16[i][k];
+            }
+        }
+        /* 32x32 PU 1 + q: positions outside the tile are masked explicitly (their bias overflows the key) */
+        {
+            uint32_t m = 0xFFFFFFFFu;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const uint32_t key = (s32[k] << FS_KEY_SHIFT) + idx[k];
+                m                  = min(m, (vmask >> k) & 1u ? key : 0xFFFFFFFFu);
+            }
+            m = __reduce_min_sync(0xffffffffu, m);
+            if (lane == 0)
+                atomicMin(&sbest[1 + q], m);
+#pragma unroll
+            for (int k = 0; k < 8; k++) s64[k] += s32[k];
+        }
+    }
+    {
+        uint32_t m = 0xFFFFFFFFu;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const uint32_t key = (s64[k] << FS_KEY_SHIFT) + idx[k];
+            m                  = min(m, (vmask >> k) & 1u ? key : 0xFFFFFFFFu);
+        }
+        m = __reduce_min_sync(0xffffffffu, m);
+        if (lane == 0)
+            atomicMin(&sbest[0], m);
+    }
+}
+
+__global__ void __launch_bounds__(FS_THREADS, 2) k_fullsearch(MeJob *jobs, FsTileList *list, const uint8_t *pool) {
+    extern __shared__ __align__(16) uint32_t fs_smem[];
+    uint32_t *win   = fs_smem; /* [4][FS_ROWS][FS_PW] */
+    uint32_t *srcw  = fs_smem + 4 * FS_ROWS * FS_PW; /* [64][16] (32 rows used for sub-sampled SAD) */
+    uint32_t *sbest = srcw + 64 * 16; /* [85] packed (sad << 11 | tile position) */
+    __shared__ uint32_t s_tile;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t total = list->count > list->cap ? 0u : list->count;
+
+    for (;;) {
+        __syncthreads();
+        if (tid == 0)
+            s_tile = atomicAdd(&list->next, 1u);
+        __syncthreads();
+        const uint32_t ti = s_tile;
+        if (ti >= total)
+            break;
+        const FsTile  tile = list->tiles[ti];
+        MeJob        *j    = &jobs[tile.job];
+        const FsTask  f    = j->fs_tasks[tile.task];
+        const uint32_t b   = tile.task / ME_NREF;
+        const bool    sub  = j->p.me_search_method == ME_GPU_SUB_SAD_SEARCH;
+        const MePlaneGeom pl = j->g.plane[0];
+        const int org_x = (int)(b % (uint32_t)j->g.b64_cols) * 64, org_y = (int)(b / (uint32_t)j->g.b64_cols) * 64;
+        const int wvalid = min(FS_TW, f.w - (int)tile.tx), hvalid = min(FS_TH, f.h - (int)tile.ty);
+
+        /* stage: source block rows (every other row for sub-sampled SAD) */
+        {
+            const uint8_t *sp = plane_ptr(pool, j->g, j->src_slot, 0) + (size_t)(pl.pad + org_y) * pl.stride + pl.pad + org_x;
+            const int      nrows = sub ? 32 : 64, rstep = sub ? 2 : 1;
+            for (int i = tid; i < nrows * 16; i += FS_THREADS) {
+                const int r = i >> 4, cw = i & 15;
+                srcw[i]     = *(const uint32_t *)(sp + (size_t)(r * rstep) * pl.stride + cw * 4);
+            }
+            if (tid < ME_NPU)
+                sbest[tid] = 0xFFFFFFFFu;
+        }
+        /* stage: reference window, four copies shifted by 0..3 bytes */
+        {
+            const int      gx = org_x + f.x0 + (int)tile.tx, gy = org_y + f.y0 + (int)tile.ty;
+            const uint8_t *w00 = plane_ptr(pool, j->g, f.ref_slot, 0) + (size_t)(pl.pad + gy) * pl.stride + pl.pad + gx;
+            const int      a   = (int)((uintptr_t)w00 & 3);
+            const uint32_t *g0 = (const uint32_t *)(w00 - a);
+            const int      nrows = hvalid + (sub ? 62 : 63) + 1;
+            for (int i = tid; i < nrows * FS_PW; i += FS_THREADS) {
+                const int       r = i / FS_PW, cw = i - r * FS_PW;
+                const uint32_t *g = g0 + (size_t)r * (pl.stride >> 2) + cw;
+                const uint32_t  w0 = g[0], w1 = g[1], w2 = g[2];
+#pragma unroll
+                for (int s = 0; s < 4; s++) {
+                    const int t = a + s;
+                    win[(s * FS_ROWS + r) * FS_PW + cw] =
+                        t < 4 ? __funnelshift_r(w0, w1, 8 * t) : __funnelshift_r(w1, w2, 8 * (t - 4));
+                }
+            }
+        }
+        __syncthreads();
+        /* compute: warp -> 32 x 8 positions, lane -> (byte shift s, row), 8 positions x = s + 4k per thread */
+        {
+            const int xw0 = (warp & 1) * 32, yw0 = (warp >> 1) * 8;
+            if (xw0 < wvalid && yw0 < hvalid) {
+                const int s = lane >> 3, ly = yw0 + (lane & 7);
+                if (sub)
+                    fs_compute<true>(win + s * FS_ROWS * FS_PW, srcw, sbest, xw0, ly, s, wvalid, hvalid, lane);
+                else
+                    fs_compute<false>(win + s * FS_ROWS * FS_PW, srcw, sbest, xw0, ly, s, wvalid, hvalid, lane);
+            }
+        }
+        __syncthreads();
+        /* merge the tile's best keys into the task's 64-bit (sad, scan order) keys */
+        if (tid < ME_NPU) {
+            const uint32_t key = sbest[tid];
+            if (key != 0xFFFFFFFFu) {
+                const uint32_t raw = key >> FS_KEY_SHIFT, pos = key & ((1u << FS_KEY_SHIFT) - 1u);
+                const uint32_t lx = pos & (FS_TW - 1), ly = pos / FS_TW;
+                const uint32_t sad = sub ? raw << 1 : raw;
+                const uint32_t ord = f.probe ? 0u : 1u + (tile.ty + ly) * (uint32_t)f.w + tile.tx + lx;
+                atomicMin(&j->keys[(size_t)tile.task * ME_NPU + tid], ((unsigned long long)sad << 32) | ord);
+            }
+        }
+    }
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * k_epilogue: one CTA per b64
+ * ---------------------------------------------------------------------------------------------- */
+#define EP_THREADS 96
+__global__ void __launch_bounds__(EP_THREADS) k_epilogue(MeJob *jobs) {
+    __shared__ uint32_t best_sad[ME_NREF][ME_NPU], best_mv[ME_NREF][ME_NPU], me_distortion[ME_NPU];
+    MeJob         *j = &jobs[blockIdx.y];
+    const uint32_t b = blockIdx.x;
+    const int      tid = threadIdx.x;
+    EpiCtx         e;
+    e.j    = j;
+    e.p    = &j->p;
+    e.s    = &j->state[b];
+    e.keys = &j->keys[(size_t)b * ME_NREF * ME_NPU];
+    e.b    = b;
+    const int org_x = (int)(b % (uint32_t)j->g.b64_cols) * 64, org_y = (int)(b / (uint32_t)j->g.b64_cols) * 64;
+    e.b64_w         = (uint32_t)min(64, j->g.width - org_x);
+    e.b64_h         = (uint32_t)min(64, j->g.height - org_y);
+    e.best_sad      = best_sad;
+    e.best_mv       = best_mv;
+    e.me_distortion = me_distortion;
+    for (int i = tid; i < ME_NREF * ME_NPU; i += EP_THREADS) me_epi_decode(&e, i / ME_NPU, i % ME_NPU);
+    __syncthreads();
+    if (tid == 0 && j->p.enable_hme_flag && j->p.enable_me_hme_ref_pruning)
+        me_epi_prune(&e);
+    __syncthreads();
+    if (tid < j->p.max_number_of_pus_per_sb)
+        me_epi_candidates(&e, tid);
+    __syncthreads();
+    if (tid == 0) {
+        me_epi_distortion(&e);
+        me_epi_gm(&e);
+        me_epi_taps(&e);
+        atomicAdd(j->ops_total, (unsigned long long)e.s->ops);
+    }
+    if (j->dbg_best_sad)
+        for (int i = tid; i < ME_NREF * ME_NPU; i += EP_THREADS)
+            j->dbg_best_sad[(size_t)b * ME_NREF * ME_NPU + i] = best_sad[i / ME_NPU][i % ME_NPU];
+    if (j->dbg_best_mv)
+        for (int i = tid; i < ME_NREF * ME_NPU; i += EP_THREADS)
+            j->dbg_best_mv[(size_t)b * ME_NREF * ME_NPU + i] = best_mv[i / ME_NPU][i % ME_NPU];
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * integer-SAD issue-rate probe (roofline denominator): independent VABSDIFF4.ACC chains
+ * ---------------------------------------------------------------------------------------------- */
+__global__ void __launch_bounds__(256) k_sad_peak(uint32_t *out, int iters, uint32_t seed) {
+    uint32_t acc[16], a[4], b[4];
+#pragma unroll
+    for (int i = 0; i < 16; i++) acc[i] = i;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        a[i] = seed * (threadIdx.x + i);
+        b[i] = seed ^ (threadIdx.x * 77 + i);
+    }
+    for (int it = 0; it < iters; it++)
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+#pragma unroll
+            for (int i = 0; i < 16; i++) {
+                uint32_t d;
+                asm volatile("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a[i & 3]), "r"(b[r]), "r"(acc[i]));
+                acc[i] = d;
+            }
+    uint32_t s = 0;
+#pragma unroll
+    for (int i = 0; i < 16; i++) s += acc[i];
+    if (s == 0x12345678u)
+        out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * launchers
+ * ---------------------------------------------------------------------------------------------- */
+static unsigned long long g_launches = 0;
+unsigned long long me_launch_count(void) { return g_launches; }
+
+cudaError_t me_kernels_setup(void) {
+    cudaError_t e = cudaFuncSetAttribute(k_search, cudaFuncAttributeMaxDynamicSharedMemorySize, KS_SMEM_WORDS * 4);
+    if (e != cudaSuccess)
+        return e;
+    return cudaFuncSetAttribute(k_fullsearch, cudaFuncAttributeMaxDynamicSharedMemorySize, FS_SMEM_BYTES);
+}
+
+void me_launch_pad_full(uint8_t *pool, size_t slot_off, const MePlaneGeom *pl, cudaStream_t st) {
+    dim3 grid((pl->width + 2 * pl->pad + 1023) / 1024, pl->rows);
+    k_pad_full<<<grid, 256, 0, st>>>(pool, slot_off, *pl);
+    g_launches++;
+}
+
+void me_launch_downsample(uint8_t *pool, size_t slot_off, const MePlaneGeom *src, const MePlaneGeom *dst, cudaStream_t st) {
+    dim3 grid((dst->stride / 4 + 255) / 256, dst->rows);
+    k_downsample_pad<<<grid, 256, 0, st>>>(pool, slot_off, *src, *dst);
+    g_launches++;
+}
+
+void me_launch_ctrl(MeJob *jobs, int njobs, int max_b64, uint32_t stage_mask, FsTileList *list, cudaStream_t st) {
+    dim3 grid((max_b64 + 63) / 64, njobs);
+    k_ctrl<<<grid, 64, 0, st>>>(jobs, stage_mask, list);
+    g_launches++;
+}
+
+void me_launch_search(const MeJob *jobs, int njobs, int max_b64, int slots, const uint8_t *pool, cudaStream_t st) {
+    dim3 grid(slots, max_b64, njobs);
+    k_search<<<grid, KS_THREADS, KS_SMEM_WORDS * 4, st>>>(jobs, pool);
+    g_launches++;
+}
+
+void me_launch_fullsearch(MeJob *jobs, FsTileList *list, const uint8_t *pool, int ctas, cudaStream_t st) {
+    k_fullsearch<<<ctas, FS_THREADS, FS_SMEM_BYTES, st>>>(jobs, list, pool);
+    g_launches++;
+}
+
+void me_launch_epilogue(MeJob *jobs, int njobs, int max_b64, cudaStream_t st) {
+    dim3 grid(max_b64, njobs);
+    k_epilogue<<<grid, EP_THREADS, 0, st>>>(jobs);
+    g_launches++;
+}
+
+/* returns VABSDIFF4 lane-ops per second on the current device */
+double me_measure_sad_peak(cudaStream_t st) {
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    uint32_t *out = nullptr;
+    if (cudaMalloc(&out, (size_t)sms * 8 * 256 * 4) != cudaSuccess)
+        return 0.0;
+    const int iters = 8192;
+    k_sad_peak<<<sms * 8, 256, 0, st>>>(out, 256, 1234567u);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    double best = 0.0;
+    for (int rep = 0; rep < 3; rep++) {
+        cudaEventRecord(e0, st);
+        k_sad_peak<<<sms * 8, 256, 0, st>>>(out, iters, 1234567u);
+        cudaEventRecord(e1, st);
+        cudaEventSynchronize(e1);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double rate = 64.0 * iters * (double)sms * 8 * 256 / (ms * 1e-3);
+        if (rate > best)
+            best = rate;
+    }
+    g_launches += 4;
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(out);
+    return best;
+}

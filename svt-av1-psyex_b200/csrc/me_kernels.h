@@ -1,0 +1,30 @@
+/* me_kernels.h - launch wrappers of me_kernels.cu (internal to libme_gpu.so) */
+#ifndef ME_KERNELS_H
+#define ME_KERNELS_H
+
+#include <cuda_runtime.h>
+
+#include "me_types.h"
+
+#define FS_TW 64 /* full-search tile: 64 x 32 search positions per CTA iteration */
+#define FS_TH 32
+
+typedef struct FsTileList {
+    unsigned int count; /* tiles appended by k_ctrl */
+    unsigned int next; /* next tile to hand out (k_fullsearch) */
+    unsigned int cap;
+    unsigned int overflow;
+    FsTile      *tiles;
+} FsTileList;
+
+cudaError_t        me_kernels_setup(void);
+unsigned long long me_launch_count(void);
+void   me_launch_pad_full(uint8_t *pool, size_t slot_off, const MePlaneGeom *pl, cudaStream_t st);
+void   me_launch_downsample(uint8_t *pool, size_t slot_off, const MePlaneGeom *src, const MePlaneGeom *dst, cudaStream_t st);
+void   me_launch_ctrl(MeJob *jobs, int njobs, int max_b64, uint32_t stage_mask, FsTileList *list, cudaStream_t st);
+void   me_launch_search(const MeJob *jobs, int njobs, int max_b64, int slots, const uint8_t *pool, cudaStream_t st);
+void   me_launch_fullsearch(MeJob *jobs, FsTileList *list, const uint8_t *pool, int ctas, cudaStream_t st);
+void   me_launch_epilogue(MeJob *jobs, int njobs, int max_b64, cudaStream_t st);
+double me_measure_sad_peak(cudaStream_t st);
+
+#endif

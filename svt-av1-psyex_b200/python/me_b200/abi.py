@@ -137,7 +137,7 @@ REF_LIB = os.path.join(REPO, "oracle", "_ref", "libme_ref.so")
 GPU_SYMBOLS = [
     "me_gpu_init", "me_gpu_shutdown", "me_gpu_last_error", "me_gpu_device_count", "me_gpu_register_picture",
     "me_gpu_register_picture_unpadded", "me_gpu_release_picture", "me_gpu_read_pyramid", "me_gpu_plane_geometry",
-    "me_gpu_submit", "me_gpu_wait", "me_gpu_derive_params", "me_gpu_get_timings",
+    "me_gpu_submit", "me_gpu_wait", "me_gpu_derive_params", "me_gpu_get_timings", "me_gpu_measure_sad_peak",
 ]
 
 
@@ -157,6 +157,7 @@ def load_gpu_lib():
     lib.me_gpu_wait.argtypes = [u64, C.POINTER(MeGpuOutputs)]
     lib.me_gpu_derive_params.argtypes = [C.POINTER(MeGpuEncoderConfig), C.POINTER(MeGpuParams)]
     lib.me_gpu_get_timings.argtypes = [C.POINTER(MeGpuTimings)]
+    lib.me_gpu_measure_sad_peak.restype = C.c_double
     return lib
 
 

@@ -1,0 +1,74 @@
+"""Shared case construction for the tests: encoder config -> ME controls, synthetic pictures, reference lists."""
+import ctypes as C
+import functools
+
+import numpy as np
+
+from me_b200 import abi, planes, synth
+
+
+@functools.lru_cache(maxsize=None)
+def host_lib():
+    return abi.load_host_lib()
+
+
+def derive(preset, width, height, poc, n_pictures, force_refs=None, qp=35, **kw):
+    """MeGpuParams + reference lists of picture `poc` in a random-access 5-layer sequence."""
+    tl = synth.RA5_RPS[poc % 16][0]
+    cfg = abi.MeGpuEncoderConfig(enc_mode=preset, qp=qp, hierarchical_levels=4, width=width, height=height,
+                                 picture_number=poc, temporal_layer_index=tl, is_ref=1 if tl < 4 else 0, **kw)
+    if force_refs:
+        cfg.force_ref_l0, cfg.force_ref_l1 = force_refs
+    p = abi.MeGpuParams()
+    rc = host_lib().me_gpu_derive_params(C.byref(cfg), C.byref(p))
+    assert rc == 0
+    _, l0, l1 = synth.ref_lists(poc, n_pictures, p.num_of_ref_pic_to_search[0], p.num_of_ref_pic_to_search[1])
+    p.num_of_ref_pic_to_search[0] = len(l0)
+    p.num_of_ref_pic_to_search[1] = len(l1)
+    if not l1:
+        p.num_of_list_to_search = 1
+    return cfg, p, l0, l1
+
+
+class PictureSet:
+    """Synthetic pictures with CPU-built pyramids (by `builder`: an Oracle or Reference checker)."""
+
+    def __init__(self, width, height, n_pictures, kind, builder, seed=1234):
+        self.w, self.h, self.n = width, height, n_pictures
+        self.seq = synth.Sequence(width, height, n_pictures, kind=kind, seed=seed)
+        self.builder = builder
+        self.pics = {}
+
+    def get(self, poc):
+        if poc not in self.pics:
+            p = planes.Picture(self.w, self.h, poc)
+            p.set_luma(self.seq.luma(poc))
+            self.builder.build_pyramid(p)
+            self.pics[poc] = p
+        return self.pics[poc]
+
+
+class Emulator:
+    """tests/emul/libme_emul.so: the product's control logic on the CPU (test harness)."""
+
+    def __init__(self):
+        import os
+        self.lib = C.CDLL(os.path.join(os.path.dirname(__file__), "emul", "libme_emul.so"))
+        self.lib.emul_me_picture.argtypes = [C.POINTER(abi.OraclePicture), C.POINTER(abi.RefArray),
+                                             C.POINTER(abi.MeGpuParams), C.POINTER(abi.MeGpuOutputs),
+                                             C.POINTER(abi.u64)]
+
+    def me_picture(self, src, refs, params):
+        from me_b200 import checkers
+        out = planes.Outputs(src.width, src.height, params)
+        arr, keep = checkers._refs_array(refs)
+        s = src.c_struct()
+        ops = abi.u64(0)
+        rc = self.lib.emul_me_picture(C.byref(s), C.byref(arr), C.byref(params), C.byref(out.c), C.byref(ops))
+        assert rc == 0, rc
+        out.byte_sad_ops = ops.value
+        return out
+
+
+def used_refs(l0, l1):
+    return [len(l0), len(l1)]

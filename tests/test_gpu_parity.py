@@ -1,0 +1,98 @@
+"""GPU parity: the CUDA engine (through the C-ABI) against the CPU oracle on the same seeded inputs.
+Bit-exact: every candidate, MV, SAD, distortion statistic and parity tap."""
+import numpy as np
+import pytest
+
+from helpers import PictureSet, derive, used_refs
+from me_b200 import planes
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def oracle():
+    from me_b200.checkers import Oracle
+    return Oracle()
+
+
+@pytest.fixture(scope="module")
+def engine():
+    from me_b200.engine import Engine
+    eng = Engine(1920, 1088, 4, 3, pictures_in_flight=24)
+    yield eng
+    eng.close()
+
+
+def _register(engine, ps, pocs):
+    for k in pocs:
+        engine.register_picture(k, ps.get(k).planes[0], ps.w, ps.h)
+
+
+def _release(engine, pocs):
+    for k in pocs:
+        engine.release_picture(k)
+
+
+@pytest.mark.parametrize("size", [(320, 192), (200, 136), (64, 64), (1920, 1080)])
+def test_pyramid_matches_reference_downsampler(engine, oracle, size):
+    w, h = size
+    ps = PictureSet(w, h, 2, "motion" if w >= 200 else "iid", oracle)
+    pic = ps.get(1)
+    engine.register_picture(1, pic.planes[0], w, h)
+    got = engine.read_pyramid(1, w, h)
+    engine.release_picture(1)
+    for lvl in range(3):
+        assert np.array_equal(got[lvl], pic.planes[lvl]), f"level {lvl}"
+    # unpadded registration: the 68-pixel border is generated on the device
+    engine.register_picture_unpadded(2, np.ascontiguousarray(pic.interior(0)))
+    got = engine.read_pyramid(2, w, h)
+    engine.release_picture(2)
+    for lvl in range(3):
+        assert np.array_equal(got[lvl], pic.planes[lvl]), f"unpadded level {lvl}"
+
+
+CASES = [(preset, poc, kind) for preset in (8, 4, 2, 6, 10, 0, -1) for poc in (16, 8, 4, 1, 7) for kind in ("motion", "iid")
+         if not (preset <= 0 and kind == "iid" and poc != 1)]
+
+
+@pytest.mark.parametrize("size", [(320, 192), (200, 136)])
+@pytest.mark.parametrize("preset,poc,kind", CASES)
+def test_me_parity_small(engine, oracle, size, preset, poc, kind):
+    w, h = size
+    n = 33
+    ps = PictureSet(w, h, n, kind, oracle)
+    cfg, p, l0, l1 = derive(preset, w, h, poc, n)
+    pocs = sorted(set([poc] + l0 + l1))
+    _register(engine, ps, pocs)
+    try:
+        got = engine.me_picture(poc, w, h, p, [l0, l1])
+    finally:
+        _release(engine, pocs)
+    exp = oracle.me_picture(ps.get(poc), [[ps.get(k) for k in l0], [ps.get(k) for k in l1]], p)
+    bad = planes.compare_outputs(exp, got, used_refs=used_refs(l0, l1))
+    assert not bad, bad
+    assert exp.byte_sad_ops == got.byte_sad_ops
+
+
+@pytest.mark.parametrize("preset,poc,kind,first,count", [(8, 4, "motion", 0, 510), (4, 8, "motion", 200, 40),
+                                                         (4, 1, "iid", 490, 20), (2, 2, "motion", 29, 3)])
+def test_me_parity_1080p_sample(engine, oracle, preset, poc, kind, first, count):
+    """Full-size pictures: the GPU does the whole picture, the oracle a sample of b64s (seconds of CPU)."""
+    w, h, n = 1920, 1080, 17
+    ps = PictureSet(w, h, n, kind, oracle)
+    cfg, p, l0, l1 = derive(preset, w, h, poc, n)
+    pocs = sorted(set([poc] + l0 + l1))
+    _register(engine, ps, pocs)
+    try:
+        got = engine.me_picture(poc, w, h, p, [l0, l1])
+    finally:
+        _release(engine, pocs)
+    exp = oracle.me_picture(ps.get(poc), [[ps.get(k) for k in l0], [ps.get(k) for k in l1]], p, first, count)
+    for name in exp.arrays:
+        a, b = exp.arrays[name][first:first + count], got.arrays[name][first:first + count]
+        if name in planes.DEBUG_FIELDS:
+            mask = np.zeros((2, 4), dtype=bool)
+            mask[0, :len(l0)] = True
+            mask[1, :len(l1)] = True
+            a, b = a[:, mask], b[:, mask]
+        assert np.array_equal(a, b), name
