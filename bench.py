@@ -1,0 +1,388 @@
+#!/usr/bin/env python
+"""bench.py - open-loop ME frames/s of the B200 engine (and of the reference's CPU path beside it).
+
+Workload (BASELINE.json configs[1]): 1920x1080 8-bit, preset 4, mini-GOP 16 (5-layer random access),
+2 references per list, default HME + integer search areas, synthetic "motion" sequence.
+One step = open-loop ME of the 16 pictures of one mini-GOP (POC 17..32 of a 33-picture sequence), i.e. the
+whole hot path: pyramid, pre-HME/HME, integer full search, candidate construction, results in host memory.
+
+  value  frames/s with the pictures (and pyramids) already resident in HBM; results still return to the host
+  e2e    frames/s through the C-ABI with host buffers: every step uploads its 16 source planes from pinned
+         host memory (pyramids built on the device), runs ME, downloads the MeSbResults images, releases
+  roofline    dominant kernel vs the measured VABSDIFF4 issue rate (integer-SAD roofline)
+  cpu_baseline  the reference's own svt_aom_motion_estimation_b64 + AVX2 kernels (oracle/_ref) on the host cores
+
+Usage: python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--kind motion|iid]
+Under torchrun every rank runs the same workload on its own GPU (weak scaling, no collective on the path).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import threading
+import time
+from concurrent.futures import ThreadPoolExecutor
+
+import numpy as np
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(REPO, "svt-av1-psyex_b200", "python"))
+sys.path.insert(0, os.path.join(REPO, "tests"))
+
+from me_b200 import abi, planes, synth  # noqa: E402
+
+W, H, PRESET, NPIC, FORCE_REFS = 1920, 1080, 4, 33, (2, 2)
+# decode order of mini-GOP 2 (POC 17..32)
+STEP_POCS = [32 if g == 0 else 16 + g for g in synth.RA5_DECODE_ORDER]
+
+
+def derive(poc):
+    from helpers import derive as _d
+    return _d(PRESET, W, H, poc, NPIC, force_refs=FORCE_REFS)
+
+
+def rank_info():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi style clock / throttle-reason samples during the timed region (pynvml)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.samples, self.reasons, self.stop_flag, self.max_mhz = [], set(), False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if not self.nv:
+            return
+        names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+        while not self.stop_flag:
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                r = self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, n in names.items():
+                    if r & bit:
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def make_pictures(kind, pinned):
+    """padded full-resolution planes of the 33 pictures, in pinned host memory when torch+CUDA are there"""
+    seq = synth.Sequence(W, H, NPIC, kind=kind)
+    rows, stride = H + 136, W + 136
+    out = {}
+    for poc in range(NPIC):
+        if pinned:
+            import torch
+            t = torch.empty((rows, stride), dtype=torch.uint8).pin_memory()
+            a = t.numpy()
+            out[poc] = (a, t)
+        else:
+            out[poc] = (np.empty((rows, stride), dtype=np.uint8), None)
+        out[poc][0][...] = np.pad(seq.luma(poc), 68, mode="edge")
+    return out
+
+
+def pinned_outputs(params):
+    """MeGpuOutputs (product fields only) backed by pinned memory"""
+    import torch
+    o = planes.Outputs(W, H, params, debug=False)
+    keep = []
+    for name, arr in list(o.arrays.items()):
+        t = torch.zeros(arr.nbytes, dtype=torch.uint8).pin_memory()
+        a = t.numpy().view(arr.dtype).reshape(arr.shape)
+        o.arrays[name] = a
+        setattr(o.c, name, C.cast(a.ctypes.data, dict(abi.MeGpuOutputs._fields_)[name]))
+        keep.append(t)
+    o._keep = keep
+    return o
+
+
+# --------------------------------------------------------------------------------------------------
+# reference CPU arm (oracle/_ref: the reference's own sources compiled in place)
+# --------------------------------------------------------------------------------------------------
+class CpuArm:
+    """The reference's ME (svt_aom_motion_estimation_b64 + AVX2 kernels, oracle/_ref) on host threads."""
+
+    def __init__(self, kind, pocs, threads, simd=1):
+        from me_b200 import checkers
+        self.ref = checkers.Reference()
+        self.threads, self.simd, self.pocs = threads, simd, pocs
+        seq = synth.Sequence(W, H, NPIC, kind=kind)
+        pics = {}
+
+        def get(k):
+            if k not in pics:
+                p = planes.Picture(W, H, k)
+                p.set_luma(seq.luma(k))
+                self.ref.build_pyramid(p)
+                pics[k] = p
+            return pics[k]
+
+        self.work, self.keep = [], []
+        for poc in pocs:
+            cfg, p, l0, l1 = derive(poc)
+            refs = [[get(k) for k in l0], [get(k) for k in l1]]
+            out = planes.Outputs(W, H, p, debug=False)
+            arr, keep = checkers._refs_array(refs)
+            s = get(poc).c_struct()
+            self.keep.append((refs, out, arr, keep, s, p))
+            for first in range(0, 510, 6):  # 510 b64 per picture in chunks of 6
+                self.work.append((s, arr, p, out, first))
+        # fill the RTCD table on one thread before fanning out
+        s, arr, p, out, _ = self.work[0]
+        self.ref.lib.ref_me_b64_range(C.byref(s), C.byref(arr), C.byref(p), C.byref(out.c), 0, 1, simd)
+        self.pool = ThreadPoolExecutor(threads)
+
+    def _run(self, item):
+        s, arr, p, out, first = item
+        rc = self.ref.lib.ref_me_b64_range(C.byref(s), C.byref(arr), C.byref(p), C.byref(out.c), first, 6, self.simd)
+        assert rc == 0
+
+    def step(self):
+        """ME of every picture of the arm once; returns seconds"""
+        t0 = time.perf_counter()
+        list(self.pool.map(self._run, self.work))
+        return time.perf_counter() - t0
+
+
+def cpu_model():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except Exception:
+        pass
+    return "unknown"
+
+
+def reference_main(args):
+    rank, _, world = rank_info()
+    if rank != 0:
+        return 0
+    threads = os.cpu_count() or 1
+    arm = CpuArm(args.kind, STEP_POCS, threads)
+    for _ in range(args.warmup):
+        arm.step()
+    t_total = 0.0
+    for _ in range(args.steps):
+        t_total += arm.step()
+    n = 16 * args.steps
+    value = n / t_total
+    sample = f"the 16 pictures of the step, all 510 b64 each, per step; {threads} threads"
+    line = {
+        "impl": "reference", "metric": "open-loop ME frames/sec", "value": value, "unit": "frames/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_total / max(1, args.steps),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": workload_config(args.kind),
+        "cpu_baseline": {"value": value, "unit": "frames/s", "cores": threads, "kind": "reference", "sample": sample,
+                         "cpu": cpu_model(), "simd": "avx2 (svt_*_avx2 kernels behind the reference's RTCD pointers)"},
+        "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def workload_config(kind):
+    return {"workload": "1080p 8-bit preset 4, mini-GOP 16, 2 refs/list, default HME + integer search areas "
+                        "(BASELINE.json configs[1])", "width": W, "height": H, "preset": PRESET, "refs": list(FORCE_REFS),
+            "pictures_per_step": 16, "sequence": f"synthetic {kind}, seed 1234, 33 pictures", "qp": 35,
+            "l2": "flushed between steps (256 MiB write)"}
+
+
+# --------------------------------------------------------------------------------------------------
+# B200 arm
+# --------------------------------------------------------------------------------------------------
+def gpu_main(args):
+    import torch
+    import torch.distributed as dist
+    from me_b200.engine import Engine
+
+    rank, local_rank, world = rank_info()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the engine has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    pics = make_pictures(args.kind, pinned=True)
+    jobs = {poc: derive(poc) for poc in STEP_POCS}
+    outs = {poc: pinned_outputs(jobs[poc][1]) for poc in STEP_POCS}
+    eng = Engine(W, H, 4, 3, pictures_in_flight=40, devices=[local_rank])
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def reg(poc):
+        a, _ = pics[poc]
+        eng.register_picture_ptr(poc, a.ctypes.data, a.strides[0], W, H)
+
+    def submit(poc):
+        _, p, l0, l1 = jobs[poc]
+        eng.submit(poc, p, [l0, l1])
+
+    def step_resident():
+        for poc in STEP_POCS:
+            submit(poc)
+        for poc in STEP_POCS:
+            eng.wait(poc, outs[poc])
+
+    def step_e2e():
+        for poc in STEP_POCS:
+            reg(poc)
+            submit(poc)
+        for poc in STEP_POCS:
+            eng.wait(poc, outs[poc])
+        for poc in STEP_POCS:
+            eng.release_picture(poc)
+
+    def timed(step_fn, steps, warmup):
+        for _ in range(warmup):
+            step_fn()
+        barrier()
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        l0 = eng.timings().kernel_launches
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            flush_buf.zero_()
+            torch.cuda.synchronize()
+            step_fn()
+        barrier()
+        dt = time.perf_counter() - t0
+        sampler.stop_flag = True
+        sampler.join()
+        launches = eng.timings().kernel_launches - l0
+        if world > 1:
+            t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        return dt, launches, sampler.summary()
+
+    # resident arm: everything registered once
+    for poc in range(NPIC):
+        reg(poc)
+    dt_res, launches, clocks = timed(step_resident, args.steps, args.warmup)
+
+    # roofline pass: one picture at a time, every launch bracketed by events on its stream
+    eng.set_profiling(True)
+    prof = {"k_search_ms": 0.0, "k_fullsearch_ms": 0.0, "k_fullsearch_main_ms": 0.0, "k_ctrl_ms": 0.0, "k_epilogue_ms": 0.0,
+            "total_ms": 0.0, "ops": 0, "ops_fs": 0}
+    for rep in range(2):
+        for k in prof:
+            prof[k] = 0 if k.startswith("ops") else 0.0
+        for poc in STEP_POCS:
+            flush_buf.zero_()
+            torch.cuda.synchronize()
+            submit(poc)
+            eng.wait(poc, outs[poc])
+            t = eng.timings()
+            for k in ("k_search_ms", "k_fullsearch_ms", "k_fullsearch_main_ms", "k_ctrl_ms", "k_epilogue_ms", "total_ms"):
+                prof[k] += getattr(t, k)
+            prof["ops"] += t.byte_sad_ops
+            prof["ops_fs"] += t.byte_sad_ops_fullsearch
+    eng.set_profiling(False)
+    sad_peak = 4.0 * eng.sad_peak()  # byte-SADs / s
+
+    # e2e arm: sources of the step uploaded every step
+    for poc in STEP_POCS:
+        eng.release_picture(poc)
+    dt_e2e, _, _ = timed(step_e2e, args.steps, args.warmup)
+
+    checksum = int(sum(int(outs[p]["me_mv_array"].astype(np.uint64).sum()) for p in STEP_POCS) & 0xFFFFFFFF)
+    eng.close()
+
+    n_frames = 16 * args.steps * world
+    value = n_frames / dt_res
+    e2e = n_frames / dt_e2e
+    h2d = 16 * (W + 136) * (H + 136)
+    d2h = sum(sum(a.nbytes for a in outs[p].arrays.values()) for p in STEP_POCS)
+
+    ops_hme = prof["ops"] - prof["ops_fs"]
+    kernels = {
+        "k_search": {"ms_per_step": prof["k_search_ms"], "byte_sads_per_step": ops_hme},
+        "k_fullsearch": {"ms_per_step": prof["k_fullsearch_ms"], "byte_sads_per_step": prof["ops_fs"]},
+        "k_ctrl": {"ms_per_step": prof["k_ctrl_ms"]},
+        "k_epilogue": {"ms_per_step": prof["k_epilogue_ms"]},
+    }
+    dom = "k_search" if prof["k_search_ms"] >= prof["k_fullsearch_ms"] else "k_fullsearch"
+    dom_ms, dom_ops = kernels[dom]["ms_per_step"], kernels[dom]["byte_sads_per_step"]
+    achieved = dom_ops / (dom_ms * 1e-3) / 1e12 if dom_ms > 0 else 0.0
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(REPO, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    roofline = {
+        "bound": "int_sad", "kernel": dom, "achieved": achieved, "peak": sad_peak / 1e12, "unit": "Tbyte-SAD/s",
+        "frac": achieved / (sad_peak / 1e12) if sad_peak else None, "traffic": None,
+        "peak_source": "VABSDIFF4.U8.ACC issue rate measured live by k_sad_peak on this GPU x 4 bytes",
+        "launches_per_step": 16 * (6 if dom == "k_search" else 2),
+        "kernels": kernels, "serial_ms_per_step": prof["total_ms"],
+        "whole_path_frac": (prof["ops"] / (prof["total_ms"] * 1e-3)) / sad_peak if sad_peak and prof["total_ms"] else None,
+        "hbm_peak_gbs": peaks.get("hbm_gbs"),
+    }
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        threads = os.cpu_count() or 1
+        arm = CpuArm(args.kind, STEP_POCS, threads)
+        arm.step()
+        reps, dt = 0, 0.0
+        while dt < 4.0 and reps < 20:
+            dt += arm.step()
+            reps += 1
+        cpu_baseline = {"value": 16 * reps / dt, "unit": "frames/s", "cores": threads, "kind": "reference",
+                        "sample": f"the step's 16 pictures x {reps} repetitions, all 510 b64 each, {dt:.1f} s wall on "
+                                  f"{threads} threads", "cpu": cpu_model(), "simd": "avx2"}
+    if rank == 0:
+        line = {
+            "metric": "open-loop ME frames/sec", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * dt_res / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": workload_config(args.kind),
+            "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": 1e3 * dt_e2e / args.steps},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
+            "result_checksum": checksum,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--kind", default="motion", choices=["motion", "iid"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_main(args)
+    return gpu_main(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -229,8 +229,18 @@ typedef struct MeGpuTimings {
     float total_ms;
     uint64_t kernel_launches; /* cumulative launches of this library's kernels */
     uint64_t byte_sad_ops; /* algorithmic byte-SAD count of the last waited picture */
+    uint64_t byte_sad_ops_fullsearch; /* the part of byte_sad_ops spent in the integer full search */
+    /* per-kernel-class device time of the last waited picture; filled only in profiling mode
+     * (me_gpu_set_profiling(1)), where each launch is bracketed by events on the job's stream */
+    float k_search_ms; /* sum over the k_search launches (zz, pre-HME, HME L0/L1/L2, centre SADs) */
+    float k_fullsearch_ms; /* sum over the two k_fullsearch launches (probe round, main round) */
+    float k_fullsearch_main_ms; /* the main-round k_fullsearch launch alone */
+    float k_ctrl_ms; /* sum over the k_ctrl launches */
+    float k_epilogue_ms;
 } MeGpuTimings;
 int me_gpu_get_timings(MeGpuTimings *t);
+/* profiling mode: bracket every kernel launch of a job with CUDA events (adds ~30 event records per picture) */
+void me_gpu_set_profiling(int on);
 /* measured VABSDIFF4 lane-operations per second of the engine's first device (x4 = byte-SADs / s): the
  * denominator of the integer-SAD roofline; 0.0 when the engine is not initialised */
 double me_gpu_measure_sad_peak(void);

@@ -150,6 +150,7 @@ ME_HD void mc_stage_init(CtrlCtx *c) {
             c->f[li * ME_NR + ri].valid = 0;
         }
     s->ops      = 0;
+    s->ops_fs   = 0;
     c->s->pending = PEND_NONE;
 }
 
@@ -626,7 +627,9 @@ ME_HD void mc_fs_emit(CtrlCtx *c, int li, int ri, int16_t x0, int16_t y0, int16_
     f->y0       = y0;
     f->w        = w;
     f->h        = h;
-    c->s->ops += (uint64_t)w * h * (c->p->me_search_method == ME_GPU_SUB_SAD_SEARCH ? 64 * 32 : 64 * 64);
+    const uint64_t n = (uint64_t)w * h * (c->p->me_search_method == ME_GPU_SUB_SAD_SEARCH ? 64 * 32 : 64 * 64);
+    c->s->ops += n;
+    c->s->ops_fs += n;
 }
 
 /* ME:1441-1510: centre the area, clamp to the picture +-63, emit the main search */

@@ -43,6 +43,9 @@ struct JobCtx {
     int          device = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t  ev[5] = {}; /* start, hme done, search done, end, (spare) */
+    cudaEvent_t  pev[64] = {}; /* profiling mode: (begin, end) pairs around every kernel launch */
+    int          pkind[32] = {}; /* kernel class of each pair: 0 ctrl, 1 search, 2 fullsearch probe round, 3 fullsearch main, 4 epilogue */
+    int          npairs = 0;
     MeJob       *h_job = nullptr; /* pinned */
     MeJob       *d_job = nullptr;
     FsTileList  *d_list = nullptr;
@@ -78,6 +81,7 @@ struct Engine {
     uint64_t            submit_counter = 0, register_counter = 0;
     MeGpuTimings        last{};
     std::mutex          mu;
+    bool                profiling = false;
     std::string         err;
 };
 
@@ -125,9 +129,10 @@ int alloc_job(Device &d, JobCtx &jc, const MePicGeom &gm, int max_l0, int max_l1
     jc.tile_cap  = (uint32_t)(nb * ME_NREF * 64);
     CU(cudaStreamCreateWithFlags(&jc.stream, cudaStreamNonBlocking));
     for (auto &e : jc.ev) CU(cudaEventCreate(&e));
+    for (auto &e : jc.pev) CU(cudaEventCreate(&e));
     CU(cudaMallocHost((void **)&jc.h_job, sizeof(MeJob)));
     CU(cudaMallocHost((void **)&jc.h_list, sizeof(FsTileList)));
-    CU(cudaMallocHost((void **)&jc.h_ops, sizeof(unsigned long long)));
+    CU(cudaMallocHost((void **)&jc.h_ops, 2 * sizeof(unsigned long long)));
     CU(dalloc(&jc.d_job, 1));
     CU(dalloc(&jc.d_list, 1));
     CU(dalloc(&jc.state, nb));
@@ -147,7 +152,7 @@ int alloc_job(Device &d, JobCtx &jc, const MePicGeom &gm, int max_l0, int max_l1
     CU(dalloc(&jc.dbg_hme, nb * ME_NREF));
     CU(dalloc(&jc.dbg_do_ref, nb * ME_NREF));
     CU(dalloc(&jc.dbg_area, nb * ME_NREF * 4));
-    CU(dalloc(&jc.ops_total, 1));
+    CU(dalloc(&jc.ops_total, 2));
     CU(cudaMemset(jc.tasks, 0, nb * ME_SLOTS * sizeof(SearchTask)));
     CU(cudaMemset(jc.results, 0, nb * ME_SLOTS * sizeof(SearchResult)));
     return ME_GPU_OK;
@@ -156,6 +161,8 @@ int alloc_job(Device &d, JobCtx &jc, const MePicGeom &gm, int max_l0, int max_l1
 void free_job(JobCtx &jc) {
     if (jc.stream) cudaStreamDestroy(jc.stream);
     for (auto &e : jc.ev)
+        if (e) cudaEventDestroy(e);
+    for (auto &e : jc.pev)
         if (e) cudaEventDestroy(e);
     cudaFreeHost(jc.h_job); cudaFreeHost(jc.h_list); cudaFreeHost(jc.h_ops);
     void *ptrs[] = {jc.d_job, jc.d_list, jc.state, jc.tasks, jc.results, jc.fs_tasks, jc.keys, jc.tiles, jc.total, jc.cands,
@@ -504,7 +511,7 @@ int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
     CU(cudaMemsetAsync(jc->total, 0, nb * j.pu_count, st));
     CU(cudaMemsetAsync(jc->cands, 0, nb * j.pu_count * p.max_cand, st));
     CU(cudaMemsetAsync(jc->mvs, 0, nb * j.pu_count * p.max_refs * sizeof(uint32_t), st));
-    CU(cudaMemsetAsync(jc->ops_total, 0, sizeof(unsigned long long), st));
+    CU(cudaMemsetAsync(jc->ops_total, 0, 2 * sizeof(unsigned long long), st));
 
     const int  nbi  = (int)nb;
     const bool zz   = p.me_early_exit_th || p.me_safe_limit_zz_th;
@@ -515,9 +522,28 @@ int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
     /* Each ctrl launch runs the stages between two search launches; a search launch is skipped when the
      * stage before it cannot have emitted tasks. */
     uint32_t mask = 1u << ST_INIT;
-    auto     flush = [&](int slots) {
+    jc->npairs = 0;
+    const bool prof = g.profiling;
+    /* profiling mode: a (begin, end) event pair around each launch, tagged with its kernel class */
+    auto pbegin = [&](int kind) {
+        if (prof && jc->npairs < 32) {
+            jc->pkind[jc->npairs] = kind;
+            cudaEventRecord(jc->pev[2 * jc->npairs], st);
+        }
+    };
+    auto pend = [&]() {
+        if (prof && jc->npairs < 32) {
+            cudaEventRecord(jc->pev[2 * jc->npairs + 1], st);
+            jc->npairs++;
+        }
+    };
+    auto flush = [&](int slots) {
+        pbegin(0);
         me_launch_ctrl(jc->d_job, 1, nbi, mask, jc->d_list, st);
+        pend();
+        pbegin(1);
         me_launch_search(jc->d_job, 1, nbi, slots, d.pool, st);
+        pend();
         mask = 0;
     };
     if (zz) flush(ME_NREF);
@@ -537,14 +563,24 @@ int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
     flush(ME_NREF * 2);
     CU(cudaEventRecord(jc->ev[1], st));
     const int fs_ctas = d.sms * 2;
+    pbegin(0);
     me_launch_ctrl(jc->d_job, 1, nbi, 1u << ST_PROBE, jc->d_list, st);
+    pend();
+    pbegin(2);
     me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, fs_ctas, st);
+    pend();
     /* second round: main searches of the probed references */
     CU(cudaMemsetAsync(jc->d_list, 0, 2 * sizeof(unsigned int), st)); /* count = next = 0 */
+    pbegin(0);
     me_launch_ctrl(jc->d_job, 1, nbi, 1u << ST_MAIN, jc->d_list, st);
+    pend();
+    pbegin(3);
     me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, fs_ctas, st);
+    pend();
     CU(cudaEventRecord(jc->ev[2], st));
+    pbegin(4);
     me_launch_epilogue(jc->d_job, 1, nbi, st);
+    pend();
     CU(cudaEventRecord(jc->ev[3], st));
     CU(cudaGetLastError());
 
@@ -602,7 +638,7 @@ int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out) {
     D2H(out->search_area, jc->dbg_area, nb * ME_NREF * 4 * sizeof(int16_t));
 #undef D2H
     CU(cudaMemcpyAsync(jc->h_list, jc->d_list, sizeof(FsTileList), cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(jc->h_ops, jc->ops_total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(jc->h_ops, jc->ops_total, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     CU(cudaEventRecord(jc->ev[4], st));
     lk.unlock();
     cudaError_t e = cudaStreamSynchronize(st);
@@ -615,9 +651,21 @@ int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out) {
     cudaEventElapsedTime(&t.search_ms, jc->ev[1], jc->ev[2]);
     cudaEventElapsedTime(&t.epilogue_ms, jc->ev[2], jc->ev[3]);
     cudaEventElapsedTime(&t.total_ms, jc->ev[0], jc->ev[4]);
+    for (int i = 0; i < jc->npairs; i++) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, jc->pev[2 * i], jc->pev[2 * i + 1]);
+        switch (jc->pkind[i]) {
+        case 0: t.k_ctrl_ms += ms; break;
+        case 1: t.k_search_ms += ms; break;
+        case 2: t.k_fullsearch_ms += ms; break;
+        case 3: t.k_fullsearch_ms += ms; t.k_fullsearch_main_ms += ms; break;
+        default: t.k_epilogue_ms += ms; break;
+        }
+    }
     t.pyramid_ms      = 0.f;
     t.kernel_launches = me_launch_count();
-    t.byte_sad_ops    = *jc->h_ops;
+    t.byte_sad_ops    = jc->h_ops[0];
+    t.byte_sad_ops_fullsearch = jc->h_ops[1];
     g.last            = t;
     out->b64_count    = (uint32_t)nb;
     out->pu_count     = P;
@@ -638,6 +686,11 @@ int me_gpu_get_timings(MeGpuTimings *t) {
     *t                 = g.last;
     t->kernel_launches = me_launch_count();
     return ME_GPU_OK;
+}
+
+void me_gpu_set_profiling(int on) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    g.profiling = on != 0;
 }
 
 /* VABSDIFF4 lane-operations per second of device 0 of the engine (x4 = byte-SADs per second): the measured

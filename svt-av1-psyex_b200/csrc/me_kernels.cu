@@ -493,7 +493,8 @@ __global__ void __launch_bounds__(EP_THREADS) k_epilogue(MeJob *jobs) {
         me_epi_distortion(&e);
         me_epi_gm(&e);
         me_epi_taps(&e);
-        atomicAdd(j->ops_total, (unsigned long long)e.s->ops);
+        atomicAdd(&j->ops_total[0], (unsigned long long)e.s->ops);
+        atomicAdd(&j->ops_total[1], (unsigned long long)e.s->ops_fs);
     }
     if (j->dbg_best_sad)
         for (int i = tid; i < ME_NREF * ME_NPU; i += EP_THREADS)

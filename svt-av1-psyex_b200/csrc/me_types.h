@@ -87,6 +87,7 @@ typedef struct B64State {
     uint8_t  pend00[ME_NL][ME_NR]; /* check_00_center SADs in flight */
     uint8_t  pending; /* MePending: which task results the next stage has to consume */
     uint64_t ops; /* algorithmic byte-SAD count, SURVEY 8(d) */
+    uint64_t ops_fs; /* part of ops spent in the integer full search */
 } B64State;
 
 /* one svt_sad_loop_kernel call. Coordinates are in the plane's own interior coordinate system (may be
@@ -154,7 +155,7 @@ typedef struct MeJob {
     uint64_t *dbg_hme_sad;
     uint8_t  *dbg_do_ref;
     int16_t  *dbg_area;
-    unsigned long long *ops_total; /* one counter per job */
+    unsigned long long *ops_total; /* [2] per job: all byte-SADs, full-search byte-SADs */
 } MeJob;
 
 /* geometry of a width x height picture (both multiples of 8) in the pool */

@@ -108,7 +108,9 @@ class MeGpuOutputs(C.Structure):
 class MeGpuTimings(C.Structure):
     _fields_ = [("pyramid_ms", C.c_float), ("hme_ms", C.c_float), ("search_ms", C.c_float),
                 ("epilogue_ms", C.c_float), ("total_ms", C.c_float), ("kernel_launches", u64),
-                ("byte_sad_ops", u64)]
+                ("byte_sad_ops", u64), ("byte_sad_ops_fullsearch", u64), ("k_search_ms", C.c_float),
+                ("k_fullsearch_ms", C.c_float), ("k_fullsearch_main_ms", C.c_float), ("k_ctrl_ms", C.c_float),
+                ("k_epilogue_ms", C.c_float)]
 
 
 class OraclePlane(C.Structure):
@@ -137,7 +139,7 @@ REF_LIB = os.path.join(REPO, "oracle", "_ref", "libme_ref.so")
 GPU_SYMBOLS = [
     "me_gpu_init", "me_gpu_shutdown", "me_gpu_last_error", "me_gpu_device_count", "me_gpu_register_picture",
     "me_gpu_register_picture_unpadded", "me_gpu_release_picture", "me_gpu_read_pyramid", "me_gpu_plane_geometry",
-    "me_gpu_submit", "me_gpu_wait", "me_gpu_derive_params", "me_gpu_get_timings", "me_gpu_measure_sad_peak",
+    "me_gpu_submit", "me_gpu_wait", "me_gpu_derive_params", "me_gpu_get_timings", "me_gpu_measure_sad_peak", "me_gpu_set_profiling",
 ]
 
 

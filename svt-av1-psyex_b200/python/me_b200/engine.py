@@ -98,6 +98,9 @@ class Engine:
         self._check(self.lib.me_gpu_get_timings(C.byref(t)))
         return t
 
+    def set_profiling(self, on):
+        self.lib.me_gpu_set_profiling(1 if on else 0)
+
     def sad_peak(self):
         """measured VABSDIFF4 lane-ops/s of the device (x4 = byte-SADs/s)"""
         return float(self.lib.me_gpu_measure_sad_peak())
