@@ -117,6 +117,18 @@ ME_HD uint32_t mc_result(const CtrlCtx *c, int slot, int16_t *x, int16_t *y) {
 
 ME_HD int mc_ref_active(const CtrlCtx *c, int li) { return c->p->temporal_layer_index > 0 || li == 0; }
 
+/* p_sb_best_sad = MAX_SAD_VALUE for every PU (svt_initialize_buffer_32bits, ME:1366), as keys. Separate from
+ * mc_stage_init so that the device can spread the 680 stores over a whole CTA. */
+ME_HD void mc_init_keys(unsigned long long *keys, int first, int stride) {
+    for (int k = first; k < ME_NREF * ME_NPU; k += stride) keys[k] = ME_KEY_INIT;
+}
+
+#if defined(__CUDA_ARCH__)
+#define MC_KEY_LOAD(p) __ldcg(p) /* keys are written with atomics at L2: read them there */
+#else
+#define MC_KEY_LOAD(p) (*(p))
+#endif
+
 /* ------------------------------------------------------------------------------------------------ */
 ME_HD void mc_stage_init(CtrlCtx *c) {
     B64State *s = c->s;
@@ -146,7 +158,6 @@ ME_HD void mc_stage_init(CtrlCtx *c) {
             s->sw[li][ri] = s->sh[li][ri] = 0;
             for (int k = 0; k < 4; k++) s->sa_final[li][ri][k] = 0;
             s->probed[li][ri] = s->searched[li][ri] = s->pend00[li][ri] = 0;
-            for (int k = 0; k < ME_NPU; k++) c->keys[(li * ME_NR + ri) * ME_NPU + k] = ME_KEY_INIT;
             c->f[li * ME_NR + ri].valid = 0;
         }
     s->ops      = 0;
@@ -687,10 +698,10 @@ ME_HD void mc_main_emit_after_probe(CtrlCtx *c) {
             if (!s->do_ref[li][ri] || !s->probed[li][ri])
                 continue;
             const unsigned long long *key = &c->keys[(li * ME_NR + ri) * ME_NPU];
-            const uint32_t            mean = (uint32_t)(key[0] >> 32) / 64;
+            const uint32_t            mean = (uint32_t)(MC_KEY_LOAD(&key[0]) >> 32) / 64;
             uint32_t                  ssq  = 0;
             for (int i = 0; i < 64; i++) {
-                int32_t d = (int32_t)(uint32_t)(key[21 + i] >> 32) - (int32_t)mean;
+                int32_t d = (int32_t)(uint32_t)(MC_KEY_LOAD(&key[21 + i]) >> 32) - (int32_t)mean;
                 ssq += (uint32_t)(d * d);
             }
             const uint32_t var = ssq / 64;

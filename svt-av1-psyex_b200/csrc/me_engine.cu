@@ -82,6 +82,7 @@ struct Engine {
     MeGpuTimings        last{};
     std::mutex          mu;
     bool                profiling = false;
+    bool                legacy = false; /* ME_GPU_LEGACY=1: one launch per stage instead of k_hme (debugging) */
     std::string         err;
 };
 
@@ -319,6 +320,7 @@ int me_gpu_init(int device_count, const int *device_ids, int max_width, int max_
             return fail(ME_GPU_ERR_UNSUPPORTED, "sm_100a device required");
         d.sms = prop.multiProcessorCount;
         CU(me_kernels_setup());
+        CU(me_hme_setup());
         CU(cudaStreamCreateWithFlags(&d.upload, cudaStreamNonBlocking));
         CU(cudaMalloc((void **)&d.pool, (size_t)g.nslots * g.gmax.slot_bytes + 65536));
         CU(cudaMemset(d.pool, 0, (size_t)g.nslots * g.gmax.slot_bytes + 65536));
@@ -346,6 +348,7 @@ int me_gpu_init(int device_count, const int *device_ids, int max_width, int max_
             CU(cudaSetDevice(ids[i]));
             CU(cudaEventCreateWithFlags(&s.ready[i], cudaEventDisableTiming));
         }
+    g.legacy      = getenv("ME_GPU_LEGACY") && atoi(getenv("ME_GPU_LEGACY")) != 0;
     g.initialised = true;
     return ME_GPU_OK;
 }
@@ -513,15 +516,7 @@ int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
     CU(cudaMemsetAsync(jc->mvs, 0, nb * j.pu_count * p.max_refs * sizeof(uint32_t), st));
     CU(cudaMemsetAsync(jc->ops_total, 0, 2 * sizeof(unsigned long long), st));
 
-    const int  nbi  = (int)nb;
-    const bool zz   = p.me_early_exit_th || p.me_safe_limit_zz_th;
-    const bool phme = p.prehme_enable != 0;
-    const bool l1ee = phme && p.prehme_l1_early_exit && p.num_of_list_to_search == 2;
-    const bool l0 = p.enable_hme_flag && p.enable_hme_level0_flag, l1 = p.enable_hme_flag && p.enable_hme_level1_flag,
-               l2 = p.enable_hme_flag && p.enable_hme_level2_flag;
-    /* Each ctrl launch runs the stages between two search launches; a search launch is skipped when the
-     * stage before it cannot have emitted tasks. */
-    uint32_t mask = 1u << ST_INIT;
+    const int nbi = (int)nb;
     jc->npairs = 0;
     const bool prof = g.profiling;
     /* profiling mode: a (begin, end) event pair around each launch, tagged with its kernel class */
@@ -537,46 +532,63 @@ int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
             jc->npairs++;
         }
     };
-    auto flush = [&](int slots) {
-        pbegin(0);
-        me_launch_ctrl(jc->d_job, 1, nbi, mask, jc->d_list, st);
-        pend();
+    if (!g.legacy) {
+        /* the whole per-b64 chain in one launch; large search areas come back as tiles */
         pbegin(1);
-        me_launch_search(jc->d_job, 1, nbi, slots, d.pool, st);
+        me_launch_hme(jc->d_job, 1, nbi, jc->d_list, d.pool, st);
         pend();
-        mask = 0;
-    };
-    if (zz) flush(ME_NREF);
-    mask |= 1u << ST_PREHME0;
-    if (phme) flush(ME_NREF * 2);
-    if (l1ee) {
-        mask |= 1u << ST_PREHME1;
+        CU(cudaEventRecord(jc->ev[1], st));
+        pbegin(3);
+        me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, d.sms * 2, st);
+        pend();
+    } else {
+        const bool zz   = p.me_early_exit_th || p.me_safe_limit_zz_th;
+        const bool phme = p.prehme_enable != 0;
+        const bool l1ee = phme && p.prehme_l1_early_exit && p.num_of_list_to_search == 2;
+        const bool l0 = p.enable_hme_flag && p.enable_hme_level0_flag, l1 = p.enable_hme_flag && p.enable_hme_level1_flag,
+                   l2 = p.enable_hme_flag && p.enable_hme_level2_flag;
+        /* one launch per stage (debug path): ctrl launches run the stages between two search launches */
+        uint32_t mask = 1u << ST_INIT;
+        auto flush = [&](int slots) {
+            pbegin(0);
+            me_launch_ctrl(jc->d_job, 1, nbi, mask, jc->d_list, st);
+            pend();
+            pbegin(1);
+            me_launch_search(jc->d_job, 1, nbi, slots, d.pool, st);
+            pend();
+            mask = 0;
+        };
+        if (zz) flush(ME_NREF);
+        mask |= 1u << ST_PREHME0;
+        if (phme) flush(ME_NREF * 2);
+        if (l1ee) {
+            mask |= 1u << ST_PREHME1;
+            flush(ME_NREF * 2);
+        }
+        mask |= 1u << ST_HME_L0;
+        if (l0) flush(ME_NREF * 4);
+        mask |= 1u << ST_HME_L1;
+        if (l1) flush(ME_NREF * 4);
+        mask |= 1u << ST_HME_L2;
+        if (l2) flush(ME_NREF * 4);
+        mask |= 1u << ST_CENTRE;
         flush(ME_NREF * 2);
+        CU(cudaEventRecord(jc->ev[1], st));
+        const int fs_ctas = d.sms * 2;
+        pbegin(0);
+        me_launch_ctrl(jc->d_job, 1, nbi, 1u << ST_PROBE, jc->d_list, st);
+        pend();
+        pbegin(2);
+        me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, fs_ctas, st);
+        pend();
+        CU(cudaMemsetAsync(jc->d_list, 0, 2 * sizeof(unsigned int), st)); /* count = next = 0 */
+        pbegin(0);
+        me_launch_ctrl(jc->d_job, 1, nbi, 1u << ST_MAIN, jc->d_list, st);
+        pend();
+        pbegin(3);
+        me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, fs_ctas, st);
+        pend();
     }
-    mask |= 1u << ST_HME_L0;
-    if (l0) flush(ME_NREF * 4);
-    mask |= 1u << ST_HME_L1;
-    if (l1) flush(ME_NREF * 4);
-    mask |= 1u << ST_HME_L2;
-    if (l2) flush(ME_NREF * 4);
-    mask |= 1u << ST_CENTRE;
-    flush(ME_NREF * 2);
-    CU(cudaEventRecord(jc->ev[1], st));
-    const int fs_ctas = d.sms * 2;
-    pbegin(0);
-    me_launch_ctrl(jc->d_job, 1, nbi, 1u << ST_PROBE, jc->d_list, st);
-    pend();
-    pbegin(2);
-    me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, fs_ctas, st);
-    pend();
-    /* second round: main searches of the probed references */
-    CU(cudaMemsetAsync(jc->d_list, 0, 2 * sizeof(unsigned int), st)); /* count = next = 0 */
-    pbegin(0);
-    me_launch_ctrl(jc->d_job, 1, nbi, 1u << ST_MAIN, jc->d_list, st);
-    pend();
-    pbegin(3);
-    me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, fs_ctas, st);
-    pend();
     CU(cudaEventRecord(jc->ev[2], st));
     pbegin(4);
     me_launch_epilogue(jc->d_job, 1, nbi, st);
@@ -663,7 +675,7 @@ int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out) {
         }
     }
     t.pyramid_ms      = 0.f;
-    t.kernel_launches = me_launch_count();
+    t.kernel_launches = me_launch_count() + me_hme_launch_count();
     t.byte_sad_ops    = jc->h_ops[0];
     t.byte_sad_ops_fullsearch = jc->h_ops[1];
     g.last            = t;
@@ -675,7 +687,8 @@ int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out) {
         free_slot_if_idle(s);
     }
     if (overflow)
-        return fail(ME_GPU_ERR_UNSUPPORTED, "full-search tile list overflowed");
+        return fail(ME_GPU_ERR_UNSUPPORTED, jc->h_list->overflow == 2 ? "a search window exceeds the staging buffer of k_hme"
+                                                                      : "full-search tile list overflowed");
     return ME_GPU_OK;
 }
 
@@ -684,7 +697,7 @@ int me_gpu_get_timings(MeGpuTimings *t) {
     if (!t)
         return ME_GPU_ERR_BAD_ARG;
     *t                 = g.last;
-    t->kernel_launches = me_launch_count();
+    t->kernel_launches = me_launch_count() + me_hme_launch_count();
     return ME_GPU_OK;
 }
 

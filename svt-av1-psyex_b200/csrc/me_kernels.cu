@@ -113,6 +113,8 @@ __global__ void __launch_bounds__(64) k_ctrl(MeJob *jobs, uint32_t stage_mask, F
     c.b64_h = (uint32_t)min(64, j->g.height - c.org_y);
     c.pic_w = j->g.width;
     c.pic_h = j->g.height;
+    if (stage_mask & (1u << ST_INIT))
+        mc_init_keys(c.keys, 0, 1);
     for (int st = 0; st < ST_COUNT; st++)
         if (stage_mask & (1u << st))
             mc_run_stage(&c, st);
@@ -136,7 +138,9 @@ __global__ void __launch_bounds__(64) k_ctrl(MeJob *jobs, uint32_t stage_mask, F
                     t->job  = (uint16_t)blockIdx.y;
                     t->tx   = (uint16_t)(tx * FS_TW);
                     t->ty   = (uint16_t)(ty * FS_TH);
-                    t->pad_ = 0;
+                    t->ref_slot = f.ref_slot;
+                    t->x0 = f.x0; t->y0 = f.y0; t->w = f.w; t->h = f.h;
+                    t->probe = f.probe;
                 }
         }
     }
@@ -396,7 +400,9 @@ __global__ void __launch_bounds__(FS_THREADS, 2) k_fullsearch(MeJob *jobs, FsTil
             break;
         const FsTile  tile = list->tiles[ti];
         MeJob        *j    = &jobs[tile.job];
-        const FsTask  f    = j->fs_tasks[tile.task];
+        FsTask        f;
+        f.valid = 1; f.probe = tile.probe; f.ref_slot = tile.ref_slot;
+        f.x0 = tile.x0; f.y0 = tile.y0; f.w = tile.w; f.h = tile.h;
         const uint32_t b   = tile.task / ME_NREF;
         const bool    sub  = j->p.me_search_method == ME_GPU_SUB_SAD_SEARCH;
         const MePlaneGeom pl = j->g.plane[0];

@@ -26,5 +26,9 @@ void   me_launch_search(const MeJob *jobs, int njobs, int max_b64, int slots, co
 void   me_launch_fullsearch(MeJob *jobs, FsTileList *list, const uint8_t *pool, int ctas, cudaStream_t st);
 void   me_launch_epilogue(MeJob *jobs, int njobs, int max_b64, cudaStream_t st);
 double me_measure_sad_peak(cudaStream_t st);
+/* me_hme.cu */
+cudaError_t        me_hme_setup(void);
+unsigned long long me_hme_launch_count(void);
+void   me_launch_hme(MeJob *jobs, int njobs, int max_b64, FsTileList *list, const uint8_t *pool, cudaStream_t st);
 
 #endif

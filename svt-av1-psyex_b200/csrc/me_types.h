@@ -126,7 +126,9 @@ typedef struct FsTile { /* a rectangle of search positions of one FsTask, unit o
     uint32_t task; /* b64 * ME_NREF + li * ME_NR + ri */
     uint16_t job;
     uint16_t tx, ty; /* tile origin inside the search area */
-    uint16_t pad_;
+    uint16_t ref_slot;
+    int16_t  x0, y0, w, h; /* the task's search area (copied: the FsTask slot is reused by the next round) */
+    uint8_t  probe, pad_[3];
 } FsTile;
 
 /* one picture's ME job; an array of these (one per picture of a batch) lives in HBM */

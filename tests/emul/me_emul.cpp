@@ -135,6 +135,8 @@ extern "C" int emul_me_picture(const OraclePicture *src, const OraclePicture *co
     for (int stage = 0; stage < ST_COUNT; stage++) {
         for (int b = 0; b < nb; b++) {
             CtrlCtx c = ctx_of(b);
+            if (stage == ST_INIT)
+                mc_init_keys(c.keys, 0, 1);
             mc_run_stage(&c, stage);
         }
         if (stage <= ST_CENTRE) {
