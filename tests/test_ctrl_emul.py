@@ -1,0 +1,43 @@
+"""The product's control logic (csrc/me_ctrl.h: the code k_hme / k_epilogue run on the device) executed on the
+CPU by tests/emul with scalar stand-ins for the search kernels, against the oracle. Pins every stage, prune,
+search-area rule and the candidate construction without a GPU."""
+import pytest
+
+from helpers import Emulator, PictureSet, derive, used_refs
+from me_b200 import planes
+from me_b200.checkers import Oracle
+
+CASES = [(preset, poc, kind) for preset in (8, 4, 2, 6, 10, 5) for poc in (16, 8, 4, 1, 7) for kind in ("motion", "iid")]
+
+
+@pytest.fixture(scope="module")
+def tools():
+    return Oracle(), Emulator()
+
+
+@pytest.mark.parametrize("preset,poc,kind", CASES)
+def test_control_logic_matches_oracle(tools, preset, poc, kind):
+    oracle, emul = tools
+    w, h, n = 200, 136, 33
+    ps = PictureSet(w, h, n, kind, oracle)
+    cfg, p, l0, l1 = derive(preset, w, h, poc, n)
+    refs = [[ps.get(k) for k in l0], [ps.get(k) for k in l1]]
+    a = oracle.me_picture(ps.get(poc), refs, p)
+    b = emul.me_picture(ps.get(poc), refs, p)
+    bad = planes.compare_outputs(a, b, used_refs=used_refs(l0, l1))
+    assert not bad, bad
+    assert a.byte_sad_ops == b.byte_sad_ops
+
+
+@pytest.mark.parametrize("force", [(1, 0), (1, 1), (2, 2), (4, 3)])
+def test_reference_count_variants(tools, force):
+    """single reference / one per list / general candidate construction (motion_estimation.c:2532-2835)"""
+    oracle, emul = tools
+    w, h, n, poc = 200, 136, 33, 7
+    ps = PictureSet(w, h, n, "motion", oracle)
+    cfg, p, l0, l1 = derive(4, w, h, poc, n, force_refs=force)
+    refs = [[ps.get(k) for k in l0], [ps.get(k) for k in l1]]
+    a = oracle.me_picture(ps.get(poc), refs, p)
+    b = emul.me_picture(ps.get(poc), refs, p)
+    bad = planes.compare_outputs(a, b, used_refs=used_refs(l0, l1))
+    assert not bad, bad

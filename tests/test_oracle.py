@@ -1,0 +1,142 @@
+"""The CPU oracle (oracle/me_oracle*.c) pinned against the reference: golden vectors frozen from the reference's
+own code (tests/golden, see make_golden.py) and - in the build container - the reference itself (oracle/_ref)
+on the parameter tables of the reference's unit tests (test/SadTest.cc, test/PictureOperatorTest.cc)."""
+import ctypes as C
+import glob
+import os
+import re
+
+import numpy as np
+import pytest
+
+from helpers import PictureSet, derive, used_refs
+from me_b200 import abi, planes
+from me_b200.checkers import Oracle, Reference
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+have_ref = pytest.mark.skipif(not Reference.available(), reason="oracle/_ref not built (needs /root/reference)")
+
+
+@pytest.fixture(scope="module")
+def oracle():
+    return Oracle()
+
+
+def _golden_cases():
+    out = []
+    for f in sorted(glob.glob(os.path.join(GOLD, "me_*.npz"))):
+        m = re.match(r"me_(\d+)x(\d+)_m(-?\d+)_poc(\d+)_(\w+)\.npz", os.path.basename(f))
+        out.append((f, int(m.group(1)), int(m.group(2)), int(m.group(3)), int(m.group(4)), m.group(5)))
+    return out
+
+
+@pytest.mark.parametrize("case", _golden_cases(), ids=lambda c: os.path.basename(c[0])[:-4])
+def test_oracle_reproduces_golden_vectors(oracle, case):
+    f, w, h, preset, poc, kind = case
+    gold = np.load(f)
+    ps = PictureSet(w, h, 33, kind, oracle)
+    cfg, p, l0, l1 = derive(preset, w, h, poc, 33)
+    assert l0 == list(gold["l0"]) and l1 == list(gold["l1"])
+    out = oracle.me_picture(ps.get(poc), [[ps.get(k) for k in l0], [ps.get(k) for k in l1]], p)
+    mask = np.zeros((2, 4), dtype=bool)
+    mask[0, :len(l0)] = True
+    mask[1, :len(l1)] = True
+    assert len(gold.files) >= 18
+    for name in gold.files:
+        if name in ("l0", "l1"):
+            continue
+        a, b = out.arrays[name], gold[name]
+        if name in planes.DEBUG_FIELDS:
+            a, b = a[:, mask], b[:, mask]
+        assert np.array_equal(a, b), name
+
+
+@have_ref
+@pytest.mark.parametrize("size", [(1920, 1080), (960, 540), (176, 144), (88, 72)])  # PictureOperatorTest.cc:232-234
+@pytest.mark.parametrize("step", [2, 4, 8])
+def test_downsample_2d_matches_reference(oracle, size, step):
+    ref = Reference()
+    w, h = size
+    rng = np.random.default_rng(w * 10 + step)
+    for _ in range(3):
+        stride = w + 3
+        src = rng.integers(0, 256, size=(h, stride), dtype=np.uint8)
+        a = np.zeros((h // step + 1, w // step + 8), dtype=np.uint8)
+        b = np.zeros_like(a)
+        oracle.lib.oracle_downsample_2d(src.ctypes.data, stride, w, h, a.ctypes.data, a.shape[1], step)
+        ref.lib.ref_downsample_2d(src.ctypes.data, stride, w, h, b.ctypes.data, b.shape[1], step)
+        assert np.array_equal(a, b)
+
+
+# TEST_LOOP_AREAS (SadTest.cc:433-444) and a spread of its block sizes (SadTest.cc:62-107)
+LOOP_AREAS = [(8, 15), (16, 31), (12, 31), (64, 125), (192, 75), (128, 50), (64, 25), (240, 200), (144, 120), (96, 80),
+              (48, 40), (240, 120), (192, 96), (144, 72), (24, 12), (288, 120), (192, 60), (128, 100), (48, 50), (80, 80)]
+BLOCKS = [(64, 64), (64, 32), (32, 32), (32, 16), (16, 16), (16, 8), (16, 7), (8, 8), (24, 24), (48, 64), (64, 24), (6, 6),
+          (4, 16), (12, 5), (128, 64)]
+PATTERNS = ["REF_MAX", "SRC_MAX", "RANDOM", "UNALIGN"]
+
+
+@have_ref
+@pytest.mark.parametrize("pattern", PATTERNS)
+def test_sad_loop_matches_reference(oracle, pattern):
+    """svt_sad_loop_kernel_c semantics incl. tie-breaking and skip_search_line (SadTest.cc:474-539)."""
+    ref = Reference()
+    rng = np.random.default_rng(hash(pattern) & 0xFFFF)
+    for (bw, bh) in BLOCKS:
+        for (sw, sh) in LOOP_AREAS[::3]:
+            for skip in (0, 1):
+                rstride = 127 if pattern == "UNALIGN" and bw + sw <= 127 else bw + sw + 8
+                sstride = bw + 5
+                src = np.zeros((bh, sstride), dtype=np.uint8)
+                refb = np.zeros((bh + sh + 1, rstride), dtype=np.uint8)
+                if pattern == "REF_MAX":
+                    refb[...] = 255
+                elif pattern == "SRC_MAX":
+                    src[...] = 255
+                else:
+                    src[...] = rng.integers(0, 256, size=src.shape, dtype=np.uint8)
+                    # few distinct values: many exact ties, so the scan-order tie-break is exercised
+                    refb[...] = rng.integers(0, 4, size=refb.shape, dtype=np.uint8) * 60
+                res = []
+                for lib, fn in ((oracle.lib, "oracle_sad_loop"), (ref.lib, "ref_sad_loop")):
+                    best, x, y = abi.u64(0), abi.i16(-7), abi.i16(-9)
+                    getattr(lib, fn)(src.ctypes.data, sstride, refb.ctypes.data, rstride, bh, bw, C.byref(best), C.byref(x),
+                                     C.byref(y), rstride, skip, sw, sh)
+                    res.append((best.value, x.value, y.value))
+                assert res[0] == res[1], (bw, bh, sw, sh, skip, res)
+
+
+@have_ref
+@pytest.mark.parametrize("preset,poc,kind", [(8, 16, "motion"), (8, 2, "iid"), (6, 8, "motion"), (4, 1, "motion"), (4, 8, "iid"),
+                                            (2, 7, "motion"), (10, 4, "iid"), (5, 2, "motion"), (7, 1, "iid")])
+@pytest.mark.parametrize("size", [(320, 192), (264, 200)])
+def test_oracle_matches_reference_me(oracle, size, preset, poc, kind):
+    """Whole path, every output and tap, against svt_aom_motion_estimation_b64 of the reference."""
+    ref = Reference()
+    w, h = size
+    ps = PictureSet(w, h, 33, kind, ref)
+    ps2 = PictureSet(w, h, 33, kind, oracle)
+    cfg, p, l0, l1 = derive(preset, w, h, poc, 33)
+    for k in [poc] + l0 + l1:  # pyramids: reference downsampler vs restatement
+        for lvl in range(3):
+            assert np.array_equal(ps.get(k).planes[lvl], ps2.get(k).planes[lvl])
+    refs = [[ps.get(k) for k in l0], [ps.get(k) for k in l1]]
+    a = oracle.me_picture(ps.get(poc), refs, p)
+    b = ref.me_picture(ps.get(poc), refs, p)
+    fields = [f for f in a.arrays if f != "search_area"]
+    bad = planes.compare_outputs(a, b, fields=fields, used_refs=used_refs(l0, l1))
+    assert not bad, bad
+
+
+@have_ref
+def test_reference_simd_equals_reference_c():
+    """The timed CPU baseline (AVX2 kernels behind the RTCD pointers) gives the same results as the C path."""
+    ref = Reference()
+    w, h = 320, 192
+    ps = PictureSet(w, h, 33, "motion", ref)
+    cfg, p, l0, l1 = derive(4, w, h, 4, 33)
+    refs = [[ps.get(k) for k in l0], [ps.get(k) for k in l1]]
+    a = ref.me_picture(ps.get(4), refs, p, simd=0)
+    b = ref.me_picture(ps.get(4), refs, p, simd=1)
+    bad = planes.compare_outputs(a, b, fields=planes.PRODUCT_FIELDS)
+    assert not bad, bad
