@@ -33,6 +33,7 @@ sys.path.insert(0, os.path.join(REPO, "tests"))
 from me_b200 import abi, planes, synth  # noqa: E402
 
 W, H, PRESET, NPIC, FORCE_REFS = 1920, 1080, 4, 33, (2, 2)
+NSETS, SET_STRIDE = 3, 1000  # copies of the sequence in the pool (distinct picture numbers: poc + 1000 * set)
 # decode order of mini-GOP 2 (POC 17..32)
 STEP_POCS = [32 if g == 0 else 16 + g for g in synth.RA5_DECODE_ORDER]
 
@@ -74,7 +75,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(n)
             except Exception:
                 pass
-            time.sleep(0.05)
+            time.sleep(0.25)
 
     def summary(self):
         s = sorted(self.samples)
@@ -98,18 +99,20 @@ def make_pictures(kind, pinned):
     return out
 
 
-def pinned_outputs(params):
-    """MeGpuOutputs (product fields only) backed by pinned memory"""
+def pinned_outputs(params, eng):
+    """MeGpuOutputs (product fields only) carved out of ONE pinned buffer at the engine's slab offsets, so that
+    the results of a picture come back with a single device->host copy"""
     import torch
     o = planes.Outputs(W, H, params, debug=False)
-    keep = []
-    for name, arr in list(o.arrays.items()):
-        t = torch.zeros(arr.nbytes, dtype=torch.uint8).pin_memory()
-        a = t.numpy().view(arr.dtype).reshape(arr.shape)
+    offs, total = eng.output_layout(W, H, params)
+    slab = torch.zeros(total, dtype=torch.uint8).pin_memory()
+    base = slab.numpy()
+    for i, name in enumerate(planes.PRODUCT_FIELDS):
+        arr = o.arrays[name]
+        a = base[offs[i]:offs[i] + arr.nbytes].view(arr.dtype).reshape(arr.shape)
         o.arrays[name] = a
         setattr(o.c, name, C.cast(a.ctypes.data, dict(abi.MeGpuOutputs._fields_)[name]))
-        keep.append(t)
-    o._keep = keep
+    o._keep = slab
     return o
 
 
@@ -202,7 +205,8 @@ def workload_config(kind):
     return {"workload": "1080p 8-bit preset 4, mini-GOP 16, 2 refs/list, default HME + integer search areas "
                         "(BASELINE.json configs[1])", "width": W, "height": H, "preset": PRESET, "refs": list(FORCE_REFS),
             "pictures_per_step": 16, "sequence": f"synthetic {kind}, seed 1234, 33 pictures", "qp": 35,
-            "l2": "flushed between steps (256 MiB write)"}
+            "l2": f"inputs larger than L2: {NSETS} resident copies of the sequence ({NSETS} x 109 MB of planes) used in "
+                  "rotation, step k reads copy k % 3"}
 
 
 # --------------------------------------------------------------------------------------------------
@@ -227,50 +231,59 @@ def gpu_main(args):
 
     pics = make_pictures(args.kind, pinned=True)
     jobs = {poc: derive(poc) for poc in STEP_POCS}
-    outs = {poc: pinned_outputs(jobs[poc][1]) for poc in STEP_POCS}
-    eng = Engine(W, H, 4, 3, pictures_in_flight=40, devices=[local_rank])
-    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    eng = Engine(W, H, 4, 3, pictures_in_flight=NSETS * NPIC + 4, devices=[local_rank])
+    outs = {poc: pinned_outputs(jobs[poc][1], eng) for poc in STEP_POCS}
+    state = {"k": 0}
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # profiling pass only
 
-    def reg(poc):
+    def reg(poc, st):
         a, _ = pics[poc]
-        eng.register_picture_ptr(poc, a.ctypes.data, a.strides[0], W, H)
+        eng.register_picture_ptr(poc + SET_STRIDE * st, a.ctypes.data, a.strides[0], W, H)
 
-    def submit(poc):
+    def submit(poc, st):
+        # picture numbers of a set are offset by a constant: distances (all ME reads) are unchanged
         _, p, l0, l1 = jobs[poc]
-        eng.submit(poc, p, [l0, l1])
+        q = abi.MeGpuParams.from_buffer_copy(p)
+        q.picture_number = poc + SET_STRIDE * st
+        eng.submit_out(poc + SET_STRIDE * st, q, [[k + SET_STRIDE * st for k in l0], [k + SET_STRIDE * st for k in l1]],
+                       outs[poc])
 
     def step_resident():
+        st = state["k"] % NSETS
+        state["k"] += 1
         for poc in STEP_POCS:
-            submit(poc)
+            submit(poc, st)
         for poc in STEP_POCS:
-            eng.wait(poc, outs[poc])
+            eng.wait(poc + SET_STRIDE * st, outs[poc])
 
     def step_e2e():
+        st = state["k"] % NSETS
+        state["k"] += 1
         for poc in STEP_POCS:
-            reg(poc)
-            submit(poc)
+            reg(poc, st)
+            submit(poc, st)
         for poc in STEP_POCS:
-            eng.wait(poc, outs[poc])
+            eng.wait(poc + SET_STRIDE * st, outs[poc])
         for poc in STEP_POCS:
-            eng.release_picture(poc)
+            eng.release_picture(poc + SET_STRIDE * st)
 
     def timed(step_fn, steps, warmup):
         for _ in range(warmup):
             step_fn()
         barrier()
         sampler = ClockSampler(local_rank)
-        sampler.start()
+        if not os.environ.get("BENCH_NO_SAMPLER"):
+            sampler.start()
         l0 = eng.timings().kernel_launches
         barrier()
         t0 = time.perf_counter()
         for _ in range(steps):
-            flush_buf.zero_()
-            torch.cuda.synchronize()
             step_fn()
         barrier()
         dt = time.perf_counter() - t0
         sampler.stop_flag = True
-        sampler.join()
+        if sampler.is_alive():
+            sampler.join()
         launches = eng.timings().kernel_launches - l0
         if world > 1:
             t = torch.tensor([dt], dtype=torch.float64, device="cuda")
@@ -279,8 +292,9 @@ def gpu_main(args):
         return dt, launches, sampler.summary()
 
     # resident arm: everything registered once
-    for poc in range(NPIC):
-        reg(poc)
+    for st in range(NSETS):
+        for poc in range(NPIC):
+            reg(poc, st)
     dt_res, launches, clocks = timed(step_resident, args.steps, args.warmup)
 
     # roofline pass: one picture at a time, every launch bracketed by events on its stream
@@ -293,8 +307,8 @@ def gpu_main(args):
         for poc in STEP_POCS:
             flush_buf.zero_()
             torch.cuda.synchronize()
-            submit(poc)
-            eng.wait(poc, outs[poc])
+            submit(poc, rep)
+            eng.wait(poc + SET_STRIDE * rep, outs[poc])
             t = eng.timings()
             for k in ("k_search_ms", "k_fullsearch_ms", "k_fullsearch_main_ms", "k_ctrl_ms", "k_epilogue_ms", "total_ms"):
                 prof[k] += getattr(t, k)
@@ -304,8 +318,9 @@ def gpu_main(args):
     sad_peak = 4.0 * eng.sad_peak()  # byte-SADs / s
 
     # e2e arm: sources of the step uploaded every step
-    for poc in STEP_POCS:
-        eng.release_picture(poc)
+    for st in range(NSETS):
+        for poc in STEP_POCS:
+            eng.release_picture(poc + SET_STRIDE * st)
     dt_e2e, _, _ = timed(step_e2e, args.steps, args.warmup)
 
     checksum = int(sum(int(outs[p]["me_mv_array"].astype(np.uint64).sum()) for p in STEP_POCS) & 0xFFFFFFFF)

@@ -27,6 +27,7 @@
 #ifndef ME_GPU_H
 #define ME_GPU_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -215,6 +216,16 @@ int me_gpu_plane_geometry(int width, int height, int level, int *plane_w, int *p
 int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
                   const uint64_t ref_picture_numbers[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS]);
 int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out);
+/* Same as me_gpu_submit, with the destination of the results known up front: the device->host copies are queued
+ * on the job's stream right behind the last kernel, so that me_gpu_wait(picture_number, out) only has to wait.
+ * `out` (the struct and the arrays it points to) must stay valid and unchanged until that wait returns. */
+int me_gpu_submit_out(uint64_t picture_number, const MeGpuParams *params,
+                      const uint64_t ref_picture_numbers[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS], MeGpuOutputs *out);
+/* Byte offsets of the 11 product arrays of MeGpuOutputs (total_me_candidate_index ... rc_me_allow_gm, in struct
+ * order) inside the engine's per-picture result slab. A caller that carves its arrays out of ONE (pinned) buffer
+ * at these offsets gets them with a single device->host copy; any other arrangement works, with one copy per
+ * non-adjacent array. */
+int me_gpu_output_layout(int width, int height, const MeGpuParams *params, size_t offsets[11], size_t *total_bytes);
 
 /* host-side restatement of svt_aom_sig_deriv_me and the pcs/scs settings it depends on */
 int me_gpu_derive_params(const MeGpuEncoderConfig *cfg, MeGpuParams *params);

@@ -34,8 +34,42 @@ struct Slot {
     int         width = 0, height = 0;
     int         refcount = 0; /* jobs in flight that read this slot */
     bool        release_pending = false;
+    bool        ready_seen[8] = {}; /* the host has observed ready[dev] complete: no stream wait needed */
     cudaEvent_t ready[8] = {}; /* per device: pyramid complete on that device */
 };
+
+/* uploaded in one copy at submit; the tail (list header + counters) comes back in one copy */
+struct JobTail {
+    FsTileList         list;
+    unsigned long long ops[2];
+};
+struct JobHead {
+    MeJob   job;
+    JobTail tail;
+};
+
+/* product outputs of one picture in one device slab WITHOUT gaps: the 32-bit arrays first, then the byte
+ * arrays. off[] / bytes[] are indexed in MeGpuOutputs field order (total, cands, mvs, six distortion arrays,
+ * two flag arrays); order[] lists the fields by increasing offset. */
+struct OutLayout {
+    size_t off[11], bytes[11], total;
+    int    order[11];
+};
+OutLayout output_layout(size_t nb, size_t P, size_t max_cand, size_t max_refs) {
+    OutLayout    L;
+    const size_t b[11] = {nb * P, nb * P * max_cand, nb * P * max_refs * 4, nb * 4, nb * 4, nb * 4, nb * 4, nb * 4, nb * 4, nb, nb};
+    const int    ord[11] = {2, 3, 4, 5, 6, 7, 8, 0, 1, 9, 10};
+    size_t       o = 0;
+    for (int k = 0; k < 11; k++) {
+        const int i = ord[k];
+        L.order[k] = i;
+        L.off[i]   = o;
+        L.bytes[i] = b[i];
+        o += b[i];
+    }
+    L.total = o;
+    return L;
+}
 
 struct JobCtx {
     bool         busy = false;
@@ -46,18 +80,21 @@ struct JobCtx {
     cudaEvent_t  pev[64] = {}; /* profiling mode: (begin, end) pairs around every kernel launch */
     int          pkind[32] = {}; /* kernel class of each pair: 0 ctrl, 1 search, 2 fullsearch probe round, 3 fullsearch main, 4 epilogue */
     int          npairs = 0;
-    MeJob       *h_job = nullptr; /* pinned */
-    MeJob       *d_job = nullptr;
-    FsTileList  *d_list = nullptr;
-    FsTileList  *h_list = nullptr; /* pinned copy of the header for overflow checks */
-    unsigned long long *h_ops = nullptr; /* pinned */
+    bool         prof = false;
+    JobHead     *h_head = nullptr; /* pinned: what is uploaded at submit */
+    JobHead     *d_head = nullptr;
+    MeJob       *h_job = nullptr, *d_job = nullptr; /* = &head->job */
+    FsTileList  *d_list = nullptr; /* = &d_head->list */
+    JobTail     *h_tail = nullptr; /* pinned: tile-list header + byte-SAD counters read back after the job */
+    uint8_t     *out_slab = nullptr; /* device: total | cands | mvs | dist[6] | flags[2], see output_layout() */
+    size_t       out_cap = 0;
+    bool         d2h_enqueued = false; /* outputs were given at submit: the copies are already on the stream */
     std::vector<int> slots_used;
     /* device buffers */
     B64State *state = nullptr; SearchTask *tasks = nullptr; SearchResult *results = nullptr; FsTask *fs_tasks = nullptr;
     unsigned long long *keys = nullptr; FsTile *tiles = nullptr;
-    uint8_t *total = nullptr, *cands = nullptr; uint32_t *mvs = nullptr, *dist = nullptr; uint8_t *flags = nullptr;
     uint32_t *dbg_sad = nullptr, *dbg_mv = nullptr; int16_t *dbg_centre = nullptr; uint64_t *dbg_hme = nullptr;
-    uint8_t *dbg_do_ref = nullptr; int16_t *dbg_area = nullptr; unsigned long long *ops_total = nullptr;
+    uint8_t *dbg_do_ref = nullptr; int16_t *dbg_area = nullptr;
     size_t cap_cands = 0, cap_mvs = 0;
     uint32_t tile_cap = 0;
 };
@@ -131,29 +168,26 @@ int alloc_job(Device &d, JobCtx &jc, const MePicGeom &gm, int max_l0, int max_l1
     CU(cudaStreamCreateWithFlags(&jc.stream, cudaStreamNonBlocking));
     for (auto &e : jc.ev) CU(cudaEventCreate(&e));
     for (auto &e : jc.pev) CU(cudaEventCreate(&e));
-    CU(cudaMallocHost((void **)&jc.h_job, sizeof(MeJob)));
-    CU(cudaMallocHost((void **)&jc.h_list, sizeof(FsTileList)));
-    CU(cudaMallocHost((void **)&jc.h_ops, 2 * sizeof(unsigned long long)));
-    CU(dalloc(&jc.d_job, 1));
-    CU(dalloc(&jc.d_list, 1));
+    CU(cudaMallocHost((void **)&jc.h_head, sizeof(JobHead)));
+    CU(cudaMallocHost((void **)&jc.h_tail, sizeof(JobTail)));
+    CU(dalloc(&jc.d_head, 1));
+    jc.h_job  = &jc.h_head->job;
+    jc.d_job  = &jc.d_head->job;
+    jc.d_list = &jc.d_head->tail.list;
+    jc.out_cap = output_layout(nb, ME_NPU, max_cand ? max_cand : 1, max_refs ? max_refs : 1).total;
+    CU(cudaMalloc((void **)&jc.out_slab, jc.out_cap));
     CU(dalloc(&jc.state, nb));
     CU(dalloc(&jc.tasks, nb * ME_SLOTS));
     CU(dalloc(&jc.results, nb * ME_SLOTS));
     CU(dalloc(&jc.fs_tasks, nb * ME_NREF));
     CU(dalloc(&jc.keys, nb * ME_NREF * ME_NPU));
     CU(dalloc(&jc.tiles, (size_t)jc.tile_cap));
-    CU(dalloc(&jc.total, nb * ME_NPU));
-    CU(dalloc(&jc.cands, jc.cap_cands));
-    CU(dalloc(&jc.mvs, jc.cap_mvs));
-    CU(dalloc(&jc.dist, nb * 6));
-    CU(dalloc(&jc.flags, nb * 2));
     CU(dalloc(&jc.dbg_sad, nb * ME_NREF * ME_NPU));
     CU(dalloc(&jc.dbg_mv, nb * ME_NREF * ME_NPU));
     CU(dalloc(&jc.dbg_centre, nb * ME_NREF * 2));
     CU(dalloc(&jc.dbg_hme, nb * ME_NREF));
     CU(dalloc(&jc.dbg_do_ref, nb * ME_NREF));
     CU(dalloc(&jc.dbg_area, nb * ME_NREF * 4));
-    CU(dalloc(&jc.ops_total, 2));
     CU(cudaMemset(jc.tasks, 0, nb * ME_SLOTS * sizeof(SearchTask)));
     CU(cudaMemset(jc.results, 0, nb * ME_SLOTS * sizeof(SearchResult)));
     return ME_GPU_OK;
@@ -165,10 +199,9 @@ void free_job(JobCtx &jc) {
         if (e) cudaEventDestroy(e);
     for (auto &e : jc.pev)
         if (e) cudaEventDestroy(e);
-    cudaFreeHost(jc.h_job); cudaFreeHost(jc.h_list); cudaFreeHost(jc.h_ops);
-    void *ptrs[] = {jc.d_job, jc.d_list, jc.state, jc.tasks, jc.results, jc.fs_tasks, jc.keys, jc.tiles, jc.total, jc.cands,
-                    jc.mvs, jc.dist, jc.flags, jc.dbg_sad, jc.dbg_mv, jc.dbg_centre, jc.dbg_hme, jc.dbg_do_ref, jc.dbg_area,
-                    jc.ops_total};
+    cudaFreeHost(jc.h_head); cudaFreeHost(jc.h_tail);
+    void *ptrs[] = {jc.d_head, jc.state, jc.tasks, jc.results, jc.fs_tasks, jc.keys, jc.tiles, jc.out_slab, jc.dbg_sad, jc.dbg_mv,
+                    jc.dbg_centre, jc.dbg_hme, jc.dbg_do_ref, jc.dbg_area};
     for (void *p : ptrs) cudaFree(p);
     jc = JobCtx();
 }
@@ -245,6 +278,7 @@ int register_common(uint64_t picture_number, const uint8_t *src, int stride, int
     sl.height         = height;
     sl.refcount       = 0;
     sl.release_pending = false;
+    for (auto &v : sl.ready_seen) v = false;
     g.by_number[picture_number] = s;
     return build_and_replicate(s, owner, gm, !padded);
 }
@@ -427,9 +461,55 @@ int me_gpu_read_pyramid(uint64_t picture_number, uint8_t *full, uint8_t *quarter
     return ME_GPU_OK;
 }
 
-int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
-                  const uint64_t ref_picture_numbers[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS]) {
-    std::lock_guard<std::mutex> lk(g.mu);
+/* enqueue the device->host copies of a finished (or running) job on its stream. Product outputs live in one
+ * device slab in MeGpuOutputs order: destination arrays that are adjacent in the same relative layout
+ * (me_gpu_output_layout) are fetched with a single copy. */
+static int enqueue_d2h(JobCtx *jc, const MeGpuOutputs *out) {
+    const MeJob    &j  = *jc->h_job;
+    const size_t    nb = (size_t)j.g.b64_count;
+    const OutLayout L  = output_layout(nb, j.pu_count, j.p.max_cand, j.p.max_refs);
+    cudaStream_t    st = jc->stream;
+    uint8_t *dst[11] = {out->total_me_candidate_index, out->me_candidate_array, (uint8_t *)out->me_mv_array,
+                        (uint8_t *)out->me_64x64_distortion, (uint8_t *)out->me_32x32_distortion,
+                        (uint8_t *)out->me_16x16_distortion, (uint8_t *)out->me_8x8_distortion,
+                        (uint8_t *)out->me_8x8_cost_variance, (uint8_t *)out->rc_me_distortion,
+                        out->stationary_block_present_sb, out->rc_me_allow_gm};
+    /* runs of destination arrays that are exactly adjacent in slab order come back with one copy */
+    for (int k = 0; k < 11;) {
+        const int i = L.order[k];
+        if (!dst[i]) {
+            k++;
+            continue;
+        }
+        int    e = k;
+        size_t n = L.bytes[i];
+        while (e + 1 < 11 && dst[L.order[e + 1]] && dst[L.order[e + 1]] == dst[i] + n) {
+            e++;
+            n += L.bytes[L.order[e]];
+        }
+        CU(cudaMemcpyAsync(dst[i], jc->out_slab + L.off[i], n, cudaMemcpyDeviceToHost, st));
+        k = e + 1;
+    }
+#define D2H(dstp, src, bytes)                                                               \
+    do {                                                                                    \
+        if (dstp)                                                                           \
+            CU(cudaMemcpyAsync((dstp), (src), (bytes), cudaMemcpyDeviceToHost, st));        \
+    } while (0)
+    D2H(out->p_sb_best_sad, jc->dbg_sad, nb * ME_NREF * ME_NPU * 4);
+    D2H(out->p_sb_best_mv, jc->dbg_mv, nb * ME_NREF * ME_NPU * 4);
+    D2H(out->hme_search_centre, jc->dbg_centre, nb * ME_NREF * 2 * sizeof(int16_t));
+    D2H(out->hme_sad, jc->dbg_hme, nb * ME_NREF * sizeof(uint64_t));
+    D2H(out->do_ref, jc->dbg_do_ref, nb * ME_NREF);
+    D2H(out->search_area, jc->dbg_area, nb * ME_NREF * 4 * sizeof(int16_t));
+#undef D2H
+    CU(cudaMemcpyAsync(jc->h_tail, &jc->d_head->tail, sizeof(JobTail), cudaMemcpyDeviceToHost, st));
+    CU(cudaEventRecord(jc->ev[4], st));
+    jc->d2h_enqueued = true;
+    return ME_GPU_OK;
+}
+
+static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
+                         const uint64_t ref_picture_numbers[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS], const MeGpuOutputs *out) {
     if (!g.initialised)
         return fail(ME_GPU_ERR_STATE, "not initialised");
     if (!params || !ref_picture_numbers)
@@ -451,8 +531,8 @@ int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
     auto it = g.by_number.find(picture_number);
     if (it == g.by_number.end())
         return fail(ME_GPU_ERR_NOT_FOUND, "source picture not registered");
-    const int src_slot = it->second;
-    const Slot &src    = g.slots[src_slot];
+    const int   src_slot = it->second;
+    const Slot &src      = g.slots[src_slot];
     /* device: pictures are dealt round-robin */
     const size_t di = (size_t)(g.submit_counter % g.dev.size());
     Device      &d  = g.dev[di];
@@ -464,12 +544,13 @@ int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
         }
     if (!jc)
         return fail(ME_GPU_ERR_STATE, "too many pictures in flight: call me_gpu_wait first");
-    for (auto &c : d.jobs)
-        if (c.busy && c.picture_number == picture_number)
-            return fail(ME_GPU_ERR_STATE, "picture already submitted");
+    for (auto &dv : g.dev)
+        for (auto &c : dv.jobs)
+            if (c.busy && c.picture_number == picture_number)
+                return fail(ME_GPU_ERR_STATE, "picture already submitted");
 
     MeJob &j = *jc->h_job;
-    memset(&j, 0, sizeof j);
+    memset(jc->h_head, 0, sizeof(JobHead));
     j.p = p;
     me_make_geom(&j.g, src.width, src.height);
     j.g.slot_bytes = g.gmax.slot_bytes;
@@ -490,31 +571,47 @@ int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
         }
     j.pu_count = (uint32_t)me_exported_pu_count(&p);
     const size_t nb = (size_t)j.g.b64_count;
-    if (nb * j.pu_count * p.max_cand > jc->cap_cands || nb * j.pu_count * p.max_refs > jc->cap_mvs || p.max_cand == 0 || p.max_refs == 0)
+    if (p.max_cand == 0 || p.max_refs == 0)
+        return fail(ME_GPU_ERR_BAD_ARG, "max_cand / max_refs must be set (pcs->pa_me_data)");
+    const OutLayout L = output_layout(nb, j.pu_count, p.max_cand, p.max_refs);
+    if (L.total > jc->out_cap)
         return fail(ME_GPU_ERR_BAD_ARG, "max_cand / max_refs exceed what me_gpu_init allocated");
     if ((uint64_t)max_tiles_per_task(&p) * nb * ME_NREF > jc->tile_cap)
         return fail(ME_GPU_ERR_UNSUPPORTED, "search area too large for the tile list");
+    if (out && out->b64_count < nb)
+        return fail(ME_GPU_ERR_BAD_ARG, "MeGpuOutputs.b64_count is smaller than the picture's b64 count");
     j.state = jc->state; j.tasks = jc->tasks; j.results = jc->results; j.fs_tasks = jc->fs_tasks; j.keys = jc->keys;
-    j.total_me_candidate_index = jc->total; j.me_candidate_array = jc->cands; j.me_mv_array = jc->mvs;
-    j.dist = jc->dist; j.flags = jc->flags;
+    j.total_me_candidate_index = jc->out_slab + L.off[0];
+    j.me_candidate_array       = jc->out_slab + L.off[1];
+    j.me_mv_array              = (uint32_t *)(jc->out_slab + L.off[2]);
+    j.dist                     = (uint32_t *)(jc->out_slab + L.off[3]);
+    j.flags                    = jc->out_slab + L.off[9];
     j.dbg_best_sad = jc->dbg_sad; j.dbg_best_mv = jc->dbg_mv; j.dbg_centre = jc->dbg_centre; j.dbg_hme_sad = jc->dbg_hme;
-    j.dbg_do_ref = jc->dbg_do_ref; j.dbg_area = jc->dbg_area; j.ops_total = jc->ops_total;
+    j.dbg_do_ref = jc->dbg_do_ref; j.dbg_area = jc->dbg_area;
+    j.ops_total = jc->d_head->tail.ops;
+    JobTail &tl = jc->h_head->tail;
+    tl.list.count = tl.list.next = tl.list.overflow = 0;
+    tl.list.cap   = jc->tile_cap;
+    tl.list.tiles = jc->tiles;
+    tl.ops[0] = tl.ops[1] = 0;
 
     CU(cudaSetDevice(d.id));
     cudaStream_t st = jc->stream;
-    for (int s : jc->slots_used) CU(cudaStreamWaitEvent(st, g.slots[s].ready[di], 0));
+    for (int s : jc->slots_used) {
+        Slot &sl = g.slots[s];
+        if (sl.ready_seen[di])
+            continue;
+        if (cudaEventQuery(sl.ready[di]) == cudaSuccess)
+            sl.ready_seen[di] = true;
+        else {
+            cudaGetLastError();
+            CU(cudaStreamWaitEvent(st, sl.ready[di], 0));
+        }
+    }
     CU(cudaEventRecord(jc->ev[0], st));
-    CU(cudaMemcpyAsync(jc->d_job, jc->h_job, sizeof(MeJob), cudaMemcpyHostToDevice, st));
-    FsTileList hl;
-    hl.count = hl.next = hl.overflow = 0;
-    hl.cap   = jc->tile_cap;
-    hl.tiles = jc->tiles;
-    *jc->h_list = hl;
-    CU(cudaMemcpyAsync(jc->d_list, jc->h_list, sizeof(FsTileList), cudaMemcpyHostToDevice, st));
-    CU(cudaMemsetAsync(jc->total, 0, nb * j.pu_count, st));
-    CU(cudaMemsetAsync(jc->cands, 0, nb * j.pu_count * p.max_cand, st));
-    CU(cudaMemsetAsync(jc->mvs, 0, nb * j.pu_count * p.max_refs * sizeof(uint32_t), st));
-    CU(cudaMemsetAsync(jc->ops_total, 0, 2 * sizeof(unsigned long long), st));
+    CU(cudaMemcpyAsync(jc->d_head, jc->h_head, sizeof(JobHead), cudaMemcpyHostToDevice, st));
+    /* candidate / MV entries that no PU writes must read 0, as in the zero-initialised MeSbResults */
+    CU(cudaMemsetAsync(jc->out_slab, 0, L.total, st));
 
     const int nbi = (int)nb;
     jc->npairs = 0;
@@ -537,7 +634,7 @@ int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
         pbegin(1);
         me_launch_hme(jc->d_job, 1, nbi, jc->d_list, d.pool, st);
         pend();
-        CU(cudaEventRecord(jc->ev[1], st));
+        if (prof) CU(cudaEventRecord(jc->ev[1], st));
         pbegin(3);
         me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, d.sms * 2, st);
         pend();
@@ -573,7 +670,7 @@ int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
         if (l2) flush(ME_NREF * 4);
         mask |= 1u << ST_CENTRE;
         flush(ME_NREF * 2);
-        CU(cudaEventRecord(jc->ev[1], st));
+        if (prof) CU(cudaEventRecord(jc->ev[1], st));
         const int fs_ctas = d.sms * 2;
         pbegin(0);
         me_launch_ctrl(jc->d_job, 1, nbi, 1u << ST_PROBE, jc->d_list, st);
@@ -589,17 +686,47 @@ int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
         me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, fs_ctas, st);
         pend();
     }
-    CU(cudaEventRecord(jc->ev[2], st));
+    if (prof) CU(cudaEventRecord(jc->ev[2], st));
     pbegin(4);
     me_launch_epilogue(jc->d_job, 1, nbi, st);
     pend();
-    CU(cudaEventRecord(jc->ev[3], st));
+    if (prof) CU(cudaEventRecord(jc->ev[3], st));
     CU(cudaGetLastError());
-
+    jc->d2h_enqueued = false;
+    jc->prof         = prof;
+    if (out) {
+        int rc = enqueue_d2h(jc, out);
+        if (rc)
+            return rc;
+    }
     jc->busy           = true;
     jc->picture_number = picture_number;
     for (int s : jc->slots_used) g.slots[s].refcount++;
     g.submit_counter++;
+    return ME_GPU_OK;
+}
+
+int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
+                  const uint64_t ref_picture_numbers[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS]) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    return submit_locked(picture_number, params, ref_picture_numbers, nullptr);
+}
+
+int me_gpu_submit_out(uint64_t picture_number, const MeGpuParams *params,
+                      const uint64_t ref_picture_numbers[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS], MeGpuOutputs *out) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!out)
+        return fail(ME_GPU_ERR_BAD_ARG, "null outputs");
+    return submit_locked(picture_number, params, ref_picture_numbers, out);
+}
+
+int me_gpu_output_layout(int width, int height, const MeGpuParams *params, size_t offsets[11], size_t *total_bytes) {
+    if (!params || !offsets || !total_bytes || width <= 0 || height <= 0)
+        return ME_GPU_ERR_BAD_ARG;
+    const size_t    nb = (size_t)((width + 63) / 64) * (size_t)((height + 63) / 64);
+    const OutLayout L  = output_layout(nb, (size_t)me_exported_pu_count(params), params->max_cand, params->max_refs);
+    for (int i = 0; i < 11; i++) offsets[i] = L.off[i];
+    *total_bytes = L.total;
     return ME_GPU_OK;
 }
 
@@ -621,48 +748,28 @@ int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out) {
         return fail(ME_GPU_ERR_NOT_FOUND, "picture was not submitted");
     const MeJob   &j  = *jc->h_job;
     const size_t   nb = (size_t)j.g.b64_count;
-    const uint32_t P  = j.pu_count;
     if (out->b64_count < nb)
         return fail(ME_GPU_ERR_BAD_ARG, "MeGpuOutputs.b64_count is smaller than the picture's b64 count");
     CU(cudaSetDevice(dv->id));
-    cudaStream_t st = jc->stream;
-#define D2H(dst, src, bytes)                                                                \
-    do {                                                                                    \
-        if (dst)                                                                            \
-            CU(cudaMemcpyAsync((dst), (src), (bytes), cudaMemcpyDeviceToHost, st));         \
-    } while (0)
-    D2H(out->total_me_candidate_index, jc->total, nb * P);
-    D2H(out->me_candidate_array, jc->cands, nb * P * j.p.max_cand);
-    D2H(out->me_mv_array, jc->mvs, nb * P * j.p.max_refs * sizeof(uint32_t));
-    D2H(out->me_64x64_distortion, jc->dist + 0 * nb, nb * 4);
-    D2H(out->me_32x32_distortion, jc->dist + 1 * nb, nb * 4);
-    D2H(out->me_16x16_distortion, jc->dist + 2 * nb, nb * 4);
-    D2H(out->me_8x8_distortion, jc->dist + 3 * nb, nb * 4);
-    D2H(out->me_8x8_cost_variance, jc->dist + 4 * nb, nb * 4);
-    D2H(out->rc_me_distortion, jc->dist + 5 * nb, nb * 4);
-    D2H(out->stationary_block_present_sb, jc->flags + 0 * nb, nb);
-    D2H(out->rc_me_allow_gm, jc->flags + 1 * nb, nb);
-    D2H(out->p_sb_best_sad, jc->dbg_sad, nb * ME_NREF * ME_NPU * 4);
-    D2H(out->p_sb_best_mv, jc->dbg_mv, nb * ME_NREF * ME_NPU * 4);
-    D2H(out->hme_search_centre, jc->dbg_centre, nb * ME_NREF * 2 * sizeof(int16_t));
-    D2H(out->hme_sad, jc->dbg_hme, nb * ME_NREF * sizeof(uint64_t));
-    D2H(out->do_ref, jc->dbg_do_ref, nb * ME_NREF);
-    D2H(out->search_area, jc->dbg_area, nb * ME_NREF * 4 * sizeof(int16_t));
-#undef D2H
-    CU(cudaMemcpyAsync(jc->h_list, jc->d_list, sizeof(FsTileList), cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(jc->h_ops, jc->ops_total, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
-    CU(cudaEventRecord(jc->ev[4], st));
+    if (!jc->d2h_enqueued) {
+        int rc = enqueue_d2h(jc, out);
+        if (rc)
+            return rc;
+    }
+    cudaEvent_t done = jc->ev[4];
     lk.unlock();
-    cudaError_t e = cudaStreamSynchronize(st);
+    cudaError_t e = cudaEventSynchronize(done);
     lk.lock();
     if (e != cudaSuccess)
         return fail(ME_GPU_ERR_CUDA, std::string("job failed: ") + cudaGetErrorString(e));
-    const bool overflow = jc->h_list->overflow != 0;
+    const unsigned overflow = jc->h_tail->list.overflow;
     MeGpuTimings t{};
-    cudaEventElapsedTime(&t.hme_ms, jc->ev[0], jc->ev[1]);
-    cudaEventElapsedTime(&t.search_ms, jc->ev[1], jc->ev[2]);
-    cudaEventElapsedTime(&t.epilogue_ms, jc->ev[2], jc->ev[3]);
     cudaEventElapsedTime(&t.total_ms, jc->ev[0], jc->ev[4]);
+    if (jc->prof) {
+        cudaEventElapsedTime(&t.hme_ms, jc->ev[0], jc->ev[1]);
+        cudaEventElapsedTime(&t.search_ms, jc->ev[1], jc->ev[2]);
+        cudaEventElapsedTime(&t.epilogue_ms, jc->ev[2], jc->ev[3]);
+    }
     for (int i = 0; i < jc->npairs; i++) {
         float ms = 0.f;
         cudaEventElapsedTime(&ms, jc->pev[2 * i], jc->pev[2 * i + 1]);
@@ -674,21 +781,20 @@ int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out) {
         default: t.k_epilogue_ms += ms; break;
         }
     }
-    t.pyramid_ms      = 0.f;
     t.kernel_launches = me_launch_count() + me_hme_launch_count();
-    t.byte_sad_ops    = jc->h_ops[0];
-    t.byte_sad_ops_fullsearch = jc->h_ops[1];
+    t.byte_sad_ops    = jc->h_tail->ops[0];
+    t.byte_sad_ops_fullsearch = jc->h_tail->ops[1];
     g.last            = t;
     out->b64_count    = (uint32_t)nb;
-    out->pu_count     = P;
+    out->pu_count     = j.pu_count;
     jc->busy          = false;
     for (int s : jc->slots_used) {
         g.slots[s].refcount--;
         free_slot_if_idle(s);
     }
     if (overflow)
-        return fail(ME_GPU_ERR_UNSUPPORTED, jc->h_list->overflow == 2 ? "a search window exceeds the staging buffer of k_hme"
-                                                                      : "full-search tile list overflowed");
+        return fail(ME_GPU_ERR_UNSUPPORTED, overflow == 2 ? "a search window exceeds the staging buffer of k_hme"
+                                                           : "full-search tile list overflowed");
     return ME_GPU_OK;
 }
 

@@ -139,7 +139,7 @@ REF_LIB = os.path.join(REPO, "oracle", "_ref", "libme_ref.so")
 GPU_SYMBOLS = [
     "me_gpu_init", "me_gpu_shutdown", "me_gpu_last_error", "me_gpu_device_count", "me_gpu_register_picture",
     "me_gpu_register_picture_unpadded", "me_gpu_release_picture", "me_gpu_read_pyramid", "me_gpu_plane_geometry",
-    "me_gpu_submit", "me_gpu_wait", "me_gpu_derive_params", "me_gpu_get_timings", "me_gpu_measure_sad_peak", "me_gpu_set_profiling",
+    "me_gpu_submit", "me_gpu_wait", "me_gpu_derive_params", "me_gpu_get_timings", "me_gpu_measure_sad_peak", "me_gpu_set_profiling", "me_gpu_submit_out", "me_gpu_output_layout",
 ]
 
 
@@ -157,6 +157,9 @@ def load_gpu_lib():
     lib.me_gpu_plane_geometry.argtypes = [C.c_int, C.c_int, C.c_int] + [C.POINTER(C.c_int)] * 5
     lib.me_gpu_submit.argtypes = [u64, C.POINTER(MeGpuParams), C.POINTER(RefNumbers)]
     lib.me_gpu_wait.argtypes = [u64, C.POINTER(MeGpuOutputs)]
+    lib.me_gpu_submit_out.argtypes = [u64, C.POINTER(MeGpuParams), C.POINTER(RefNumbers), C.POINTER(MeGpuOutputs)]
+    lib.me_gpu_output_layout.argtypes = [C.c_int, C.c_int, C.POINTER(MeGpuParams), C.POINTER(C.c_size_t * 11),
+                                         C.POINTER(C.c_size_t)]
     lib.me_gpu_derive_params.argtypes = [C.POINTER(MeGpuEncoderConfig), C.POINTER(MeGpuParams)]
     lib.me_gpu_get_timings.argtypes = [C.POINTER(MeGpuTimings)]
     lib.me_gpu_measure_sad_peak.restype = C.c_double

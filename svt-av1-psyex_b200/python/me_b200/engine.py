@@ -81,6 +81,19 @@ class Engine:
                 arr[li][ri] = n
         self._check(self.lib.me_gpu_submit(picture_number, C.byref(params), C.byref(arr)))
 
+    def submit_out(self, picture_number, params, ref_numbers, out: Outputs):
+        """submit with the result arrays known up front: the D2H copies are queued behind the last kernel"""
+        arr = abi.RefNumbers()
+        for li, lst in enumerate(ref_numbers):
+            for ri, n in enumerate(lst):
+                arr[li][ri] = n
+        self._check(self.lib.me_gpu_submit_out(picture_number, C.byref(params), C.byref(arr), C.byref(out.c)))
+
+    def output_layout(self, width, height, params):
+        offs, total = (C.c_size_t * 11)(), C.c_size_t(0)
+        self._check(self.lib.me_gpu_output_layout(width, height, C.byref(params), C.byref(offs), C.byref(total)))
+        return list(offs), total.value
+
     def wait(self, picture_number, out: Outputs):
         self._check(self.lib.me_gpu_wait(picture_number, C.byref(out.c)))
         return out
