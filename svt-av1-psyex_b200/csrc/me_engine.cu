@@ -105,6 +105,8 @@ struct Device {
     cudaStream_t upload = nullptr;
     int          sms = 148;
     std::vector<JobCtx> jobs;
+    struct MapSet { int width, height; HmeMaps maps; };
+    std::vector<MapSet> mapsets; /* TMA descriptors of the pool per picture size seen (normally one) */
 };
 
 struct Engine {
@@ -631,8 +633,24 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
     };
     if (!g.legacy) {
         /* the whole per-b64 chain in one launch; large search areas come back as tiles */
+        const HmeMaps *maps = nullptr;
+        for (auto &ms : d.mapsets)
+            if (ms.width == j.g.width && ms.height == j.g.height)
+                maps = &ms.maps;
+        if (!maps) {
+            Device::MapSet ms;
+            ms.width  = j.g.width;
+            ms.height = j.g.height;
+            const int rc = me_hme_make_maps(&ms.maps, d.pool, &j.g, g.nslots);
+            if (rc)
+                return fail(ME_GPU_ERR_CUDA, rc < 0 ? "the driver does not export cuTensorMapEncodeTiled"
+                                                    : "cuTensorMapEncodeTiled failed (CUresult " + std::to_string(rc) + ")");
+            d.mapsets.reserve(16); /* pointers into the vector stay valid for the launches in flight (by-value copies anyway) */
+            d.mapsets.push_back(ms);
+            maps = &d.mapsets.back().maps;
+        }
         pbegin(1);
-        me_launch_hme(jc->d_job, 1, nbi, jc->d_list, d.pool, st);
+        me_launch_hme(jc->d_job, 1, nbi, jc->d_list, d.pool, maps, st);
         pend();
         if (prof) CU(cudaEventRecord(jc->ev[1], st));
         pbegin(3);

@@ -23,8 +23,10 @@
  *          areas of up to FS_WARP_MAX positions)
  * Larger search areas are cut into 64x32-position tiles and appended to the work list of k_fullsearch.
  */
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 
 #include "me_ctrl.h"
 #include "me_kernels.h"
@@ -39,6 +41,30 @@
 #define HM_ITEM_POS_B 32 /* ... lane = block row */
 #define HM_ITEM_POS_FS 16 /* ... full-search positions */
 
+#define HM_RAW_BYTES 16896 /* one window buffer (two of them: the job being searched and the one in flight) */
+
+/* source-block pitches in shared memory (words): padded so that lanes on different block rows hit different banks */
+#define HM_SRC0_PITCH 24
+#define HM_SRC1_PITCH 12
+#define HM_SRC2_PITCH 4
+
+struct HmPlan { /* how a task is cut into jobs (written by warp 0 at the start of a stage) */
+    int16_t pwb, neb; /* positions per x band, evaluated rows per y band */
+    uint8_t nxb, nyb, map, kx;
+    uint8_t g_log2, new_path, pad_[2];
+};
+
+struct HmJobD {
+    int task, px0, pw, e0, ne;
+    int xt, y0, aoff; /* TMA column (multiple of 16) and row of the window; byte offset of position px0 in a window row */
+    int pitch, nrows8, map, slot;
+    int off; /* byte offset of the window in the ring */
+    int ncls, nchunk, total; /* unit enumeration of the SAD loop */
+    uint32_t m_chunk, m_cls;
+};
+#define HM_NBAR 8 /* window jobs in flight (ring of job descriptors and mbarriers) */
+#define HM_RING_BYTES (2 * HM_RAW_BYTES)
+
 struct HmeShared {
     B64State           s;
     SearchTask         t[ME_SLOTS];
@@ -48,8 +74,17 @@ struct HmeShared {
     int                item_first[ME_SLOTS + 1]; /* prefix sums: items of task i are [first[i], first[i+1]) */
     int                item_rows[ME_SLOTS]; /* search rows per item */
     int                next_item;
-    alignas(16) uint32_t buf[HM_WARPS][HM_BUF_WORDS + 8]; /* +8: masked over-reads of the last window row stay inside */
+    HmPlan             plan[ME_SLOTS];
+    int                job_first[ME_SLOTS + 1]; /* prefix sums of the window jobs */
+    alignas(8) unsigned long long mbar[HM_NBAR]; /* TMA completion of the windows in flight */
+    HmJobD             jobd[HM_NBAR];
+    int                fetched_pub[2]; /* jobs fetched so far, as seen by the whole CTA at the start of job n: [n & 1] */
+    alignas(16) uint32_t src0[64 * HM_SRC0_PITCH], src1[32 * HM_SRC1_PITCH], src2[16 * HM_SRC2_PITCH]; /* the b64's source block on the three planes (padded pitches) */
+    /* per-warp staging buffers of the item path; the two window buffers of the job path alias them
+       (2 x HM_RAW_BYTES + 128 bytes of slack for masked over-reads) */
+    alignas(128) uint32_t buf[HM_WARPS][HM_BUF_WORDS + 8];
 };
+static_assert(sizeof(uint32_t) * HM_WARPS * (HM_BUF_WORDS + 8) >= 2 * HM_RAW_BYTES + 128, "window buffers alias the warp buffers");
 
 __device__ __forceinline__ uint32_t hm_vsad4(uint32_t a, uint32_t b, uint32_t c) {
     uint32_t d;
@@ -70,6 +105,7 @@ __device__ __forceinline__ void hm_stage_window(uint32_t *win, const uint32_t *g
                                                 int lane) {
     const int      n = nrows * pitch;
     const uint32_t m = hm_magic((uint32_t)pitch);
+#pragma unroll 4
     for (int i = lane; i < n; i += 32) {
         const int r = (int)hm_div((uint32_t)i, (uint32_t)pitch, m), cw = i - r * pitch;
         win[i]      = __ldg(g0 + (size_t)r * stride_words + cw);
@@ -144,17 +180,18 @@ __device__ unsigned long long search_item(const SearchTask &t, int e_lo, int e_h
                 const int       o  = a + x, sh = (o & 3) * 8;
                 const uint32_t *wp = win + (skip ? 2 * ee : ee) * pitch + (o >> 2);
                 const uint4    *sp = (const uint4 *)srcw;
-                uint32_t        sad = 0;
+                uint32_t        s0 = 0, s1 = 0, s2 = 0, s3 = 0; /* independent chains: the SAD pipe has 4-cycle latency */
 #pragma unroll 4
                 for (int r = 0; r < rows; r++) {
                     const uint4    s4 = sp[r];
                     const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3], w4 = wp[4];
-                    sad = hm_vsad4(s4.x, __funnelshift_r(w0, w1, sh), sad);
-                    sad = hm_vsad4(s4.y, __funnelshift_r(w1, w2, sh), sad);
-                    sad = hm_vsad4(s4.z, __funnelshift_r(w2, w3, sh), sad);
-                    sad = hm_vsad4(s4.w, __funnelshift_r(w3, w4, sh), sad);
+                    s0 = hm_vsad4(s4.x, __funnelshift_r(w0, w1, sh), s0);
+                    s1 = hm_vsad4(s4.y, __funnelshift_r(w1, w2, sh), s1);
+                    s2 = hm_vsad4(s4.z, __funnelshift_r(w2, w3, sh), s2);
+                    s3 = hm_vsad4(s4.w, __funnelshift_r(w3, w4, sh), s3);
                     wp += rstep;
                 }
+                const uint32_t sad = (s0 + s1) + (s2 + s3);
                 if (sad < best) { /* positions arrive in increasing scan order per lane: first minimum kept */
                     best = sad;
                     bidx = (uint32_t)((e0 + ee) * t.sa_w + x);
@@ -211,17 +248,17 @@ __device__ unsigned long long search_item(const SearchTask &t, int e_lo, int e_h
                 const int       ee = (int)hm_div((uint32_t)p, saw, sam), x = p - ee * t.sa_w;
                 const int       o  = a + x, sh = (o & 3) * 8;
                 const uint32_t *wp = win + (skip ? 2 * ee : ee) * pitch + (o >> 2);
-                uint32_t        part = 0;
+                uint32_t        p0 = 0, p1 = 0, p2 = 0, p3 = 0;
                 if (!masked) {
 #pragma unroll
                     for (int k = 0; k < 4; k++)
                         if (k < npass) {
                             const uint32_t *q  = wp + off[k];
                             const uint32_t  w0 = q[0], w1 = q[1], w2 = q[2], w3 = q[3], w4 = q[4];
-                            part = hm_vsad4(sw[k][0], __funnelshift_r(w0, w1, sh), part);
-                            part = hm_vsad4(sw[k][1], __funnelshift_r(w1, w2, sh), part);
-                            part = hm_vsad4(sw[k][2], __funnelshift_r(w2, w3, sh), part);
-                            part = hm_vsad4(sw[k][3], __funnelshift_r(w3, w4, sh), part);
+                            p0 = hm_vsad4(sw[k][0], __funnelshift_r(w0, w1, sh), p0);
+                            p1 = hm_vsad4(sw[k][1], __funnelshift_r(w1, w2, sh), p1);
+                            p2 = hm_vsad4(sw[k][2], __funnelshift_r(w2, w3, sh), p2);
+                            p3 = hm_vsad4(sw[k][3], __funnelshift_r(w3, w4, sh), p3);
                         }
                 } else {
 #pragma unroll
@@ -229,13 +266,13 @@ __device__ unsigned long long search_item(const SearchTask &t, int e_lo, int e_h
                         if (k < npass) {
                             const uint32_t *q  = wp + off[k];
                             const uint32_t  w0 = q[0], w1 = q[1], w2 = q[2], w3 = q[3], w4 = q[4];
-                            part = hm_vsad4(sw[k][0], __funnelshift_r(w0, w1, sh) & mk[k][0], part);
-                            part = hm_vsad4(sw[k][1], __funnelshift_r(w1, w2, sh) & mk[k][1], part);
-                            part = hm_vsad4(sw[k][2], __funnelshift_r(w2, w3, sh) & mk[k][2], part);
-                            part = hm_vsad4(sw[k][3], __funnelshift_r(w3, w4, sh) & mk[k][3], part);
+                            p0 = hm_vsad4(sw[k][0], __funnelshift_r(w0, w1, sh) & mk[k][0], p0);
+                            p1 = hm_vsad4(sw[k][1], __funnelshift_r(w1, w2, sh) & mk[k][1], p1);
+                            p2 = hm_vsad4(sw[k][2], __funnelshift_r(w2, w3, sh) & mk[k][2], p2);
+                            p3 = hm_vsad4(sw[k][3], __funnelshift_r(w3, w4, sh) & mk[k][3], p3);
                         }
                 }
-                const uint32_t sad = __reduce_add_sync(0xffffffffu, part);
+                const uint32_t sad = __reduce_add_sync(0xffffffffu, (p0 + p1) + (p2 + p3));
                 if (sad < best) {
                     best = sad;
                     bidx = (uint32_t)((e0 + ee) * t.sa_w + x);
@@ -249,6 +286,250 @@ __device__ unsigned long long search_item(const SearchTask &t, int e_lo, int e_h
             const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
             key                            = other < key ? other : key;
         }
+    return key;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Window jobs: the whole CTA works on one search window at a time.
+ *
+ * A job is a band of a task's search area (all of it when the window fits). Its reference window is
+ * fetched by TMA (cp.async.bulk.tensor: one box, or a few stacked ones, form a dense row-major window whose
+ * row pitch is the box width) one job ahead of the SAD loop, into one of two buffers, and completes on the
+ * buffer's mbarrier. TMA boxes start on 16-byte columns, so search position x sits at byte
+ * aoff + x of a window row; unaligned words are funnel-shifted in registers.
+ *
+ * SAD loop: a unit = KX positions of one search row that share their byte alignment (x = ca + 4k), so
+ * that the NW + KX - 1 shifted reference words of a block row feed NW * KX VABSDIFF4; units of small
+ * search areas are split over G lanes by block rows and joined by shuffles. Results merge as
+ * (sad << 32 | scan index) keys: the minimum key is the first minimum of the reference's scan.
+ * ---------------------------------------------------------------------------------------------- */
+__device__ __forceinline__ uint32_t hm_smem(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void hm_mbar_init(uint32_t bar) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void hm_mbar_expect(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void hm_mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    while (!done)
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(done)
+                     : "r"(bar), "r"(parity)
+                     : "memory");
+}
+__device__ __forceinline__ void hm_tma_box(uint32_t dst, const void *map, int x, int y, int z, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(z), "r"(bar)
+                 : "memory");
+}
+
+/* box widths of the tensor maps, by plane: sixteenth {48, 80, 224}, quarter {80}, full {96, 128} */
+__host__ __device__ __forceinline__ int hm_map_width(int m) {
+    return m == 0 ? 48 : m == 1 ? 80 : m == 2 ? 224 : m == 3 ? 80 : m == 4 ? 96 : 128;
+}
+__host__ __device__ __forceinline__ int hm_map_level(int m) { return m < 3 ? 2 : m == 3 ? 1 : 0; }
+/* rows per box: the usual window of the stage that uses the map in ONE box (the TMA unit takes a box every ~35 cycles
+ * per SM whatever its size: tools/tma_bench.cu); taller windows stack boxes */
+__host__ __device__ __forceinline__ int hm_map_rows(int m) {
+    return m == 0 ? 64 : m == 1 ? 56 : m == 2 ? 24 : m == 3 ? 40 : 72;
+}
+
+/* cut one task into window jobs (or leave it to the per-warp path: picture-edge blocks) */
+__device__ void hm_plan_task(const SearchTask &t, const MeJob *j, int org_x, int org_y, HmPlan &pl) {
+    pl.new_path = 0;
+    pl.nxb = pl.nyb = 0;
+    const int lv = t.level, full = 64 >> lv;
+    if (t.bw != full || t.sx != (org_x >> lv) || t.sy != (org_y >> lv) || (int)t.rows * t.row_step > full || t.sa_w < 1)
+        return;
+    const MePlaneGeom &g    = j->g.plane[lv];
+    const bool         skip = t.bw == 16 && t.rows <= 16 && t.skip_line;
+    const int          ymul = skip ? 2 : 1, erows = skip ? (t.sa_h >> 1) : t.sa_h;
+    if (erows < 1)
+        return;
+    const int span = (t.rows - 1) * t.row_step;
+    const int a16  = (g.pad + t.rx) & 15;
+    const int first = lv == 2 ? 0 : lv == 1 ? 3 : 4, last = lv == 2 ? 2 : lv == 1 ? 3 : 5;
+    const int maxw  = hm_map_width(last);
+    int       pwb = t.sa_w, nxb = 1;
+    if (a16 + t.sa_w - 1 + t.bw > maxw) { /* too wide for one box: bands of a multiple of 16 positions (same alignment) */
+        pwb = (maxw - 15 - t.bw + 1) & ~15;
+        nxb = (t.sa_w + pwb - 1) / pwb;
+    }
+    const int need = a16 + pwb - 1 + t.bw;
+    int       map  = first;
+    while (map < last && hm_map_width(map) < need) map++;
+    const int pitch    = hm_map_width(map);
+    const int rows_cap = (HM_RAW_BYTES / pitch) / hm_map_rows(map) * hm_map_rows(map);
+    const int ne_max   = (rows_cap - span - 1) / ymul + 1;
+    if (rows_cap < span + 1 || ne_max < 1 || nxb > 255)
+        return;
+    const int nyb = (erows + ne_max - 1) / ne_max, neb = (erows + nyb - 1) / nyb;
+    if (nyb > 255)
+        return;
+    const int kx      = (t.bw == 16 && pwb >= 16) ? 4 : 2;
+    const int ncls    = min(4, pwb), per_cls = (pwb + 3) >> 2, nchunk = (per_cls + kx - 1) / kx;
+    const int units   = ncls * nchunk * neb;
+    int       g_log2  = 2 - lv; /* lanes per unit: the 16-byte column segments of the block row ... */
+    while (g_log2 < 5 && (units << g_log2) < 96 && ((2 << g_log2) >> (2 - lv)) <= (int)t.rows) g_log2++; /* ... x row groups */
+    pl.pwb = (int16_t)pwb;
+    pl.neb = (int16_t)neb;
+    pl.nxb = (uint8_t)nxb;
+    pl.nyb = (uint8_t)nyb;
+    pl.map = (uint8_t)map;
+    pl.kx  = (uint8_t)kx;
+    pl.g_log2   = (uint8_t)g_log2;
+    pl.new_path = 1;
+}
+
+/* job number -> job (called by whole warps) */
+__device__ __forceinline__ void hm_job_decode(const SearchTask *tasks, const HmPlan *plans, const int *job_first, const MeJob *j,
+                                              int jb, int lane, HmJobD &J) {
+    const unsigned hit = __ballot_sync(0xffffffffu, job_first[lane] <= jb && jb < job_first[lane + 1]);
+    J.task             = __ffs(hit) - 1;
+    const SearchTask  &t  = tasks[J.task];
+    const HmPlan      &pl = plans[J.task];
+    const MePlaneGeom &g  = j->g.plane[t.level];
+    const int  k = jb - job_first[J.task], yb = k / pl.nxb, xb = k - yb * pl.nxb;
+    const bool skip = t.bw == 16 && t.rows <= 16 && t.skip_line;
+    const int  ymul = skip ? 2 : 1, erows = skip ? (t.sa_h >> 1) : t.sa_h;
+    J.px0 = xb * pl.pwb;
+    J.pw  = min((int)pl.pwb, t.sa_w - J.px0);
+    J.e0  = yb * pl.neb;
+    J.ne  = min((int)pl.neb, erows - J.e0);
+    const int x0 = g.pad + t.rx + J.px0;
+    J.xt   = x0 & ~15;
+    J.aoff = x0 & 15;
+    J.y0   = g.pad + t.ry + ymul * J.e0 + (skip ? 1 : 0);
+    J.map    = pl.map;
+    J.pitch  = hm_map_width(pl.map);
+    const int br = hm_map_rows(pl.map);
+    J.nrows8 = ((J.ne - 1) * ymul + (t.rows - 1) * t.row_step + 1 + br - 1) / br * br; /* whole boxes */
+    J.slot   = t.ref_slot;
+    J.ncls   = min(4, J.pw);
+    J.nchunk = (((J.pw + 3) >> 2) + pl.kx - 1) / pl.kx;
+    J.total  = (J.ncls * J.nchunk * J.ne) << pl.g_log2;
+    J.m_chunk = hm_magic((uint32_t)J.nchunk);
+    J.m_cls   = hm_magic((uint32_t)J.ncls);
+}
+
+/* warp 0: start the TMA transfer of a job's window to `raw` (shared-memory address) */
+__device__ __forceinline__ void hm_job_fetch(const HmeMaps &maps, const HmJobD &J, uint32_t raw, uint32_t bar, int lane) {
+    const int br = hm_map_rows(J.map), nbox = J.nrows8 / br;
+    if (lane == 0) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); /* earlier generic accesses to the buffer come first */
+        hm_mbar_expect(bar, (uint32_t)(J.nrows8 * J.pitch));
+    }
+    __syncwarp();
+    for (int i = lane; i < nbox; i += 32)
+        hm_tma_box(raw + (uint32_t)(i * br * J.pitch), maps.m[J.map], J.xt, J.y0 + i * br, J.slot, bar);
+}
+
+/* warp 0: fetch as many of the stage's jobs ahead of job `jb` as the ring has room for. The ring is FIFO: jobs
+ * [jb, fetched) are live, job n uses descriptor / mbarrier slot (seq0 + n) % HM_NBAR. */
+__device__ __forceinline__ void hm_fetch_ahead(const HmeMaps &maps, const SearchTask *tasks, const HmPlan *plans, const int *job_first,
+                                               HmJobD *jobd, unsigned long long *mbar, uint32_t ring, const MeJob *j, int njobs,
+                                               uint32_t seq0, int jb, int &fetched, int &head, int lane) {
+    while (fetched < njobs && fetched - jb < HM_NBAR - 1) {
+        HmJobD Jn;
+        hm_job_decode(tasks, plans, job_first, j, fetched, lane, Jn);
+        const int size = Jn.nrows8 * Jn.pitch;
+        int       off;
+        if (fetched == jb)
+            off = 0;
+        else {
+            const int tail = jobd[(seq0 + jb) % HM_NBAR].off;
+            if (head > tail) {
+                if (head + size <= HM_RING_BYTES)
+                    off = head;
+                else if (size <= tail)
+                    off = 0;
+                else
+                    break;
+            } else if (head + size <= tail)
+                off = head;
+            else
+                break;
+        }
+        Jn.off                = off;
+        head                  = off + size;
+        const uint32_t slot   = (seq0 + (uint32_t)fetched) % HM_NBAR;
+        if (lane == 0)
+            jobd[slot] = Jn;
+        __syncwarp();
+        hm_job_fetch(maps, Jn, ring + (uint32_t)off, hm_smem(&mbar[slot]), lane);
+        fetched++;
+    }
+}
+
+/* the SAD loop of one job over the CTA; returns this warp's best key (same value in every lane) */
+/* the SAD loop of one job over the CTA; returns this warp's best key (same value in every lane).
+ * A unit (KX positions) is spread over G = 2^g_log2 lanes: the 16-byte column segments of the block row (bw / 16 of
+ * them, adjacent lanes -> adjacent banks) times row groups; partial sums are joined by shuffles. */
+template <int KX>
+__device__ __forceinline__ unsigned long long hm_job_search(const HmJobD &J, const SearchTask &t, int g_log2, const uint32_t *raw,
+                                                            const uint32_t *src, int src_pitch4, int warp, int lane) {
+    const bool skip = t.bw == 16 && t.rows <= 16 && t.skip_line;
+    const int  ymul = skip ? 2 : 1, rows = t.rows, step = t.row_step;
+    const int  pitchw = J.pitch >> 2, G = 1 << g_log2;
+    const int  ncs_log2 = 2 - t.level, RG = G >> ncs_log2; /* column segments: 1 / 2 / 4 on the sixteenth / quarter / full plane */
+    const int  ncls = J.ncls, nchunk = J.nchunk, total = J.total;
+    const uint32_t m_chunk = J.m_chunk, m_cls = J.m_cls;
+    unsigned long long key = ((unsigned long long)ME_SAD_LOOP_INIT << 32) | 0xFFFFFFFFull;
+    for (int base = warp * 32; base < total; base += HM_THREADS) {
+        const int  u  = base + lane;
+        const bool on = u < total;
+        const int  g = u & (G - 1), v = u >> g_log2;
+        const int  cs = g & ((1 << ncs_log2) - 1), rg = g >> ncs_log2;
+        const int  v1 = (int)hm_div((uint32_t)v, (uint32_t)nchunk, m_chunk), chunk = v - v1 * nchunk;
+        const int  e = (int)hm_div((uint32_t)v1, (uint32_t)ncls, m_cls), ca = v1 - e * ncls;
+        const int  o = J.aoff + ca + 4 * KX * chunk, sh = (o & 3) * 8;
+        uint32_t   acc[KX];
+#pragma unroll
+        for (int k = 0; k < KX; k++) acc[k] = 0;
+        if (on) {
+            const uint32_t *wp = raw + (e * ymul + rg * step) * pitchw + (o >> 2) + 4 * cs;
+            const uint4    *sp = reinterpret_cast<const uint4 *>(src) + rg * step * src_pitch4 + cs;
+            const int       dw = step * pitchw * RG, ds = step * src_pitch4 * RG;
+#pragma unroll 4
+            for (int r = rg; r < rows; r += RG) {
+                const uint4 s4 = *sp;
+                uint32_t    w[4 + KX];
+#pragma unroll
+                for (int q = 0; q < 4 + KX; q++) w[q] = wp[q];
+#pragma unroll
+                for (int q = 0; q < 3 + KX; q++) w[q] = __funnelshift_r(w[q], w[q + 1], sh);
+#pragma unroll
+                for (int k = 0; k < KX; k++) {
+                    acc[k] = hm_vsad4(s4.x, w[k], acc[k]);
+                    acc[k] = hm_vsad4(s4.y, w[k + 1], acc[k]);
+                    acc[k] = hm_vsad4(s4.z, w[k + 2], acc[k]);
+                    acc[k] = hm_vsad4(s4.w, w[k + 3], acc[k]);
+                }
+                wp += dw;
+                sp += ds;
+            }
+        }
+        for (int d = G >> 1; d; d >>= 1)
+#pragma unroll
+            for (int k = 0; k < KX; k++) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], d);
+        if (on && g == 0) {
+            const uint32_t idx0 = (uint32_t)((J.e0 + e) * t.sa_w + J.px0);
+#pragma unroll
+            for (int k = 0; k < KX; k++) {
+                const int x = ca + 4 * (KX * chunk + k);
+                if (x < J.pw && acc[k] < ME_SAD_LOOP_INIT) {
+                    const unsigned long long cand = ((unsigned long long)acc[k] << 32) | (idx0 + (uint32_t)x);
+                    key                           = cand < key ? cand : key;
+                }
+            }
+        }
+    }
+    for (int d = 16; d; d >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, d);
+        key                            = other < key ? other : key;
+    }
     return key;
 }
 
@@ -298,15 +579,15 @@ __device__ void fullsearch_item(const FsTask &f, int y_lo, int y_hi, const MeJob
 #pragma unroll
                 for (int b = 0; b < 2; b++) {
                     const uint32_t *wp = win + (y - y0 + 8 * (by + 4 * b)) * pitch + (o >> 2);
-                    uint32_t        acc = 0;
+                    uint32_t        acc0 = 0, acc1 = 0;
 #pragma unroll
                     for (int r = 0; r < NR; r++) {
                         const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2];
-                        acc = hm_vsad4(sw[b][r][0], __funnelshift_r(w0, w1, sh), acc);
-                        acc = hm_vsad4(sw[b][r][1], __funnelshift_r(w1, w2, sh), acc);
+                        acc0 = hm_vsad4(sw[b][r][0], __funnelshift_r(w0, w1, sh), acc0);
+                        acc1 = hm_vsad4(sw[b][r][1], __funnelshift_r(w1, w2, sh), acc1);
                         wp += pitch * RSTEP;
                     }
-                    a8[b] = acc;
+                    a8[b] = acc0 + acc1;
                 }
                 uint32_t s16[2], s32[2];
 #pragma unroll
@@ -372,8 +653,9 @@ __device__ void hm_emit_tiles(const FsTask &f, FsTileList *list, uint32_t task, 
 /* ------------------------------------------------------------------------------------------------
  * k_hme
  * ---------------------------------------------------------------------------------------------- */
-__global__ void __launch_bounds__(HM_THREADS, 4) k_hme(MeJob *jobs, FsTileList *list, const uint8_t *pool) {
-    extern __shared__ __align__(16) unsigned char hm_raw[];
+__global__ void __launch_bounds__(HM_THREADS, 5)
+    k_hme(MeJob *jobs, FsTileList *list, const uint8_t *pool, const __grid_constant__ HmeMaps maps) {
+    extern __shared__ __align__(1024) unsigned char hm_raw[];
     HmeShared     &sm  = *reinterpret_cast<HmeShared *>(hm_raw);
     MeJob         *j   = &jobs[blockIdx.y];
     const int      b   = blockIdx.x;
@@ -404,22 +686,58 @@ __global__ void __launch_bounds__(HM_THREADS, 4) k_hme(MeJob *jobs, FsTileList *
         sm.r[i].found = 0;
         sm.r[i].x = sm.r[i].y = 0;
     }
+    if (tid == 0) {
+        for (int i = 0; i < HM_NBAR; i++) hm_mbar_init(hm_smem(&sm.mbar[i]));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    /* the b64's source block on the three planes stays in shared memory for the whole chain (rows below a short
+       picture-edge block are padding: loaded, never summed) */
+    for (int i = tid; i < 64 * 16 + 32 * 8 + 16 * 4; i += HM_THREADS) {
+        const int lv = i < 64 * 16 ? 0 : i < 64 * 16 + 32 * 8 ? 1 : 2;
+        const int k  = i - (lv == 0 ? 0 : lv == 1 ? 64 * 16 : 64 * 16 + 32 * 8);
+        const int wr = 16 >> lv, r = k / wr, cw = k - r * wr;
+        const MePlaneGeom &pl = j->g.plane[lv];
+        const uint8_t     *sp = hm_plane(pool, j->g, j->src_slot, lv) + (size_t)(pl.pad + (c.org_y >> lv) + r) * pl.stride + pl.pad +
+                            (c.org_x >> lv);
+        const int sp_w = lv == 0 ? HM_SRC0_PITCH : lv == 1 ? HM_SRC1_PITCH : HM_SRC2_PITCH;
+        (lv == 0 ? sm.src0 : lv == 1 ? sm.src1 : sm.src2)[r * sp_w + cw] = __ldg((const uint32_t *)sp + cw);
+    }
     __threadfence();
     __syncthreads();
+    uint32_t  seq  = 0; /* window jobs so far: job n uses mbarrier n % HM_NBAR, parity (n / HM_NBAR) & 1 */
+    uint8_t  *raw0 = reinterpret_cast<uint8_t *>(&sm.buf[0][0]);
+    int       fetched = 0, head = 0; /* warp 0: ring state of the stage */
 
+#ifdef ME_HME_TRACE
+    long long tr[ST_COUNT][4];
+    long long t_begin = clock64();
+#endif
     for (int st = 0; st < ST_COUNT; st++) {
+#ifdef ME_HME_TRACE
+        long long tr0 = clock64();
+#endif
         if (tid == 0) {
             mc_run_stage(&c, st);
             sm.next_item = 0;
         }
         __syncthreads();
+#ifdef ME_HME_TRACE
+        long long tr1 = clock64();
+#endif
         const bool search_stage = st <= ST_CENTRE;
         /* warp 0: cut the tasks into work items (bands of search rows) */
         if (warp == 0) {
-            int n = 0, rows_per = 1;
+            int n = 0, rows_per = 1, nj = 0;
             if (search_stage) {
                 const SearchTask t = sm.t[lane];
-                if (t.valid) {
+                HmPlan           pl;
+                pl.new_path = 0;
+                if (t.valid)
+                    hm_plan_task(t, j, c.org_x, c.org_y, pl);
+                sm.plan[lane] = pl;
+                if (pl.new_path)
+                    nj = (int)pl.nxb * (int)pl.nyb;
+                else if (t.valid) {
                     const bool skip  = t.bw == 16 && t.rows <= 16 && t.skip_line;
                     const int  erows = skip ? (t.sa_h >> 1) : t.sa_h;
                     const bool modeB = t.rows * ((((t.bw + 3) >> 2) + 3) >> 2) >= 32;
@@ -437,18 +755,85 @@ __global__ void __launch_bounds__(HM_THREADS, 4) k_hme(MeJob *jobs, FsTileList *
                         hm_emit_tiles(f, list, (uint32_t)b * ME_NREF + (uint32_t)lane, (uint16_t)blockIdx.y);
                 }
             }
-            int incl = n;
+            int incl = n, inclj = nj;
             for (int o = 1; o < 32; o <<= 1) {
-                const int v = __shfl_up_sync(0xffffffffu, incl, o);
-                if (lane >= o)
+                const int v = __shfl_up_sync(0xffffffffu, incl, o), vj = __shfl_up_sync(0xffffffffu, inclj, o);
+                if (lane >= o) {
                     incl += v;
+                    inclj += vj;
+                }
             }
             sm.item_first[lane + 1] = incl;
+            sm.job_first[lane + 1]  = inclj;
             sm.item_rows[lane]      = rows_per;
             if (lane == 0)
-                sm.item_first[0] = 0;
+                sm.item_first[0] = sm.job_first[0] = 0;
+            __syncwarp();
+            fetched = 0;
+            head    = 0;
+            if (search_stage)
+                hm_fetch_ahead(maps, sm.t, sm.plan, sm.job_first, sm.jobd, sm.mbar, hm_smem(raw0), j, sm.job_first[ME_SLOTS], seq,
+                               0, fetched, head, lane);
+            if (lane == 0)
+                sm.fetched_pub[0] = fetched;
         }
         __syncthreads();
+#ifdef ME_HME_TRACE
+        long long tr2 = clock64();
+#endif
+        /* window jobs: the CTA searches job n while the TMA transfers of the following jobs are in flight */
+        const int njobs = search_stage ? sm.job_first[ME_SLOTS] : 0;
+        {
+            const uint32_t seq0 = seq;
+#ifdef ME_HME_TRACE
+            long long tj_fetch = 0, tj_wait = 0, tj_comp = 0, tj_bar = 0;
+#endif
+            for (int jb = 0; jb < njobs; jb++, seq++) {
+#ifdef ME_HME_TRACE
+                const long long q0 = clock64();
+#endif
+                if (warp == 0 && jb > 0)
+                    hm_fetch_ahead(maps, sm.t, sm.plan, sm.job_first, sm.jobd, sm.mbar, hm_smem(raw0), j, njobs, seq0, jb, fetched,
+                                   head, lane);
+#ifdef ME_HME_TRACE
+                const long long q1 = clock64();
+#endif
+                if (sm.fetched_pub[jb & 1] <= jb)
+                    __syncthreads(); /* the ring had no room to fetch this job ahead: warp 0 has just done it */
+                const uint32_t    slot = seq % HM_NBAR;
+                const HmJobD      J    = sm.jobd[slot];
+                const SearchTask &t    = sm.t[J.task];
+                const HmPlan     &pl   = sm.plan[J.task];
+                const uint32_t   *raw  = reinterpret_cast<const uint32_t *>(raw0 + J.off);
+                hm_mbar_wait(hm_smem(&sm.mbar[slot]), (seq / HM_NBAR) & 1);
+#ifdef ME_HME_TRACE
+                const long long q2 = clock64();
+#endif
+                unsigned long long key;
+                const uint32_t *srcb = t.level == 2 ? sm.src2 : t.level == 1 ? sm.src1 : sm.src0;
+                const int       sp4  = (t.level == 2 ? HM_SRC2_PITCH : t.level == 1 ? HM_SRC1_PITCH : HM_SRC0_PITCH) / 4;
+                if (pl.kx == 4)
+                    key = hm_job_search<4>(J, t, pl.g_log2, raw, srcb, sp4, warp, lane);
+                else
+                    key = hm_job_search<2>(J, t, pl.g_log2, raw, srcb, sp4, warp, lane);
+                if (lane == 0)
+                    atomicMin(&sm.tkey[J.task], key);
+                if (tid == 0)
+                    sm.fetched_pub[(jb + 1) & 1] = fetched;
+#ifdef ME_HME_TRACE
+                const long long q3 = clock64();
+#endif
+                __syncthreads(); /* the window's ring space is free again */
+#ifdef ME_HME_TRACE
+                tj_fetch += q1 - q0; tj_wait += q2 - q1; tj_comp += q3 - q2; tj_bar += clock64() - q3;
+#endif
+            }
+#ifdef ME_HME_TRACE
+            if (blockIdx.y == 0 && b == 100 && (tid == 0 || tid == 96) && njobs)
+                printf("b %d tid %d st %d jobs %d: fetch %lld wait %lld compute %lld barrier %lld\n", b, tid, st, njobs, tj_fetch, tj_wait,
+                       tj_comp, tj_bar);
+#endif
+        }
         const int total = sm.item_first[ME_SLOTS];
         for (;;) {
             int it = 0;
@@ -481,7 +866,16 @@ __global__ void __launch_bounds__(HM_THREADS, 4) k_hme(MeJob *jobs, FsTileList *
         }
         if (!search_stage)
             __threadfence(); /* the probe keys are read (at L2) by thread 0 in the next stage */
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); /* warp buffers written here are TMA targets later */
+#ifdef ME_HME_TRACE
+        long long tr3w = clock64();
+#endif
         __syncthreads();
+#ifdef ME_HME_TRACE
+        long long tr3 = clock64();
+        tr[st][0] = tr1 - tr0; tr[st][1] = tr2 - tr1; tr[st][2] = tr3 - tr2; tr[st][3] = tr3w - tr2;
+        if (tid == 0 && blockIdx.y == 0 && (b == 100 || b == 300)) printf("b %d st %d items %d\n", b, st, total);
+#endif
         if (search_stage && tid < ME_SLOTS && sm.t[tid].valid) {
             /* key -> what the callers of svt_sad_loop_kernel see */
             const SearchTask &t   = sm.t[tid];
@@ -501,6 +895,14 @@ __global__ void __launch_bounds__(HM_THREADS, 4) k_hme(MeJob *jobs, FsTileList *
         }
         __syncthreads();
     }
+#ifdef ME_HME_TRACE
+    if (blockIdx.y == 0 && (b == 100 || b == 300) && (tid == 0 || tid == 96)) {
+        for (int st = 0; st < ST_COUNT; st++)
+            printf("b %d tid %d stage %d: ctrl %lld partition %lld items+barrier %lld (own items %lld) cycles\n", b, tid, st,
+                   tr[st][0], tr[st][1], tr[st][2], tr[st][3]);
+        printf("b %d tid %d total %lld cycles\n", b, tid, clock64() - t_begin);
+    }
+#endif
     /* the epilogue (after the tiled searches) continues from the state in HBM */
     {
         const uint32_t *src = reinterpret_cast<const uint32_t *>(&sm.s);
@@ -516,8 +918,34 @@ cudaError_t me_hme_setup(void) {
     return cudaFuncSetAttribute(k_hme, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HmeShared));
 }
 
-void me_launch_hme(MeJob *jobs, int njobs, int max_b64, FsTileList *list, const uint8_t *pool, cudaStream_t st) {
+/* tensor maps of the pool's planes for pictures of geometry g (TMA: rank 3 = byte column, row, pool slot) */
+int me_hme_make_maps(HmeMaps *maps, const uint8_t *pool, const MePicGeom *g, int nslots) {
+    typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                 const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static_assert(sizeof(CUtensorMap) == 128, "HmeMaps holds CUtensorMap images");
+    EncodeFn                        encode = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", (void **)&encode, cudaEnableDefault, &qres) != cudaSuccess || !encode ||
+        qres != cudaDriverEntryPointSuccess)
+        return -1;
+    for (int m = 0; m < HM_NMAPS; m++) {
+        const MePlaneGeom &pl = g->plane[hm_map_level(m)];
+        cuuint64_t dims[3]    = {(cuuint64_t)pl.stride, (cuuint64_t)pl.rows, (cuuint64_t)nslots};
+        cuuint64_t strides[2] = {(cuuint64_t)pl.stride, (cuuint64_t)g->slot_bytes};
+        cuuint32_t box[3] = {(cuuint32_t)hm_map_width(m), (cuuint32_t)hm_map_rows(m), 1}, estr[3] = {1, 1, 1};
+        CUresult   r = encode(reinterpret_cast<CUtensorMap *>(maps->m[m]), CU_TENSOR_MAP_DATA_TYPE_UINT8, 3,
+                              const_cast<uint8_t *>(pool) + pl.offset, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS)
+            return (int)r;
+    }
+    return 0;
+}
+
+void me_launch_hme(MeJob *jobs, int njobs, int max_b64, FsTileList *list, const uint8_t *pool, const HmeMaps *maps,
+                   cudaStream_t st) {
     dim3 grid(max_b64, njobs);
-    k_hme<<<grid, HM_THREADS, sizeof(HmeShared), st>>>(jobs, list, pool);
+    k_hme<<<grid, HM_THREADS, sizeof(HmeShared), st>>>(jobs, list, pool, *maps);
     g_hme_launches++;
 }

@@ -27,8 +27,17 @@ void   me_launch_fullsearch(MeJob *jobs, FsTileList *list, const uint8_t *pool, 
 void   me_launch_epilogue(MeJob *jobs, int njobs, int max_b64, cudaStream_t st);
 double me_measure_sad_peak(cudaStream_t st);
 /* me_hme.cu */
+#define HM_NMAPS 6
+/* TMA descriptors (CUtensorMap, 128 bytes each) of the three planes of the pool as (x, row, slot) byte tensors, one per
+ * box width that k_hme stages search windows with; passed to the kernel by value (__grid_constant__) */
+typedef struct HmeMaps {
+    alignas(64) unsigned char m[HM_NMAPS][128];
+} HmeMaps;
 cudaError_t        me_hme_setup(void);
 unsigned long long me_hme_launch_count(void);
-void   me_launch_hme(MeJob *jobs, int njobs, int max_b64, FsTileList *list, const uint8_t *pool, cudaStream_t st);
+/* 0 on success; -1 when the driver has no cuTensorMapEncodeTiled, else the CUresult of the failed encode */
+int    me_hme_make_maps(HmeMaps *maps, const uint8_t *pool, const MePicGeom *g, int nslots);
+void   me_launch_hme(MeJob *jobs, int njobs, int max_b64, FsTileList *list, const uint8_t *pool, const HmeMaps *maps,
+                     cudaStream_t st);
 
 #endif

@@ -8,6 +8,8 @@
  */
 #include <cstdlib>
 #include <cstring>
+#include <map>
+#include <string>
 #include <vector>
 
 #include "me_ctrl.h"
@@ -138,6 +140,26 @@ extern "C" int emul_me_picture(const OraclePicture *src, const OraclePicture *co
             if (stage == ST_INIT)
                 mc_init_keys(c.keys, 0, 1);
             mc_run_stage(&c, stage);
+        }
+        if (getenv("ME_EMUL_DUMP")) { /* task-shape histogram of this stage (kernel tuning aid) */
+            std::map<std::string, int> hist;
+            char                       key[128];
+            if (stage <= ST_CENTRE) {
+                for (size_t i = 0; i < tasks.size(); i++)
+                    if (tasks[i].valid) {
+                        const SearchTask &t = tasks[i];
+                        snprintf(key, sizeof key, "L%d bw%-2d rows%-2d step%d skip%d sa %3dx%-3d", t.level, t.bw, t.rows, t.row_step,
+                                 t.skip_line, t.sa_w, t.sa_h);
+                        hist[key]++;
+                    }
+            } else {
+                for (size_t i = 0; i < fs.size(); i++)
+                    if (fs[i].valid) {
+                        snprintf(key, sizeof key, "FS probe%d %3dx%-3d", fs[i].probe, fs[i].w, fs[i].h);
+                        hist[key]++;
+                    }
+            }
+            for (auto &kv : hist) fprintf(stderr, "stage %d  %-48s x %d\n", stage, kv.first.c_str(), kv.second);
         }
         if (stage <= ST_CENTRE) {
             for (size_t i = 0; i < tasks.size(); i++)
