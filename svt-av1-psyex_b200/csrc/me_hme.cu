@@ -33,7 +33,7 @@
 
 #define HM_WARPS 4
 #define HM_THREADS (HM_WARPS * 32)
-#define HM_BUF_WORDS 2112 /* per-warp staging buffer: source block (<= 512 words) + reference window (15 rows x
+#define HM_BUF_WORDS 2048 /* per-warp staging buffer: source block (<= 512 words) + reference window (15 rows x
                              131 words of the widest pre-HME strip fit; taller windows are banded) */
 #define FS_WARP_MAX 256 /* search areas up to this many positions (and <= FS_WARP_MAXW wide) stay in k_hme */
 #define FS_WARP_MAXW 48
@@ -41,7 +41,7 @@
 #define HM_ITEM_POS_B 32 /* ... lane = block row */
 #define HM_ITEM_POS_FS 16 /* ... full-search positions */
 
-#define HM_RAW_BYTES 16896 /* one window buffer (two of them: the job being searched and the one in flight) */
+#define HM_RAW_BYTES 16384 /* largest window of a job: half of the ring */
 
 /* source-block pitches in shared memory (words): padded so that lanes on different block rows hit different banks */
 #define HM_SRC0_PITCH 24
@@ -54,14 +54,17 @@ struct HmPlan { /* how a task is cut into jobs (written by warp 0 at the start o
     uint8_t g_log2, new_path, pad_[2];
 };
 
-struct HmJobD {
-    int task, px0, pw, e0, ne;
-    int xt, y0, aoff; /* TMA column (multiple of 16) and row of the window; byte offset of position px0 in a window row */
-    int pitch, nrows8, map, slot;
-    int off; /* byte offset of the window in the ring */
-    int ncls, nchunk, total; /* unit enumeration of the SAD loop */
+struct HmJobD { /* one window job, 32 bytes */
+    int16_t  px0, pw, e0, ne; /* band of search positions: columns [px0, px0 + pw), evaluated rows [e0, e0 + ne) */
+    int16_t  xt, y0; /* TMA column (multiple of 16) and row of the window */
+    uint16_t off128; /* window offset in the ring, in 128-byte units */
+    uint16_t nrows; /* window rows (whole boxes) */
+    uint16_t total; /* lanes' worth of work of the SAD loop: units x lanes per unit */
+    uint8_t  task, map, aoff /* byte offset of position px0 in a window row */, ncls, nchunk;
+    int8_t   dep; /* last earlier job of the stage whose window overlaps this one (-1: none) */
     uint32_t m_chunk, m_cls;
 };
+#define HM_MAXJOBS 48 /* window jobs per stage; tasks beyond go to the per-warp path */
 #define HM_NBAR 8 /* window jobs in flight (ring of job descriptors and mbarriers) */
 #define HM_RING_BYTES (2 * HM_RAW_BYTES)
 
@@ -77,8 +80,7 @@ struct HmeShared {
     HmPlan             plan[ME_SLOTS];
     int                job_first[ME_SLOTS + 1]; /* prefix sums of the window jobs */
     alignas(8) unsigned long long mbar[HM_NBAR]; /* TMA completion of the windows in flight */
-    HmJobD             jobd[HM_NBAR];
-    int                fetched_pub[2]; /* jobs fetched so far, as seen by the whole CTA at the start of job n: [n & 1] */
+    HmJobD             jobs[HM_MAXJOBS];
     alignas(16) uint32_t src0[64 * HM_SRC0_PITCH], src1[32 * HM_SRC1_PITCH], src2[16 * HM_SRC2_PITCH]; /* the b64's source block on the three planes (padded pitches) */
     /* per-warp staging buffers of the item path; the two window buffers of the job path alias them
        (2 x HM_RAW_BYTES + 128 bytes of slack for masked over-reads) */
@@ -305,18 +307,18 @@ __device__ unsigned long long search_item(const SearchTask &t, int e_lo, int e_h
  * ---------------------------------------------------------------------------------------------- */
 __device__ __forceinline__ uint32_t hm_smem(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-__device__ __forceinline__ void hm_mbar_init(uint32_t bar) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
+__device__ __forceinline__ void hm_mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
 }
 __device__ __forceinline__ void hm_mbar_expect(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void hm_mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t done = 0;
-    while (!done)
-        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+    while (!done) /* suspend-time hint: a waiting warp should not take issue slots from the warps it waits for */
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3; selp.u32 %0, 1, 0, p; }"
                      : "=r"(done)
-                     : "r"(bar), "r"(parity)
+                     : "r"(bar), "r"(parity), "r"(1000u)
                      : "memory");
 }
 __device__ __forceinline__ void hm_tma_box(uint32_t dst, const void *map, int x, int y, int z, uint32_t bar) {
@@ -383,87 +385,59 @@ __device__ void hm_plan_task(const SearchTask &t, const MeJob *j, int org_x, int
     pl.new_path = 1;
 }
 
-/* job number -> job (called by whole warps) */
-__device__ __forceinline__ void hm_job_decode(const SearchTask *tasks, const HmPlan *plans, const int *job_first, const MeJob *j,
-                                              int jb, int lane, HmJobD &J) {
-    const unsigned hit = __ballot_sync(0xffffffffu, job_first[lane] <= jb && jb < job_first[lane + 1]);
-    J.task             = __ffs(hit) - 1;
-    const SearchTask  &t  = tasks[J.task];
-    const HmPlan      &pl = plans[J.task];
+/* job number -> job descriptor (one thread per job) */
+__device__ void hm_job_decode(const SearchTask *tasks, const HmPlan *plans, const int *job_first, const MeJob *j, int jb, HmJobD &J) {
+    int task = 0;
+    for (int step = 16; step; step >>= 1) /* last task with job_first[task] <= jb */
+        if (job_first[task + step] <= jb)
+            task += step;
+    const SearchTask  &t  = tasks[task];
+    const HmPlan      &pl = plans[task];
     const MePlaneGeom &g  = j->g.plane[t.level];
-    const int  k = jb - job_first[J.task], yb = k / pl.nxb, xb = k - yb * pl.nxb;
+    const int  k = jb - job_first[task], yb = k / pl.nxb, xb = k - yb * pl.nxb;
     const bool skip = t.bw == 16 && t.rows <= 16 && t.skip_line;
     const int  ymul = skip ? 2 : 1, erows = skip ? (t.sa_h >> 1) : t.sa_h;
-    J.px0 = xb * pl.pwb;
-    J.pw  = min((int)pl.pwb, t.sa_w - J.px0);
-    J.e0  = yb * pl.neb;
-    J.ne  = min((int)pl.neb, erows - J.e0);
-    const int x0 = g.pad + t.rx + J.px0;
-    J.xt   = x0 & ~15;
-    J.aoff = x0 & 15;
-    J.y0   = g.pad + t.ry + ymul * J.e0 + (skip ? 1 : 0);
+    const int  px0 = xb * pl.pwb, pw = min((int)pl.pwb, t.sa_w - px0);
+    const int  e0 = yb * pl.neb, ne = min((int)pl.neb, erows - e0);
+    const int  x0 = g.pad + t.rx + px0, br = hm_map_rows(pl.map);
+    const int  ncls = min(4, pw), nchunk = (((pw + 3) >> 2) + pl.kx - 1) / pl.kx;
+    J.task   = (uint8_t)task;
     J.map    = pl.map;
-    J.pitch  = hm_map_width(pl.map);
-    const int br = hm_map_rows(pl.map);
-    J.nrows8 = ((J.ne - 1) * ymul + (t.rows - 1) * t.row_step + 1 + br - 1) / br * br; /* whole boxes */
-    J.slot   = t.ref_slot;
-    J.ncls   = min(4, J.pw);
-    J.nchunk = (((J.pw + 3) >> 2) + pl.kx - 1) / pl.kx;
-    J.total  = (J.ncls * J.nchunk * J.ne) << pl.g_log2;
-    J.m_chunk = hm_magic((uint32_t)J.nchunk);
-    J.m_cls   = hm_magic((uint32_t)J.ncls);
+    J.px0    = (int16_t)px0;
+    J.pw     = (int16_t)pw;
+    J.e0     = (int16_t)e0;
+    J.ne     = (int16_t)ne;
+    J.xt     = (int16_t)(x0 & ~15);
+    J.aoff   = (uint8_t)(x0 & 15);
+    J.y0     = (int16_t)(g.pad + t.ry + ymul * e0 + (skip ? 1 : 0));
+    J.nrows  = (uint16_t)(((ne - 1) * ymul + (t.rows - 1) * t.row_step + 1 + br - 1) / br * br); /* whole boxes */
+    J.off128 = 0;
+    J.ncls   = (uint8_t)ncls;
+    J.nchunk = (uint8_t)nchunk;
+    J.total  = (uint16_t)((ncls * nchunk * ne) << pl.g_log2);
+    J.dep    = -1;
+    J.m_chunk = hm_magic((uint32_t)nchunk);
+    J.m_cls   = hm_magic((uint32_t)ncls);
 }
 
-/* warp 0: start the TMA transfer of a job's window to `raw` (shared-memory address) */
-__device__ __forceinline__ void hm_job_fetch(const HmeMaps &maps, const HmJobD &J, uint32_t raw, uint32_t bar, int lane) {
-    const int br = hm_map_rows(J.map), nbox = J.nrows8 / br;
-    if (lane == 0) {
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); /* earlier generic accesses to the buffer come first */
-        hm_mbar_expect(bar, (uint32_t)(J.nrows8 * J.pitch));
-    }
-    __syncwarp();
-    for (int i = lane; i < nbox; i += 32)
-        hm_tma_box(raw + (uint32_t)(i * br * J.pitch), maps.m[J.map], J.xt, J.y0 + i * br, J.slot, bar);
-}
-
-/* warp 0: fetch as many of the stage's jobs ahead of job `jb` as the ring has room for. The ring is FIFO: jobs
- * [jb, fetched) are live, job n uses descriptor / mbarrier slot (seq0 + n) % HM_NBAR. */
-__device__ __forceinline__ void hm_fetch_ahead(const HmeMaps &maps, const SearchTask *tasks, const HmPlan *plans, const int *job_first,
-                                               HmJobD *jobd, unsigned long long *mbar, uint32_t ring, const MeJob *j, int njobs,
-                                               uint32_t seq0, int jb, int &fetched, int &head, int lane) {
-    while (fetched < njobs && fetched - jb < HM_NBAR - 1) {
-        HmJobD Jn;
-        hm_job_decode(tasks, plans, job_first, j, fetched, lane, Jn);
-        const int size = Jn.nrows8 * Jn.pitch;
-        int       off;
-        if (fetched == jb)
-            off = 0;
-        else {
-            const int tail = jobd[(seq0 + jb) % HM_NBAR].off;
-            if (head > tail) {
-                if (head + size <= HM_RING_BYTES)
-                    off = head;
-                else if (size <= tail)
-                    off = 0;
-                else
-                    break;
-            } else if (head + size <= tail)
-                off = head;
-            else
-                break;
-        }
-        Jn.off                = off;
-        head                  = off + size;
-        const uint32_t slot   = (seq0 + (uint32_t)fetched) % HM_NBAR;
-        if (lane == 0)
-            jobd[slot] = Jn;
-        __syncwarp();
-        hm_job_fetch(maps, Jn, ring + (uint32_t)off, hm_smem(&mbar[slot]), lane);
+/* Thread 0, before the CTA searches job `jb`: request the windows of the following jobs while the ring has room.
+ * Jobs are searched in order with a CTA barrier after each, so the jobs before `jb` are done: job n can go as soon as
+ * the last earlier job on its ring bytes (dep) is one of them. Job n (N = seq0 + n over the whole kernel) completes
+ * on mbarrier N % HM_NBAR; at most HM_NBAR jobs are in flight, so the previous user of the mbarrier is done too. */
+__device__ __forceinline__ void hm_fetch_ahead(const HmeMaps &maps, const SearchTask *tasks, const HmJobD *jobs, unsigned long long *full,
+                                               uint32_t ring, int njobs, uint32_t seq0, int jb, int &fetched) {
+    while (fetched < njobs && fetched - jb < HM_NBAR && jobs[fetched].dep < jb) {
+        const HmJobD  &Jn  = jobs[fetched];
+        const uint32_t bar = hm_smem(&full[(seq0 + (uint32_t)fetched) % HM_NBAR]);
+        const int      pitch = hm_map_width(Jn.map), off = (int)Jn.off128 * 128, br = hm_map_rows(Jn.map);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); /* earlier generic accesses to the ring come first */
+        hm_mbar_expect(bar, (uint32_t)((int)Jn.nrows * pitch));
+        for (int y = 0; y < (int)Jn.nrows; y += br)
+            hm_tma_box(ring + (uint32_t)(off + y * pitch), maps.m[Jn.map], Jn.xt, Jn.y0 + y, tasks[Jn.task].ref_slot, bar);
         fetched++;
     }
 }
 
-/* the SAD loop of one job over the CTA; returns this warp's best key (same value in every lane) */
 /* the SAD loop of one job over the CTA; returns this warp's best key (same value in every lane).
  * A unit (KX positions) is spread over G = 2^g_log2 lanes: the 16-byte column segments of the block row (bw / 16 of
  * them, adjacent lanes -> adjacent banks) times row groups; partial sums are joined by shuffles. */
@@ -472,7 +446,7 @@ __device__ __forceinline__ unsigned long long hm_job_search(const HmJobD &J, con
                                                             const uint32_t *src, int src_pitch4, int warp, int lane) {
     const bool skip = t.bw == 16 && t.rows <= 16 && t.skip_line;
     const int  ymul = skip ? 2 : 1, rows = t.rows, step = t.row_step;
-    const int  pitchw = J.pitch >> 2, G = 1 << g_log2;
+    const int  pitchw = hm_map_width(J.map) >> 2, G = 1 << g_log2;
     const int  ncs_log2 = 2 - t.level, RG = G >> ncs_log2; /* column segments: 1 / 2 / 4 on the sixteenth / quarter / full plane */
     const int  ncls = J.ncls, nchunk = J.nchunk, total = J.total;
     const uint32_t m_chunk = J.m_chunk, m_cls = J.m_cls;
@@ -687,7 +661,7 @@ __global__ void __launch_bounds__(HM_THREADS, 5)
         sm.r[i].x = sm.r[i].y = 0;
     }
     if (tid == 0) {
-        for (int i = 0; i < HM_NBAR; i++) hm_mbar_init(hm_smem(&sm.mbar[i]));
+        for (int i = 0; i < HM_NBAR; i++) hm_mbar_init(hm_smem(&sm.mbar[i]), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     /* the b64's source block on the three planes stays in shared memory for the whole chain (rows below a short
@@ -706,7 +680,7 @@ __global__ void __launch_bounds__(HM_THREADS, 5)
     __syncthreads();
     uint32_t  seq  = 0; /* window jobs so far: job n uses mbarrier n % HM_NBAR, parity (n / HM_NBAR) & 1 */
     uint8_t  *raw0 = reinterpret_cast<uint8_t *>(&sm.buf[0][0]);
-    int       fetched = 0, head = 0; /* warp 0: ring state of the stage */
+    int       fetched = 0; /* warp 0: jobs of the stage whose windows have been requested */
 
 #ifdef ME_HME_TRACE
     long long tr[ST_COUNT][4];
@@ -734,17 +708,32 @@ __global__ void __launch_bounds__(HM_THREADS, 5)
                 pl.new_path = 0;
                 if (t.valid)
                     hm_plan_task(t, j, c.org_x, c.org_y, pl);
-                sm.plan[lane] = pl;
                 if (pl.new_path)
                     nj = (int)pl.nxb * (int)pl.nyb;
-                else if (t.valid) {
+                if (t.valid) { /* the per-warp split, used when the task cannot be a window job */
                     const bool skip  = t.bw == 16 && t.rows <= 16 && t.skip_line;
                     const int  erows = skip ? (t.sa_h >> 1) : t.sa_h;
                     const bool modeB = t.rows * ((((t.bw + 3) >> 2) + 3) >> 2) >= 32;
                     rows_per         = max(1, (modeB ? HM_ITEM_POS_B : HM_ITEM_POS_A) / max(1, (int)t.sa_w));
                     n                = (erows + rows_per - 1) / rows_per;
                 }
-                sm.tkey[lane] = none;
+                int inclj = nj;
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int vj = __shfl_up_sync(0xffffffffu, inclj, o);
+                    if (lane >= o)
+                        inclj += vj;
+                }
+                const bool over = inclj > HM_MAXJOBS; /* job table full: this task and the ones after it go per-warp */
+                const int  kept = __reduce_max_sync(0xffffffffu, over ? 0 : inclj);
+                if (over) {
+                    pl.new_path = 0;
+                    inclj       = kept;
+                }
+                if (pl.new_path)
+                    n = 0;
+                sm.plan[lane]          = pl;
+                sm.job_first[lane + 1] = inclj;
+                sm.tkey[lane]          = none;
             } else if (lane < ME_NREF) {
                 const FsTask f = sm.f[lane];
                 if (f.valid) {
@@ -755,34 +744,51 @@ __global__ void __launch_bounds__(HM_THREADS, 5)
                         hm_emit_tiles(f, list, (uint32_t)b * ME_NREF + (uint32_t)lane, (uint16_t)blockIdx.y);
                 }
             }
-            int incl = n, inclj = nj;
+            int incl = n;
             for (int o = 1; o < 32; o <<= 1) {
-                const int v = __shfl_up_sync(0xffffffffu, incl, o), vj = __shfl_up_sync(0xffffffffu, inclj, o);
-                if (lane >= o) {
+                const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o)
                     incl += v;
-                    inclj += vj;
-                }
             }
             sm.item_first[lane + 1] = incl;
-            sm.job_first[lane + 1]  = inclj;
             sm.item_rows[lane]      = rows_per;
             if (lane == 0)
                 sm.item_first[0] = sm.job_first[0] = 0;
-            __syncwarp();
-            fetched = 0;
-            head    = 0;
-            if (search_stage)
-                hm_fetch_ahead(maps, sm.t, sm.plan, sm.job_first, sm.jobd, sm.mbar, hm_smem(raw0), j, sm.job_first[ME_SLOTS], seq,
-                               0, fetched, head, lane);
-            if (lane == 0)
-                sm.fetched_pub[0] = fetched;
         }
         __syncthreads();
+        const int njobs = search_stage ? sm.job_first[ME_SLOTS] : 0;
+        for (int jb = tid; jb < njobs; jb += HM_THREADS) hm_job_decode(sm.t, sm.plan, sm.job_first, j, jb, sm.jobs[jb]);
+        if (njobs > 0)
+            __syncthreads();
+        if (warp == 0 && njobs > 0) {
+            if (lane == 0) { /* ring placement, in job order (FIFO): depends on the sizes only, never on timing */
+                int cur = 0;
+                for (int jb = 0; jb < njobs; jb++) {
+                    const int size = (int)sm.jobs[jb].nrows * hm_map_width(sm.jobs[jb].map);
+                    if (cur + size > HM_RING_BYTES)
+                        cur = 0;
+                    sm.jobs[jb].off128 = (uint16_t)(cur >> 7);
+                    cur += size;
+                }
+            }
+            __syncwarp();
+            for (int n = lane; n < njobs; n += 32) { /* ring dependencies (at most HM_NBAR jobs are in flight) */
+                const int off = (int)sm.jobs[n].off128 * 128, size = (int)sm.jobs[n].nrows * hm_map_width(sm.jobs[n].map);
+                int       dep = -1;
+                for (int k = max(0, n - (HM_NBAR - 1)); k < n; k++) {
+                    const int offk = (int)sm.jobs[k].off128 * 128, sizek = (int)sm.jobs[k].nrows * hm_map_width(sm.jobs[k].map);
+                    if (off < offk + sizek && offk < off + size)
+                        dep = k;
+                }
+                sm.jobs[n].dep = (int8_t)dep;
+            }
+            __syncwarp();
+            fetched = 0;
+        }
 #ifdef ME_HME_TRACE
         long long tr2 = clock64();
 #endif
         /* window jobs: the CTA searches job n while the TMA transfers of the following jobs are in flight */
-        const int njobs = search_stage ? sm.job_first[ME_SLOTS] : 0;
         {
             const uint32_t seq0 = seq;
 #ifdef ME_HME_TRACE
@@ -792,19 +798,17 @@ __global__ void __launch_bounds__(HM_THREADS, 5)
 #ifdef ME_HME_TRACE
                 const long long q0 = clock64();
 #endif
-                if (warp == 0 && jb > 0)
-                    hm_fetch_ahead(maps, sm.t, sm.plan, sm.job_first, sm.jobd, sm.mbar, hm_smem(raw0), j, njobs, seq0, jb, fetched,
-                                   head, lane);
+                if (tid == 0)
+                    hm_fetch_ahead(maps, sm.t, sm.jobs, sm.mbar, hm_smem(raw0), njobs, seq0, jb, fetched);
 #ifdef ME_HME_TRACE
                 const long long q1 = clock64();
 #endif
-                if (sm.fetched_pub[jb & 1] <= jb)
-                    __syncthreads(); /* the ring had no room to fetch this job ahead: warp 0 has just done it */
                 const uint32_t    slot = seq % HM_NBAR;
-                const HmJobD      J    = sm.jobd[slot];
+                const HmJobD      J    = sm.jobs[jb];
                 const SearchTask &t    = sm.t[J.task];
                 const HmPlan     &pl   = sm.plan[J.task];
-                const uint32_t   *raw  = reinterpret_cast<const uint32_t *>(raw0 + J.off);
+                const uint32_t   *raw  = reinterpret_cast<const uint32_t *>(raw0 + (size_t)J.off128 * 128);
+                __syncwarp();
                 hm_mbar_wait(hm_smem(&sm.mbar[slot]), (seq / HM_NBAR) & 1);
 #ifdef ME_HME_TRACE
                 const long long q2 = clock64();
@@ -813,17 +817,15 @@ __global__ void __launch_bounds__(HM_THREADS, 5)
                 const uint32_t *srcb = t.level == 2 ? sm.src2 : t.level == 1 ? sm.src1 : sm.src0;
                 const int       sp4  = (t.level == 2 ? HM_SRC2_PITCH : t.level == 1 ? HM_SRC1_PITCH : HM_SRC0_PITCH) / 4;
                 if (pl.kx == 4)
-                    key = hm_job_search<4>(J, t, pl.g_log2, raw, srcb, sp4, warp, lane);
+                    key = hm_job_search<4>(J, t, pl.g_log2, raw, srcb, sp4, (warp + jb) & (HM_WARPS - 1), lane);
                 else
-                    key = hm_job_search<2>(J, t, pl.g_log2, raw, srcb, sp4, warp, lane);
+                    key = hm_job_search<2>(J, t, pl.g_log2, raw, srcb, sp4, (warp + jb) & (HM_WARPS - 1), lane);
                 if (lane == 0)
                     atomicMin(&sm.tkey[J.task], key);
-                if (tid == 0)
-                    sm.fetched_pub[(jb + 1) & 1] = fetched;
 #ifdef ME_HME_TRACE
                 const long long q3 = clock64();
 #endif
-                __syncthreads(); /* the window's ring space is free again */
+                __syncthreads(); /* the window's ring bytes are free again */
 #ifdef ME_HME_TRACE
                 tj_fetch += q1 - q0; tj_wait += q2 - q1; tj_comp += q3 - q2; tj_bar += clock64() - q3;
 #endif
