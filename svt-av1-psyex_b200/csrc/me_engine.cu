@@ -653,8 +653,10 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
         me_launch_hme(jc->d_job, 1, nbi, jc->d_list, d.pool, maps, st);
         pend();
         if (prof) CU(cudaEventRecord(jc->ev[1], st));
+        static const int skip = getenv("ME_GPU_SKIP") ? atoi(getenv("ME_GPU_SKIP")) : 0; /* timing experiments only: results wrong */
         pbegin(3);
-        me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, d.sms * 2, st);
+        if (!(skip & 1))
+            me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, d.sms * 2, st);
         pend();
     } else {
         const bool zz   = p.me_early_exit_th || p.me_safe_limit_zz_th;
@@ -706,7 +708,9 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
     }
     if (prof) CU(cudaEventRecord(jc->ev[2], st));
     pbegin(4);
-    me_launch_epilogue(jc->d_job, 1, nbi, st);
+    static const int skip_epi = getenv("ME_GPU_SKIP") ? atoi(getenv("ME_GPU_SKIP")) & 2 : 0; /* timing experiments only */
+    if (!skip_epi)
+        me_launch_epilogue(jc->d_job, 1, nbi, st);
     pend();
     if (prof) CU(cudaEventRecord(jc->ev[3], st));
     CU(cudaGetLastError());

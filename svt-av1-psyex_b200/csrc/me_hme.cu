@@ -27,12 +27,14 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "me_ctrl.h"
 #include "me_kernels.h"
 
 #define HM_WARPS 4
-#define HM_THREADS (HM_WARPS * 32)
+#define HM_THREADS (HM_WARPS * 32) /* search threads */
+#define HM_ALL_THREADS (HM_THREADS + 32) /* + the warp that requests the windows (TMA) */
 #define HM_BUF_WORDS 2048 /* per-warp staging buffer: source block (<= 512 words) + reference window (15 rows x
                              131 words of the widest pre-HME strip fit; taller windows are banded) */
 #define FS_WARP_MAX 256 /* search areas up to this many positions (and <= FS_WARP_MAXW wide) stay in k_hme */
@@ -51,7 +53,7 @@
 struct HmPlan { /* how a task is cut into jobs (written by warp 0 at the start of a stage) */
     int16_t pwb, neb; /* positions per x band, evaluated rows per y band */
     uint8_t nxb, nyb, map, kx;
-    uint8_t g_log2, new_path, pad_[2];
+    uint8_t g_log2, new_path, small /* few units: one warp searches the job */, win128 /* window bytes / 128 */;
 };
 
 struct HmJobD { /* one window job, 32 bytes */
@@ -77,6 +79,7 @@ struct HmeShared {
     int                item_first[ME_SLOTS + 1]; /* prefix sums: items of task i are [first[i], first[i+1]) */
     int                item_rows[ME_SLOTS]; /* search rows per item */
     int                next_item;
+    int                warp_mode; /* this stage's window jobs are searched one per warp, four at a time */
     HmPlan             plan[ME_SLOTS];
     int                job_first[ME_SLOTS + 1]; /* prefix sums of the window jobs */
     alignas(8) unsigned long long mbar[HM_NBAR]; /* TMA completion of the windows in flight */
@@ -367,14 +370,20 @@ __device__ void hm_plan_task(const SearchTask &t, const MeJob *j, int org_x, int
     const int ne_max   = (rows_cap - span - 1) / ymul + 1;
     if (rows_cap < span + 1 || ne_max < 1 || nxb > 255)
         return;
+    const int kx      = (t.bw == 16 && pwb >= 16) ? 4 : 2;
+    const int ncls    = min(4, pwb), per_cls = (pwb + 3) >> 2, nchunk = (per_cls + kx - 1) / kx;
     const int nyb = (erows + ne_max - 1) / ne_max, neb = (erows + nyb - 1) / nyb;
     if (nyb > 255)
         return;
-    const int kx      = (t.bw == 16 && pwb >= 16) ? 4 : 2;
-    const int ncls    = min(4, pwb), per_cls = (pwb + 3) >> 2, nchunk = (per_cls + kx - 1) / kx;
     const int units   = ncls * nchunk * neb;
+    const int win     = pitch * (((neb - 1) * ymul + span + 1 + hm_map_rows(map) - 1) / hm_map_rows(map) * hm_map_rows(map));
+    /* few units and a window of which four fit the ring: the job is searched by ONE warp (four jobs at a time per CTA) */
+    pl.small  = units <= 16 && win <= HM_RING_BYTES / 4;
+    pl.win128 = (uint8_t)min(255, win >> 7);
     int       g_log2  = 2 - lv; /* lanes per unit: the 16-byte column segments of the block row ... */
-    while (g_log2 < 5 && (units << g_log2) < 96 && ((2 << g_log2) >> (2 - lv)) <= (int)t.rows) g_log2++; /* ... x row groups */
+    while (g_log2 < 5 && (pl.small ? (units << (g_log2 + 1)) <= 32 : (units << g_log2) < 96) &&
+           ((2 << g_log2) >> (2 - lv)) <= (int)t.rows)
+        g_log2++; /* ... x row groups: up to a warp's (small job) or most of a CTA's worth of lanes */
     pl.pwb = (int16_t)pwb;
     pl.neb = (int16_t)neb;
     pl.nxb = (uint8_t)nxb;
@@ -430,7 +439,6 @@ __device__ __forceinline__ void hm_fetch_ahead(const HmeMaps &maps, const Search
         const HmJobD  &Jn  = jobs[fetched];
         const uint32_t bar = hm_smem(&full[(seq0 + (uint32_t)fetched) % HM_NBAR]);
         const int      pitch = hm_map_width(Jn.map), off = (int)Jn.off128 * 128, br = hm_map_rows(Jn.map);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); /* earlier generic accesses to the ring come first */
         hm_mbar_expect(bar, (uint32_t)((int)Jn.nrows * pitch));
         for (int y = 0; y < (int)Jn.nrows; y += br)
             hm_tma_box(ring + (uint32_t)(off + y * pitch), maps.m[Jn.map], Jn.xt, Jn.y0 + y, tasks[Jn.task].ref_slot, bar);
@@ -443,7 +451,7 @@ __device__ __forceinline__ void hm_fetch_ahead(const HmeMaps &maps, const Search
  * them, adjacent lanes -> adjacent banks) times row groups; partial sums are joined by shuffles. */
 template <int KX>
 __device__ __forceinline__ unsigned long long hm_job_search(const HmJobD &J, const SearchTask &t, int g_log2, const uint32_t *raw,
-                                                            const uint32_t *src, int src_pitch4, int warp, int lane) {
+                                                            const uint32_t *src, int src_pitch4, int warp, int nthr, int lane) {
     const bool skip = t.bw == 16 && t.rows <= 16 && t.skip_line;
     const int  ymul = skip ? 2 : 1, rows = t.rows, step = t.row_step;
     const int  pitchw = hm_map_width(J.map) >> 2, G = 1 << g_log2;
@@ -451,7 +459,7 @@ __device__ __forceinline__ unsigned long long hm_job_search(const HmJobD &J, con
     const int  ncls = J.ncls, nchunk = J.nchunk, total = J.total;
     const uint32_t m_chunk = J.m_chunk, m_cls = J.m_cls;
     unsigned long long key = ((unsigned long long)ME_SAD_LOOP_INIT << 32) | 0xFFFFFFFFull;
-    for (int base = warp * 32; base < total; base += HM_THREADS) {
+    for (int base = warp * 32; base < total; base += nthr) {
         const int  u  = base + lane;
         const bool on = u < total;
         const int  g = u & (G - 1), v = u >> g_log2;
@@ -627,13 +635,15 @@ __device__ void hm_emit_tiles(const FsTask &f, FsTileList *list, uint32_t task, 
 /* ------------------------------------------------------------------------------------------------
  * k_hme
  * ---------------------------------------------------------------------------------------------- */
-__global__ void __launch_bounds__(HM_THREADS, 5)
+__global__ void __launch_bounds__(HM_ALL_THREADS, 5)
     k_hme(MeJob *jobs, FsTileList *list, const uint8_t *pool, const __grid_constant__ HmeMaps maps) {
     extern __shared__ __align__(1024) unsigned char hm_raw[];
     HmeShared     &sm  = *reinterpret_cast<HmeShared *>(hm_raw);
     MeJob         *j   = &jobs[blockIdx.y];
     const int      b   = blockIdx.x;
-    const int      tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int      lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool     producer = warp == HM_WARPS; /* warp 4 only requests windows; it takes no part in strided loops */
+    const int      tid = producer ? (1 << 28) : (int)threadIdx.x;
     unsigned long long *keys = &j->keys[(size_t)b * ME_NREF * ME_NPU];
     const unsigned long long none = ((unsigned long long)ME_SAD_LOOP_INIT << 32) | 0xFFFFFFFFull;
 
@@ -680,11 +690,15 @@ __global__ void __launch_bounds__(HM_THREADS, 5)
     __syncthreads();
     uint32_t  seq  = 0; /* window jobs so far: job n uses mbarrier n % HM_NBAR, parity (n / HM_NBAR) & 1 */
     uint8_t  *raw0 = reinterpret_cast<uint8_t *>(&sm.buf[0][0]);
-    int       fetched = 0; /* warp 0: jobs of the stage whose windows have been requested */
+    int       fetched = 0; /* producer: jobs of the stage whose windows have been requested */
 
 #ifdef ME_HME_TRACE
     long long tr[ST_COUNT][4];
     long long t_begin = clock64();
+    unsigned long long gt_begin, gt_stage[ST_COUNT];
+    unsigned smid;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_begin));
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
 #endif
     for (int st = 0; st < ST_COUNT; st++) {
 #ifdef ME_HME_TRACE
@@ -731,6 +745,10 @@ __global__ void __launch_bounds__(HM_THREADS, 5)
                 }
                 if (pl.new_path)
                     n = 0;
+                /* warp mode: every window job of the stage is small */
+                const unsigned big = __ballot_sync(0xffffffffu, pl.new_path && !pl.small);
+                if (lane == 0)
+                    sm.warp_mode = big == 0;
                 sm.plan[lane]          = pl;
                 sm.job_first[lane + 1] = inclj;
                 sm.tkey[lane]          = none;
@@ -760,16 +778,30 @@ __global__ void __launch_bounds__(HM_THREADS, 5)
         for (int jb = tid; jb < njobs; jb += HM_THREADS) hm_job_decode(sm.t, sm.plan, sm.job_first, j, jb, sm.jobs[jb]);
         if (njobs > 0)
             __syncthreads();
-        if (warp == 0 && njobs > 0) {
+        if (producer && njobs > 0) {
             if (lane == 0) { /* ring placement, in job order (FIFO): depends on the sizes only, never on timing */
                 int cur = 0;
-                for (int jb = 0; jb < njobs; jb++) {
-                    const int size = (int)sm.jobs[jb].nrows * hm_map_width(sm.jobs[jb].map);
-                    if (cur + size > HM_RING_BYTES)
-                        cur = 0;
-                    sm.jobs[jb].off128 = (uint16_t)(cur >> 7);
-                    cur += size;
-                }
+                if (sm.warp_mode) {
+                    /* the four jobs of a batch are searched together: batches alternate between the ring halves when
+                       they fit one, else every batch starts at 0 (then the next batch is fetched after this one) */
+                    for (int jb0 = 0; jb0 < njobs; jb0 += HM_WARPS) {
+                        int bytes = 0;
+                        for (int jb = jb0; jb < min(njobs, jb0 + HM_WARPS); jb++)
+                            bytes += (int)sm.jobs[jb].nrows * hm_map_width(sm.jobs[jb].map);
+                        cur = (bytes <= HM_RING_BYTES / 2 && ((jb0 / HM_WARPS) & 1)) ? HM_RING_BYTES / 2 : 0;
+                        for (int jb = jb0; jb < min(njobs, jb0 + HM_WARPS); jb++) {
+                            sm.jobs[jb].off128 = (uint16_t)(cur >> 7);
+                            cur += (int)sm.jobs[jb].nrows * hm_map_width(sm.jobs[jb].map);
+                        }
+                    }
+                } else
+                    for (int jb = 0; jb < njobs; jb++) {
+                        const int size = (int)sm.jobs[jb].nrows * hm_map_width(sm.jobs[jb].map);
+                        if (cur + size > HM_RING_BYTES)
+                            cur = 0;
+                        sm.jobs[jb].off128 = (uint16_t)(cur >> 7);
+                        cur += size;
+                    }
             }
             __syncwarp();
             for (int n = lane; n < njobs; n += 32) { /* ring dependencies (at most HM_NBAR jobs are in flight) */
@@ -783,61 +815,53 @@ __global__ void __launch_bounds__(HM_THREADS, 5)
                 sm.jobs[n].dep = (int8_t)dep;
             }
             __syncwarp();
-            fetched = 0;
         }
+        fetched = 0;
 #ifdef ME_HME_TRACE
         long long tr2 = clock64();
 #endif
-        /* window jobs: the CTA searches job n while the TMA transfers of the following jobs are in flight */
+        /* window jobs, searched while the TMA transfers of the following jobs are in flight: large jobs by the whole
+           CTA one after the other, small ones by one warp each, four at a time */
         {
             const uint32_t seq0 = seq;
-#ifdef ME_HME_TRACE
-            long long tj_fetch = 0, tj_wait = 0, tj_comp = 0, tj_bar = 0;
-#endif
-            for (int jb = 0; jb < njobs; jb++, seq++) {
-#ifdef ME_HME_TRACE
-                const long long q0 = clock64();
-#endif
-                if (tid == 0)
-                    hm_fetch_ahead(maps, sm.t, sm.jobs, sm.mbar, hm_smem(raw0), njobs, seq0, jb, fetched);
-#ifdef ME_HME_TRACE
-                const long long q1 = clock64();
-#endif
-                const uint32_t    slot = seq % HM_NBAR;
-                const HmJobD      J    = sm.jobs[jb];
-                const SearchTask &t    = sm.t[J.task];
-                const HmPlan     &pl   = sm.plan[J.task];
-                const uint32_t   *raw  = reinterpret_cast<const uint32_t *>(raw0 + (size_t)J.off128 * 128);
-                __syncwarp();
-                hm_mbar_wait(hm_smem(&sm.mbar[slot]), (seq / HM_NBAR) & 1);
-#ifdef ME_HME_TRACE
-                const long long q2 = clock64();
-#endif
-                unsigned long long key;
-                const uint32_t *srcb = t.level == 2 ? sm.src2 : t.level == 1 ? sm.src1 : sm.src0;
-                const int       sp4  = (t.level == 2 ? HM_SRC2_PITCH : t.level == 1 ? HM_SRC1_PITCH : HM_SRC0_PITCH) / 4;
-                if (pl.kx == 4)
-                    key = hm_job_search<4>(J, t, pl.g_log2, raw, srcb, sp4, (warp + jb) & (HM_WARPS - 1), lane);
-                else
-                    key = hm_job_search<2>(J, t, pl.g_log2, raw, srcb, sp4, (warp + jb) & (HM_WARPS - 1), lane);
-                if (lane == 0)
-                    atomicMin(&sm.tkey[J.task], key);
-#ifdef ME_HME_TRACE
-                const long long q3 = clock64();
-#endif
-                __syncthreads(); /* the window's ring bytes are free again */
-#ifdef ME_HME_TRACE
-                tj_fetch += q1 - q0; tj_wait += q2 - q1; tj_comp += q3 - q2; tj_bar += clock64() - q3;
-#endif
+            const bool     wmode = njobs > 0 && sm.warp_mode != 0;
+            const int      per_iter = wmode ? HM_WARPS : 1;
+            for (int jb0 = 0; jb0 < njobs; jb0 += per_iter) {
+                if (producer) {
+                    if (lane == 0) {
+                        if (jb0 == 0) /* generic-proxy accesses to the ring (per-warp path of earlier stages) come first */
+                            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                        hm_fetch_ahead(maps, sm.t, sm.jobs, sm.mbar, hm_smem(raw0), njobs, seq0, jb0, fetched);
+                    }
+                    __syncthreads();
+                    continue;
+                }
+                const int jb = wmode ? jb0 + warp : jb0;
+                if (jb < njobs) {
+                    const uint32_t    slot = (seq0 + (uint32_t)jb) % HM_NBAR, par = ((seq0 + (uint32_t)jb) / HM_NBAR) & 1;
+                    __syncwarp();
+                    hm_mbar_wait(hm_smem(&sm.mbar[slot]), par); /* also orders the producer's ring placement before the read */
+                    const HmJobD      J    = sm.jobs[jb];
+                    const SearchTask &t    = sm.t[J.task];
+                    const HmPlan     &pl   = sm.plan[J.task];
+                    const uint32_t   *raw  = reinterpret_cast<const uint32_t *>(raw0 + (size_t)J.off128 * 128);
+                    const uint32_t   *srcb = t.level == 2 ? sm.src2 : t.level == 1 ? sm.src1 : sm.src0;
+                    const int sp4 = (t.level == 2 ? HM_SRC2_PITCH : t.level == 1 ? HM_SRC1_PITCH : HM_SRC0_PITCH) / 4;
+                    const int widx = wmode ? 0 : (warp + jb) & (HM_WARPS - 1), nthr = wmode ? 32 : HM_THREADS;
+                    unsigned long long key;
+                    if (pl.kx == 4)
+                        key = hm_job_search<4>(J, t, pl.g_log2, raw, srcb, sp4, widx, nthr, lane);
+                    else
+                        key = hm_job_search<2>(J, t, pl.g_log2, raw, srcb, sp4, widx, nthr, lane);
+                    if (lane == 0)
+                        atomicMin(&sm.tkey[J.task], key);
+                }
+                __syncthreads(); /* the windows' ring bytes are free again */
             }
-#ifdef ME_HME_TRACE
-            if (blockIdx.y == 0 && b == 100 && (tid == 0 || tid == 96) && njobs)
-                printf("b %d tid %d st %d jobs %d: fetch %lld wait %lld compute %lld barrier %lld\n", b, tid, st, njobs, tj_fetch, tj_wait,
-                       tj_comp, tj_bar);
-#endif
+            seq += (uint32_t)njobs;
         }
         const int total = sm.item_first[ME_SLOTS];
-        for (;;) {
+        for (; !producer;) {
             int it = 0;
             if (lane == 0)
                 it = atomicAdd(&sm.next_item, 1);
@@ -876,7 +900,7 @@ __global__ void __launch_bounds__(HM_THREADS, 5)
 #ifdef ME_HME_TRACE
         long long tr3 = clock64();
         tr[st][0] = tr1 - tr0; tr[st][1] = tr2 - tr1; tr[st][2] = tr3 - tr2; tr[st][3] = tr3w - tr2;
-        if (tid == 0 && blockIdx.y == 0 && (b == 100 || b == 300)) printf("b %d st %d items %d\n", b, st, total);
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_stage[st]));
 #endif
         if (search_stage && tid < ME_SLOTS && sm.t[tid].valid) {
             /* key -> what the callers of svt_sad_loop_kernel see */
@@ -898,12 +922,16 @@ __global__ void __launch_bounds__(HM_THREADS, 5)
         __syncthreads();
     }
 #ifdef ME_HME_TRACE
-    if (blockIdx.y == 0 && (b == 100 || b == 300) && (tid == 0 || tid == 96)) {
+    if (0 && blockIdx.y == 0 && (b == 100 || b == 300) && (tid == 0 || tid == 96)) {
         for (int st = 0; st < ST_COUNT; st++)
             printf("b %d tid %d stage %d: ctrl %lld partition %lld items+barrier %lld (own items %lld) cycles\n", b, tid, st,
                    tr[st][0], tr[st][1], tr[st][2], tr[st][3]);
         printf("b %d tid %d total %lld cycles\n", b, tid, clock64() - t_begin);
     }
+    if (tid == 0)
+        printf("CTA %d sm %u t0 %llu st %llu %llu %llu %llu %llu %llu %llu %llu %llu\n", b, smid, gt_begin, gt_stage[0] - gt_begin,
+               gt_stage[1] - gt_begin, gt_stage[2] - gt_begin, gt_stage[3] - gt_begin, gt_stage[4] - gt_begin, gt_stage[5] - gt_begin,
+               gt_stage[6] - gt_begin, gt_stage[7] - gt_begin, gt_stage[8] - gt_begin);
 #endif
     /* the epilogue (after the tiled searches) continues from the state in HBM */
     {
@@ -917,7 +945,7 @@ static unsigned long long g_hme_launches = 0;
 unsigned long long me_hme_launch_count(void) { return g_hme_launches; }
 
 cudaError_t me_hme_setup(void) {
-    return cudaFuncSetAttribute(k_hme, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HmeShared));
+    return cudaFuncSetAttribute(k_hme, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HmeShared) + 65536);
 }
 
 /* tensor maps of the pool's planes for pictures of geometry g (TMA: rank 3 = byte column, row, pool slot) */
@@ -948,6 +976,7 @@ int me_hme_make_maps(HmeMaps *maps, const uint8_t *pool, const MePicGeom *g, int
 void me_launch_hme(MeJob *jobs, int njobs, int max_b64, FsTileList *list, const uint8_t *pool, const HmeMaps *maps,
                    cudaStream_t st) {
     dim3 grid(max_b64, njobs);
-    k_hme<<<grid, HM_THREADS, sizeof(HmeShared), st>>>(jobs, list, pool, *maps);
+    static const int extra = getenv("ME_HME_EXTRA_SMEM") ? atoi(getenv("ME_HME_EXTRA_SMEM")) : 0; /* occupancy experiments */
+    k_hme<<<grid, HM_ALL_THREADS, sizeof(HmeShared) + extra, st>>>(jobs, list, pool, *maps);
     g_hme_launches++;
 }
