@@ -53,7 +53,7 @@
 struct HmPlan { /* how a task is cut into jobs (written by warp 0 at the start of a stage) */
     int16_t pwb, neb; /* positions per x band, evaluated rows per y band */
     uint8_t nxb, nyb, map, kx;
-    uint8_t g_log2, new_path, small /* few units: one warp searches the job */, win128 /* window bytes / 128 */;
+    uint8_t g_log2, new_path, team /* warps that search a job: 1 or 2 for jobs of few units, else 4 */, pad_;
 };
 
 struct HmJobD { /* one window job, 32 bytes */
@@ -70,6 +70,10 @@ struct HmJobD { /* one window job, 32 bytes */
 #define HM_NBAR 8 /* window jobs in flight (ring of job descriptors and mbarriers) */
 #define HM_RING_BYTES (2 * HM_RAW_BYTES)
 
+#ifdef ME_HME_TRACE
+__device__ unsigned g_trace_cnt;
+#endif
+
 struct HmeShared {
     B64State           s;
     SearchTask         t[ME_SLOTS];
@@ -79,7 +83,7 @@ struct HmeShared {
     int                item_first[ME_SLOTS + 1]; /* prefix sums: items of task i are [first[i], first[i+1]) */
     int                item_rows[ME_SLOTS]; /* search rows per item */
     int                next_item;
-    int                warp_mode; /* this stage's window jobs are searched one per warp, four at a time */
+    int                team; /* warps per window job in this stage (4 / team jobs are searched at a time) */
     HmPlan             plan[ME_SLOTS];
     int                job_first[ME_SLOTS + 1]; /* prefix sums of the window jobs */
     alignas(8) unsigned long long mbar[HM_NBAR]; /* TMA completion of the windows in flight */
@@ -377,13 +381,13 @@ __device__ void hm_plan_task(const SearchTask &t, const MeJob *j, int org_x, int
         return;
     const int units   = ncls * nchunk * neb;
     const int win     = pitch * (((neb - 1) * ymul + span + 1 + hm_map_rows(map) - 1) / hm_map_rows(map) * hm_map_rows(map));
-    /* few units and a window of which four fit the ring: the job is searched by ONE warp (four jobs at a time per CTA) */
-    pl.small  = units <= 16 && win <= HM_RING_BYTES / 4;
-    pl.win128 = (uint8_t)min(255, win >> 7);
-    int       g_log2  = 2 - lv; /* lanes per unit: the 16-byte column segments of the block row ... */
-    while (g_log2 < 5 && (pl.small ? (units << (g_log2 + 1)) <= 32 : (units << g_log2) < 96) &&
+    /* jobs of few units are searched by one warp each, four at a time per CTA, when four windows fit the ring (measured:
+       two warps per job with the next batch in flight is slower than one warp per job and no prefetch of the next batch) */
+    pl.team = (uint8_t)(units <= 16 && win <= HM_RING_BYTES / 4 ? 1 : 4);
+    int g_log2 = 2 - lv; /* lanes per unit: the 16-byte column segments of the block row ... */
+    while (g_log2 < 5 && (pl.team < 4 ? (units << (g_log2 + 1)) <= 32 * pl.team : (units << g_log2) < 96) &&
            ((2 << g_log2) >> (2 - lv)) <= (int)t.rows)
-        g_log2++; /* ... x row groups: up to a warp's (small job) or most of a CTA's worth of lanes */
+        g_log2++; /* ... x row groups: up to the team's worth of lanes */
     pl.pwb = (int16_t)pwb;
     pl.neb = (int16_t)neb;
     pl.nxb = (uint8_t)nxb;
@@ -745,10 +749,10 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
                 }
                 if (pl.new_path)
                     n = 0;
-                /* warp mode: every window job of the stage is small */
-                const unsigned big = __ballot_sync(0xffffffffu, pl.new_path && !pl.small);
+                /* warps per job in this stage: the largest team any of its window jobs needs */
+                const int team = __reduce_max_sync(0xffffffffu, pl.new_path ? (int)pl.team : 1);
                 if (lane == 0)
-                    sm.warp_mode = big == 0;
+                    sm.team = team;
                 sm.plan[lane]          = pl;
                 sm.job_first[lane + 1] = inclj;
                 sm.tkey[lane]          = none;
@@ -781,15 +785,16 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
         if (producer && njobs > 0) {
             if (lane == 0) { /* ring placement, in job order (FIFO): depends on the sizes only, never on timing */
                 int cur = 0;
-                if (sm.warp_mode) {
-                    /* the four jobs of a batch are searched together: batches alternate between the ring halves when
-                       they fit one, else every batch starts at 0 (then the next batch is fetched after this one) */
-                    for (int jb0 = 0; jb0 < njobs; jb0 += HM_WARPS) {
+                if (sm.team < HM_WARPS) {
+                    /* the jobs of a batch are searched together: batches alternate between the ring halves when they
+                       fit one, else every batch starts at 0 (then the next batch is fetched after this one) */
+                    const int per = HM_WARPS / sm.team;
+                    for (int jb0 = 0; jb0 < njobs; jb0 += per) {
                         int bytes = 0;
-                        for (int jb = jb0; jb < min(njobs, jb0 + HM_WARPS); jb++)
+                        for (int jb = jb0; jb < min(njobs, jb0 + per); jb++)
                             bytes += (int)sm.jobs[jb].nrows * hm_map_width(sm.jobs[jb].map);
-                        cur = (bytes <= HM_RING_BYTES / 2 && ((jb0 / HM_WARPS) & 1)) ? HM_RING_BYTES / 2 : 0;
-                        for (int jb = jb0; jb < min(njobs, jb0 + HM_WARPS); jb++) {
+                        cur = (bytes <= HM_RING_BYTES / 2 && ((jb0 / per) & 1)) ? HM_RING_BYTES / 2 : 0;
+                        for (int jb = jb0; jb < min(njobs, jb0 + per); jb++) {
                             sm.jobs[jb].off128 = (uint16_t)(cur >> 7);
                             cur += (int)sm.jobs[jb].nrows * hm_map_width(sm.jobs[jb].map);
                         }
@@ -824,8 +829,7 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
            CTA one after the other, small ones by one warp each, four at a time */
         {
             const uint32_t seq0 = seq;
-            const bool     wmode = njobs > 0 && sm.warp_mode != 0;
-            const int      per_iter = wmode ? HM_WARPS : 1;
+            const int      team = njobs > 0 ? sm.team : HM_WARPS, per_iter = HM_WARPS / team;
             for (int jb0 = 0; jb0 < njobs; jb0 += per_iter) {
                 if (producer) {
                     if (lane == 0) {
@@ -836,7 +840,7 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
                     __syncthreads();
                     continue;
                 }
-                const int jb = wmode ? jb0 + warp : jb0;
+                const int jb = jb0 + warp / team;
                 if (jb < njobs) {
                     const uint32_t    slot = (seq0 + (uint32_t)jb) % HM_NBAR, par = ((seq0 + (uint32_t)jb) / HM_NBAR) & 1;
                     __syncwarp();
@@ -847,7 +851,7 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
                     const uint32_t   *raw  = reinterpret_cast<const uint32_t *>(raw0 + (size_t)J.off128 * 128);
                     const uint32_t   *srcb = t.level == 2 ? sm.src2 : t.level == 1 ? sm.src1 : sm.src0;
                     const int sp4 = (t.level == 2 ? HM_SRC2_PITCH : t.level == 1 ? HM_SRC1_PITCH : HM_SRC0_PITCH) / 4;
-                    const int widx = wmode ? 0 : (warp + jb) & (HM_WARPS - 1), nthr = wmode ? 32 : HM_THREADS;
+                    const int widx = team == HM_WARPS ? (warp + jb) & (HM_WARPS - 1) : warp % team, nthr = 32 * team;
                     unsigned long long key;
                     if (pl.kx == 4)
                         key = hm_job_search<4>(J, t, pl.g_log2, raw, srcb, sp4, widx, nthr, lane);
@@ -927,6 +931,10 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
             printf("b %d tid %d stage %d: ctrl %lld partition %lld items+barrier %lld (own items %lld) cycles\n", b, tid, st,
                    tr[st][0], tr[st][1], tr[st][2], tr[st][3]);
         printf("b %d tid %d total %lld cycles\n", b, tid, clock64() - t_begin);
+    }
+    if (tid == 0) { /* print only once every CTA of the launch is past its last stage (bounded wait): printf stalls the SM */
+        const unsigned old = atomicAdd(&g_trace_cnt, 1u), target = (old / gridDim.x + 1u) * gridDim.x;
+        for (int spin = 0; spin < 4000000 && *(volatile unsigned *)&g_trace_cnt < target; spin++) __nanosleep(100);
     }
     if (tid == 0)
         printf("CTA %d sm %u t0 %llu st %llu %llu %llu %llu %llu %llu %llu %llu %llu\n", b, smid, gt_begin, gt_stage[0] - gt_begin,

@@ -472,13 +472,20 @@ __global__ void __launch_bounds__(FS_THREADS, 2) k_fullsearch(MeJob *jobs, FsTil
 #define EP_THREADS 96
 __global__ void __launch_bounds__(EP_THREADS) k_epilogue(MeJob *jobs) {
     __shared__ uint32_t best_sad[ME_NREF][ME_NPU], best_mv[ME_NREF][ME_NPU], me_distortion[ME_NPU];
+    __shared__ B64State st; /* the block's state (HBM, written by k_hme): every later access is a shared-memory one */
     MeJob         *j = &jobs[blockIdx.y];
     const uint32_t b = blockIdx.x;
     const int      tid = threadIdx.x;
+    {
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(&j->state[b]);
+        uint32_t       *dst = reinterpret_cast<uint32_t *>(&st);
+        for (int i = tid; i < (int)(sizeof(B64State) / 4); i += EP_THREADS) dst[i] = src[i];
+    }
+    __syncthreads();
     EpiCtx         e;
     e.j    = j;
     e.p    = &j->p;
-    e.s    = &j->state[b];
+    e.s    = &st;
     e.keys = &j->keys[(size_t)b * ME_NREF * ME_NPU];
     e.b    = b;
     const int org_x = (int)(b % (uint32_t)j->g.b64_cols) * 64, org_y = (int)(b / (uint32_t)j->g.b64_cols) * 64;
