@@ -66,7 +66,7 @@ struct HmJobD { /* one window job, 32 bytes */
     int8_t   dep; /* last earlier job of the stage whose window overlaps this one (-1: none) */
     uint32_t m_chunk, m_cls;
 };
-#define HM_MAXJOBS 48 /* window jobs per stage; tasks beyond go to the per-warp path */
+#define HM_MAXJOBS 32 /* window jobs per stage; tasks beyond go to the per-warp path */
 #define HM_NBAR 8 /* window jobs in flight (ring of job descriptors and mbarriers) */
 #define HM_RING_BYTES (2 * HM_RAW_BYTES)
 
