@@ -96,3 +96,41 @@ def test_me_parity_1080p_sample(engine, oracle, preset, poc, kind, first, count)
             mask[1, :len(l1)] = True
             a, b = a[:, mask], b[:, mask]
         assert np.array_equal(a, b), name
+
+
+def test_me_parity_odd_size(engine, oracle):
+    """Width and height that are not multiples of 64 (partial b64s on both edges: the per-warp search path)."""
+    w, h, n, preset, poc = 136, 72, 9, 4, 4
+    ps = PictureSet(w, h, n, "motion", oracle)
+    cfg, p, l0, l1 = derive(preset, w, h, poc, n)
+    pocs = sorted(set([poc] + l0 + l1))
+    _register(engine, ps, pocs)
+    try:
+        got = engine.me_picture(poc, w, h, p, [l0, l1])
+    finally:
+        _release(engine, pocs)
+    exp = oracle.me_picture(ps.get(poc), [[ps.get(k) for k in l0], [ps.get(k) for k in l1]], p)
+    bad = planes.compare_outputs(exp, got, used_refs=used_refs(l0, l1))
+    assert not bad, bad
+
+
+def test_pictures_in_flight_out_of_order(engine, oracle):
+    """Several pictures submitted before any wait, waited for in another order (job contexts, streams, result slabs)."""
+    w, h, n, preset = 320, 192, 17, 4
+    ps = PictureSet(w, h, n, "motion", oracle)
+    jobs = {poc: derive(preset, w, h, poc, n) for poc in (16, 8, 4, 12, 2)}
+    pocs = sorted(set(k for poc, (_, _, l0, l1) in jobs.items() for k in [poc] + l0 + l1))
+    _register(engine, ps, pocs)
+    try:
+        for poc, (_, p, l0, l1) in jobs.items():
+            engine.submit(poc, p, [l0, l1])
+        got = {}
+        for poc in (4, 2, 16, 12, 8):
+            got[poc] = planes.Outputs(w, h, jobs[poc][1])
+            engine.wait(poc, got[poc])
+    finally:
+        _release(engine, pocs)
+    for poc, (_, p, l0, l1) in jobs.items():
+        exp = oracle.me_picture(ps.get(poc), [[ps.get(k) for k in l0], [ps.get(k) for k in l1]], p)
+        bad = planes.compare_outputs(exp, got[poc], used_refs=used_refs(l0, l1))
+        assert not bad, (poc, bad)

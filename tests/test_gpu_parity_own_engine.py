@@ -1,0 +1,75 @@
+"""GPU parity cases that need an engine of their own (the C-ABI holds one engine per process: these run after the
+module-scoped engine of test_gpu_parity.py has been shut down): 4K geometry, two devices in one process."""
+import numpy as np
+import pytest
+
+from helpers import PictureSet, derive, used_refs
+from me_b200 import planes
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def oracle():
+    from me_b200.checkers import Oracle
+    return Oracle()
+
+
+def _register(engine, ps, pocs):
+    for k in pocs:
+        engine.register_picture(k, ps.get(k).planes[0], ps.w, ps.h)
+
+
+@pytest.mark.parametrize("preset,poc,first,count", [(4, 8, 1000, 6), (2, 4, 2039, 1)])
+def test_me_parity_4k_sample(oracle, preset, poc, first, count):
+    """BASELINE configs[2] geometry (3840x2160, 2040 b64): whole picture on the GPU, a few b64s on the oracle."""
+    from me_b200.engine import Engine
+    w, h, n = 3840, 2160, 17
+    ps = PictureSet(w, h, n, "motion", oracle)
+    cfg, p, l0, l1 = derive(preset, w, h, poc, n)
+    pocs = sorted(set([poc] + l0 + l1))
+    eng = Engine(w, h, 4, 3, pictures_in_flight=8)
+    try:
+        _register(eng, ps, pocs)
+        got = eng.me_picture(poc, w, h, p, [l0, l1])
+    finally:
+        eng.close()
+    exp = oracle.me_picture(ps.get(poc), [[ps.get(k) for k in l0], [ps.get(k) for k in l1]], p, first, count)
+    for name in exp.arrays:
+        a, b = exp.arrays[name][first:first + count], got.arrays[name][first:first + count]
+        if name in planes.DEBUG_FIELDS:
+            mask = np.zeros((2, 4), dtype=bool)
+            mask[0, :len(l0)] = True
+            mask[1, :len(l1)] = True
+            a, b = a[:, mask], b[:, mask]
+        assert np.array_equal(a, b), name
+
+
+def test_two_devices_in_one_process(oracle):
+    """me_gpu_init over two devices: pyramids replicated over NVLink, jobs dealt round-robin, results identical."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from me_b200.engine import Engine
+    w, h, n, preset = 320, 192, 17, 4
+    ps = PictureSet(w, h, n, "motion", oracle)
+    jobs = {poc: derive(preset, w, h, poc, n) for poc in (16, 8, 4, 12)}
+    pocs = sorted(set(k for poc, (_, _, l0, l1) in jobs.items() for k in [poc] + l0 + l1))
+    eng = Engine(w, h, 4, 3, pictures_in_flight=24, devices=[0, 1])
+    try:
+        _register(eng, ps, pocs)
+        pyr = eng.read_pyramid(pocs[0], w, h)  # read from the LAST device: the replica
+        for lvl in range(3):
+            assert np.array_equal(pyr[lvl], ps.get(pocs[0]).planes[lvl]), lvl
+        for poc, (_, p, l0, l1) in jobs.items():
+            eng.submit(poc, p, [l0, l1])
+        got = {}
+        for poc in jobs:
+            got[poc] = planes.Outputs(w, h, jobs[poc][1])
+            eng.wait(poc, got[poc])
+    finally:
+        eng.close()
+    for poc, (_, p, l0, l1) in jobs.items():
+        exp = oracle.me_picture(ps.get(poc), [[ps.get(k) for k in l0], [ps.get(k) for k in l1]], p)
+        bad = planes.compare_outputs(exp, got[poc], used_refs=used_refs(l0, l1))
+        assert not bad, (poc, bad)
