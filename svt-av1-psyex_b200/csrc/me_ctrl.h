@@ -53,7 +53,33 @@ typedef struct CtrlCtx {
     int32_t             org_x, org_y;
     uint32_t            b64_w, b64_h;
     int32_t             pic_w, pic_h;
+    /* A stage can be run by several cooperating threads of one warp (k_hme): the loops over (list, reference) are
+     * independent per reference, so thread `lane` takes reference slot `only` (= li * ME_NR + ri; -1: all of them) and
+     * the steps that look across references are run by lane 0 alone, with a warp barrier between steps. One thread
+     * (host emulation, legacy kernel): only = -1, lane = 0, nlanes = 1. */
+    int32_t             only, lane, nlanes;
 } CtrlCtx;
+
+#define MC_MINE(c, li, ri) ((c)->only < 0 || (c)->only == (li) * ME_NR + (ri))
+/* loop bounds over lists / references / task slots: everything for only < 0, else exactly this thread's reference, so that
+ * cooperating lanes run the loop body together (SIMT) instead of one after the other */
+#define MC_L0(c) ((c)->only < 0 ? 0 : (c)->only / ME_NR)
+#define MC_L1(c, n) ((c)->only < 0 ? (int)(n) : MC_MIN((int)(n), (c)->only / ME_NR + 1))
+#define MC_R0(c) ((c)->only < 0 ? 0 : (c)->only % ME_NR)
+#define MC_R1(c, n) ((c)->only < 0 ? (int)(n) : MC_MIN((int)(n), (c)->only % ME_NR + 1))
+#define MC_K0(c, per) ((c)->only < 0 ? 0 : (c)->only * (per))
+#define MC_K1(c, per) ((c)->only < 0 ? ME_NREF * (per) : MC_MIN(ME_NREF * (per), ((c)->only + 1) * (per)))
+#if defined(__CUDA_ARCH__)
+#define MC_SYNC(c)                \
+    do {                          \
+        if ((c)->nlanes > 1)      \
+            __syncwarp();         \
+    } while (0)
+#define MC_OPS_ADD(p, v) atomicAdd(reinterpret_cast<unsigned long long *>(p), (unsigned long long)(v))
+#else
+#define MC_SYNC(c) ((void)0)
+#define MC_OPS_ADD(p, v) (*(p) += (v))
+#endif
 
 /* ME:1239-1243 svt_aom_get_scaled_picture_distance */
 ME_HD uint16_t mc_scaled_distance(uint16_t dist) { return (uint16_t)(((dist * 5) / 8) + ((dist % 8) ? 1 : 0)); }
@@ -76,7 +102,7 @@ ME_HD void mc_clamp_axis(int org, int16_t *origin, int16_t *size, int pad, int d
 }
 
 ME_HD void mc_clear_tasks(CtrlCtx *c) {
-    for (int i = 0; i < ME_SLOTS; i++) c->t[i].valid = 0;
+    for (int i = c->lane; i < ME_SLOTS; i += c->nlanes) c->t[i].valid = 0;
 }
 
 /* describe one svt_sad_loop_kernel call; sub halves the rows and doubles the strides (ME:891-909) */
@@ -101,7 +127,7 @@ ME_HD void mc_emit(CtrlCtx *c, int slot, int level, int li, int ri, int ox, int 
     uint64_t lines = (uint64_t)sa_h;
     if (bw == 16 && t->rows <= 16 && skip)
         lines = (uint64_t)(sa_h / 2);
-    c->s->ops += lines * (uint64_t)sa_w * bw * t->rows;
+    MC_OPS_ADD(&c->s->ops, lines * (uint64_t)sa_w * bw * t->rows);
 }
 
 /* result of a task as the callers of svt_sad_loop_kernel see it: sad doubled for sub-sampled SAD; x / y
@@ -132,8 +158,8 @@ ME_HD void mc_init_keys(unsigned long long *keys, int first, int stride) {
 /* ------------------------------------------------------------------------------------------------ */
 ME_HD void mc_stage_init(CtrlCtx *c) {
     B64State *s = c->s;
-    for (int li = 0; li < ME_NL; li++)
-        for (int ri = 0; ri < ME_NR; ri++) {
+    for (int li = MC_L0(c); li < MC_L1(c, ME_NL); li++)
+        for (int ri = MC_R0(c); ri < MC_R1(c, ME_NR); ri++) {
             for (int a = 0; a < 2; a++)
                 for (int b = 0; b < 2; b++) {
                     s->l0x[li][ri][a][b] = s->l0y[li][ri][a][b] = 0;
@@ -160,19 +186,20 @@ ME_HD void mc_stage_init(CtrlCtx *c) {
             s->probed[li][ri] = s->searched[li][ri] = s->pend00[li][ri] = 0;
             c->f[li * ME_NR + ri].valid = 0;
         }
-    s->ops      = 0;
-    s->ops_fs   = 0;
-    c->s->pending = PEND_NONE;
+    if (c->lane == 0) {
+        s->ops        = 0;
+        s->ops_fs     = 0;
+        c->s->pending = PEND_NONE;
+    }
 }
 
 /* ME:2382-2437 / 1667-1689: zero-MV SAD of the block, every other row */
 ME_HD void mc_zz_emit(CtrlCtx *c) {
     const MeGpuParams *p = c->p;
-    mc_clear_tasks(c);
     if (!(p->me_early_exit_th || p->me_safe_limit_zz_th))
         return;
-    for (int li = 0; li < p->num_of_list_to_search; li++)
-        for (int ri = 0; ri < p->num_of_ref_pic_to_search[li]; ri++) {
+    for (int li = MC_L0(c); li < MC_L1(c, p->num_of_list_to_search); li++)
+        for (int ri = MC_R0(c); ri < MC_R1(c, p->num_of_ref_pic_to_search[li]); ri++) {
             if (!mc_ref_active(c, li))
                 continue;
             mc_emit(c, li * ME_NR + ri, 0, li, ri, c->org_x, c->org_y, 0, 0, c->b64_w, c->b64_h, 1, 0, 1, 1);
@@ -240,7 +267,9 @@ ME_HD void mc_prehme_emit_list(CtrlCtx *c, int li) {
         return;
     const MePlaneGeom *pl = &c->j->g.plane[2];
     const int          ox = (int16_t)c->org_x >> 2, oy = (int16_t)c->org_y >> 2;
-    for (int ri = 0; ri < p->num_of_ref_pic_to_search[li]; ri++) {
+    if (c->only >= 0 && c->only / ME_NR != li)
+        return;
+    for (int ri = MC_R0(c); ri < MC_R1(c, p->num_of_ref_pic_to_search[li]); ri++) {
         uint32_t f = mc_scaled_distance(mc_ref_distance(c, li, ri));
         for (int sr = 0; sr < 2; sr++) {
             if (mc_prehme_early_exit(c, li, ri, sr))
@@ -266,7 +295,7 @@ ME_HD void mc_prehme_emit_list(CtrlCtx *c, int li) {
 }
 
 ME_HD void mc_prehme_consume_tasks(CtrlCtx *c) {
-    for (int k = 0; k < ME_NREF * 2; k++) {
+    for (int k = MC_K0(c, 2); k < MC_K1(c, 2); k++) {
         if (!c->t[k].valid)
             continue;
         MePreHme *d = &c->s->phme[(k >> 1) / ME_NR][(k >> 1) % ME_NR][k & 1];
@@ -351,8 +380,8 @@ ME_HD void mc_l0_emit(CtrlCtx *c) {
     B64State          *s  = c->s;
     const MePlaneGeom *pl = &c->j->g.plane[2];
     const int          ox = (int16_t)c->org_x >> 2, oy = (int16_t)c->org_y >> 2;
-    for (int li = 0; li < p->num_of_list_to_search; li++)
-        for (int ri = 0; ri < p->num_of_ref_pic_to_search[li]; ri++) {
+    for (int li = MC_L0(c); li < MC_L1(c, p->num_of_list_to_search); li++)
+        for (int ri = MC_R0(c); ri < MC_R1(c, p->num_of_ref_pic_to_search[li]); ri++) {
             if (p->me_early_exit_th && s->zz_sad[li][ri] < (p->me_early_exit_th >> 2)) {
                 mc_fill_quadrants(s->l0x[li][ri], s->l0y[li][ri], s->l0sad[li][ri], 0, 0, 0);
                 continue;
@@ -399,8 +428,8 @@ ME_HD void mc_worst_quadrant(const B64State *s, int li, int ri, uint8_t *w, uint
 ME_HD void mc_l0_consume(CtrlCtx *c) {
     const MeGpuParams *p = c->p;
     B64State          *s = c->s;
-    for (int li = 0; li < ME_NL; li++)
-        for (int ri = 0; ri < ME_NR; ri++) {
+    for (int li = MC_L0(c); li < MC_L1(c, ME_NL); li++)
+        for (int ri = MC_R0(c); ri < MC_R1(c, ME_NR); ri++) {
             const int base = (li * ME_NR + ri) * 4;
             if (!c->t[base].valid)
                 continue;
@@ -445,8 +474,8 @@ ME_HD void mc_refine_emit(CtrlCtx *c, int level, int slot, int li, int ri, int16
 ME_HD void mc_l1_emit(CtrlCtx *c) {
     const MeGpuParams *p = c->p;
     B64State          *s = c->s;
-    for (int li = 0; li < p->num_of_list_to_search; li++)
-        for (int ri = 0; ri < p->num_of_ref_pic_to_search[li]; ri++) {
+    for (int li = MC_L0(c); li < MC_L1(c, p->num_of_list_to_search); li++)
+        for (int ri = MC_R0(c); ri < MC_R1(c, p->num_of_ref_pic_to_search[li]); ri++) {
             if (!mc_ref_active(c, li))
                 continue;
             if (p->me_early_exit_th && s->zz_sad[li][ri] < (p->me_early_exit_th >> 2)) {
@@ -477,8 +506,8 @@ ME_HD void mc_l1_emit(CtrlCtx *c) {
 ME_HD void mc_l2_emit(CtrlCtx *c) {
     const MeGpuParams *p = c->p;
     B64State          *s = c->s;
-    for (int li = 0; li < p->num_of_list_to_search; li++)
-        for (int ri = 0; ri < p->num_of_ref_pic_to_search[li]; ri++) {
+    for (int li = MC_L0(c); li < MC_L1(c, p->num_of_list_to_search); li++)
+        for (int ri = MC_R0(c); ri < MC_R1(c, p->num_of_ref_pic_to_search[li]); ri++) {
             if (!mc_ref_active(c, li))
                 continue;
             for (int sr_h = 0; sr_h < p->num_hme_sa_h; sr_h++)
@@ -498,7 +527,7 @@ ME_HD void mc_l2_emit(CtrlCtx *c) {
 
 ME_HD void mc_refine_consume(CtrlCtx *c, int level) {
     B64State *s = c->s;
-    for (int k = 0; k < ME_NREF * 4; k++) {
+    for (int k = MC_K0(c, 4); k < MC_K1(c, 4); k++) {
         if (!c->t[k].valid)
             continue;
         const int li = (k >> 2) / ME_NR, ri = (k >> 2) % ME_NR, sr_w = (k >> 1) & 1, sr_h = k & 1;
@@ -593,8 +622,8 @@ ME_HD void mc_centre_emit(CtrlCtx *c) {
     B64State          *s  = c->s;
     const MePlaneGeom *pl = &c->j->g.plane[0];
     const int16_t      ox = (int16_t)c->org_x, oy = (int16_t)c->org_y;
-    for (int li = 0; li < p->num_of_list_to_search; li++)
-        for (int ri = 0; ri < p->num_of_ref_pic_to_search[li]; ri++) {
+    for (int li = MC_L0(c); li < MC_L1(c, p->num_of_list_to_search); li++)
+        for (int ri = MC_R0(c); ri < MC_R1(c, p->num_of_ref_pic_to_search[li]); ri++) {
             if (!s->do_ref[li][ri])
                 continue;
             int16_t  cx = s->sc_x[li][ri], cy = s->sc_y[li][ri];
@@ -639,8 +668,8 @@ ME_HD void mc_fs_emit(CtrlCtx *c, int li, int ri, int16_t x0, int16_t y0, int16_
     f->w        = w;
     f->h        = h;
     const uint64_t n = (uint64_t)w * h * (c->p->me_search_method == ME_GPU_SUB_SAD_SEARCH ? 64 * 32 : 64 * 64);
-    c->s->ops += n;
-    c->s->ops_fs += n;
+    MC_OPS_ADD(&c->s->ops, n);
+    MC_OPS_ADD(&c->s->ops_fs, n);
 }
 
 /* ME:1441-1510: centre the area, clamp to the picture +-63, emit the main search */
@@ -662,9 +691,9 @@ ME_HD void mc_main_emit(CtrlCtx *c, int li, int ri, int16_t w, int16_t h) {
 ME_HD void mc_probe_emit(CtrlCtx *c) {
     const MeGpuParams *p = c->p;
     B64State          *s = c->s;
-    for (int k = 0; k < ME_NREF; k++) c->f[k].valid = 0;
-    for (int li = 0; li < p->num_of_list_to_search; li++)
-        for (int ri = 0; ri < p->num_of_ref_pic_to_search[li]; ri++) {
+    for (int k = MC_K0(c, 1); k < MC_K1(c, 1); k++) c->f[k].valid = 0;
+    for (int li = MC_L0(c); li < MC_L1(c, p->num_of_list_to_search); li++)
+        for (int ri = MC_R0(c); ri < MC_R1(c, p->num_of_ref_pic_to_search[li]); ri++) {
             if (!s->do_ref[li][ri])
                 continue;
             int16_t w = s->sw[li][ri], h = s->sh[li][ri];
@@ -692,9 +721,9 @@ ME_HD void mc_probe_emit(CtrlCtx *c) {
 ME_HD void mc_main_emit_after_probe(CtrlCtx *c) {
     const MeGpuParams *p = c->p;
     B64State          *s = c->s;
-    for (int k = 0; k < ME_NREF; k++) c->f[k].valid = 0;
-    for (int li = 0; li < p->num_of_list_to_search; li++)
-        for (int ri = 0; ri < p->num_of_ref_pic_to_search[li]; ri++) {
+    for (int k = MC_K0(c, 1); k < MC_K1(c, 1); k++) c->f[k].valid = 0;
+    for (int li = MC_L0(c); li < MC_L1(c, p->num_of_list_to_search); li++)
+        for (int ri = MC_R0(c); ri < MC_R1(c, p->num_of_ref_pic_to_search[li]); ri++) {
             if (!s->do_ref[li][ri] || !s->probed[li][ri])
                 continue;
             const unsigned long long *key = &c->keys[(li * ME_NR + ri) * ME_NPU];
@@ -723,82 +752,119 @@ ME_HD void mc_main_emit_after_probe(CtrlCtx *c) {
         }
 }
 
+/* consume the results of the previous stage's tasks. The zero-MV decision looks across references: lane 0 alone. */
 ME_HD void mc_consume_pending(CtrlCtx *c) {
-    switch (c->s->pending) {
-    case PEND_ZZ: mc_zz_consume(c); break;
+    const int pending = c->s->pending;
+    MC_SYNC(c); /* every lane has read `pending` before lane 0 resets it */
+    switch (pending) {
+    case PEND_ZZ:
+        if (c->lane == 0) {
+            const int only = c->only;
+            c->only        = -1;
+            mc_zz_consume(c);
+            c->only = only;
+        }
+        break;
     case PEND_PHME: mc_prehme_consume_tasks(c); break;
     case PEND_L0: mc_l0_consume(c); break;
     case PEND_L1: mc_refine_consume(c, 1); break;
     case PEND_L2: mc_refine_consume(c, 2); break;
     default: break;
     }
-    c->s->pending = PEND_NONE;
+    if (c->lane == 0)
+        c->s->pending = PEND_NONE;
+    MC_SYNC(c);
 }
 
-/* one control stage of one b64 */
+/* a step that looks across references: lane 0 alone, over all references */
+#define MC_SERIAL(c, call)         \
+    do {                           \
+        if ((c)->lane == 0) {      \
+            const int only_ = (c)->only; \
+            (c)->only = -1;        \
+            call;                  \
+            (c)->only = only_;     \
+        }                          \
+        MC_SYNC(c);                \
+    } while (0)
+
+/* one control stage of one b64 (see CtrlCtx: run by one thread, or by the lanes of a warp with a barrier per step) */
 ME_HD void mc_run_stage(CtrlCtx *c, int stage) {
     const MeGpuParams *p = c->p;
     switch (stage) {
     case ST_INIT:
         mc_stage_init(c);
+        mc_clear_tasks(c);
+        MC_SYNC(c);
         mc_zz_emit(c);
         break;
     case ST_PREHME0:
         mc_consume_pending(c);
         mc_clear_tasks(c);
+        MC_SYNC(c);
         if (p->prehme_enable) {
             mc_prehme_emit_list(c, 0);
             if (!p->prehme_l1_early_exit)
                 mc_prehme_emit_list(c, 1);
-            c->s->pending = PEND_PHME;
+            if (c->lane == 0)
+                c->s->pending = PEND_PHME;
         }
         break;
     case ST_PREHME1:
         mc_consume_pending(c);
         mc_clear_tasks(c);
+        MC_SYNC(c);
         if (p->prehme_enable && p->prehme_l1_early_exit) {
             mc_prehme_emit_list(c, 1);
-            c->s->pending = PEND_PHME;
+            if (c->lane == 0)
+                c->s->pending = PEND_PHME;
         }
         break;
     case ST_HME_L0:
         mc_consume_pending(c);
         if (p->prehme_enable)
-            mc_prehme_finish(c);
+            MC_SERIAL(c, mc_prehme_finish(c));
         mc_clear_tasks(c);
+        MC_SYNC(c);
         if (p->enable_hme_flag && p->enable_hme_level0_flag) {
             mc_l0_emit(c);
-            c->s->pending = PEND_L0;
+            if (c->lane == 0)
+                c->s->pending = PEND_L0;
         }
         break;
     case ST_HME_L1:
         mc_consume_pending(c);
         mc_clear_tasks(c);
+        MC_SYNC(c);
         if (p->enable_hme_flag && p->enable_hme_level1_flag) {
             mc_l1_emit(c);
-            c->s->pending = PEND_L1;
+            if (c->lane == 0)
+                c->s->pending = PEND_L1;
         }
         break;
     case ST_HME_L2:
         mc_consume_pending(c);
         mc_clear_tasks(c);
+        MC_SYNC(c);
         if (p->enable_hme_flag && p->enable_hme_level2_flag) {
             mc_l2_emit(c);
-            c->s->pending = PEND_L2;
+            if (c->lane == 0)
+                c->s->pending = PEND_L2;
         }
         break;
     case ST_CENTRE:
         mc_consume_pending(c);
         mc_clear_tasks(c);
-        mc_final_centre(c);
+        MC_SERIAL(c, mc_final_centre(c));
         if (p->enable_hme_flag) /* prune_ref = enable_hme_flag && me_type != ME_MCTF, ME:3103 */
-            mc_hme_prune(c);
+            MC_SERIAL(c, mc_hme_prune(c));
         mc_centre_emit(c);
         break;
     case ST_PROBE: mc_probe_emit(c); break;
     case ST_MAIN: mc_main_emit_after_probe(c); break;
     default: break;
     }
+    MC_SYNC(c);
 }
 
 /* ------------------------------------------------------------------------------------------------

@@ -665,6 +665,9 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
     c.b64_h = (uint32_t)min(64, j->g.height - c.org_y);
     c.pic_w = j->g.width;
     c.pic_h = j->g.height;
+    c.only = min(lane, ME_NREF); /* warp 0 runs the control stages: lane = (list, reference) slot, lanes >= ME_NREF only help clearing */
+    c.lane = lane;
+    c.nlanes = 32;
     const bool sub = j->p.me_search_method == ME_GPU_SUB_SAD_SEARCH;
 
     mc_init_keys(keys, tid, HM_THREADS);
@@ -708,9 +711,10 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
 #ifdef ME_HME_TRACE
         long long tr0 = clock64();
 #endif
-        if (tid == 0) {
+        if (warp == 0) {
             mc_run_stage(&c, st);
-            sm.next_item = 0;
+            if (lane == 0)
+                sm.next_item = 0;
         }
         __syncthreads();
 #ifdef ME_HME_TRACE
@@ -926,7 +930,7 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
         __syncthreads();
     }
 #ifdef ME_HME_TRACE
-    if (0 && blockIdx.y == 0 && (b == 100 || b == 300) && (tid == 0 || tid == 96)) {
+    if (blockIdx.y == 0 && b == 100 && tid == 0) {
         for (int st = 0; st < ST_COUNT; st++)
             printf("b %d tid %d stage %d: ctrl %lld partition %lld items+barrier %lld (own items %lld) cycles\n", b, tid, st,
                    tr[st][0], tr[st][1], tr[st][2], tr[st][3]);

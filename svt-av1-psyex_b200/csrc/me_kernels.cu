@@ -113,6 +113,9 @@ __global__ void __launch_bounds__(64) k_ctrl(MeJob *jobs, uint32_t stage_mask, F
     c.b64_h = (uint32_t)min(64, j->g.height - c.org_y);
     c.pic_w = j->g.width;
     c.pic_h = j->g.height;
+    c.only = -1; /* one thread runs the whole stage */
+    c.lane = 0;
+    c.nlanes = 1;
     if (stage_mask & (1u << ST_INIT))
         mc_init_keys(c.keys, 0, 1);
     for (int st = 0; st < ST_COUNT; st++)

@@ -131,6 +131,7 @@ extern "C" int emul_me_picture(const OraclePicture *src, const OraclePicture *co
         c.org_x = (b % j.g.b64_cols) * 64; c.org_y = (b / j.g.b64_cols) * 64;
         c.b64_w = (uint32_t)MC_MIN(64, j.g.width - c.org_x); c.b64_h = (uint32_t)MC_MIN(64, j.g.height - c.org_y);
         c.pic_w = j.g.width; c.pic_h = j.g.height;
+        c.only = -1; c.lane = 0; c.nlanes = 1;
         return c;
     };
     /* the same stage sequence the engine launches (me_engine.cu, run_job) */
