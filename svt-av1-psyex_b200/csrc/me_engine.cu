@@ -104,6 +104,8 @@ struct Device {
     uint8_t     *pool = nullptr;
     cudaStream_t upload = nullptr;
     int          sms = 148;
+    uint8_t     *stage = nullptr; /* landing buffer of contiguous host->device copies (one picture, reused in stream order) */
+    size_t       stage_bytes = 0;
     std::vector<JobCtx> jobs;
     struct MapSet { int width, height; HmeMaps maps; };
     std::vector<MapSet> mapsets; /* TMA descriptors of the pool per picture size seen (normally one) */
@@ -265,14 +267,19 @@ int register_common(uint64_t picture_number, const uint8_t *src, int stride, int
     Device      &d     = g.dev[owner];
     const size_t off   = (size_t)s * g.gmax.slot_bytes + gm.plane[0].offset;
     CU(cudaSetDevice(d.id));
-    if (padded) {
-        const uint8_t *top_left = src + (size_t)(org_y - ME_PAD_FULL) * stride + (org_x - ME_PAD_FULL);
-        CU(cudaMemcpy2DAsync(d.pool + off, gm.plane[0].stride, top_left, stride, width + 2 * ME_PAD_FULL,
-                             height + 2 * ME_PAD_FULL, cudaMemcpyHostToDevice, d.upload));
-    } else {
-        CU(cudaMemcpy2DAsync(d.pool + off + (size_t)ME_PAD_FULL * gm.plane[0].stride + ME_PAD_FULL, gm.plane[0].stride, src,
-                             stride, width, height, cudaMemcpyHostToDevice, d.upload));
-    }
+    /* rows of the source to their place in the pool. When the source rows are (nearly) contiguous and 4-byte granular, one
+       contiguous copy into the landing buffer plus a re-pitch kernel: a pitched copy of 2 KB rows reaches a third of the
+       PCIe rate. Otherwise (wide strides, odd alignment) the pitched copy. */
+    const uint8_t *first     = padded ? src + (size_t)(org_y - ME_PAD_FULL) * stride + (org_x - ME_PAD_FULL) : src;
+    const int      row_bytes = padded ? width + 2 * ME_PAD_FULL : width, rows = padded ? height + 2 * ME_PAD_FULL : height;
+    uint8_t       *dst       = d.pool + off + (padded ? 0 : (size_t)ME_PAD_FULL * gm.plane[0].stride + ME_PAD_FULL);
+    const size_t   span      = (size_t)(rows - 1) * (size_t)stride + (size_t)row_bytes;
+    if (stride > 0 && !(stride & 3) && !(row_bytes & 3) && !((uintptr_t)first & 3) && span <= d.stage_bytes &&
+        (size_t)stride * 4 <= (size_t)row_bytes * 5) {
+        CU(cudaMemcpyAsync(d.stage, first, span, cudaMemcpyHostToDevice, d.upload));
+        me_launch_repitch(d.stage, stride, dst, gm.plane[0].stride, row_bytes, rows, d.upload);
+    } else
+        CU(cudaMemcpy2DAsync(dst, gm.plane[0].stride, first, stride, row_bytes, rows, cudaMemcpyHostToDevice, d.upload));
     Slot &sl          = g.slots[s];
     sl.used           = true;
     sl.picture_number = picture_number;
@@ -308,6 +315,7 @@ void me_gpu_shutdown(void) {
         for (auto &jc : d.jobs) free_job(jc);
         if (d.upload) cudaStreamDestroy(d.upload);
         cudaFree(d.pool);
+        cudaFree(d.stage);
     }
     for (auto &s : g.slots)
         for (auto &e : s.ready)
@@ -360,6 +368,8 @@ int me_gpu_init(int device_count, const int *device_ids, int max_width, int max_
         CU(cudaStreamCreateWithFlags(&d.upload, cudaStreamNonBlocking));
         CU(cudaMalloc((void **)&d.pool, (size_t)g.nslots * g.gmax.slot_bytes + 65536));
         CU(cudaMemset(d.pool, 0, (size_t)g.nslots * g.gmax.slot_bytes + 65536));
+        d.stage_bytes = (size_t)(g.gmax.width + 2 * ME_PAD_FULL) * (size_t)(g.gmax.height + 2 * ME_PAD_FULL) * 5 / 4;
+        CU(cudaMalloc((void **)&d.stage, d.stage_bytes));
         d.jobs.resize((size_t)njobs);
         for (auto &jc : d.jobs) {
             int rc = alloc_job(d, jc, g.gmax, max_refs_l0, max_refs_l1);

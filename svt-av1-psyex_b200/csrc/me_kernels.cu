@@ -65,6 +65,16 @@ __global__ void __launch_bounds__(256) k_downsample_pad(uint8_t *pool, size_t sl
     *(uint32_t *)(d + (size_t)py * dst.stride + wx * 4) = out;
 }
 
+/* rows of `row_bytes` bytes from a contiguous staging copy (pitch src_pitch) to their place in the pool (pitch dst_pitch);
+ * all three are multiples of 4. A contiguous host->device copy followed by this runs at three times the rate of a
+ * pitched cudaMemcpy2DAsync of 2 KB rows (tools/h2d_probe.cu: 48 vs 16 GB/s). */
+__global__ void __launch_bounds__(256) k_repitch(const uint8_t *__restrict__ src, int src_pitch, uint8_t *__restrict__ dst, int dst_pitch,
+                                                 int row_words) {
+    const int wx = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (wx < row_words)
+        *(uint32_t *)(dst + (size_t)y * dst_pitch + 4 * wx) = *(const uint32_t *)(src + (size_t)y * src_pitch + 4 * wx);
+}
+
 /* replicate the interior of the full plane into its 68-pixel border (rows and columns) */
 __global__ void __launch_bounds__(256) k_pad_full(uint8_t *pool, size_t slot_off, MePlaneGeom pl) {
     const int wx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -587,6 +597,12 @@ void me_launch_search(const MeJob *jobs, int njobs, int max_b64, int slots, cons
 
 void me_launch_fullsearch(MeJob *jobs, FsTileList *list, const uint8_t *pool, int ctas, cudaStream_t st) {
     k_fullsearch<<<ctas, FS_THREADS, FS_SMEM_BYTES, st>>>(jobs, list, pool);
+    g_launches++;
+}
+
+void me_launch_repitch(const uint8_t *src, int src_pitch, uint8_t *dst, int dst_pitch, int row_bytes, int rows, cudaStream_t st) {
+    dim3 grid((row_bytes / 4 + 255) / 256, rows);
+    k_repitch<<<grid, 256, 0, st>>>(src, src_pitch, dst, dst_pitch, row_bytes / 4);
     g_launches++;
 }
 
