@@ -128,7 +128,7 @@ class CpuArm:
         self.ref = checkers.Reference()
         self.threads, self.simd, self.pocs = threads, simd, pocs
         seq = synth.Sequence(W, H, NPIC, kind=kind)
-        pics = {}
+        pics = self.pics = {}  # keeps the planes alive: the C structs built below point into them
 
         def get(k):
             if k not in pics:
