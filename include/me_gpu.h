@@ -20,6 +20,10 @@
  *   MeGpuOutputs             <- pcs->pa_me_data->me_results[b64] (me_sb_results.h:28-51) and the
  *                               per-b64 pcs arrays written by compute_distortion /
  *                               perform_gm_detection (motion_estimation.c:2964,2838)
+ *   me_gpu_dg_detector       <- the TASK_DG_DETECTOR_HME segments of one (source, reference) pair:
+ *                               early_hme's dispatch + semaphore wait (pd_process.c:561-625) and
+ *                               dg_detector_hme_level0 / early_hme_b64 (pd_process.c:393-560)
+ *   MeGpuDgMetrics           <- DGDetectorMetrics (pcs.h:731-737)
  *
  * There is no CPU fallback behind this interface: every call fails with
  * ME_GPU_ERR_NO_DEVICE when no CUDA device is usable.
@@ -226,6 +230,20 @@ int me_gpu_submit_out(uint64_t picture_number, const MeGpuParams *params,
  * at these offsets gets them with a single device->host copy; any other arrangement works, with one copy per
  * non-adjacent array. */
 int me_gpu_output_layout(int width, int height, const MeGpuParams *params, size_t offsets[11], size_t *total_bytes);
+
+/* dynamic-GOP detector ------------------------------------------------------------------- */
+typedef struct MeGpuDgMetrics { /* DGDetectorMetrics, pcs.h:731-737 (seg_completed has no meaning here) */
+    uint64_t tot_dist; /* sum of the per-b64 HME-L0 SADs */
+    uint32_t tot_cplx; /* b64s whose SAD exceeds 16*16*30 */
+    uint32_t tot_active; /* b64s with a non-zero vector */
+    int32_t  sum_in_vectors; /* inward minus outward pointing vector components */
+} MeGpuDgMetrics;
+/* One full-SAD svt_sad_loop_kernel search per b64 of the source's sixteenth plane (16x16 block) in the reference's
+ * sixteenth plane, search area 16 / 64 / 128 squared by input_resolution (<= 360p / <= 480p / larger,
+ * pd_process.c:497-498), reduced to the four picture metrics. Both pictures must be registered and of equal size.
+ * Synchronous, like early_hme (which blocks on frame_done_sem): returns when *metrics is written. */
+int me_gpu_dg_detector(uint64_t src_picture_number, uint64_t ref_picture_number, uint8_t input_resolution,
+                       MeGpuDgMetrics *metrics);
 
 /* host-side restatement of svt_aom_sig_deriv_me and the pcs/scs settings it depends on */
 int me_gpu_derive_params(const MeGpuEncoderConfig *cfg, MeGpuParams *params);

@@ -65,6 +65,10 @@ int oracle_me_b64_range(const OraclePicture *src,
                         const MeGpuParams *params, MeGpuOutputs *out, uint32_t first, uint32_t count,
                         uint64_t *byte_sad_ops);
 
+/* dynamic-GOP detector (me_oracle_dg.c): HME level 0 of every b64 of src against ref on the sixteenth planes,
+ * reduced to the DGDetectorMetrics of the pair */
+int oracle_dg_detector(const OraclePicture *src, const OraclePicture *ref, uint8_t input_resolution, MeGpuDgMetrics *out);
+
 #ifdef __cplusplus
 }
 #endif

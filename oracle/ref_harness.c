@@ -398,3 +398,51 @@ REF_API int ref_me_b64_range(const OraclePicture *src, const OraclePicture *cons
     free(geo); free(rp); free(res); free(md); free(m); free(scs); free(pcs);
     return 0;
 }
+
+/* Dynamic-GOP detector: the reference's dg_detector_hme_level0 (Codec/pd_process.c:492) run as ONE segment
+ * covering the picture, on a PictureParentControlSet that holds only what the function reads; early_hme's
+ * metric reset (:569-573) is done here. The mutex and the semaphore are the reference's own (svt_threads.c). */
+void dg_detector_hme_level0(struct PictureParentControlSet *ppcs, uint32_t seg_idx);
+
+REF_API int ref_dg_detector(const OraclePicture *src, const OraclePicture *ref, uint8_t input_resolution, MeGpuDgMetrics *out,
+                            int simd) {
+    set_rtcd(simd);
+    PictureParentControlSet *pcs = calloc(1, sizeof *pcs), *rpcs = calloc(1, sizeof *rpcs);
+    SequenceControlSet      *scs = calloc(1, sizeof *scs);
+    DGDetectorSeg           *dg  = calloc(1, sizeof *dg);
+    EbObjectWrapper         *sw = calloc(1, sizeof *sw), *rw = calloc(1, sizeof *rw);
+    EbPaReferenceObject     *so = calloc(1, sizeof *so), *ro = calloc(1, sizeof *ro);
+    if (!pcs || !rpcs || !scs || !dg || !sw || !rw || !so || !ro)
+        return -1;
+    EbPictureBufferDesc s16, r16;
+    desc_from_plane(&s16, &src->sixteenth);
+    desc_from_plane(&r16, &ref->sixteenth);
+    so->sixteenth_downsampled_picture_ptr = &s16;
+    ro->sixteenth_downsampled_picture_ptr = &r16;
+    sw->object_ptr = so;
+    rw->object_ptr = ro;
+    pcs->pa_ref_pic_wrapper  = sw;
+    rpcs->pa_ref_pic_wrapper = rw;
+    pcs->scs                 = scs;
+    scs->b64_size            = 64;
+    pcs->input_resolution    = (EbInputResolution)input_resolution;
+    pcs->aligned_width       = (uint16_t)((src->full.width + 7) & ~7);
+    pcs->aligned_height      = (uint16_t)((src->full.height + 7) & ~7);
+    pcs->me_segments_column_count = pcs->me_segments_row_count = 1;
+    pcs->dg_detector         = dg;
+    dg->ref_pic              = rpcs;
+    dg->metrics_mutex        = svt_create_mutex();
+    dg->frame_done_sem       = svt_create_semaphore(0, 1);
+    if (!dg->metrics_mutex || !dg->frame_done_sem)
+        return -1;
+    dg_detector_hme_level0(pcs, 0);
+    svt_block_on_semaphore(dg->frame_done_sem); /* posted by the last (only) segment */
+    out->tot_dist       = dg->metrics.tot_dist;
+    out->tot_cplx       = dg->metrics.tot_cplx;
+    out->tot_active     = dg->metrics.tot_active;
+    out->sum_in_vectors = dg->metrics.sum_in_vectors;
+    svt_destroy_mutex(dg->metrics_mutex);
+    svt_destroy_semaphore(dg->frame_done_sem);
+    free(ro); free(so); free(rw); free(sw); free(dg); free(scs); free(rpcs); free(pcs);
+    return 0;
+}

@@ -106,6 +106,8 @@ struct Device {
     int          sms = 148;
     uint8_t     *stage = nullptr; /* landing buffer of contiguous host->device copies (one picture, reused in stream order) */
     size_t       stage_bytes = 0;
+    cudaStream_t    dg_stream = nullptr; /* dynamic-GOP detector: its own stream, a device accumulator, a pinned landing struct */
+    MeGpuDgMetrics *dg_acc = nullptr, *dg_host = nullptr;
     std::vector<JobCtx> jobs;
     struct MapSet { int width, height; HmeMaps maps; };
     std::vector<MapSet> mapsets; /* TMA descriptors of the pool per picture size seen (normally one) */
@@ -119,7 +121,8 @@ struct Engine {
     std::vector<Slot>   slots;
     std::map<uint64_t, int> by_number;
     int                 max_l0 = 0, max_l1 = 0;
-    uint64_t            submit_counter = 0, register_counter = 0;
+    uint64_t            submit_counter = 0, register_counter = 0, dg_counter = 0;
+    std::mutex          dg_mu; /* one detector call at a time (they share the per-device accumulator) */
     MeGpuTimings        last{};
     std::mutex          mu;
     bool                profiling = false;
@@ -314,6 +317,9 @@ void me_gpu_shutdown(void) {
         cudaDeviceSynchronize();
         for (auto &jc : d.jobs) free_job(jc);
         if (d.upload) cudaStreamDestroy(d.upload);
+        if (d.dg_stream) cudaStreamDestroy(d.dg_stream);
+        cudaFree(d.dg_acc);
+        cudaFreeHost(d.dg_host);
         cudaFree(d.pool);
         cudaFree(d.stage);
     }
@@ -370,6 +376,9 @@ int me_gpu_init(int device_count, const int *device_ids, int max_width, int max_
         CU(cudaMemset(d.pool, 0, (size_t)g.nslots * g.gmax.slot_bytes + 65536));
         d.stage_bytes = (size_t)(g.gmax.width + 2 * ME_PAD_FULL) * (size_t)(g.gmax.height + 2 * ME_PAD_FULL) * 5 / 4;
         CU(cudaMalloc((void **)&d.stage, d.stage_bytes));
+        CU(cudaStreamCreateWithFlags(&d.dg_stream, cudaStreamNonBlocking));
+        CU(cudaMalloc((void **)&d.dg_acc, sizeof(MeGpuDgMetrics)));
+        CU(cudaMallocHost((void **)&d.dg_host, sizeof(MeGpuDgMetrics)));
         d.jobs.resize((size_t)njobs);
         for (auto &jc : d.jobs) {
             int rc = alloc_job(d, jc, g.gmax, max_refs_l0, max_refs_l1);
@@ -813,7 +822,7 @@ int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out) {
         default: t.k_epilogue_ms += ms; break;
         }
     }
-    t.kernel_launches = me_launch_count() + me_hme_launch_count();
+    t.kernel_launches = me_launch_count() + me_hme_launch_count() + me_dg_launch_count();
     t.byte_sad_ops    = jc->h_tail->ops[0];
     t.byte_sad_ops_fullsearch = jc->h_tail->ops[1];
     g.last            = t;
@@ -830,12 +839,63 @@ int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out) {
     return ME_GPU_OK;
 }
 
+/* TASK_DG_DETECTOR_HME of one (source, reference) pair: one launch of k_dg_hme on the detector's stream, the four
+ * sums come back in one 24-byte copy. Calls alternate between the devices (every device holds every picture). */
+int me_gpu_dg_detector(uint64_t src_picture_number, uint64_t ref_picture_number, uint8_t input_resolution,
+                       MeGpuDgMetrics *metrics) {
+    std::lock_guard<std::mutex>  dg(g.dg_mu);
+    std::unique_lock<std::mutex> lk(g.mu);
+    if (!g.initialised)
+        return fail(ME_GPU_ERR_STATE, "not initialised");
+    if (!metrics)
+        return fail(ME_GPU_ERR_BAD_ARG, "null metrics");
+    auto si = g.by_number.find(src_picture_number), ri = g.by_number.find(ref_picture_number);
+    if (si == g.by_number.end() || ri == g.by_number.end())
+        return fail(ME_GPU_ERR_NOT_FOUND, "picture not registered");
+    const int ss = si->second, rs = ri->second;
+    if (g.slots[ss].width != g.slots[rs].width || g.slots[ss].height != g.slots[rs].height)
+        return fail(ME_GPU_ERR_BAD_ARG, "source and reference picture sizes differ");
+    const size_t di = (size_t)(g.dg_counter++ % g.dev.size());
+    Device      &d  = g.dev[di];
+    MePicGeom    gm;
+    me_make_geom(&gm, g.slots[ss].width, g.slots[ss].height);
+    gm.slot_bytes = g.gmax.slot_bytes;
+    /* pd_process.c:497-498: 16 up to 360p, 64 up to 480p, else 128 (EbInputResolution, definitions.h:2079) */
+    const int sa = input_resolution <= 1 ? 16 : input_resolution <= 2 ? 64 : 128;
+    CU(cudaSetDevice(d.id));
+    for (int s : {ss, rs}) {
+        Slot &sl = g.slots[s];
+        if (!sl.ready_seen[di])
+            CU(cudaStreamWaitEvent(d.dg_stream, sl.ready[di], 0));
+        sl.refcount++;
+    }
+    cudaError_t e = cudaMemsetAsync(d.dg_acc, 0, sizeof(MeGpuDgMetrics), d.dg_stream);
+    if (e == cudaSuccess) {
+        me_launch_dg(d.pool, &gm, (uint32_t)ss, (uint32_t)rs, sa, d.dg_acc, d.dg_stream);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(d.dg_host, d.dg_acc, sizeof(MeGpuDgMetrics), cudaMemcpyDeviceToHost, d.dg_stream);
+    lk.unlock();
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(d.dg_stream);
+    lk.lock();
+    for (int s : {ss, rs}) {
+        g.slots[s].refcount--;
+        free_slot_if_idle(s);
+    }
+    if (e != cudaSuccess)
+        return fail(ME_GPU_ERR_CUDA, std::string("dynamic-GOP detector failed: ") + cudaGetErrorString(e));
+    *metrics = *d.dg_host;
+    return ME_GPU_OK;
+}
+
 int me_gpu_get_timings(MeGpuTimings *t) {
     std::lock_guard<std::mutex> lk(g.mu);
     if (!t)
         return ME_GPU_ERR_BAD_ARG;
     *t                 = g.last;
-    t->kernel_launches = me_launch_count() + me_hme_launch_count();
+    t->kernel_launches = me_launch_count() + me_hme_launch_count() + me_dg_launch_count();
     return ME_GPU_OK;
 }
 

@@ -40,5 +40,10 @@ unsigned long long me_hme_launch_count(void);
 int    me_hme_make_maps(HmeMaps *maps, const uint8_t *pool, const MePicGeom *g, int nslots);
 void   me_launch_hme(MeJob *jobs, int njobs, int max_b64, FsTileList *list, const uint8_t *pool, const HmeMaps *maps,
                      cudaStream_t st);
+/* me_dg.cu: dynamic-GOP detector HME level 0 of one (source, reference) pair, summed into *acc (device memory, zeroed
+ * by the caller on the same stream) */
+unsigned long long me_dg_launch_count(void);
+void   me_launch_dg(const uint8_t *pool, const MePicGeom *g, uint32_t src_slot, uint32_t ref_slot, int sa, MeGpuDgMetrics *acc,
+                    cudaStream_t st);
 
 #endif

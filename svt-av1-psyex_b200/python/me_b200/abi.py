@@ -113,6 +113,13 @@ class MeGpuTimings(C.Structure):
                 ("k_epilogue_ms", C.c_float)]
 
 
+class MeGpuDgMetrics(C.Structure):
+    _fields_ = [("tot_dist", u64), ("tot_cplx", u32), ("tot_active", u32), ("sum_in_vectors", C.c_int32)]
+
+    def as_tuple(self):
+        return (self.tot_dist, self.tot_cplx, self.tot_active, self.sum_in_vectors)
+
+
 class OraclePlane(C.Structure):
     _fields_ = [("buf", C.c_void_p), ("stride", i32), ("org_x", i32), ("org_y", i32), ("width", i32),
                 ("height", i32)]
@@ -140,6 +147,7 @@ GPU_SYMBOLS = [
     "me_gpu_init", "me_gpu_shutdown", "me_gpu_last_error", "me_gpu_device_count", "me_gpu_register_picture",
     "me_gpu_register_picture_unpadded", "me_gpu_release_picture", "me_gpu_read_pyramid", "me_gpu_plane_geometry",
     "me_gpu_submit", "me_gpu_wait", "me_gpu_derive_params", "me_gpu_get_timings", "me_gpu_measure_sad_peak", "me_gpu_set_profiling", "me_gpu_submit_out", "me_gpu_output_layout",
+    "me_gpu_dg_detector",
 ]
 
 
@@ -162,6 +170,7 @@ def load_gpu_lib():
                                          C.POINTER(C.c_size_t)]
     lib.me_gpu_derive_params.argtypes = [C.POINTER(MeGpuEncoderConfig), C.POINTER(MeGpuParams)]
     lib.me_gpu_get_timings.argtypes = [C.POINTER(MeGpuTimings)]
+    lib.me_gpu_dg_detector.argtypes = [u64, u64, u8, C.POINTER(MeGpuDgMetrics)]
     lib.me_gpu_measure_sad_peak.restype = C.c_double
     return lib
 

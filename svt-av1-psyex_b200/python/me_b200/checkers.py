@@ -32,10 +32,19 @@ class Oracle:
                                              C.POINTER(abi.u64), C.POINTER(abi.i16), C.POINTER(abi.i16), abi.u32,
                                              abi.u8, abi.i16, abi.i16]
         self.lib.oracle_downsample_2d.argtypes = [C.c_void_p, abi.u32, abi.u32, abi.u32, C.c_void_p, abi.u32, abi.u32]
+        self.lib.oracle_dg_detector.argtypes = [C.POINTER(abi.OraclePicture), C.POINTER(abi.OraclePicture), abi.u8,
+                                                C.POINTER(abi.MeGpuDgMetrics)]
 
     def build_pyramid(self, pic: Picture):
         s = pic.c_struct()
         self.lib.oracle_build_pyramid(C.byref(s))
+
+    def dg_detector(self, src: Picture, ref: Picture, input_resolution):
+        a, b, m = src.c_struct(), ref.c_struct(), abi.MeGpuDgMetrics()
+        rc = self.lib.oracle_dg_detector(C.byref(a), C.byref(b), input_resolution, C.byref(m))
+        if rc != 0:
+            raise RuntimeError(f"oracle_dg_detector failed: {rc}")
+        return m.as_tuple()
 
     def me_picture(self, src: Picture, refs, params, first=0, count=1 << 30, debug=True):
         out = Outputs(src.width, src.height, params, debug=debug)
@@ -67,6 +76,15 @@ class Reference:
                                           C.POINTER(abi.u64), C.POINTER(abi.i16), C.POINTER(abi.i16), abi.u32,
                                           abi.u8, abi.i16, abi.i16]
         self.lib.ref_downsample_2d.argtypes = [C.c_void_p, abi.u32, abi.u32, abi.u32, C.c_void_p, abi.u32, abi.u32]
+        self.lib.ref_dg_detector.argtypes = [C.POINTER(abi.OraclePicture), C.POINTER(abi.OraclePicture), abi.u8,
+                                             C.POINTER(abi.MeGpuDgMetrics), C.c_int]
+
+    def dg_detector(self, src: Picture, ref: Picture, input_resolution, simd=0):
+        a, b, m = src.c_struct(), ref.c_struct(), abi.MeGpuDgMetrics()
+        rc = self.lib.ref_dg_detector(C.byref(a), C.byref(b), input_resolution, C.byref(m), simd)
+        if rc != 0:
+            raise RuntimeError(f"ref_dg_detector failed: {rc}")
+        return m.as_tuple()
 
     @staticmethod
     def available():

@@ -106,6 +106,13 @@ class Engine:
         out.byte_sad_ops = t.byte_sad_ops
         return out
 
+    # dynamic-GOP detector -------------------------------------------------------------------------
+    def dg_detector(self, src_picture_number, ref_picture_number, input_resolution):
+        """(tot_dist, tot_cplx, tot_active, sum_in_vectors) of the pair, as early_hme leaves them in DGDetectorMetrics"""
+        m = abi.MeGpuDgMetrics()
+        self._check(self.lib.me_gpu_dg_detector(src_picture_number, ref_picture_number, input_resolution, C.byref(m)))
+        return m.as_tuple()
+
     def timings(self):
         t = abi.MeGpuTimings()
         self._check(self.lib.me_gpu_get_timings(C.byref(t)))

@@ -4,7 +4,7 @@ compiled in place from /root/reference by oracle/Makefile). Run in the build con
     python tests/golden/make_golden.py
 
 Writes tests/golden/me_<case>.npz (every MeGpuOutputs field the reference produces) and
-tests/golden/derive_params.json (svt_aom_sig_deriv_me outputs). Inputs are regenerated from the seeded
+tests/golden/derive_params.json (svt_aom_sig_deriv_me outputs) and tests/golden/dg_metrics.json (dg_detector_hme_level0). Inputs are regenerated from the seeded
 synthetic sequence (me_b200/synth.py), so only outputs are stored.
 """
 import ctypes as C
@@ -18,7 +18,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(HERE, "..", "..", "svt-av1-psyex_b200", "python"))
 sys.path.insert(0, os.path.join(HERE, ".."))
 
-from helpers import PictureSet, derive, host_lib  # noqa: E402
+from helpers import DG_CASES, DgPictures, PictureSet, derive, host_lib  # noqa: E402
 from me_b200 import abi  # noqa: E402
 from me_b200.checkers import Reference  # noqa: E402
 
@@ -55,6 +55,13 @@ def main():
         table.append({"preset": preset, "width": w, "height": h, "tl": tl, "params": ref.derive_params(cfg, n.value, z.value).as_dict()})
     json.dump(table, open(os.path.join(HERE, "derive_params.json"), "w"))
     print("wrote derive_params.json:", len(table), "cases")
+    # dynamic-GOP detector metrics of dg_detector_hme_level0 (pd_process.c:492)
+    dg = []
+    for (w, h, res, kind, a, b) in DG_CASES:
+        ps = DgPictures(w, h, kind, ref)
+        dg.append({"case": [w, h, res, kind, a, b], "metrics": list(ref.dg_detector(ps.get(a), ps.get(b), res))})
+    json.dump(dg, open(os.path.join(HERE, "dg_metrics.json"), "w"))
+    print("wrote dg_metrics.json:", len(dg), "cases")
 
 
 if __name__ == "__main__":

@@ -72,3 +72,32 @@ class Emulator:
 
 def used_refs(l0, l1):
     return [len(l0), len(l1)]
+
+
+# dynamic-GOP detector cases: (width, height, input_resolution class, kind, source poc, reference poc).
+# "blocks" pictures are 8x8-pixel constant blocks of uniform noise: unrelated pictures whose sixteenth planes keep
+# their contrast, so that tot_cplx counts; "flat" pictures are constant (90 for even, 60 for odd pocs): every search
+# position ties, and the SAD of an even/odd pair is exactly the tot_cplx threshold 16*16*30 (not counted).
+DG_CASES = [(320, 192, 1, "motion", 8, 0), (320, 192, 2, "iid", 4, 3), (320, 192, 4, "motion", 4, 3), (320, 192, 4, "blocks", 2, 1),
+            (264, 200, 4, "motion", 8, 0), (264, 200, 2, "blocks", 1, 2), (136, 72, 3, "iid", 1, 0), (136, 72, 0, "blocks", 1, 0),
+            (640, 360, 2, "motion", 8, 0), (640, 360, 4, "blocks", 3, 5), (64, 64, 4, "iid", 1, 0), (320, 192, 4, "flat", 2, 2), (200, 136, 2, "flat", 2, 1),
+            (1280, 720, 3, "motion", 16, 0)]
+
+
+class DgPictures(PictureSet):
+    def __init__(self, width, height, kind, builder, seed=77):
+        self.kind = kind
+        super().__init__(width, height, 33, kind if kind in ("motion", "iid") else "iid", builder, seed=seed)
+
+    def get(self, poc):
+        if poc not in self.pics and self.kind in ("blocks", "flat"):
+            rng = np.random.default_rng([self.seq.seed, poc, 5])
+            small = rng.integers(0, 256, size=((self.h + 7) // 8, (self.w + 7) // 8), dtype=np.uint8)
+            luma = np.repeat(np.repeat(small, 8, axis=0), 8, axis=1)[:self.h, :self.w]
+            if self.kind == "flat":
+                luma = np.full((self.h, self.w), 60 if poc & 1 else 90, dtype=np.uint8)
+            p = planes.Picture(self.w, self.h, poc)
+            p.set_luma(np.ascontiguousarray(luma))
+            self.builder.build_pyramid(p)
+            self.pics[poc] = p
+        return super().get(poc)

@@ -31,7 +31,7 @@ def _probe(structs):
 
 def test_ctypes_layout_matches_header():
     structs = [("MeGpuParams", abi.MeGpuParams), ("MeGpuEncoderConfig", abi.MeGpuEncoderConfig),
-               ("MeGpuOutputs", abi.MeGpuOutputs), ("MeGpuTimings", abi.MeGpuTimings)]
+               ("MeGpuOutputs", abi.MeGpuOutputs), ("MeGpuTimings", abi.MeGpuTimings), ("MeGpuDgMetrics", abi.MeGpuDgMetrics)]
     got = _probe(structs)
     for name, cls in structs:
         assert int(got[name]) == C.sizeof(cls), name

@@ -134,3 +134,42 @@ def test_pictures_in_flight_out_of_order(engine, oracle):
         exp = oracle.me_picture(ps.get(poc), [[ps.get(k) for k in l0], [ps.get(k) for k in l1]], p)
         bad = planes.compare_outputs(exp, got[poc], used_refs=used_refs(l0, l1))
         assert not bad, (poc, bad)
+
+
+def test_dg_detector_parity(engine, oracle):
+    """k_dg_hme through me_gpu_dg_detector against the restatement of dg_detector_hme_level0, every metric exact;
+    the golden metrics (frozen from the reference itself) are checked on the way."""
+    import json
+    import os
+    from helpers import DG_CASES, DgPictures
+    gold = {tuple(e["case"]): tuple(e["metrics"]) for e in json.load(open(os.path.join(os.path.dirname(__file__), "golden",
+                                                                                        "dg_metrics.json")))}
+    for case in DG_CASES:
+        w, h, res, kind, a, b = case
+        ps = DgPictures(w, h, kind, oracle)
+        pocs = sorted({a, b})
+        _register(engine, ps, pocs)
+        got = engine.dg_detector(a, b, res)
+        swapped = engine.dg_detector(b, a, res)
+        _release(engine, pocs)
+        assert got == oracle.dg_detector(ps.get(a), ps.get(b), res) == gold[case], case
+        assert swapped == oracle.dg_detector(ps.get(b), ps.get(a), res), case
+
+
+def test_dg_detector_parity_1080p_and_errors(engine, oracle):
+    from helpers import DgPictures
+    from me_b200.engine import MeGpuError
+    for kind, a, b in (("motion", 24, 16), ("blocks", 1, 2)):
+        ps = DgPictures(1920, 1080, kind, oracle)
+        _register(engine, ps, [a, b])
+        got = engine.dg_detector(a, b, 4)
+        with pytest.raises(MeGpuError):
+            engine.dg_detector(a, 999, 4)
+        _release(engine, [a, b])
+        assert got == oracle.dg_detector(ps.get(a), ps.get(b), 4), kind
+    small, big = DgPictures(320, 192, "iid", oracle), DgPictures(640, 360, "iid", oracle)
+    engine.register_picture(1, small.get(1).planes[0], 320, 192)
+    engine.register_picture(2, big.get(2).planes[0], 640, 360)
+    with pytest.raises(MeGpuError):
+        engine.dg_detector(1, 2, 4)
+    _release(engine, [1, 2])

@@ -9,7 +9,9 @@ import re
 import numpy as np
 import pytest
 
-from helpers import PictureSet, derive, used_refs
+import json
+
+from helpers import DG_CASES, DgPictures, PictureSet, derive, used_refs
 from me_b200 import abi, planes
 from me_b200.checkers import Oracle, Reference
 
@@ -140,3 +142,35 @@ def test_reference_simd_equals_reference_c():
     b = ref.me_picture(ps.get(4), refs, p, simd=1)
     bad = planes.compare_outputs(a, b, fields=planes.PRODUCT_FIELDS)
     assert not bad, bad
+
+
+def _dg_golden():
+    return json.load(open(os.path.join(GOLD, "dg_metrics.json")))
+
+
+@pytest.mark.parametrize("entry", _dg_golden(), ids=lambda e: "dg_" + "_".join(str(v) for v in e["case"]))
+def test_dg_detector_reproduces_golden_metrics(oracle, entry):
+    """oracle_dg_detector against DGDetectorMetrics frozen from the reference's dg_detector_hme_level0."""
+    w, h, res, kind, a, b = entry["case"]
+    ps = DgPictures(w, h, kind, oracle)
+    assert list(oracle.dg_detector(ps.get(a), ps.get(b), res)) == entry["metrics"]
+
+
+def test_dg_golden_covers_every_metric():
+    g = _dg_golden()
+    assert [e["case"] for e in g] == [list(c) for c in DG_CASES]
+    for k in range(4):  # every metric is non-zero somewhere, and sum_in_vectors takes both signs
+        assert any(e["metrics"][k] != 0 for e in g)
+    assert any(e["metrics"][3] < 0 for e in g) and any(e["metrics"][3] > 0 for e in g)
+
+
+@have_ref
+@pytest.mark.parametrize("case", DG_CASES[:13], ids=lambda c: "dg_" + "_".join(str(v) for v in c))
+def test_dg_detector_matches_reference(oracle, case):
+    """restatement == the reference's own C == the reference's AVX2 sad_loop behind the RTCD pointer"""
+    ref = Reference()
+    w, h, res, kind, a, b = case
+    ps = DgPictures(w, h, kind, ref)
+    want = ref.dg_detector(ps.get(a), ps.get(b), res, simd=0)
+    assert oracle.dg_detector(ps.get(a), ps.get(b), res) == want
+    assert ref.dg_detector(ps.get(a), ps.get(b), res, simd=1) == want
