@@ -20,6 +20,10 @@
  *   MeGpuOutputs             <- pcs->pa_me_data->me_results[b64] (me_sb_results.h:28-51) and the
  *                               per-b64 pcs arrays written by compute_distortion /
  *                               perform_gm_detection (motion_estimation.c:2964,2838)
+ *   me_gpu_submit with me_type = ME_GPU_ME_MCTF
+ *                            <- the svt_aom_motion_estimation_b64 call of the temporal filter, one (centre,
+ *                               neighbour) pair per job (temporal_filtering.c:3144-3187); results in the tf_*
+ *                               arrays of MeGpuOutputs
  *   me_gpu_dg_detector       <- the TASK_DG_DETECTOR_HME segments of one (source, reference) pair:
  *                               early_hme's dispatch + semaphore wait (pd_process.c:561-625) and
  *                               dg_detector_hme_level0 / early_hme_b64 (pd_process.c:393-560)
@@ -45,6 +49,10 @@ extern "C" {
 
 #define ME_GPU_SUB_SAD_SEARCH 0 /* definitions.h:2071 */
 #define ME_GPU_FULL_SAD_SEARCH 1
+
+/* MeGpuParams.me_type (EbMeType, me_context.h:44-50): the two callers of svt_aom_motion_estimation_b64 on this path */
+#define ME_GPU_ME_MCTF 1 /* temporal-filter ME: one reference, HME + integer search only, early exit on a low HME SAD */
+#define ME_GPU_ME_OPEN_LOOP 3 /* TASK_PAME */
 
 /* error codes (0 = ok); the host maps non-zero to EB_ErrorInsufficientResources / EB_ErrorUndefined */
 #define ME_GPU_OK 0
@@ -140,6 +148,9 @@ typedef struct MeGpuParams {
     uint32_t me_early_exit_th;
     uint32_t me_safe_limit_zz_th;
     uint32_t prev_me_stage_based_exit_th;
+    /* ---- caller of svt_aom_motion_estimation_b64 ---- */
+    uint8_t  me_type; /* ME_GPU_ME_OPEN_LOOP (me_process.c:215) or ME_GPU_ME_MCTF (temporal_filtering.c:3182) */
+    uint16_t tf_me_exit_th; /* me_ctx->tf_me_exit_th = tf_ctrls.me_exit_th (temporal_filtering.c:3171); ME_MCTF only */
 } MeGpuParams;
 
 /* What the encoder knows before svt_aom_sig_deriv_me runs; input of me_gpu_derive_params(). */
@@ -188,6 +199,17 @@ typedef struct MeGpuOutputs {
     uint64_t *hme_sad; /* [b64][2][4] search_results.hme_sad at exit */
     uint8_t  *do_ref; /* [b64][2][4] */
     int16_t  *search_area; /* [b64][2][4][4] final (origin_x, origin_y, width, height) of the integer search */
+    /* ME_GPU_ME_MCTF results (the only product outputs of that mode; the arrays above are not written except the
+     * taps): what the temporal filter reads from the MeContext after the call (temporal_filtering.c:1867-1870,
+     * 2640-2690, 3190-3192) */
+    uint32_t *tf_best_sad; /* [b64][85] p_sb_best_sad[0][0]; MAX_SAD_VALUE where the integer search did not run */
+    uint32_t *tf_best_mv; /* [b64][85] p_sb_best_mv[0][0] */
+    int16_t  *tf_hme_centre; /* [b64][2] search_results[0][0].hme_sc_x, hme_sc_y */
+    uint32_t *tf_hme_sad; /* [b64] search_results[0][0].hme_sad after hme_b64 */
+    uint8_t  *tf_early_exit; /* [b64] 1: hme_sad < tf_me_exit_th, tf_use_pred_64x64_only_th was forced to 0xFF
+                                (motion_estimation.c:3109-3113) and the integer search skipped */
+    uint32_t  tf_tot_horz_blks; /* out: b64s with |hme_sc_x| > |hme_sc_y| (motion_estimation.c:2469-2474) */
+    uint32_t  tf_tot_vert_blks; /* out: the others */
 } MeGpuOutputs;
 
 /* library / device lifecycle -------------------------------------------------------------
@@ -230,6 +252,23 @@ int me_gpu_submit_out(uint64_t picture_number, const MeGpuParams *params,
  * at these offsets gets them with a single device->host copy; any other arrangement works, with one copy per
  * non-adjacent array. */
 int me_gpu_output_layout(int width, int height, const MeGpuParams *params, size_t offsets[11], size_t *total_bytes);
+
+/* What the temporal filter knows before svt_aom_sig_deriv_me_tf runs; input of me_gpu_derive_params_tf(). */
+typedef struct MeGpuTfConfig {
+    uint8_t  hme_me_level; /* pcs->tf_ctrls.hme_me_level, 0..4 (TfControls, definitions.h:166) */
+    uint8_t  qp_opt; /* pcs->tf_ctrls.qp_opt */
+    uint8_t  qp; /* scs->static_config.qp */
+    uint8_t  is_ref; /* centre_pcs->is_ref */
+    uint8_t  temporal_layer_index; /* centre_pcs->temporal_layer_index */
+    uint16_t me_exit_th; /* pcs->tf_ctrls.me_exit_th */
+    uint16_t width; /* luma size, multiple of 8 */
+    uint16_t height;
+    uint64_t picture_number; /* of the centre picture */
+} MeGpuTfConfig;
+/* host-side restatement of svt_aom_sig_deriv_me_tf (enc_mode_config.c:834-874), the tf_enable_hme_* switch
+ * (enc_mode_config.c:1646-1668), set_hme_search_params_mctf(ctx, 0) and the per-call MeContext fields of
+ * produce_temporally_filtered_pic (temporal_filtering.c:3144-3181): one list, one reference */
+int me_gpu_derive_params_tf(const MeGpuTfConfig *cfg, MeGpuParams *params);
 
 /* dynamic-GOP detector ------------------------------------------------------------------- */
 typedef struct MeGpuDgMetrics { /* DGDetectorMetrics, pcs.h:731-737 (seg_completed has no meaning here) */

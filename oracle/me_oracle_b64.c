@@ -575,7 +575,9 @@ static void stage_integer_search(B64Ctx *c) {
             if (!c->do_ref[li][ri])
                 continue;
             int16_t  cx = c->sc_x[li][ri], cy = c->sc_y[li][ri];
-            uint16_t dist = scaled_distance(ref_distance(c, li, ri)); /* me_type != ME_MCTF */
+            uint16_t dist = ref_distance(c, li, ri);
+            if (p->me_type != ME_GPU_ME_MCTF) /* ME:1300-1302 */
+                dist = scaled_distance(dist);
             int16_t  w = (int16_t)OR_MIN(p->me_sa.sa_min.width * dist, p->me_sa.sa_max.width);
             int16_t  h = (int16_t)OR_MIN(p->me_sa.sa_min.height * dist, p->me_sa.sa_max.height);
             if (p->mv_sa_adj_enabled && (!p->mv_sa_adj_nearest_ref_only || ri == 0)) {
@@ -902,7 +904,21 @@ static void stage_gm_detection(B64Ctx *c, const B64Out *o, MeGpuOutputs *out, ui
                         out->rc_me_allow_gm[b] = 1;
 }
 
-/* ME:3076-3153 svt_aom_motion_estimation_b64 for ME_OPEN_LOOP */
+/* what the temporal filter reads from the MeContext after an ME_MCTF call (temporal_filtering.c:1867-1870, 2640-2690) */
+static void tf_outputs(const B64Ctx *c, MeGpuOutputs *out, uint32_t b, int early_exit) {
+    if (out->tf_best_sad) memcpy(out->tf_best_sad + (size_t)b * NPU, c->best_sad[0][0], sizeof c->best_sad[0][0]);
+    if (out->tf_best_mv) memcpy(out->tf_best_mv + (size_t)b * NPU, c->best_mv[0][0], sizeof c->best_mv[0][0]);
+    if (out->tf_hme_centre) {
+        out->tf_hme_centre[2 * b]     = c->sc_x[0][0];
+        out->tf_hme_centre[2 * b + 1] = c->sc_y[0][0];
+    }
+    if (out->tf_hme_sad) out->tf_hme_sad[b] = (uint32_t)c->hme_sad[0][0];
+    if (out->tf_early_exit) out->tf_early_exit[b] = (uint8_t)early_exit;
+}
+
+static void parity_taps(const B64Ctx *c, MeGpuOutputs *out, uint32_t b);
+
+/* ME:3076-3153 svt_aom_motion_estimation_b64 for ME_OPEN_LOOP and ME_MCTF */
 static void me_b64(B64Ctx *c, MeGpuOutputs *out, uint32_t b, uint32_t pu_count) {
     const MeGpuParams *p = c->p;
     init_b64(c);
@@ -917,7 +933,20 @@ static void me_b64(B64Ctx *c, MeGpuOutputs *out, uint32_t b, uint32_t pu_count) 
         if (p->enable_hme_level2_flag) stage_hme_l2(c);
     }
     stage_final_centre(c);
-    const int prune_ref = p->enable_hme_flag; /* me_type != ME_MCTF */
+    if (p->me_type == ME_GPU_ME_MCTF) {
+        /* ME:2469-2474 (end of hme_b64), :3109-3113 early exit, :3126 nothing after the integer search */
+        if (OR_ABS(c->sc_x[0][0]) > OR_ABS(c->sc_y[0][0]))
+            out->tf_tot_horz_blks++;
+        else
+            out->tf_tot_vert_blks++;
+        const int early_exit = c->hme_sad[0][0] < p->tf_me_exit_th;
+        if (!early_exit)
+            stage_integer_search(c);
+        tf_outputs(c, out, b, early_exit);
+        parity_taps(c, out, b);
+        return;
+    }
+    const int prune_ref = p->enable_hme_flag; /* && me_type != ME_MCTF, ME:3103 */
     if (prune_ref)
         stage_hme_prune(c);
     stage_integer_search(c);
@@ -940,7 +969,10 @@ static void me_b64(B64Ctx *c, MeGpuOutputs *out, uint32_t b, uint32_t pu_count) 
     if (p->gm_enabled)
         stage_gm_detection(c, &o, out, b);
 
-    /* parity taps */
+    parity_taps(c, out, b);
+}
+
+static void parity_taps(const B64Ctx *c, MeGpuOutputs *out, uint32_t b) {
     if (out->p_sb_best_sad) memcpy(out->p_sb_best_sad + (size_t)b * NL * NR * NPU, c->best_sad, sizeof c->best_sad);
     if (out->p_sb_best_mv) memcpy(out->p_sb_best_mv + (size_t)b * NL * NR * NPU, c->best_mv, sizeof c->best_mv);
     for (int li = 0; li < NL; li++)
@@ -979,6 +1011,13 @@ int oracle_me_b64_range(const OraclePicture *src, const OraclePicture *const ref
     c->pic_w = pic_w;
     c->pic_h = pic_h;
     const uint32_t pu_count = (uint32_t)exported_pu_count(params);
+    if (params->me_type == ME_GPU_ME_MCTF) {
+        if (params->num_of_list_to_search != 1 || params->num_of_ref_pic_to_search[0] != 1)
+            return ME_GPU_ERR_BAD_ARG;
+        if (first == 0)
+            out->tf_tot_horz_blks = out->tf_tot_vert_blks = 0;
+    } else if (params->me_type != ME_GPU_ME_OPEN_LOOP)
+        return ME_GPU_ERR_BAD_ARG;
     for (uint32_t b = first; b < first + count && b < total; b++) {
         c->org_x = (int32_t)(b % bw) * 64;
         c->org_y = (int32_t)(b / bw) * 64;

@@ -123,7 +123,8 @@ REF_API void ref_pad_full(OraclePicture *pic) {
 }
 
 static void ctx_from_params(MeContext *m, const MeGpuParams *p) {
-    m->me_type                = ME_OPEN_LOOP;
+    m->me_type                = (EbMeType)p->me_type; /* ME_GPU_ME_* carry the EbMeType values */
+    m->tf_me_exit_th          = p->tf_me_exit_th;
     m->num_of_list_to_search  = p->num_of_list_to_search;
     m->num_of_ref_pic_to_search[0] = p->num_of_ref_pic_to_search[0];
     m->num_of_ref_pic_to_search[1] = p->num_of_ref_pic_to_search[1];
@@ -279,6 +280,7 @@ REF_API int ref_derive_params(const MeGpuEncoderConfig *cfg, const RefMrpInputs 
     out->temporal_layer_index            = cfg->temporal_layer_index;
     out->similar_brightness_refs         = cfg->similar_brightness_refs;
     out->is_ref                          = cfg->is_ref;
+    out->me_type                         = ME_GPU_ME_OPEN_LOOP; /* me_process.c:215 */
     free(m);
     free(scs);
     free(pcs);
@@ -369,7 +371,8 @@ REF_API int ref_me_b64_range(const OraclePicture *src, const OraclePicture *cons
         m->quarter_b64_buffer_stride   = sq.stride_y;
         m->sixteenth_b64_buffer        = &ss.buffer_y[(ss.org_y + (oy >> 2)) * ss.stride_y + ss.org_x + (ox >> 2)];
         m->sixteenth_b64_buffer_stride = ss.stride_y;
-        m->me_type                     = ME_OPEN_LOOP;
+        m->me_type                     = (EbMeType)p->me_type;
+        m->tf_use_pred_64x64_only_th   = 1; /* temporal_filtering.c:3174 sets tf_ctrls.use_pred_64x64_only_th; 0xFF marks the exit */
         /* canonical state for data the reference leaves stale between blocks (never read for an output) */
         for (int li = 0; li < 2; li++)
             for (int ri = 0; ri < 4; ri++)
@@ -380,6 +383,16 @@ REF_API int ref_me_b64_range(const OraclePicture *src, const OraclePicture *cons
 
         svt_aom_motion_estimation_b64(pcs, b, ox, oy, m, &sf);
 
+        if (p->me_type == ME_GPU_ME_MCTF) {
+            if (out->tf_best_sad) memcpy(out->tf_best_sad + (size_t)b * 85, m->p_sb_best_sad[0][0], 85 * sizeof(uint32_t));
+            if (out->tf_best_mv) memcpy(out->tf_best_mv + (size_t)b * 85, m->p_sb_best_mv[0][0], 85 * sizeof(uint32_t));
+            if (out->tf_hme_centre) {
+                out->tf_hme_centre[2 * b]     = m->search_results[0][0].hme_sc_x;
+                out->tf_hme_centre[2 * b + 1] = m->search_results[0][0].hme_sc_y;
+            }
+            if (out->tf_hme_sad) out->tf_hme_sad[b] = (uint32_t)m->search_results[0][0].hme_sad;
+            if (out->tf_early_exit) out->tf_early_exit[b] = m->tf_use_pred_64x64_only_th == (uint8_t)~0;
+        }
         if (out->p_sb_best_sad) memcpy(out->p_sb_best_sad + (size_t)b * 2 * 4 * 85, m->p_sb_best_sad, sizeof m->p_sb_best_sad);
         if (out->p_sb_best_mv) memcpy(out->p_sb_best_mv + (size_t)b * 2 * 4 * 85, m->p_sb_best_mv, sizeof m->p_sb_best_mv);
         for (int li = 0; li < 2; li++)
@@ -395,7 +408,53 @@ REF_API int ref_me_b64_range(const OraclePicture *src, const OraclePicture *cons
     }
     out->b64_count = total;
     out->pu_count  = P;
+    if (p->me_type == ME_GPU_ME_MCTF) { /* counted by hme_b64 (ME:2469-2474) over the blocks of this call */
+        out->tf_tot_horz_blks = m->tf_tot_horz_blks;
+        out->tf_tot_vert_blks = m->tf_tot_vert_blks;
+    }
     free(geo); free(rp); free(res); free(md); free(m); free(scs); free(pcs);
+    return 0;
+}
+
+/* static in the reference (temporal_filtering.c:2760): level 0 copies hme_l0_sa_default_tf into hme_l0_sa */
+static void harness_set_hme_search_params_mctf0(MeContext *m) { m->hme_l0_sa = m->hme_l0_sa_default_tf; }
+
+/* The reference's svt_aom_sig_deriv_me_tf (Codec/enc_mode_config.c:834) on a pcs that carries the TfControls fields
+ * it reads; the tf_enable_hme_* switch of svt_aom_sig_deriv_multi_processes (:1646-1668, inside a function that
+ * needs a fully built encoder) is restated. */
+REF_API int ref_derive_params_tf(const MeGpuTfConfig *cfg, MeGpuParams *out) {
+    PictureParentControlSet *pcs = calloc(1, sizeof *pcs);
+    SequenceControlSet      *scs = calloc(1, sizeof *scs);
+    MeContext               *m   = calloc(1, sizeof *m);
+    if (!pcs || !scs || !m)
+        return -1;
+    pcs->scs                   = scs;
+    pcs->tf_ctrls.hme_me_level = cfg->hme_me_level;
+    pcs->tf_ctrls.qp_opt       = cfg->qp_opt;
+    pcs->tf_ctrls.me_exit_th   = cfg->me_exit_th;
+    scs->static_config.qp      = cfg->qp;
+    svt_aom_derive_input_resolution(&scs->input_resolution, (uint32_t)cfg->width * cfg->height);
+    pcs->input_resolution          = scs->input_resolution;
+    pcs->tf_enable_hme_flag        = 1;
+    pcs->tf_enable_hme_level0_flag = 1;
+    pcs->tf_enable_hme_level1_flag = cfg->hme_me_level <= 2;
+    pcs->tf_enable_hme_level2_flag = cfg->hme_me_level == 0;
+    svt_aom_sig_deriv_me_tf(pcs, m);
+    harness_set_hme_search_params_mctf0(m);
+    memset(out, 0, sizeof *out);
+    params_from_ctx(out, m);
+    out->me_type                  = ME_GPU_ME_MCTF;
+    out->tf_me_exit_th            = pcs->tf_ctrls.me_exit_th;
+    out->picture_number           = cfg->picture_number;
+    out->input_resolution         = (uint8_t)scs->input_resolution;
+    out->enable_me_8x8 = out->enable_me_16x16 = 1;
+    out->max_number_of_pus_per_sb = SQUARE_PU_COUNT;
+    out->pcs_temporal_layer_index = out->temporal_layer_index = cfg->temporal_layer_index;
+    out->is_ref                   = cfg->is_ref;
+    out->num_of_list_to_search    = 1;
+    out->num_of_ref_pic_to_search[0] = 1;
+    out->max_refs = out->max_cand = out->max_l0 = 1;
+    free(m); free(scs); free(pcs);
     return 0;
 }
 

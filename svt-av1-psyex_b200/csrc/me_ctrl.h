@@ -189,6 +189,7 @@ ME_HD void mc_stage_init(CtrlCtx *c) {
     if (c->lane == 0) {
         s->ops        = 0;
         s->ops_fs     = 0;
+        s->tf_exit    = 0;
         c->s->pending = PEND_NONE;
     }
 }
@@ -627,7 +628,9 @@ ME_HD void mc_centre_emit(CtrlCtx *c) {
             if (!s->do_ref[li][ri])
                 continue;
             int16_t  cx = s->sc_x[li][ri], cy = s->sc_y[li][ri];
-            uint16_t dist = mc_scaled_distance(mc_ref_distance(c, li, ri));
+            uint16_t dist = mc_ref_distance(c, li, ri);
+            if (p->me_type != ME_GPU_ME_MCTF) /* ME:1300-1302 */
+                dist = mc_scaled_distance(dist);
             int16_t  w = (int16_t)MC_MIN(p->me_sa.sa_min.width * dist, p->me_sa.sa_max.width);
             int16_t  h = (int16_t)MC_MIN(p->me_sa.sa_min.height * dist, p->me_sa.sa_max.height);
             if (p->mv_sa_adj_enabled && (!p->mv_sa_adj_nearest_ref_only || ri == 0)) {
@@ -856,12 +859,23 @@ ME_HD void mc_run_stage(CtrlCtx *c, int stage) {
         mc_consume_pending(c);
         mc_clear_tasks(c);
         MC_SERIAL(c, mc_final_centre(c));
-        if (p->enable_hme_flag) /* prune_ref = enable_hme_flag && me_type != ME_MCTF, ME:3103 */
+        if (p->me_type == ME_GPU_ME_MCTF) { /* ME:3109-3113: a low HME SAD ends the block before the integer search */
+            if (c->lane == 0)
+                c->s->tf_exit = c->s->hme_sad[0][0] < p->tf_me_exit_th;
+            MC_SYNC(c);
+        } else if (p->enable_hme_flag) /* prune_ref = enable_hme_flag && me_type != ME_MCTF, ME:3103 */
             MC_SERIAL(c, mc_hme_prune(c));
-        mc_centre_emit(c);
+        if (!c->s->tf_exit)
+            mc_centre_emit(c);
         break;
-    case ST_PROBE: mc_probe_emit(c); break;
-    case ST_MAIN: mc_main_emit_after_probe(c); break;
+    case ST_PROBE:
+        if (!c->s->tf_exit)
+            mc_probe_emit(c);
+        break;
+    case ST_MAIN:
+        if (!c->s->tf_exit)
+            mc_main_emit_after_probe(c);
+        break;
     default: break;
     }
     MC_SYNC(c);
@@ -1167,6 +1181,23 @@ ME_HD void me_epi_gm(EpiCtx *e) {
             for (int d = 0; d < 2; d++)
                 if (cnt[k][a][d] > total / 2)
                     e->j->flags[1 * nb + b] = 1;
+}
+
+/* ME_MCTF: what the temporal filter reads after the call. Per PU n (any thread), then per block (one thread). */
+ME_HD void me_epi_tf_pu(EpiCtx *e, int n) {
+    const MeJob *j = e->j;
+    j->tf_best_sad[(size_t)e->b * ME_NPU + n] = e->best_sad[0][n];
+    j->tf_best_mv[(size_t)e->b * ME_NPU + n]  = e->best_mv[0][n];
+}
+ME_HD void me_epi_tf_block(EpiCtx *e) {
+    const MeJob    *j = e->j;
+    const B64State *s = e->s;
+    j->tf_hme_centre[2 * e->b]     = s->sc_x[0][0];
+    j->tf_hme_centre[2 * e->b + 1] = s->sc_y[0][0];
+    j->tf_hme_sad[e->b]            = s->hme_sad[0][0];
+    j->tf_early_exit[e->b]         = s->tf_exit;
+    /* ME:2469-2474: the block counts as horizontal or vertical motion (exited blocks too) */
+    MC_OPS_ADD(&j->ops_total[MC_ABS(s->sc_x[0][0]) > MC_ABS(s->sc_y[0][0]) ? 2 : 3], 1);
 }
 
 /* parity taps (MeGpuOutputs debug arrays) */

@@ -41,7 +41,7 @@ struct Slot {
 /* uploaded in one copy at submit; the tail (list header + counters) comes back in one copy */
 struct JobTail {
     FsTileList         list;
-    unsigned long long ops[2];
+    unsigned long long ops[4]; /* byte-SADs, full-search byte-SADs, tf_tot_horz_blks, tf_tot_vert_blks */
 };
 struct JobHead {
     MeJob   job;
@@ -63,6 +63,23 @@ OutLayout output_layout(size_t nb, size_t P, size_t max_cand, size_t max_refs) {
     for (int k = 0; k < 11; k++) {
         const int i = ord[k];
         L.order[k] = i;
+        L.off[i]   = o;
+        L.bytes[i] = b[i];
+        o += b[i];
+    }
+    L.total = o;
+    return L;
+}
+
+/* ME_MCTF jobs use the same slab for the five tf_* arrays of MeGpuOutputs, in struct order */
+struct TfLayout {
+    size_t off[5], bytes[5], total;
+};
+TfLayout tf_layout(size_t nb) {
+    TfLayout     L;
+    const size_t b[5] = {nb * ME_NPU * 4, nb * ME_NPU * 4, nb * 2 * sizeof(int16_t), nb * 4, nb};
+    size_t       o    = 0;
+    for (int i = 0; i < 5; i++) {
         L.off[i]   = o;
         L.bytes[i] = b[i];
         o += b[i];
@@ -182,6 +199,8 @@ int alloc_job(Device &d, JobCtx &jc, const MePicGeom &gm, int max_l0, int max_l1
     jc.d_job  = &jc.d_head->job;
     jc.d_list = &jc.d_head->tail.list;
     jc.out_cap = output_layout(nb, ME_NPU, max_cand ? max_cand : 1, max_refs ? max_refs : 1).total;
+    if (jc.out_cap < tf_layout(nb).total)
+        jc.out_cap = tf_layout(nb).total;
     CU(cudaMalloc((void **)&jc.out_slab, jc.out_cap));
     CU(dalloc(&jc.state, nb));
     CU(dalloc(&jc.tasks, nb * ME_SLOTS));
@@ -495,6 +514,23 @@ static int enqueue_d2h(JobCtx *jc, const MeGpuOutputs *out) {
                         (uint8_t *)out->me_16x16_distortion, (uint8_t *)out->me_8x8_distortion,
                         (uint8_t *)out->me_8x8_cost_variance, (uint8_t *)out->rc_me_distortion,
                         out->stationary_block_present_sb, out->rc_me_allow_gm};
+    if (j.p.me_type == ME_GPU_ME_MCTF) { /* the tf_* arrays are the job's results; adjacent destinations share a copy */
+        const TfLayout T = tf_layout(nb);
+        uint8_t *tdst[5] = {(uint8_t *)out->tf_best_sad, (uint8_t *)out->tf_best_mv, (uint8_t *)out->tf_hme_centre,
+                            (uint8_t *)out->tf_hme_sad, out->tf_early_exit};
+        for (int k = 0; k < 5;) {
+            if (!tdst[k]) {
+                k++;
+                continue;
+            }
+            int    e = k;
+            size_t n = T.bytes[k];
+            while (e + 1 < 5 && tdst[e + 1] && tdst[e + 1] == tdst[k] + n) n += T.bytes[++e];
+            CU(cudaMemcpyAsync(tdst[k], jc->out_slab + T.off[k], n, cudaMemcpyDeviceToHost, st));
+            k = e + 1;
+        }
+        for (auto &d : dst) d = nullptr;
+    }
     /* runs of destination arrays that are exactly adjacent in slab order come back with one copy */
     for (int k = 0; k < 11;) {
         const int i = L.order[k];
@@ -549,6 +585,10 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
         return fail(ME_GPU_ERR_UNSUPPORTED, "low-delay HME-L0 resizing from reference (0,0)'s centre is not implemented");
     if (p.max_number_of_pus_per_sb != ME_NPU)
         return fail(ME_GPU_ERR_UNSUPPORTED, "max_number_of_pus_per_sb must be 85");
+    if (p.me_type != ME_GPU_ME_OPEN_LOOP && p.me_type != ME_GPU_ME_MCTF)
+        return fail(ME_GPU_ERR_BAD_ARG, "me_type must be ME_GPU_ME_OPEN_LOOP or ME_GPU_ME_MCTF");
+    if (p.me_type == ME_GPU_ME_MCTF && (p.num_of_list_to_search != 1 || p.num_of_ref_pic_to_search[0] != 1))
+        return fail(ME_GPU_ERR_BAD_ARG, "temporal-filter ME takes one list with one reference");
     auto it = g.by_number.find(picture_number);
     if (it == g.by_number.end())
         return fail(ME_GPU_ERR_NOT_FOUND, "source picture not registered");
@@ -610,11 +650,21 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
     j.dbg_best_sad = jc->dbg_sad; j.dbg_best_mv = jc->dbg_mv; j.dbg_centre = jc->dbg_centre; j.dbg_hme_sad = jc->dbg_hme;
     j.dbg_do_ref = jc->dbg_do_ref; j.dbg_area = jc->dbg_area;
     j.ops_total = jc->d_head->tail.ops;
+    {
+        const TfLayout T = tf_layout(nb); /* far below the open-loop layout's size */
+        j.tf_best_sad    = (uint32_t *)(jc->out_slab + T.off[0]);
+        j.tf_best_mv     = (uint32_t *)(jc->out_slab + T.off[1]);
+        j.tf_hme_centre  = (int16_t *)(jc->out_slab + T.off[2]);
+        j.tf_hme_sad     = (uint32_t *)(jc->out_slab + T.off[3]);
+        j.tf_early_exit  = jc->out_slab + T.off[4];
+        if (T.total > jc->out_cap)
+            return fail(ME_GPU_ERR_BAD_ARG, "result slab too small for the temporal-filter outputs");
+    }
     JobTail &tl = jc->h_head->tail;
     tl.list.count = tl.list.next = tl.list.overflow = 0;
     tl.list.cap   = jc->tile_cap;
     tl.list.tiles = jc->tiles;
-    tl.ops[0] = tl.ops[1] = 0;
+    tl.ops[0] = tl.ops[1] = tl.ops[2] = tl.ops[3] = 0;
 
     CU(cudaSetDevice(d.id));
     cudaStream_t st = jc->stream;
@@ -828,6 +878,10 @@ int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out) {
     g.last            = t;
     out->b64_count    = (uint32_t)nb;
     out->pu_count     = j.pu_count;
+    if (j.p.me_type == ME_GPU_ME_MCTF) {
+        out->tf_tot_horz_blks = (uint32_t)jc->h_tail->ops[2];
+        out->tf_tot_vert_blks = (uint32_t)jc->h_tail->ops[3];
+    }
     jc->busy          = false;
     for (int s : jc->slots_used) {
         g.slots[s].refcount--;

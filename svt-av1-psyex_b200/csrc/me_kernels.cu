@@ -509,18 +509,29 @@ __global__ void __launch_bounds__(EP_THREADS) k_epilogue(MeJob *jobs) {
     e.me_distortion = me_distortion;
     for (int i = tid; i < ME_NREF * ME_NPU; i += EP_THREADS) me_epi_decode(&e, i / ME_NPU, i % ME_NPU);
     __syncthreads();
-    if (tid == 0 && j->p.enable_hme_flag && j->p.enable_me_hme_ref_pruning)
-        me_epi_prune(&e);
-    __syncthreads();
-    if (tid < j->p.max_number_of_pus_per_sb)
-        me_epi_candidates(&e, tid);
-    __syncthreads();
-    if (tid == 0) {
-        me_epi_distortion(&e);
-        me_epi_gm(&e);
-        me_epi_taps(&e);
-        atomicAdd(&j->ops_total[0], (unsigned long long)e.s->ops);
-        atomicAdd(&j->ops_total[1], (unsigned long long)e.s->ops_fs);
+    if (j->p.me_type == ME_GPU_ME_MCTF) { /* no pruning, candidates or statistics (ME:3103,3126): results of slot (0,0) */
+        if (tid < ME_NPU)
+            me_epi_tf_pu(&e, tid);
+        if (tid == 0) {
+            me_epi_tf_block(&e);
+            me_epi_taps(&e);
+            atomicAdd(&j->ops_total[0], (unsigned long long)e.s->ops);
+            atomicAdd(&j->ops_total[1], (unsigned long long)e.s->ops_fs);
+        }
+    } else {
+        if (tid == 0 && j->p.enable_hme_flag && j->p.enable_me_hme_ref_pruning)
+            me_epi_prune(&e);
+        __syncthreads();
+        if (tid < j->p.max_number_of_pus_per_sb)
+            me_epi_candidates(&e, tid);
+        __syncthreads();
+        if (tid == 0) {
+            me_epi_distortion(&e);
+            me_epi_gm(&e);
+            me_epi_taps(&e);
+            atomicAdd(&j->ops_total[0], (unsigned long long)e.s->ops);
+            atomicAdd(&j->ops_total[1], (unsigned long long)e.s->ops_fs);
+        }
     }
     if (j->dbg_best_sad)
         for (int i = tid; i < ME_NREF * ME_NPU; i += EP_THREADS)

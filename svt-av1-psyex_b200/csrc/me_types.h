@@ -86,6 +86,7 @@ typedef struct B64State {
     uint8_t  searched[ME_NL][ME_NR];
     uint8_t  pend00[ME_NL][ME_NR]; /* check_00_center SADs in flight */
     uint8_t  pending; /* MePending: which task results the next stage has to consume */
+    uint8_t  tf_exit; /* ME_MCTF: hme_sad < tf_me_exit_th, the integer search is skipped (ME:3109-3113) */
     uint64_t ops; /* algorithmic byte-SAD count, SURVEY 8(d) */
     uint64_t ops_fs; /* part of ops spent in the integer full search */
 } B64State;
@@ -157,7 +158,13 @@ typedef struct MeJob {
     uint64_t *dbg_hme_sad;
     uint8_t  *dbg_do_ref;
     int16_t  *dbg_area;
-    unsigned long long *ops_total; /* [2] per job: all byte-SADs, full-search byte-SADs */
+    unsigned long long *ops_total; /* [4] per job: all byte-SADs, full-search byte-SADs, tf_tot_horz_blks, tf_tot_vert_blks */
+    /* ME_MCTF outputs (device mirrors of MeGpuOutputs.tf_*) */
+    uint32_t *tf_best_sad; /* [b64_count][ME_NPU] */
+    uint32_t *tf_best_mv;
+    int16_t  *tf_hme_centre; /* [b64_count][2] */
+    uint32_t *tf_hme_sad; /* [b64_count] */
+    uint8_t  *tf_early_exit; /* [b64_count] */
 } MeJob;
 
 /* geometry of a width x height picture (both multiples of 8) in the pool */

@@ -334,6 +334,70 @@ int me_gpu_derive_params(const MeGpuEncoderConfig *c, MeGpuParams *p) {
         p->me_early_exit_th = m <= ENC_M4 ? 0 : 64 * 64 * 8;
     p->me_safe_limit_zz_th         = mrp.safe_limit_nref == 1 ? mrp.safe_limit_zz_th : 0;
     p->prev_me_stage_based_exit_th = (c->rtc_tune && c->sc_class1) ? 64 * 64 * 4 : 0;
+    p->me_type                     = ME_GPU_ME_OPEN_LOOP; /* me_process.c:215 */
+    return ME_GPU_OK;
+}
+
+/* svt_aom_sig_deriv_me_tf (enc_mode_config.c:834-874) with tf_set_me_hme_params_oq (:598-675), the tf_enable_hme_*
+ * switch of svt_aom_sig_deriv_multi_processes (:1646-1668), set_hme_search_params_mctf(ctx, 0)
+ * (temporal_filtering.c:2760-2768) and the per-call fields of produce_temporally_filtered_pic (:3144-3181). */
+int me_gpu_derive_params_tf(const MeGpuTfConfig *c, MeGpuParams *p) {
+    if (!c || !p || (c->width & 7) || (c->height & 7) || !c->width || !c->height || c->hme_me_level > 4)
+        return ME_GPU_ERR_BAD_ARG;
+    memset(p, 0, sizeof *p);
+    const uint8_t res = input_resolution((uint32_t)c->width * c->height);
+    const int     lvl = c->hme_me_level;
+    p->me_type          = ME_GPU_ME_MCTF;
+    p->tf_me_exit_th    = c->me_exit_th;
+    p->picture_number   = c->picture_number;
+    p->input_resolution = res;
+    /* the centre picture's pcs is handed to the call; candidate construction never runs, so the export switches only
+     * keep their defaults */
+    p->enable_me_16x16 = p->enable_me_8x8 = 1;
+    p->max_number_of_pus_per_sb           = ME_GPU_SQUARE_PU_COUNT;
+    p->pcs_temporal_layer_index = p->temporal_layer_index = c->temporal_layer_index;
+    p->is_ref                      = c->is_ref;
+    p->num_of_list_to_search       = 1;
+    p->num_of_ref_pic_to_search[0] = 1;
+    p->max_refs = p->max_cand = p->max_l0 = 1;
+    p->num_hme_sa_w = p->num_hme_sa_h = 2;
+    /* hme_l0_sa = hme_l0_sa_default_tf, hme_l1_sa, hme_l2_sa, me_sa per level */
+    static const uint16_t t[5][6] = {/* l0 min, l0 max, l1, l2, me min, me max */
+                                     {30, 60, 16, 16, 60, 120}, {16, 32, 16, 16, 16, 32}, {16, 32, 16, 16, 8, 8},
+                                     {8, 8, 8, 8, 8, 8},        {4, 4, 8, 8, 8, 8}};
+    uint16_t l0min = t[lvl][0], l0max = t[lvl][1], l1 = t[lvl][2];
+    if (lvl == 2 && res <= RES_360p) {
+        l0min = l0max = l1 = 8;
+    } else if (lvl == 2 && res <= RES_480p) {
+        l0min = 8;
+        l0max = 16;
+        l1    = 8;
+    }
+    p->hme_l0_sa.sa_min = sa(l0min, l0min);
+    p->hme_l0_sa.sa_max = sa(l0max, l0max);
+    p->hme_l1_sa        = sa(l1, l1);
+    p->hme_l2_sa        = sa(t[lvl][3], t[lvl][3]);
+    p->me_sa.sa_min     = sa(t[lvl][4], t[lvl][4]);
+    p->me_sa.sa_max     = sa(t[lvl][5], t[lvl][5]);
+    if (c->qp_opt) { /* enc_mode_config.c:667-674 */
+        int q = 8 * c->qp - 125;
+        q     = q < 250 ? 250 : q > 1000 ? 1000 : q;
+        const uint16_t qw = (uint16_t)q;
+        p->me_sa.sa_min.width  = (uint16_t)DMAX(8, (p->me_sa.sa_min.width * qw) / 1000);
+        p->me_sa.sa_min.height = (uint16_t)DMAX(8, (p->me_sa.sa_min.height * qw) / 1000);
+        p->me_sa.sa_max.width  = (uint16_t)DMAX(8, (p->me_sa.sa_max.width * qw) / 1000);
+        p->me_sa.sa_max.height = (uint16_t)DMAX(8, (p->me_sa.sa_max.height * qw) / 1000);
+    }
+    p->enable_hme_flag        = 1;
+    p->enable_hme_level0_flag = 1;
+    p->enable_hme_level1_flag = lvl <= 2;
+    p->enable_hme_level2_flag = lvl == 0;
+    p->hme_search_method = p->me_search_method = lvl <= 2 ? ME_GPU_FULL_SAD_SEARCH : ME_GPU_SUB_SAD_SEARCH;
+    set_prehme(p, 0);
+    set_ref_prune(p, 0);
+    set_sr_adjustment(p, 0);
+    p->me_early_exit_th            = lvl <= 1 ? 0 : 64 * 64 * 4;
+    p->prev_me_stage_based_exit_th = lvl <= 1 ? 0 : 64 * 64 * 4;
     return ME_GPU_OK;
 }
 

@@ -50,6 +50,7 @@ class MeGpuParams(C.Structure):
         ("prehme_sa_cfg", SearchAreaMinMax * 2),
         ("prune_me_candidates_th", i32), ("me_early_exit_th", u32), ("me_safe_limit_zz_th", u32),
         ("prev_me_stage_based_exit_th", u32),
+        ("me_type", u8), ("tf_me_exit_th", u16),
     ]
 
     def as_dict(self):
@@ -90,6 +91,14 @@ class MeGpuEncoderConfig(C.Structure):
     ]
 
 
+class MeGpuTfConfig(C.Structure):
+    _fields_ = [("hme_me_level", u8), ("qp_opt", u8), ("qp", u8), ("is_ref", u8), ("temporal_layer_index", u8),
+                ("me_exit_th", u16), ("width", u16), ("height", u16), ("picture_number", u64)]
+
+
+ME_MCTF, ME_OPEN_LOOP = 1, 3  # MeGpuParams.me_type
+
+
 class MeGpuOutputs(C.Structure):
     _fields_ = [
         ("b64_count", u32), ("pu_count", u32),
@@ -102,6 +111,9 @@ class MeGpuOutputs(C.Structure):
         ("p_sb_best_sad", C.POINTER(u32)), ("p_sb_best_mv", C.POINTER(u32)),
         ("hme_search_centre", C.POINTER(i16)), ("hme_sad", C.POINTER(u64)), ("do_ref", C.POINTER(u8)),
         ("search_area", C.POINTER(i16)),
+        ("tf_best_sad", C.POINTER(u32)), ("tf_best_mv", C.POINTER(u32)), ("tf_hme_centre", C.POINTER(i16)),
+        ("tf_hme_sad", C.POINTER(u32)), ("tf_early_exit", C.POINTER(u8)),
+        ("tf_tot_horz_blks", u32), ("tf_tot_vert_blks", u32),
     ]
 
 
@@ -147,7 +159,7 @@ GPU_SYMBOLS = [
     "me_gpu_init", "me_gpu_shutdown", "me_gpu_last_error", "me_gpu_device_count", "me_gpu_register_picture",
     "me_gpu_register_picture_unpadded", "me_gpu_release_picture", "me_gpu_read_pyramid", "me_gpu_plane_geometry",
     "me_gpu_submit", "me_gpu_wait", "me_gpu_derive_params", "me_gpu_get_timings", "me_gpu_measure_sad_peak", "me_gpu_set_profiling", "me_gpu_submit_out", "me_gpu_output_layout",
-    "me_gpu_dg_detector",
+    "me_gpu_dg_detector", "me_gpu_derive_params_tf",
 ]
 
 
@@ -169,6 +181,7 @@ def load_gpu_lib():
     lib.me_gpu_output_layout.argtypes = [C.c_int, C.c_int, C.POINTER(MeGpuParams), C.POINTER(C.c_size_t * 11),
                                          C.POINTER(C.c_size_t)]
     lib.me_gpu_derive_params.argtypes = [C.POINTER(MeGpuEncoderConfig), C.POINTER(MeGpuParams)]
+    lib.me_gpu_derive_params_tf.argtypes = [C.POINTER(MeGpuTfConfig), C.POINTER(MeGpuParams)]
     lib.me_gpu_get_timings.argtypes = [C.POINTER(MeGpuTimings)]
     lib.me_gpu_dg_detector.argtypes = [u64, u64, u8, C.POINTER(MeGpuDgMetrics)]
     lib.me_gpu_measure_sad_peak.restype = C.c_double
@@ -179,5 +192,6 @@ def load_host_lib():
     """Host-only part of the product (me_gpu_derive_params); needs no GPU."""
     lib = C.CDLL(HOST_LIB)
     lib.me_gpu_derive_params.argtypes = [C.POINTER(MeGpuEncoderConfig), C.POINTER(MeGpuParams)]
+    lib.me_gpu_derive_params_tf.argtypes = [C.POINTER(MeGpuTfConfig), C.POINTER(MeGpuParams)]
     lib.me_gpu_derive_mrp_inputs.argtypes = [C.POINTER(MeGpuEncoderConfig), C.POINTER(u8), C.POINTER(u32)]
     return lib

@@ -103,6 +103,14 @@ class Reference:
             raise RuntimeError(f"ref_me_b64_range failed: {rc}")
         return out
 
+    def derive_params_tf(self, cfg):
+        p = abi.MeGpuParams()
+        self.lib.ref_derive_params_tf.argtypes = [C.POINTER(abi.MeGpuTfConfig), C.POINTER(abi.MeGpuParams)]
+        rc = self.lib.ref_derive_params_tf(C.byref(cfg), C.byref(p))
+        if rc != 0:
+            raise RuntimeError("ref_derive_params_tf failed")
+        return p
+
     def derive_params(self, cfg, safe_limit_nref, safe_limit_zz_th):
         p = abi.MeGpuParams()
         mrp = abi.RefMrpInputs(safe_limit_nref, safe_limit_zz_th)

@@ -69,9 +69,15 @@ _OUT_FIELDS = [
     ("hme_sad", np.uint64, lambda P, mc, mr: (2, 4)),
     ("do_ref", np.uint8, lambda P, mc, mr: (2, 4)),
     ("search_area", np.int16, lambda P, mc, mr: (2, 4, 4)),
+    ("tf_best_sad", np.uint32, lambda P, mc, mr: (85,)),
+    ("tf_best_mv", np.uint32, lambda P, mc, mr: (85,)),
+    ("tf_hme_centre", np.int16, lambda P, mc, mr: (2,)),
+    ("tf_hme_sad", np.uint32, lambda P, mc, mr: ()),
+    ("tf_early_exit", np.uint8, lambda P, mc, mr: ()),
 ]
-PRODUCT_FIELDS = [f[0] for f in _OUT_FIELDS[:11]]  # what the encoder consumes
-DEBUG_FIELDS = [f[0] for f in _OUT_FIELDS[11:]]  # parity taps
+PRODUCT_FIELDS = [f[0] for f in _OUT_FIELDS[:11]]  # what the encoder consumes (TASK_PAME)
+DEBUG_FIELDS = [f[0] for f in _OUT_FIELDS[11:17]]  # parity taps
+TF_FIELDS = [f[0] for f in _OUT_FIELDS[17:]]  # what the temporal filter consumes (ME_MCTF jobs)
 
 
 def exported_pu_count(params):
@@ -90,8 +96,11 @@ class Outputs:
         self.arrays = {}
         self.c = abi.MeGpuOutputs()
         self.c.b64_count = self.b64_count
+        tf = params.me_type == abi.ME_MCTF
         for name, dt, shp in _OUT_FIELDS:
             if not debug and name in DEBUG_FIELDS:
+                continue
+            if (name in TF_FIELDS) != tf and name not in DEBUG_FIELDS:
                 continue
             a = np.zeros((self.b64_count,) + shp(P, params.max_cand, params.max_refs), dtype=dt)
             self.arrays[name] = a
@@ -100,6 +109,11 @@ class Outputs:
 
     def __getitem__(self, k):
         return self.arrays[k]
+
+    @property
+    def tf_blocks(self):
+        """(tf_tot_horz_blks, tf_tot_vert_blks) of an ME_MCTF job"""
+        return (int(self.c.tf_tot_horz_blks), int(self.c.tf_tot_vert_blks))
 
 
 def compare_outputs(a, b, fields=None, used_refs=None):

@@ -121,6 +121,10 @@ extern "C" int emul_me_picture(const OraclePicture *src, const OraclePicture *co
     j.me_mv_array              = out->me_mv_array;
     j.dbg_best_sad = out->p_sb_best_sad; j.dbg_best_mv = out->p_sb_best_mv; j.dbg_centre = out->hme_search_centre;
     j.dbg_hme_sad = (uint64_t *)out->hme_sad; j.dbg_do_ref = out->do_ref; j.dbg_area = out->search_area;
+    unsigned long long totals[4] = {0, 0, 0, 0};
+    j.ops_total = totals;
+    j.tf_best_sad = out->tf_best_sad; j.tf_best_mv = out->tf_best_mv; j.tf_hme_centre = out->tf_hme_centre;
+    j.tf_hme_sad = out->tf_hme_sad; j.tf_early_exit = out->tf_early_exit;
 
     const bool     sub = params->me_search_method == ME_GPU_SUB_SAD_SEARCH;
     unsigned long long ops = 0;
@@ -185,6 +189,15 @@ extern "C" int emul_me_picture(const OraclePicture *src, const OraclePicture *co
         e.best_sad = (uint32_t(*)[ME_NPU])bs.data(); e.best_mv = (uint32_t(*)[ME_NPU])bm.data(); e.me_distortion = md.data();
         for (int k = 0; k < ME_NREF; k++)
             for (int n = 0; n < ME_NPU; n++) me_epi_decode(&e, k, n);
+        if (j.p.me_type == ME_GPU_ME_MCTF) {
+            for (int n = 0; n < ME_NPU; n++) me_epi_tf_pu(&e, n);
+            me_epi_tf_block(&e);
+            me_epi_taps(&e);
+            if (j.dbg_best_sad) memcpy(j.dbg_best_sad + (size_t)b * ME_NREF * ME_NPU, bs.data(), bs.size() * 4);
+            if (j.dbg_best_mv) memcpy(j.dbg_best_mv + (size_t)b * ME_NREF * ME_NPU, bm.data(), bm.size() * 4);
+            ops += state[b].ops;
+            continue;
+        }
         if (j.p.enable_hme_flag && j.p.enable_me_hme_ref_pruning)
             me_epi_prune(&e);
         for (int n = 0; n < j.p.max_number_of_pus_per_sb; n++) me_epi_candidates(&e, n);
@@ -201,6 +214,8 @@ extern "C" int emul_me_picture(const OraclePicture *src, const OraclePicture *co
     }
     out->b64_count = (uint32_t)nb;
     out->pu_count  = j.pu_count;
+    out->tf_tot_horz_blks = (uint32_t)totals[2];
+    out->tf_tot_vert_blks = (uint32_t)totals[3];
     if (ops_out)
         *ops_out = ops;
     return ME_GPU_OK;

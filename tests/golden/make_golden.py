@@ -18,7 +18,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(HERE, "..", "..", "svt-av1-psyex_b200", "python"))
 sys.path.insert(0, os.path.join(HERE, ".."))
 
-from helpers import DG_CASES, DgPictures, PictureSet, derive, host_lib  # noqa: E402
+from helpers import DG_CASES, TF_CASES, DgPictures, PictureSet, derive, derive_tf, host_lib  # noqa: E402
+from me_b200 import planes  # noqa: E402
 from me_b200 import abi  # noqa: E402
 from me_b200.checkers import Reference  # noqa: E402
 
@@ -33,6 +34,27 @@ DERIVE_CASES = [(p, w, h, tl) for p in (-3, -2, -1, 0, 1, 2, 3, 4, 5, 6, 7, 8, 9
 
 def case_name(w, h, preset, poc, kind):
     return f"me_{w}x{h}_m{preset}_poc{poc}_{kind}"
+
+
+TF_DERIVE_CASES = [(lvl, w, h, qp_opt, qp) for lvl in range(5) for (w, h) in ((320, 192), (640, 360), (856, 480), (1920, 1080))
+                   for (qp_opt, qp) in ((0, 35), (1, 20), (1, 35), (1, 60))]
+
+
+def make_tf_golden(ref):
+    for (w, h, lvl, kind, c, nb, th) in TF_CASES:
+        ps = PictureSet(w, h, 20, kind, ref)
+        _, p = derive_tf(lvl, w, h, c, me_exit_th=th)
+        out = ref.me_picture(ps.get(c), [[ps.get(nb)], []], p)
+        name = f"tf_{w}x{h}_l{lvl}_{kind}_c{c}_n{nb}_th{th}"
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), tf_blocks=np.array(out.tf_blocks),
+                            **{k: out.arrays[k] for k in planes.TF_FIELDS})
+        print("wrote", name)
+    table = []
+    for (lvl, w, h, qp_opt, qp) in TF_DERIVE_CASES:
+        cfg = abi.MeGpuTfConfig(hme_me_level=lvl, qp_opt=qp_opt, qp=qp, is_ref=1, me_exit_th=777, width=w, height=h, picture_number=8)
+        table.append({"case": [lvl, w, h, qp_opt, qp], "params": ref.derive_params_tf(cfg).as_dict()})
+    json.dump(table, open(os.path.join(HERE, "derive_params_tf.json"), "w"))
+    print("wrote derive_params_tf.json:", len(table), "cases")
 
 
 def main():
@@ -55,6 +77,8 @@ def main():
         table.append({"preset": preset, "width": w, "height": h, "tl": tl, "params": ref.derive_params(cfg, n.value, z.value).as_dict()})
     json.dump(table, open(os.path.join(HERE, "derive_params.json"), "w"))
     print("wrote derive_params.json:", len(table), "cases")
+    # temporal-filter ME (ME_MCTF): tf_* outputs of svt_aom_motion_estimation_b64 + derived controls
+    make_tf_golden(ref)
     # dynamic-GOP detector metrics of dg_detector_hme_level0 (pd_process.c:492)
     dg = []
     for (w, h, res, kind, a, b) in DG_CASES:

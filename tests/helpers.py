@@ -30,6 +30,16 @@ def derive(preset, width, height, poc, n_pictures, force_refs=None, qp=35, **kw)
     return cfg, p, l0, l1
 
 
+def derive_tf(level, width, height, centre, me_exit_th=0, qp_opt=0, qp=35, is_ref=1):
+    """MeGpuParams of a temporal-filter ME call (ME_MCTF) for centre picture `centre`."""
+    cfg = abi.MeGpuTfConfig(hme_me_level=level, qp_opt=qp_opt, qp=qp, is_ref=is_ref, temporal_layer_index=0,
+                            me_exit_th=me_exit_th, width=width, height=height, picture_number=centre)
+    p = abi.MeGpuParams()
+    rc = host_lib().me_gpu_derive_params_tf(C.byref(cfg), C.byref(p))
+    assert rc == 0
+    return cfg, p
+
+
 class PictureSet:
     """Synthetic pictures with CPU-built pyramids (by `builder`: an Oracle or Reference checker)."""
 
@@ -101,3 +111,10 @@ class DgPictures(PictureSet):
             self.builder.build_pyramid(p)
             self.pics[poc] = p
         return super().get(poc)
+
+
+# temporal-filter ME (ME_MCTF) cases: (width, height, tf hme_me_level, kind, centre poc, neighbour poc, me_exit_th)
+TF_CASES = [(320, 192, 0, "motion", 8, 7, 0), (320, 192, 1, "motion", 8, 11, 400), (320, 192, 2, "iid", 4, 5, 20000),
+            (320, 192, 3, "motion", 8, 9, 6000), (320, 192, 4, "iid", 8, 6, 0), (264, 200, 0, "iid", 4, 5, 20000),
+            (264, 200, 1, "motion", 8, 5, 3000), (264, 200, 2, "motion", 8, 11, 400), (200, 136, 3, "iid", 8, 11, 400),
+            (136, 72, 1, "motion", 2, 3, 1000)]

@@ -3,7 +3,7 @@ CPU by tests/emul with scalar stand-ins for the search kernels, against the orac
 search-area rule and the candidate construction without a GPU."""
 import pytest
 
-from helpers import Emulator, PictureSet, derive, used_refs
+from helpers import TF_CASES, Emulator, PictureSet, derive, derive_tf, used_refs
 from me_b200 import planes
 from me_b200.checkers import Oracle
 
@@ -41,3 +41,18 @@ def test_reference_count_variants(tools, force):
     b = emul.me_picture(ps.get(poc), refs, p)
     bad = planes.compare_outputs(a, b, used_refs=used_refs(l0, l1))
     assert not bad, bad
+
+
+@pytest.mark.parametrize("case", TF_CASES, ids=lambda c: "tf_" + "_".join(str(v) for v in c))
+def test_tf_control_logic_matches_oracle(tools, case):
+    """ME_MCTF: unscaled distance, no pruning, early exit before the integer search, tf_* results"""
+    oracle, emul = tools
+    w, h, lvl, kind, c, nb, th = case
+    ps = PictureSet(w, h, 20, kind, oracle)
+    _, p = derive_tf(lvl, w, h, c, me_exit_th=th)
+    refs = [[ps.get(nb)], []]
+    a = oracle.me_picture(ps.get(c), refs, p)
+    b = emul.me_picture(ps.get(c), refs, p)
+    bad = planes.compare_outputs(a, b, fields=planes.TF_FIELDS + planes.DEBUG_FIELDS, used_refs=[1, 0])
+    assert not bad, bad
+    assert a.tf_blocks == b.tf_blocks and a.byte_sad_ops == b.byte_sad_ops

@@ -63,3 +63,37 @@ def test_reference_counts_follow_mrp_levels():
         assert tuple(pn.num_of_ref_pic_to_search) == (n0, n1), preset
         l0, l1 = max(b0, n0), max(b1, n1)
         assert pb.max_refs == l0 + l1 and pb.max_cand == l0 + l1 + l0 * l1 + (l0 - 1) + (1 if l1 == 3 else 0)
+
+
+def _derive_tf(lvl, w, h, qp_opt, qp):
+    cfg = abi.MeGpuTfConfig(hme_me_level=lvl, qp_opt=qp_opt, qp=qp, is_ref=1, me_exit_th=777, width=w, height=h, picture_number=8)
+    p = abi.MeGpuParams()
+    assert host_lib().me_gpu_derive_params_tf(C.byref(cfg), C.byref(p)) == 0
+    return cfg, p
+
+
+def test_tf_against_golden_table():
+    """me_gpu_derive_params_tf against svt_aom_sig_deriv_me_tf outputs frozen from the reference"""
+    table = json.load(open(os.path.join(os.path.dirname(GOLD), "derive_params_tf.json")))
+    assert len(table) == 80
+    for row in table:
+        _, p = _derive_tf(*row["case"])
+        assert p.as_dict() == row["params"], row["case"]
+
+
+@pytest.mark.skipif(not Reference.available(), reason="oracle/_ref not built (needs /root/reference)")
+def test_tf_against_reference():
+    ref = Reference()
+    for lvl in range(5):
+        for (w, h) in ((320, 192), (640, 360), (856, 480), (1280, 720), (3840, 2160)):
+            for (qp_opt, qp) in ((0, 35), (1, 10), (1, 45), (1, 63)):
+                cfg, p = _derive_tf(lvl, w, h, qp_opt, qp)
+                assert p.as_dict() == ref.derive_params_tf(cfg).as_dict(), (lvl, w, h, qp_opt, qp)
+
+
+def test_tf_bad_arguments():
+    p = abi.MeGpuParams()
+    cfg = abi.MeGpuTfConfig(hme_me_level=5, width=320, height=192)
+    assert host_lib().me_gpu_derive_params_tf(C.byref(cfg), C.byref(p)) == -2
+    cfg = abi.MeGpuTfConfig(hme_me_level=1, width=322, height=192)
+    assert host_lib().me_gpu_derive_params_tf(C.byref(cfg), C.byref(p)) == -2

@@ -173,3 +173,64 @@ def test_dg_detector_parity_1080p_and_errors(engine, oracle):
     with pytest.raises(MeGpuError):
         engine.dg_detector(1, 2, 4)
     _release(engine, [1, 2])
+
+
+def _tf_cases():
+    from helpers import TF_CASES
+    return TF_CASES
+
+
+@pytest.mark.parametrize("case", _tf_cases(), ids=lambda c: "tf_" + "_".join(str(v) for v in c))
+def test_tf_me_parity_small(engine, oracle, case):
+    """Temporal-filter ME (me_type = ME_GPU_ME_MCTF) through me_gpu_submit: tf_* results, taps and byte-SAD count."""
+    from helpers import derive_tf
+    w, h, lvl, kind, c, nb, th = case
+    ps = PictureSet(w, h, 20, kind, oracle)
+    _, p = derive_tf(lvl, w, h, c, me_exit_th=th)
+    _register(engine, ps, [c, nb])
+    try:
+        got = engine.me_picture(c, w, h, p, [[nb], []])
+    finally:
+        _release(engine, [c, nb])
+    exp = oracle.me_picture(ps.get(c), [[ps.get(nb)], []], p)
+    bad = planes.compare_outputs(exp, got, fields=planes.TF_FIELDS + planes.DEBUG_FIELDS, used_refs=[1, 0])
+    assert not bad, bad
+    assert exp.tf_blocks == got.tf_blocks and sum(got.tf_blocks) == got.b64_count
+    assert exp.byte_sad_ops == got.byte_sad_ops
+
+
+@pytest.mark.parametrize("lvl,kind,th,first,count", [(0, "motion", 2000, 0, 60), (1, "motion", 0, 230, 60), (2, "iid", 30000, 450, 60)])
+def test_tf_me_parity_1080p_sample(engine, oracle, lvl, kind, th, first, count):
+    from helpers import derive_tf
+    w, h, c, nb = 1920, 1080, 8, 6
+    ps = PictureSet(w, h, 17, kind, oracle)
+    _, p = derive_tf(lvl, w, h, c, me_exit_th=th)
+    _register(engine, ps, [c, nb])
+    try:
+        got = engine.me_picture(c, w, h, p, [[nb], []])
+    finally:
+        _release(engine, [c, nb])
+    exp = oracle.me_picture(ps.get(c), [[ps.get(nb)], []], p, first, count)
+    for name in planes.TF_FIELDS:
+        assert np.array_equal(exp.arrays[name][first:first + count], got.arrays[name][first:first + count]), name
+    assert sum(got.tf_blocks) == 510
+
+
+def test_tf_me_rejects_bad_reference_counts(engine, oracle):
+    from helpers import derive_tf
+    from me_b200.engine import MeGpuError
+    w, h = 320, 192
+    ps = PictureSet(w, h, 9, "motion", oracle)
+    _register(engine, ps, [4, 5])
+    try:
+        _, p = derive_tf(1, w, h, 4)
+        p.num_of_list_to_search = 2
+        p.num_of_ref_pic_to_search[1] = 1
+        with pytest.raises(MeGpuError):
+            engine.submit(4, p, [[5], [5]])
+        _, p = derive_tf(1, w, h, 4)
+        p.me_type = 2
+        with pytest.raises(MeGpuError):
+            engine.submit(4, p, [[5], []])
+    finally:
+        _release(engine, [4, 5])

@@ -11,7 +11,7 @@ import pytest
 
 import json
 
-from helpers import DG_CASES, DgPictures, PictureSet, derive, used_refs
+from helpers import DG_CASES, TF_CASES, DgPictures, PictureSet, derive, derive_tf, used_refs
 from me_b200 import abi, planes
 from me_b200.checkers import Oracle, Reference
 
@@ -174,3 +174,47 @@ def test_dg_detector_matches_reference(oracle, case):
     want = ref.dg_detector(ps.get(a), ps.get(b), res, simd=0)
     assert oracle.dg_detector(ps.get(a), ps.get(b), res) == want
     assert ref.dg_detector(ps.get(a), ps.get(b), res, simd=1) == want
+
+
+def _tf_name(case):
+    w, h, lvl, kind, c, nb, th = case
+    return f"tf_{w}x{h}_l{lvl}_{kind}_c{c}_n{nb}_th{th}"
+
+
+@pytest.mark.parametrize("case", TF_CASES, ids=_tf_name)
+def test_oracle_reproduces_tf_golden_vectors(oracle, case):
+    """ME_MCTF: the tf_* results frozen from the reference's svt_aom_motion_estimation_b64 with me_type = ME_MCTF."""
+    w, h, lvl, kind, c, nb, th = case
+    gold = np.load(os.path.join(GOLD, _tf_name(case) + ".npz"))
+    ps = PictureSet(w, h, 20, kind, oracle)
+    _, p = derive_tf(lvl, w, h, c, me_exit_th=th)
+    out = oracle.me_picture(ps.get(c), [[ps.get(nb)], []], p)
+    for name in planes.TF_FIELDS:
+        assert np.array_equal(out.arrays[name], gold[name]), name
+    assert out.tf_blocks == tuple(gold["tf_blocks"])
+
+
+def test_tf_golden_covers_both_exits():
+    ex = [np.load(os.path.join(GOLD, _tf_name(c) + ".npz"))["tf_early_exit"] for c in TF_CASES]
+    assert any(e.all() for e in ex) and any(not e.any() for e in ex) and any(e.any() and not e.all() for e in ex)
+
+
+@have_ref
+@pytest.mark.parametrize("case", TF_CASES, ids=_tf_name)
+def test_oracle_matches_reference_tf_me(oracle, case):
+    ref = Reference()
+    w, h, lvl, kind, c, nb, th = case
+    ps = PictureSet(w, h, 20, kind, ref)
+    _, p = derive_tf(lvl, w, h, c, me_exit_th=th)
+    refs = [[ps.get(nb)], []]
+    a = oracle.me_picture(ps.get(c), refs, p)
+    b = ref.me_picture(ps.get(c), refs, p)
+    b1 = ref.me_picture(ps.get(c), refs, p, simd=1)
+    assert not planes.compare_outputs(a, b, fields=planes.TF_FIELDS)
+    assert not planes.compare_outputs(b, b1, fields=planes.TF_FIELDS)
+    assert a.tf_blocks == b.tf_blocks == b1.tf_blocks
+    # taps of the one reference, except the SADs of exited blocks (stale MeContext memory in the reference)
+    live = a.arrays["tf_early_exit"] == 0
+    for name in ("p_sb_best_mv", "hme_search_centre", "hme_sad"):
+        assert np.array_equal(a.arrays[name][:, 0, 0], b.arrays[name][:, 0, 0]), name
+    assert np.array_equal(a.arrays["p_sb_best_sad"][live, 0, 0], b.arrays["p_sb_best_sad"][live, 0, 0])
