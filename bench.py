@@ -372,9 +372,14 @@ def gpu_main(args):
         peaks = json.load(open(os.path.join(REPO, "MEASURED_PEAKS.json")))
     except Exception:
         pass
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the one `ncu --set full` capture
+    # of this workload kept under profiles/ (ncu_r1_k_hme_final_details.txt, ncu_r1_k_fullsearch_final_details.txt)
+    ncu_traffic = {("motion", "k_hme"): 15201536 + 512, ("iid", "k_fullsearch"): 13067776}
     roofline = {
         "bound": "int_sad", "kernel": dom, "achieved": achieved, "peak": sad_peak / 1e12, "unit": "Tbyte-SAD/s",
-        "frac": achieved / (sad_peak / 1e12) if sad_peak else None, "traffic": None,
+        "frac": achieved / (sad_peak / 1e12) if sad_peak else None, "traffic": ncu_traffic.get((args.kind, dom)),
+        "traffic_unit": "DRAM bytes per launch (one picture); the planes a picture's search touches are ~3.3 MB each",
+        "hbm_gbs_achieved": (ncu_traffic.get((args.kind, dom), 0) * 16 / (dom_ms * 1e-3) / 1e9) if dom_ms > 0 else None,
         "peak_source": "VABSDIFF4.U8.ACC issue rate measured live by k_sad_peak on this GPU x 4 bytes",
         "launches_per_step": 16,  # one k_hme, one k_fullsearch and one k_epilogue launch per picture
         "kernels": kernels, "serial_ms_per_step": prof["total_ms"],
