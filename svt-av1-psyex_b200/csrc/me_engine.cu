@@ -188,7 +188,7 @@ int alloc_job(Device &d, JobCtx &jc, const MePicGeom &gm, int max_l0, int max_l1
     jc.device    = d.id;
     jc.cap_cands = nb * ME_NPU * (max_cand ? max_cand : 1);
     jc.cap_mvs   = nb * ME_NPU * (max_refs ? max_refs : 1);
-    jc.tile_cap  = (uint32_t)(nb * ME_NREF * 64);
+    jc.tile_cap  = (uint32_t)(nb * ME_NREF * 64 * (32 / FS_TH));
     CU(cudaStreamCreateWithFlags(&jc.stream, cudaStreamNonBlocking));
     for (auto &e : jc.ev) CU(cudaEventCreate(&e));
     for (auto &e : jc.pev) CU(cudaEventCreate(&e));
@@ -725,7 +725,7 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
         static const int skip = getenv("ME_GPU_SKIP") ? atoi(getenv("ME_GPU_SKIP")) : 0; /* timing experiments only: results wrong */
         pbegin(3);
         if (!(skip & 1))
-            me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, d.sms * 2, st);
+            me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, d.sms * FS_CTAS_PER_SM, st);
         pend();
     } else {
         const bool zz   = p.me_early_exit_th || p.me_safe_limit_zz_th;
@@ -760,7 +760,7 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
         mask |= 1u << ST_CENTRE;
         flush(ME_NREF * 2);
         if (prof) CU(cudaEventRecord(jc->ev[1], st));
-        const int fs_ctas = d.sms * 2;
+        const int fs_ctas = d.sms * FS_CTAS_PER_SM;
         pbegin(0);
         me_launch_ctrl(jc->d_job, 1, nbi, 1u << ST_PROBE, jc->d_list, st);
         pend();

@@ -275,10 +275,9 @@ __global__ void __launch_bounds__(KS_THREADS) k_search(const MeJob *jobs, const 
 /* ------------------------------------------------------------------------------------------------
  * k_fullsearch: integer full search, all 85 square PUs per position
  * ---------------------------------------------------------------------------------------------- */
-#define FS_THREADS 256
 #define FS_PW 36 /* words per window row and copy: 4 x odd, so that 8 rows hit 8 distinct 16-byte bank groups */
-#define FS_ROWS 96 /* FS_TH + 63 window rows (+1) */
-#define FS_KEY_SHIFT 11 /* 64 x 32 tile positions */
+#define FS_ROWS (FS_TH + 64) /* FS_TH + 63 window rows (+1) */
+#define FS_KEY_SHIFT 11 /* up to 64 x 32 tile positions */
 #define FS_BIAS (1u << 17) /* added to the 8x8 SADs of positions outside the tile: they can never win */
 #define FS_SMEM_BYTES ((4 * FS_ROWS * FS_PW + 64 * 16 + 96) * 4)
 
@@ -394,7 +393,7 @@ __device__ __forceinline__ void fs_compute(const uint32_t *__restrict__ wc, cons
     }
 }
 
-__global__ void __launch_bounds__(FS_THREADS, 2) k_fullsearch(MeJob *jobs, FsTileList *list, const uint8_t *pool) {
+__global__ void __launch_bounds__(FS_THREADS, FS_CTAS_PER_SM) k_fullsearch(MeJob *jobs, FsTileList *list, const uint8_t *pool) {
     extern __shared__ __align__(16) uint32_t fs_smem[];
     uint32_t *win   = fs_smem; /* [4][FS_ROWS][FS_PW] */
     uint32_t *srcw  = fs_smem + 4 * FS_ROWS * FS_PW; /* [64][16] (32 rows used for sub-sampled SAD) */

@@ -6,8 +6,12 @@
 
 #include "me_types.h"
 
-#define FS_TW 64 /* full-search tile: 64 x 32 search positions per CTA iteration */
-#define FS_TH 32
+#define FS_TW 64 /* full-search tile: 64 x FS_TH search positions per CTA iteration, one warp per 32 x 8 positions */
+#ifndef FS_TH
+#define FS_TH 16
+#endif
+#define FS_THREADS (FS_TH * 8)
+#define FS_CTAS_PER_SM (512 / FS_THREADS) /* 128 registers per thread */
 
 typedef struct FsTileList {
     unsigned int count; /* tiles appended by k_ctrl */
