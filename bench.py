@@ -13,6 +13,7 @@ whole hot path: pyramid, pre-HME/HME, integer full search, candidate constructio
   cpu_baseline  the reference's own svt_aom_motion_estimation_b64 + AVX2 kernels (oracle/_ref) on the host cores
 
 Usage: python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--kind motion|iid]
+                       [--workload 1080p-m4|1080p-m8|4k-m2|4k-m0]   (the other BASELINE.json configs)
 Under torchrun every rank runs the same workload on its own GPU (weak scaling, no collective on the path).
 """
 import argparse
@@ -33,8 +34,35 @@ sys.path.insert(0, os.path.join(REPO, "tests"))
 
 from me_b200 import abi, planes, synth  # noqa: E402
 
+# BASELINE.json configs -> concrete workloads. `refs` None = what the preset's mrp level gives (4 + 3 at presets <= 5).
+# `sets` = resident copies of the sequence used in rotation (inputs larger than the 126 MB L2 either way);
+# `cpu_every` = the CPU arms time every n-th chunk of 6 b64s of each picture (a bounded sample, scaled back up).
+WORKLOADS = {
+    "1080p-m4": dict(w=1920, h=1080, preset=4, refs=(2, 2), sets=3, cpu_every=1, baseline_config=1,
+                     text="1080p 8-bit preset 4, mini-GOP 16, 2 refs/list, default HME + integer search areas"),
+    "1080p-m8": dict(w=1920, h=1080, preset=8, refs=(1, 1), sets=3, cpu_every=1, baseline_config=0,
+                     text="1080p 8-bit preset 8, mini-GOP 16, 1 ref/list (configs[3] = this workload, one stream per GPU)"),
+    "4k-m2": dict(w=3840, h=2160, preset=2, refs=None, sets=2, cpu_every=8, baseline_config=2,
+                  text="4K 10-bit source (8-bit ME planes) preset 2, mini-GOP 16, 4 + 3 refs, search areas up to 128x128 (x2 by MV)"),
+    "4k-m0": dict(w=3840, h=2160, preset=0, refs=None, sets=2, cpu_every=48, baseline_config=4,
+                  text="4K 8-bit preset 0, mini-GOP 16, 4 + 3 refs, HME-L0 up to 480x480, integer search up to 256x256 (x2 by MV)"),
+}
+WORKLOAD = "1080p-m4"
 W, H, PRESET, NPIC, FORCE_REFS = 1920, 1080, 4, 33, (2, 2)
 NSETS, SET_STRIDE = 3, 1000  # copies of the sequence in the pool (distinct picture numbers: poc + 1000 * set)
+CPU_EVERY = 1
+
+
+def set_workload(name):
+    global WORKLOAD, W, H, PRESET, FORCE_REFS, NSETS, CPU_EVERY
+    wl = WORKLOADS[name]
+    WORKLOAD, W, H, PRESET, FORCE_REFS, NSETS, CPU_EVERY = name, wl["w"], wl["h"], wl["preset"], wl["refs"], wl["sets"], wl["cpu_every"]
+
+
+def b64_count():
+    return ((W + 63) // 64) * ((H + 63) // 64)
+
+
 # decode order of mini-GOP 2 (POC 17..32)
 STEP_POCS = [32 if g == 0 else 16 + g for g in synth.RA5_DECODE_ORDER]
 
@@ -138,7 +166,7 @@ class CpuArm:
                 pics[k] = p
             return pics[k]
 
-        self.work, self.keep = [], []
+        self.work, self.keep, self.b64_done = [], [], 0
         for poc in pocs:
             cfg, p, l0, l1 = derive(poc)
             refs = [[get(k) for k in l0], [get(k) for k in l1]]
@@ -146,23 +174,35 @@ class CpuArm:
             arr, keep = checkers._refs_array(refs)
             s = get(poc).c_struct()
             self.keep.append((refs, out, arr, keep, s, p))
-            for first in range(0, 510, 6):  # 510 b64 per picture in chunks of 6
-                self.work.append((s, arr, p, out, first))
+            chunks = list(range(0, b64_count(), 6))  # the picture's b64s in chunks of 6 ...
+            for first in chunks[(7 * len(self.keep)) % CPU_EVERY::CPU_EVERY]:  # ... every CPU_EVERY-th of them
+                count = min(6, b64_count() - first)
+                self.work.append((s, arr, p, out, first, count))
+                self.b64_done += count
         # fill the RTCD table on one thread before fanning out
-        s, arr, p, out, _ = self.work[0]
+        s, arr, p, out, _, _ = self.work[0]
         self.ref.lib.ref_me_b64_range(C.byref(s), C.byref(arr), C.byref(p), C.byref(out.c), 0, 1, simd)
         self.pool = ThreadPoolExecutor(threads)
 
     def _run(self, item):
-        s, arr, p, out, first = item
-        rc = self.ref.lib.ref_me_b64_range(C.byref(s), C.byref(arr), C.byref(p), C.byref(out.c), first, 6, self.simd)
+        s, arr, p, out, first, count = item
+        rc = self.ref.lib.ref_me_b64_range(C.byref(s), C.byref(arr), C.byref(p), C.byref(out.c), first, count, self.simd)
         assert rc == 0
 
     def step(self):
-        """ME of every picture of the arm once; returns seconds"""
+        """ME of the sampled b64s of every picture of the arm once; returns seconds"""
         t0 = time.perf_counter()
         list(self.pool.map(self._run, self.work))
         return time.perf_counter() - t0
+
+    def pictures(self):
+        """whole pictures' worth of b64s one step() covers"""
+        return self.b64_done / b64_count()
+
+    def sample_text(self):
+        return (f"all {b64_count()} b64 of each of the step's {len(self.pocs)} pictures" if CPU_EVERY == 1 else
+                f"every {CPU_EVERY}th chunk of 6 b64s of each of the step's {len(self.pocs)} pictures "
+                f"({self.b64_done} of {len(self.pocs) * b64_count()} b64, frames/s scaled by the b64 count)")
 
 
 def cpu_model():
@@ -186,9 +226,8 @@ def reference_main(args):
     t_total = 0.0
     for _ in range(args.steps):
         t_total += arm.step()
-    n = 16 * args.steps
-    value = n / t_total
-    sample = f"the 16 pictures of the step, all 510 b64 each, per step; {threads} threads"
+    value = arm.pictures() * args.steps / t_total
+    sample = f"{arm.sample_text()}, per step; {threads} threads"
     line = {
         "impl": "reference", "metric": "open-loop ME frames/sec", "value": value, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_total / max(1, args.steps),
@@ -203,11 +242,13 @@ def reference_main(args):
 
 
 def workload_config(kind):
-    return {"workload": "1080p 8-bit preset 4, mini-GOP 16, 2 refs/list, default HME + integer search areas "
-                        "(BASELINE.json configs[1])", "width": W, "height": H, "preset": PRESET, "refs": list(FORCE_REFS),
+    wl = WORKLOADS[WORKLOAD]
+    set_mb = NPIC * (W + 136 + 120) * (H + 136) * 21 // 16 / 1e6  # three planes of a picture ~ 21/16 of the padded full plane
+    return {"workload": f"{wl['text']} (BASELINE.json configs[{wl['baseline_config']}])", "name": WORKLOAD, "width": W,
+            "height": H, "preset": PRESET, "refs": list(FORCE_REFS) if FORCE_REFS else "preset default (4 + 3)",
             "pictures_per_step": 16, "sequence": f"synthetic {kind}, seed 1234, 33 pictures", "qp": 35,
-            "l2": f"inputs larger than L2: {NSETS} resident copies of the sequence ({NSETS} x 109 MB of planes) used in "
-                  "rotation, step k reads copy k % 3"}
+            "l2": f"inputs larger than L2: {NSETS} resident copies of the sequence ({NSETS} x {set_mb:.0f} MB of planes) used "
+                  f"in rotation, step k reads copy k % {NSETS}"}
 
 
 # --------------------------------------------------------------------------------------------------
@@ -374,12 +415,13 @@ def gpu_main(args):
         pass
     # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the one `ncu --set full` capture
     # of this workload kept under profiles/ (ncu_r1_k_hme_final_details.txt, ncu_r1_k_fullsearch_final_details.txt)
-    ncu_traffic = {("motion", "k_hme"): 15201536 + 512, ("iid", "k_fullsearch"): 13067776}
+    ncu_traffic = {("1080p-m4", "motion", "k_hme"): 15201536 + 512, ("1080p-m4", "iid", "k_fullsearch"): 13067776}
+    ncu_key = (WORKLOAD, args.kind, dom)
     roofline = {
         "bound": "int_sad", "kernel": dom, "achieved": achieved, "peak": sad_peak / 1e12, "unit": "Tbyte-SAD/s",
-        "frac": achieved / (sad_peak / 1e12) if sad_peak else None, "traffic": ncu_traffic.get((args.kind, dom)),
-        "traffic_unit": "DRAM bytes per launch (one picture); the planes a picture's search touches are ~3.3 MB each",
-        "hbm_gbs_achieved": (ncu_traffic.get((args.kind, dom), 0) * 16 / (dom_ms * 1e-3) / 1e9) if dom_ms > 0 else None,
+        "frac": achieved / (sad_peak / 1e12) if sad_peak else None, "traffic": ncu_traffic.get(ncu_key),
+        "traffic_unit": "DRAM bytes per launch (one picture); the planes a picture's search touches are ~3.3 MB each at 1080p",
+        "hbm_gbs_achieved": (ncu_traffic[ncu_key] * 16 / (dom_ms * 1e-3) / 1e9) if dom_ms > 0 and ncu_key in ncu_traffic else None,
         "peak_source": "VABSDIFF4.U8.ACC issue rate measured live by k_sad_peak on this GPU x 4 bytes",
         "launches_per_step": 16,  # one k_hme, one k_fullsearch and one k_epilogue launch per picture
         "kernels": kernels, "serial_ms_per_step": prof["total_ms"],
@@ -396,9 +438,9 @@ def gpu_main(args):
         while dt < 4.0 and reps < 20:
             dt += arm.step()
             reps += 1
-        cpu_baseline = {"value": 16 * reps / dt, "unit": "frames/s", "cores": threads, "kind": "reference",
-                        "sample": f"the step's 16 pictures x {reps} repetitions, all 510 b64 each, {dt:.1f} s wall on "
-                                  f"{threads} threads", "cpu": cpu_model(), "simd": "avx2"}
+        cpu_baseline = {"value": arm.pictures() * reps / dt, "unit": "frames/s", "cores": threads, "kind": "reference",
+                        "sample": f"{arm.sample_text()} x {reps} repetitions, {dt:.1f} s wall on {threads} threads",
+                        "cpu": cpu_model(), "simd": "avx2"}
     if rank == 0:
         line = {
             "metric": "open-loop ME frames/sec", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
@@ -423,7 +465,10 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--kind", default="motion", choices=["motion", "iid"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--workload", default="1080p-m4", choices=sorted(WORKLOADS),
+                    help="BASELINE.json config to run (default: configs[1], the one the metric is quoted on at N=1)")
     args = ap.parse_args()
+    set_workload(args.workload)
     if args.impl == "reference":
         return reference_main(args)
     return gpu_main(args)

@@ -165,20 +165,27 @@ cudaError_t dalloc(T **p, size_t n) {
     return cudaMalloc((void **)p, n * sizeof(T));
 }
 
-uint32_t max_tiles_per_task(const MeGpuParams *p) {
-    /* upper bound of the main search area: sa_max, x mv-based multiplier, x1.5 for high variance, rounded */
-    uint32_t w = p->me_sa.sa_max.width, h = p->me_sa.sa_max.height;
-    if (p->mv_sa_adj_enabled) {
-        w *= p->mv_sa_adj_sa_multiplier;
-        h *= p->mv_sa_adj_sa_multiplier;
+uint64_t max_tiles_per_b64(const MeGpuParams *p) {
+    /* upper bound of the tiles one b64 can emit: every searched reference at sa_max (x1.5 for high 8x8 variance),
+       the references the MV-based adjustment applies to (reference 0 of each list when nearest_ref_only) x multiplier */
+    auto tiles = [&](uint32_t mult) -> uint64_t {
+        uint32_t w = p->me_sa.sa_max.width * mult, h = p->me_sa.sa_max.height * mult;
+        if (p->me_sr_mult2_th != 0xFFFFFFFFu) {
+            w = w * 3 / 2;
+            h = h * 3 / 2;
+        }
+        w = (w + 7) & ~7u; /* ME:1314 */
+        h = h < 3 ? 3 : h;
+        return (uint64_t)((w + FS_TW - 1) / FS_TW) * ((h + FS_TH - 1) / FS_TH);
+    };
+    uint32_t nref = 0, nmult = 0;
+    for (uint32_t li = 0; li < p->num_of_list_to_search && li < ME_NL; li++) {
+        const uint32_t n = p->num_of_ref_pic_to_search[li] < ME_NR ? p->num_of_ref_pic_to_search[li] : ME_NR;
+        nref += n;
+        if (p->mv_sa_adj_enabled)
+            nmult += p->mv_sa_adj_nearest_ref_only ? (n ? 1u : 0u) : n;
     }
-    if (p->me_sr_mult2_th != 0xFFFFFFFFu) {
-        w = w * 3 / 2;
-        h = h * 3 / 2;
-    }
-    w = (w + 7 + 8) & ~7u;
-    h = h < 3 ? 3 : h;
-    return ((w + FS_TW - 1) / FS_TW) * ((h + FS_TH - 1) / FS_TH);
+    return (nref - nmult) * tiles(1) + nmult * tiles(p->mv_sa_adj_enabled ? p->mv_sa_adj_sa_multiplier : 1);
 }
 
 int alloc_job(Device &d, JobCtx &jc, const MePicGeom &gm, int max_l0, int max_l1) {
@@ -637,7 +644,7 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
     const OutLayout L = output_layout(nb, j.pu_count, p.max_cand, p.max_refs);
     if (L.total > jc->out_cap)
         return fail(ME_GPU_ERR_BAD_ARG, "max_cand / max_refs exceed what me_gpu_init allocated");
-    if ((uint64_t)max_tiles_per_task(&p) * nb * ME_NREF > jc->tile_cap)
+    if (max_tiles_per_b64(&p) * nb > jc->tile_cap)
         return fail(ME_GPU_ERR_UNSUPPORTED, "search area too large for the tile list");
     if (out && out->b64_count < nb)
         return fail(ME_GPU_ERR_BAD_ARG, "MeGpuOutputs.b64_count is smaller than the picture's b64 count");

@@ -73,6 +73,9 @@ struct HmJobD { /* one window job, 32 bytes */
 #ifdef ME_HME_TRACE
 __device__ unsigned g_trace_cnt;
 #endif
+/* search areas at least this wide / with at least this many 8-position units take hm_job_search8 (tunable by
+   ME_HME_K8_MIN_PW / ME_HME_K8_MIN_UNITS for experiments) */
+__device__ int g_k8_min_pw = 64, g_k8_min_units = 96;
 
 struct HmeShared {
     B64State           s;
@@ -83,7 +86,8 @@ struct HmeShared {
     int                item_first[ME_SLOTS + 1]; /* prefix sums: items of task i are [first[i], first[i+1]) */
     int                item_rows[ME_SLOTS]; /* search rows per item */
     int                next_item;
-    int                team; /* warps per window job in this stage (4 / team jobs are searched at a time) */
+    int                team; /* warps per window job in this round (4 / team jobs are searched at a time) */
+    int                next_lo; /* first task of the next round of window jobs */
     HmPlan             plan[ME_SLOTS];
     int                job_first[ME_SLOTS + 1]; /* prefix sums of the window jobs */
     alignas(8) unsigned long long mbar[HM_NBAR]; /* TMA completion of the windows in flight */
@@ -374,18 +378,24 @@ __device__ void hm_plan_task(const SearchTask &t, const MeJob *j, int org_x, int
     const int ne_max   = (rows_cap - span - 1) / ymul + 1;
     if (rows_cap < span + 1 || ne_max < 1 || nxb > 255)
         return;
-    const int kx      = (t.bw == 16 && pwb >= 16) ? 4 : 2;
+    int       kx      = (t.bw == 16 && pwb >= 16) ? 4 : 2;
     const int ncls    = min(4, pwb), per_cls = (pwb + 3) >> 2, nchunk = (per_cls + kx - 1) / kx;
     const int nyb = (erows + ne_max - 1) / ne_max, neb = (erows + nyb - 1) / nyb;
     if (nyb > 255)
         return;
-    const int units   = ncls * nchunk * neb;
+    int       units   = ncls * nchunk * neb;
+    /* wide areas of 16-byte block rows: units of 8 positions on 32-byte window segments (hm_job_search8), one lane each */
+    const bool wide = t.bw == 16 && pwb >= g_k8_min_pw && 4 * ((pwb + 31) >> 5) * neb >= g_k8_min_units;
+    if (wide) {
+        kx    = 8;
+        units = 4 * (((15 + pwb - 1) >> 5) + 1) * neb;
+    }
     const int win     = pitch * (((neb - 1) * ymul + span + 1 + hm_map_rows(map) - 1) / hm_map_rows(map) * hm_map_rows(map));
     /* jobs of few units are searched by one warp each, four at a time per CTA, when four windows fit the ring (measured:
        two warps per job with the next batch in flight is slower than one warp per job and no prefetch of the next batch) */
-    pl.team = (uint8_t)(units <= 16 && win <= HM_RING_BYTES / 4 ? 1 : 4);
+    pl.team = (uint8_t)(!wide && units <= 16 && win <= HM_RING_BYTES / 4 ? 1 : 4);
     int g_log2 = 2 - lv; /* lanes per unit: the 16-byte column segments of the block row ... */
-    while (g_log2 < 5 && (pl.team < 4 ? (units << (g_log2 + 1)) <= 32 * pl.team : (units << g_log2) < 96) &&
+    while (!wide && g_log2 < 5 && (pl.team < 4 ? (units << (g_log2 + 1)) <= 32 * pl.team : (units << g_log2) < 96) &&
            ((2 << g_log2) >> (2 - lv)) <= (int)t.rows)
         g_log2++; /* ... x row groups: up to the team's worth of lanes */
     pl.pwb = (int16_t)pwb;
@@ -431,6 +441,13 @@ __device__ void hm_job_decode(const SearchTask *tasks, const HmPlan *plans, cons
     J.dep    = -1;
     J.m_chunk = hm_magic((uint32_t)nchunk);
     J.m_cls   = hm_magic((uint32_t)ncls);
+    if (pl.kx == 8) { /* hm_job_search8: (byte class, 32-byte segment of the window row, search row) */
+        const int nseg = (((int)J.aoff + pw - 1) >> 5) + 1;
+        J.ncls    = 4;
+        J.nchunk  = (uint8_t)nseg;
+        J.total   = (uint16_t)(4 * nseg * ne);
+        J.m_chunk = hm_magic((uint32_t)nseg);
+    }
 }
 
 /* Thread 0, before the CTA searches job `jb`: request the windows of the following jobs while the ring has room.
@@ -506,6 +523,69 @@ __device__ __forceinline__ unsigned long long hm_job_search(const HmJobD &J, con
             for (int k = 0; k < KX; k++) {
                 const int x = ca + 4 * (KX * chunk + k);
                 if (x < J.pw && acc[k] < ME_SAD_LOOP_INIT) {
+                    const unsigned long long cand = ((unsigned long long)acc[k] << 32) | (idx0 + (uint32_t)x);
+                    key                           = cand < key ? cand : key;
+                }
+            }
+        }
+    }
+    for (int d = 16; d; d >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, d);
+        key                            = other < key ? other : key;
+    }
+    return key;
+}
+
+/* Wide search areas of 16-byte block rows (pre-HME / HME level 0 on the sixteenth plane). A lane owns the 8 positions
+ * whose block rows start at bytes 32m + c + 4k (k = 0..7) of window row e: the 12 aligned words of the segment come in
+ * with three LDS.128 (adjacent lanes = the four byte classes c of one segment: same words, broadcast; a quarter warp
+ * reads 64 contiguous bytes: no bank conflicts, where the 4-word lane stride of hm_job_search<4> costs four wavefronts
+ * per load), 11 funnel shifts build the shifted words, and a block row is 32 VABSDIFF4. Positions left of the job's
+ * first column (byte aoff) or beyond its width are computed and dropped. */
+__device__ __forceinline__ unsigned long long hm_job_search8(const HmJobD &J, const SearchTask &t, const uint32_t *raw,
+                                                             const uint32_t *src, int src_pitch4, int warp, int nthr, int lane) {
+    const bool skip = t.bw == 16 && t.rows <= 16 && t.skip_line;
+    const int  ymul = skip ? 2 : 1, rows = t.rows, step = t.row_step;
+    const int  pitch4 = hm_map_width(J.map) >> 4; /* window row pitch in 16-byte units */
+    const int  nseg = J.nchunk, total = J.total;
+    const uint32_t m_seg = J.m_chunk;
+    unsigned long long key = ((unsigned long long)ME_SAD_LOOP_INIT << 32) | 0xFFFFFFFFull;
+    for (int base = warp * 32; base < total; base += nthr) {
+        const int  u  = base + lane;
+        const bool on = u < total;
+        const int  c = u & 3, v = u >> 2;
+        const int  e = (int)hm_div((uint32_t)v, (uint32_t)nseg, m_seg), m = v - e * nseg;
+        const int  sh = 8 * c;
+        uint32_t   acc[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) acc[k] = 0;
+        if (on) {
+            const uint4 *wp = reinterpret_cast<const uint4 *>(raw) + e * ymul * pitch4 + 2 * m;
+            const uint4 *sp = reinterpret_cast<const uint4 *>(src);
+            const int    dw = step * pitch4, ds = step * src_pitch4;
+#pragma unroll 2
+            for (int r = 0; r < rows; r++) {
+                const uint4 s4 = *sp;
+                const uint4 a = wp[0], b = wp[1], d = wp[2];
+                uint32_t    w[12] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, d.x, d.y, d.z, d.w};
+#pragma unroll
+                for (int q = 0; q < 11; q++) w[q] = __funnelshift_r(w[q], w[q + 1], sh);
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    acc[k] = hm_vsad4(s4.x, w[k], acc[k]);
+                    acc[k] = hm_vsad4(s4.y, w[k + 1], acc[k]);
+                    acc[k] = hm_vsad4(s4.z, w[k + 2], acc[k]);
+                    acc[k] = hm_vsad4(s4.w, w[k + 3], acc[k]);
+                }
+                wp += dw;
+                sp += ds;
+            }
+            const uint32_t idx0 = (uint32_t)((J.e0 + e) * t.sa_w + J.px0);
+            const int      x0   = 32 * m + c - (int)J.aoff;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const int x = x0 + 4 * k;
+                if (x >= 0 && x < J.pw && acc[k] < ME_SAD_LOOP_INIT) {
                     const unsigned long long cand = ((unsigned long long)acc[k] << 32) | (idx0 + (uint32_t)x);
                     key                           = cand < key ? cand : key;
                 }
@@ -739,27 +819,14 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
                     rows_per         = max(1, (modeB ? HM_ITEM_POS_B : HM_ITEM_POS_A) / max(1, (int)t.sa_w));
                     n                = (erows + rows_per - 1) / rows_per;
                 }
-                int inclj = nj;
-                for (int o = 1; o < 32; o <<= 1) {
-                    const int vj = __shfl_up_sync(0xffffffffu, inclj, o);
-                    if (lane >= o)
-                        inclj += vj;
-                }
-                const bool over = inclj > HM_MAXJOBS; /* job table full: this task and the ones after it go per-warp */
-                const int  kept = __reduce_max_sync(0xffffffffu, over ? 0 : inclj);
-                if (over) {
+                if (nj > HM_MAXJOBS) { /* a task that overflows the job table on its own goes to the per-warp path */
                     pl.new_path = 0;
-                    inclj       = kept;
+                    nj          = 0;
                 }
                 if (pl.new_path)
                     n = 0;
-                /* warps per job in this stage: the largest team any of its window jobs needs */
-                const int team = __reduce_max_sync(0xffffffffu, pl.new_path ? (int)pl.team : 1);
-                if (lane == 0)
-                    sm.team = team;
-                sm.plan[lane]          = pl;
-                sm.job_first[lane + 1] = inclj;
-                sm.tkey[lane]          = none;
+                sm.plan[lane] = pl;
+                sm.tkey[lane] = none;
             } else if (lane < ME_NREF) {
                 const FsTask f = sm.f[lane];
                 if (f.valid) {
@@ -782,58 +849,81 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
                 sm.item_first[0] = sm.job_first[0] = 0;
         }
         __syncthreads();
-        const int njobs = search_stage ? sm.job_first[ME_SLOTS] : 0;
-        for (int jb = tid; jb < njobs; jb += HM_THREADS) hm_job_decode(sm.t, sm.plan, sm.job_first, j, jb, sm.jobs[jb]);
-        if (njobs > 0)
-            __syncthreads();
-        if (producer && njobs > 0) {
-            if (lane == 0) { /* ring placement, in job order (FIFO): depends on the sizes only, never on timing */
-                int cur = 0;
-                if (sm.team < HM_WARPS) {
-                    /* the jobs of a batch are searched together: batches alternate between the ring halves when they
-                       fit one, else every batch starts at 0 (then the next batch is fetched after this one) */
-                    const int per = HM_WARPS / sm.team;
-                    for (int jb0 = 0; jb0 < njobs; jb0 += per) {
-                        int bytes = 0;
-                        for (int jb = jb0; jb < min(njobs, jb0 + per); jb++)
-                            bytes += (int)sm.jobs[jb].nrows * hm_map_width(sm.jobs[jb].map);
-                        cur = (bytes <= HM_RING_BYTES / 2 && ((jb0 / per) & 1)) ? HM_RING_BYTES / 2 : 0;
-                        for (int jb = jb0; jb < min(njobs, jb0 + per); jb++) {
-                            sm.jobs[jb].off128 = (uint16_t)(cur >> 7);
-                            cur += (int)sm.jobs[jb].nrows * hm_map_width(sm.jobs[jb].map);
-                        }
-                    }
-                } else
-                    for (int jb = 0; jb < njobs; jb++) {
-                        const int size = (int)sm.jobs[jb].nrows * hm_map_width(sm.jobs[jb].map);
-                        if (cur + size > HM_RING_BYTES)
-                            cur = 0;
-                        sm.jobs[jb].off128 = (uint16_t)(cur >> 7);
-                        cur += size;
-                    }
-            }
-            __syncwarp();
-            for (int n = lane; n < njobs; n += 32) { /* ring dependencies (at most HM_NBAR jobs are in flight) */
-                const int off = (int)sm.jobs[n].off128 * 128, size = (int)sm.jobs[n].nrows * hm_map_width(sm.jobs[n].map);
-                int       dep = -1;
-                for (int k = max(0, n - (HM_NBAR - 1)); k < n; k++) {
-                    const int offk = (int)sm.jobs[k].off128 * 128, sizek = (int)sm.jobs[k].nrows * hm_map_width(sm.jobs[k].map);
-                    if (off < offk + sizek && offk < off + size)
-                        dep = k;
+        /* window jobs, in rounds of up to HM_MAXJOBS jobs (whole tasks; the 4K presets' HME level 0 cuts a b64's 28
+           quadrant searches into ~280 jobs) */
+        for (int task_lo = 0; search_stage && task_lo < ME_SLOTS;) {
+            if (warp == 0) {
+                const HmPlan pl = sm.plan[lane];
+                const int    nj = lane >= task_lo && pl.new_path ? (int)pl.nxb * (int)pl.nyb : 0;
+                int          inclj = nj;
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int vj = __shfl_up_sync(0xffffffffu, inclj, o);
+                    if (lane >= o)
+                        inclj += vj;
                 }
-                sm.jobs[n].dep = (int8_t)dep;
+                const bool     over = inclj > HM_MAXJOBS; /* job table full: this task and the ones after it wait for the next round */
+                const unsigned ovm  = __ballot_sync(0xffffffffu, over);
+                const int      kept = __reduce_max_sync(0xffffffffu, over ? 0 : inclj);
+                /* warps per job in this round: the largest team any of its window jobs needs */
+                const int team = __reduce_max_sync(0xffffffffu, nj > 0 && !over ? (int)pl.team : 1);
+                sm.job_first[lane + 1] = over ? kept : inclj;
+                if (lane == 0) {
+                    sm.job_first[0] = 0;
+                    sm.team         = team;
+                    sm.next_lo      = ovm ? __ffs(ovm) - 1 : ME_SLOTS;
+                }
             }
-            __syncwarp();
-        }
-        fetched = 0;
-#ifdef ME_HME_TRACE
-        long long tr2 = clock64();
-#endif
-        /* window jobs, searched while the TMA transfers of the following jobs are in flight: large jobs by the whole
-           CTA one after the other, small ones by one warp each, four at a time */
-        {
+            __syncthreads();
+            const int njobs = sm.job_first[ME_SLOTS];
+            task_lo         = sm.next_lo;
+            if (njobs == 0)
+                break;
+            for (int jb = tid; jb < njobs; jb += HM_THREADS) hm_job_decode(sm.t, sm.plan, sm.job_first, j, jb, sm.jobs[jb]);
+            __syncthreads();
+            if (producer) {
+                if (lane == 0) { /* ring placement, in job order (FIFO): depends on the sizes only, never on timing */
+                    int cur = 0;
+                    if (sm.team < HM_WARPS) {
+                        /* the jobs of a batch are searched together: batches alternate between the ring halves when they
+                           fit one, else every batch starts at 0 (then the next batch is fetched after this one) */
+                        const int per = HM_WARPS / sm.team;
+                        for (int jb0 = 0; jb0 < njobs; jb0 += per) {
+                            int bytes = 0;
+                            for (int jb = jb0; jb < min(njobs, jb0 + per); jb++)
+                                bytes += (int)sm.jobs[jb].nrows * hm_map_width(sm.jobs[jb].map);
+                            cur = (bytes <= HM_RING_BYTES / 2 && ((jb0 / per) & 1)) ? HM_RING_BYTES / 2 : 0;
+                            for (int jb = jb0; jb < min(njobs, jb0 + per); jb++) {
+                                sm.jobs[jb].off128 = (uint16_t)(cur >> 7);
+                                cur += (int)sm.jobs[jb].nrows * hm_map_width(sm.jobs[jb].map);
+                            }
+                        }
+                    } else
+                        for (int jb = 0; jb < njobs; jb++) {
+                            const int size = (int)sm.jobs[jb].nrows * hm_map_width(sm.jobs[jb].map);
+                            if (cur + size > HM_RING_BYTES)
+                                cur = 0;
+                            sm.jobs[jb].off128 = (uint16_t)(cur >> 7);
+                            cur += size;
+                        }
+                }
+                __syncwarp();
+                for (int n = lane; n < njobs; n += 32) { /* ring dependencies (at most HM_NBAR jobs are in flight) */
+                    const int off = (int)sm.jobs[n].off128 * 128, size = (int)sm.jobs[n].nrows * hm_map_width(sm.jobs[n].map);
+                    int       dep = -1;
+                    for (int k = max(0, n - (HM_NBAR - 1)); k < n; k++) {
+                        const int offk = (int)sm.jobs[k].off128 * 128, sizek = (int)sm.jobs[k].nrows * hm_map_width(sm.jobs[k].map);
+                        if (off < offk + sizek && offk < off + size)
+                            dep = k;
+                    }
+                    sm.jobs[n].dep = (int8_t)dep;
+                }
+                __syncwarp();
+            }
+            fetched = 0;
+            /* searched while the TMA transfers of the following jobs are in flight: large jobs by the whole CTA one after
+               the other, small ones by one warp each, four at a time */
             const uint32_t seq0 = seq;
-            const int      team = njobs > 0 ? sm.team : HM_WARPS, per_iter = HM_WARPS / team;
+            const int      team = sm.team, per_iter = HM_WARPS / team;
             for (int jb0 = 0; jb0 < njobs; jb0 += per_iter) {
                 if (producer) {
                     if (lane == 0) {
@@ -857,7 +947,9 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
                     const int sp4 = (t.level == 2 ? HM_SRC2_PITCH : t.level == 1 ? HM_SRC1_PITCH : HM_SRC0_PITCH) / 4;
                     const int widx = team == HM_WARPS ? (warp + jb) & (HM_WARPS - 1) : warp % team, nthr = 32 * team;
                     unsigned long long key;
-                    if (pl.kx == 4)
+                    if (pl.kx == 8)
+                        key = hm_job_search8(J, t, raw, srcb, sp4, widx, nthr, lane);
+                    else if (pl.kx == 4)
                         key = hm_job_search<4>(J, t, pl.g_log2, raw, srcb, sp4, widx, nthr, lane);
                     else
                         key = hm_job_search<2>(J, t, pl.g_log2, raw, srcb, sp4, widx, nthr, lane);
@@ -868,6 +960,9 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
             }
             seq += (uint32_t)njobs;
         }
+#ifdef ME_HME_TRACE
+        long long tr2 = clock64();
+#endif
         const int total = sm.item_first[ME_SLOTS];
         for (; !producer;) {
             int it = 0;
@@ -957,6 +1052,14 @@ static unsigned long long g_hme_launches = 0;
 unsigned long long me_hme_launch_count(void) { return g_hme_launches; }
 
 cudaError_t me_hme_setup(void) {
+    if (getenv("ME_HME_K8_MIN_PW")) {
+        const int v = atoi(getenv("ME_HME_K8_MIN_PW"));
+        cudaMemcpyToSymbol(g_k8_min_pw, &v, sizeof(v));
+    }
+    if (getenv("ME_HME_K8_MIN_UNITS")) {
+        const int v = atoi(getenv("ME_HME_K8_MIN_UNITS"));
+        cudaMemcpyToSymbol(g_k8_min_units, &v, sizeof(v));
+    }
     return cudaFuncSetAttribute(k_hme, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HmeShared) + 65536);
 }
 

@@ -20,15 +20,22 @@ def _register(engine, ps, pocs):
         engine.register_picture(k, ps.get(k).planes[0], ps.w, ps.h)
 
 
-@pytest.mark.parametrize("preset,poc,first,count", [(4, 8, 1000, 6), (2, 4, 2039, 1)])
-def test_me_parity_4k_sample(oracle, preset, poc, first, count):
-    """BASELINE configs[2] geometry (3840x2160, 2040 b64): whole picture on the GPU, a few b64s on the oracle."""
+@pytest.mark.parametrize("preset,poc,n,kind,first,count", [
+    (4, 8, 17, "motion", 1000, 6), (2, 4, 17, "motion", 2039, 1),
+    # BASELINE configs[2]: preset 2, second mini-GOP (4 + 3 references, 128x128 areas at the far references)
+    (2, 18, 33, "iid", 777, 3), (2, 24, 33, "motion", 59, 2),
+    # BASELINE configs[4]: preset 0, HME-L0 up to 480x480, integer search up to 256x256, 7 references; the last b64s
+    # are the bottom-right corner (48 rows high)
+    (0, 18, 33, "iid", 1000, 2), (0, 24, 33, "motion", 2038, 2), (0, 32, 33, "iid", 0, 1)])
+def test_me_parity_4k_sample(oracle, preset, poc, n, kind, first, count):
+    """BASELINE configs[2] / configs[4] geometry (3840x2160, 2040 b64): whole picture on the GPU, a few b64s on the
+    oracle (a preset-0 b64 with 7 references is ~5 s of scalar C)."""
     from me_b200.engine import Engine
-    w, h, n = 3840, 2160, 17
-    ps = PictureSet(w, h, n, "motion", oracle)
+    w, h = 3840, 2160
+    ps = PictureSet(w, h, n, kind, oracle)
     cfg, p, l0, l1 = derive(preset, w, h, poc, n)
     pocs = sorted(set([poc] + l0 + l1))
-    eng = Engine(w, h, 4, 3, pictures_in_flight=8)
+    eng = Engine(w, h, 4, 3, pictures_in_flight=10)
     try:
         _register(eng, ps, pocs)
         got = eng.me_picture(poc, w, h, p, [l0, l1])

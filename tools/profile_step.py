@@ -1,4 +1,4 @@
-"""Runs a few pictures of the bench workload (for ncu / launch lists). Usage: profile_step.py [npictures] [kind]"""
+"""Runs a few pictures of a bench workload (for ncu / launch lists). Usage: profile_step.py [npictures] [kind] [workload]"""
 import os
 import sys
 
@@ -10,6 +10,7 @@ from me_b200.engine import Engine  # noqa: E402
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 4
 kind = sys.argv[2] if len(sys.argv) > 2 else "motion"
+bench.set_workload(sys.argv[3] if len(sys.argv) > 3 else "1080p-m4")
 pics = bench.make_pictures(kind, pinned=False)
 eng = Engine(bench.W, bench.H, 4, 3, pictures_in_flight=40, devices=[0])
 for poc in range(bench.NPIC):
