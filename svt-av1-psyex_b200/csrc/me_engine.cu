@@ -176,7 +176,8 @@ uint64_t max_tiles_per_b64(const MeGpuParams *p) {
         }
         w = (w + 7) & ~7u; /* ME:1314 */
         h = h < 3 ? 3 : h;
-        return (uint64_t)((w + FS_TW - 1) / FS_TW) * ((h + FS_TH - 1) / FS_TH);
+        const uint32_t tw = 4u * (uint32_t)fs_choose_kx((int)w);
+        return (uint64_t)((w + tw - 1) / tw) * ((h + FS_TH - 1) / FS_TH);
     };
     uint32_t nref = 0, nmult = 0;
     for (uint32_t li = 0; li < p->num_of_list_to_search && li < ME_NL; li++) {
@@ -195,7 +196,7 @@ int alloc_job(Device &d, JobCtx &jc, const MePicGeom &gm, int max_l0, int max_l1
     jc.device    = d.id;
     jc.cap_cands = nb * ME_NPU * (max_cand ? max_cand : 1);
     jc.cap_mvs   = nb * ME_NPU * (max_refs ? max_refs : 1);
-    jc.tile_cap  = (uint32_t)(nb * ME_NREF * 64 * (32 / FS_TH));
+    jc.tile_cap  = (uint32_t)(nb * ME_NREF * 128); /* >= max_tiles_per_b64 of every preset (832 at preset 0) */
     CU(cudaStreamCreateWithFlags(&jc.stream, cudaStreamNonBlocking));
     for (auto &e : jc.ev) CU(cudaEventCreate(&e));
     for (auto &e : jc.pev) CU(cudaEventCreate(&e));

@@ -75,7 +75,7 @@ __device__ unsigned g_trace_cnt;
 #endif
 /* search areas at least this wide / with at least this many 8-position units take hm_job_search8 (tunable by
    ME_HME_K8_MIN_PW / ME_HME_K8_MIN_UNITS for experiments) */
-__device__ int g_k8_min_pw = 64, g_k8_min_units = 96;
+__device__ int g_k8_min_pw = 64, g_k8_min_units = 64, g_team1_units = 16, g_lanes_target = 96;
 
 struct HmeShared {
     B64State           s;
@@ -393,9 +393,9 @@ __device__ void hm_plan_task(const SearchTask &t, const MeJob *j, int org_x, int
     const int win     = pitch * (((neb - 1) * ymul + span + 1 + hm_map_rows(map) - 1) / hm_map_rows(map) * hm_map_rows(map));
     /* jobs of few units are searched by one warp each, four at a time per CTA, when four windows fit the ring (measured:
        two warps per job with the next batch in flight is slower than one warp per job and no prefetch of the next batch) */
-    pl.team = (uint8_t)(!wide && units <= 16 && win <= HM_RING_BYTES / 4 ? 1 : 4);
+    pl.team = (uint8_t)(!wide && units <= g_team1_units && win <= HM_RING_BYTES / 4 ? 1 : 4);
     int g_log2 = 2 - lv; /* lanes per unit: the 16-byte column segments of the block row ... */
-    while (!wide && g_log2 < 5 && (pl.team < 4 ? (units << (g_log2 + 1)) <= 32 * pl.team : (units << g_log2) < 96) &&
+    while (!wide && g_log2 < 5 && (pl.team < 4 ? (units << (g_log2 + 1)) <= 32 * pl.team : (units << g_log2) < g_lanes_target) &&
            ((2 << g_log2) >> (2 - lv)) <= (int)t.rows)
         g_log2++; /* ... x row groups: up to the team's worth of lanes */
     pl.pwb = (int16_t)pwb;
@@ -695,27 +695,6 @@ __device__ void fullsearch_item(const FsTask &f, int y_lo, int y_hi, const MeJob
 #undef HM_MERGE
 }
 
-/* append the 64x32-position tiles of a large search area to the work list of k_fullsearch */
-__device__ void hm_emit_tiles(const FsTask &f, FsTileList *list, uint32_t task, uint16_t job) {
-    const uint32_t ntx = (uint32_t)(f.w + FS_TW - 1) / FS_TW, nty = (uint32_t)(f.h + FS_TH - 1) / FS_TH;
-    const uint32_t n = ntx * nty, base = atomicAdd(&list->count, n);
-    if (base + n > list->cap) {
-        atomicExch(&list->overflow, 1u);
-        return;
-    }
-    FsTile *t = list->tiles + base;
-    for (uint32_t ty = 0; ty < nty; ty++)
-        for (uint32_t tx = 0; tx < ntx; tx++, t++) {
-            t->task = task;
-            t->job  = job;
-            t->tx   = (uint16_t)(tx * FS_TW);
-            t->ty   = (uint16_t)(ty * FS_TH);
-            t->ref_slot = f.ref_slot;
-            t->x0 = f.x0; t->y0 = f.y0; t->w = f.w; t->h = f.h;
-            t->probe = f.probe;
-        }
-}
-
 /* ------------------------------------------------------------------------------------------------
  * k_hme
  * ---------------------------------------------------------------------------------------------- */
@@ -834,7 +813,7 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
                         rows_per = max(1, HM_ITEM_POS_FS / max(1, (int)f.w));
                         n        = (f.h + rows_per - 1) / rows_per;
                     } else
-                        hm_emit_tiles(f, list, (uint32_t)b * ME_NREF + (uint32_t)lane, (uint16_t)blockIdx.y);
+                        fs_emit_tiles(f, list, (uint32_t)b * ME_NREF + (uint32_t)lane, (uint16_t)blockIdx.y);
                 }
             }
             int incl = n;
@@ -1055,6 +1034,14 @@ cudaError_t me_hme_setup(void) {
     if (getenv("ME_HME_K8_MIN_PW")) {
         const int v = atoi(getenv("ME_HME_K8_MIN_PW"));
         cudaMemcpyToSymbol(g_k8_min_pw, &v, sizeof(v));
+    }
+    if (getenv("ME_HME_TEAM1_UNITS")) {
+        const int v = atoi(getenv("ME_HME_TEAM1_UNITS"));
+        cudaMemcpyToSymbol(g_team1_units, &v, sizeof(v));
+    }
+    if (getenv("ME_HME_LANES_TARGET")) {
+        const int v = atoi(getenv("ME_HME_LANES_TARGET"));
+        cudaMemcpyToSymbol(g_lanes_target, &v, sizeof(v));
     }
     if (getenv("ME_HME_K8_MIN_UNITS")) {
         const int v = atoi(getenv("ME_HME_K8_MIN_UNITS"));

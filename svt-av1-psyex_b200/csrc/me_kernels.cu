@@ -137,24 +137,7 @@ __global__ void __launch_bounds__(64) k_ctrl(MeJob *jobs, uint32_t stage_mask, F
             const FsTask f = c.f[k];
             if (!f.valid)
                 continue;
-            const uint32_t ntx = (uint32_t)(f.w + FS_TW - 1) / FS_TW, nty = (uint32_t)(f.h + FS_TH - 1) / FS_TH;
-            const uint32_t n = ntx * nty;
-            const uint32_t base = atomicAdd(&list->count, n);
-            if (base + n > list->cap) {
-                atomicExch(&list->overflow, 1u);
-                continue;
-            }
-            FsTile *t = list->tiles + base;
-            for (uint32_t ty = 0; ty < nty; ty++)
-                for (uint32_t tx = 0; tx < ntx; tx++, t++) {
-                    t->task = (uint32_t)b * ME_NREF + (uint32_t)k;
-                    t->job  = (uint16_t)blockIdx.y;
-                    t->tx   = (uint16_t)(tx * FS_TW);
-                    t->ty   = (uint16_t)(ty * FS_TH);
-                    t->ref_slot = f.ref_slot;
-                    t->x0 = f.x0; t->y0 = f.y0; t->w = f.w; t->h = f.h;
-                    t->probe = f.probe;
-                }
+            fs_emit_tiles(f, list, (uint32_t)b * ME_NREF + (uint32_t)k, (uint16_t)blockIdx.y);
         }
     }
 }
@@ -275,21 +258,21 @@ __global__ void __launch_bounds__(KS_THREADS) k_search(const MeJob *jobs, const 
 /* ------------------------------------------------------------------------------------------------
  * k_fullsearch: integer full search, all 85 square PUs per position
  * ---------------------------------------------------------------------------------------------- */
-#define FS_PW 36 /* words per window row and copy: 4 x odd, so that 8 rows hit 8 distinct 16-byte bank groups */
+#define FS_PW 28 /* words per window row and copy (32 + 63 + 3 bytes): 4 x odd, so that 8 rows hit 8 distinct 16-byte bank groups */
 #define FS_ROWS (FS_TH + 64) /* FS_TH + 63 window rows (+1) */
-#define FS_KEY_SHIFT 11 /* up to 64 x 32 tile positions */
+#define FS_KEY_SHIFT 10 /* 32 x 32 tile positions */
 #define FS_BIAS (1u << 17) /* added to the 8x8 SADs of positions outside the tile: they can never win */
 #define FS_SMEM_BYTES ((4 * FS_ROWS * FS_PW + 64 * 16 + 96) * 4)
 
-template <bool SUB>
+template <bool SUB, int KX>
 __device__ __forceinline__ void fs_compute(const uint32_t *__restrict__ wc, const uint32_t *__restrict__ srcw,
                                            uint32_t *sbest, int xw0, int ly, int s, int wvalid, int hvalid, int lane) {
     constexpr int RSTEP = SUB ? 2 : 1; /* window rows per summed block row */
     constexpr int NR    = SUB ? 4 : 8; /* summed rows per 8x8 block */
-    uint32_t      bias[8], idx[8];
+    uint32_t      bias[KX], idx[KX];
     uint32_t      vmask = 0;
 #pragma unroll
-    for (int k = 0; k < 8; k++) {
+    for (int k = 0; k < KX; k++) {
         const int  lx = xw0 + s + 4 * k;
         const bool v  = lx < wvalid && ly < hvalid;
         bias[k]       = v ? 0u : FS_BIAS;
@@ -297,27 +280,27 @@ __device__ __forceinline__ void fs_compute(const uint32_t *__restrict__ wc, cons
         vmask |= (v ? 1u : 0u) << k;
     }
     const int j0 = xw0 >> 2;
-    uint32_t  s64[8];
+    uint32_t  s64[KX];
 #pragma unroll
-    for (int k = 0; k < 8; k++) s64[k] = 0;
+    for (int k = 0; k < KX; k++) s64[k] = 0;
 #pragma unroll 1
     for (int q = 0; q < 4; q++) {
         const int qx = q & 1, qy = q >> 1;
-        uint32_t  s32[8];
+        uint32_t  s32[KX];
 #pragma unroll
-        for (int k = 0; k < 8; k++) s32[k] = 0;
+        for (int k = 0; k < KX; k++) s32[k] = 0;
 #pragma unroll 1
         for (int h = 0; h < 2; h++) {
-            uint32_t s16[2][8];
+            uint32_t s16[2][KX];
 #pragma unroll
-            for (int k = 0; k < 8; k++) s16[0][k] = s16[1][k] = 0;
+            for (int k = 0; k < KX; k++) s16[0][k] = s16[1][k] = 0;
 #pragma unroll
             for (int br = 0; br < 2; br++) {
-                uint32_t acc[4][8];
+                uint32_t acc[4][KX];
 #pragma unroll
                 for (int i = 0; i < 4; i++)
 #pragma unroll
-                    for (int k = 0; k < 8; k++) acc[i][k] = bias[k];
+                    for (int k = 0; k < KX; k++) acc[i][k] = bias[k];
                 const int brow = 32 * qy + 16 * h + 8 * br; /* first pixel row of this 8x8 block row */
 #pragma unroll
                 for (int r = 0; r < NR; r++) {
@@ -325,7 +308,7 @@ __device__ __forceinline__ void fs_compute(const uint32_t *__restrict__ wc, cons
                     const uint4 *sp = (const uint4 *)(srcw + (brow / RSTEP + r) * 16 + 8 * qx);
                     uint32_t     rw[16], sw[8];
 #pragma unroll
-                    for (int i = 0; i < 4; i++) {
+                    for (int i = 0; i < (7 + KX + 3) / 4; i++) {
                         const uint4 v = rp[i];
                         rw[4 * i] = v.x; rw[4 * i + 1] = v.y; rw[4 * i + 2] = v.z; rw[4 * i + 3] = v.w;
                     }
@@ -337,19 +320,19 @@ __device__ __forceinline__ void fs_compute(const uint32_t *__restrict__ wc, cons
 #pragma unroll
                     for (int cw = 0; cw < 8; cw++)
 #pragma unroll
-                        for (int k = 0; k < 8; k++) acc[cw >> 1][k] = vsad4(sw[cw], rw[cw + k], acc[cw >> 1][k]);
+                        for (int k = 0; k < KX; k++) acc[cw >> 1][k] = vsad4(sw[cw], rw[cw + k], acc[cw >> 1][k]);
                 }
                 /* four 8x8 PUs done for 8 positions: z-order index 21 + 16q + 8h + 4(i>>1) + 2br + (i&1) */
 #pragma unroll
                 for (int i = 0; i < 4; i++) {
                     uint32_t m = 0xFFFFFFFFu;
 #pragma unroll
-                    for (int k = 0; k < 8; k++) m = min(m, (acc[i][k] << FS_KEY_SHIFT) + idx[k]);
+                    for (int k = 0; k < KX; k++) m = min(m, (acc[i][k] << FS_KEY_SHIFT) + idx[k]);
                     m = __reduce_min_sync(0xffffffffu, m);
                     if (lane == 0)
                         atomicMin(&sbest[21 + 16 * q + 8 * h + 4 * (i >> 1) + 2 * br + (i & 1)], m);
 #pragma unroll
-                    for (int k = 0; k < 8; k++) s16[i >> 1][k] += acc[i][k];
+                    for (int k = 0; k < KX; k++) s16[i >> 1][k] += acc[i][k];
                 }
             }
             /* two 16x16 PUs: 5 + 4q + 2h + {0,1} */
@@ -357,19 +340,19 @@ __device__ __forceinline__ void fs_compute(const uint32_t *__restrict__ wc, cons
             for (int i = 0; i < 2; i++) {
                 uint32_t m = 0xFFFFFFFFu;
 #pragma unroll
-                for (int k = 0; k < 8; k++) m = min(m, (s16[i][k] << FS_KEY_SHIFT) + idx[k]);
+                for (int k = 0; k < KX; k++) m = min(m, (s16[i][k] << FS_KEY_SHIFT) + idx[k]);
                 m = __reduce_min_sync(0xffffffffu, m);
                 if (lane == 0)
                     atomicMin(&sbest[5 + 4 * q + 2 * h + i], m);
 #pragma unroll
-                for (int k = 0; k < 8; k++) s32[k] += s16[i][k];
+                for (int k = 0; k < KX; k++) s32[k] += s16[i][k];
             }
         }
         /* 32x32 PU 1 + q: positions outside the tile are masked explicitly (their bias overflows the key) */
         {
             uint32_t m = 0xFFFFFFFFu;
 #pragma unroll
-            for (int k = 0; k < 8; k++) {
+            for (int k = 0; k < KX; k++) {
                 const uint32_t key = (s32[k] << FS_KEY_SHIFT) + idx[k];
                 m                  = min(m, (vmask >> k) & 1u ? key : 0xFFFFFFFFu);
             }
@@ -377,13 +360,13 @@ __device__ __forceinline__ void fs_compute(const uint32_t *__restrict__ wc, cons
             if (lane == 0)
                 atomicMin(&sbest[1 + q], m);
 #pragma unroll
-            for (int k = 0; k < 8; k++) s64[k] += s32[k];
+            for (int k = 0; k < KX; k++) s64[k] += s32[k];
         }
     }
     {
         uint32_t m = 0xFFFFFFFFu;
 #pragma unroll
-        for (int k = 0; k < 8; k++) {
+        for (int k = 0; k < KX; k++) {
             const uint32_t key = (s64[k] << FS_KEY_SHIFT) + idx[k];
             m                  = min(m, (vmask >> k) & 1u ? key : 0xFFFFFFFFu);
         }
@@ -419,7 +402,8 @@ __global__ void __launch_bounds__(FS_THREADS, FS_CTAS_PER_SM) k_fullsearch(MeJob
         const bool    sub  = j->p.me_search_method == ME_GPU_SUB_SAD_SEARCH;
         const MePlaneGeom pl = j->g.plane[0];
         const int org_x = (int)(b % (uint32_t)j->g.b64_cols) * 64, org_y = (int)(b / (uint32_t)j->g.b64_cols) * 64;
-        const int wvalid = min(FS_TW, f.w - (int)tile.tx), hvalid = min(FS_TH, f.h - (int)tile.ty);
+        const int kx = tile.kx;
+        const int wvalid = min(4 * kx, f.w - (int)tile.tx), hvalid = min(FS_TH, f.h - (int)tile.ty);
 
         /* stage: source block rows (every other row for sub-sampled SAD) */
         {
@@ -454,13 +438,20 @@ __global__ void __launch_bounds__(FS_THREADS, FS_CTAS_PER_SM) k_fullsearch(MeJob
         __syncthreads();
         /* compute: warp -> 32 x 8 positions, lane -> (byte shift s, row), 8 positions x = s + 4k per thread */
         {
-            const int xw0 = (warp & 1) * 32, yw0 = (warp >> 1) * 8;
+            /* the warp -> quarter-tile assignment rotates with the tile number: partly filled tiles leave different
+               SM sub-partitions idle */
+            const int wq  = (warp + (int)ti) & 3;
+            const int xw0 = 0, yw0 = wq * 8;
             if (xw0 < wvalid && yw0 < hvalid) {
-                const int s = lane >> 3, ly = yw0 + (lane & 7);
-                if (sub)
-                    fs_compute<true>(win + s * FS_ROWS * FS_PW, srcw, sbest, xw0, ly, s, wvalid, hvalid, lane);
-                else
-                    fs_compute<false>(win + s * FS_ROWS * FS_PW, srcw, sbest, xw0, ly, s, wvalid, hvalid, lane);
+                const int       s = lane >> 3, ly = yw0 + (lane & 7);
+                const uint32_t *wc = win + s * FS_ROWS * FS_PW;
+#define FS_CALL(SUB, K) fs_compute<SUB, K>(wc, srcw, sbest, xw0, ly, s, wvalid, hvalid, lane)
+                if (sub) {
+                    if (kx == 8) FS_CALL(true, 8); else if (kx == 7) FS_CALL(true, 7); else if (kx == 6) FS_CALL(true, 6); else FS_CALL(true, 5);
+                } else {
+                    if (kx == 8) FS_CALL(false, 8); else if (kx == 7) FS_CALL(false, 7); else if (kx == 6) FS_CALL(false, 6); else FS_CALL(false, 5);
+                }
+#undef FS_CALL
             }
         }
         __syncthreads();

@@ -6,12 +6,28 @@
 
 #include "me_types.h"
 
-#define FS_TW 64 /* full-search tile: 64 x FS_TH search positions per CTA iteration, one warp per 32 x 8 positions */
+/* full-search tile: (4 * KX) x FS_TH search positions per CTA iteration; warp w takes search rows [8w, 8w + 8): lane =
+ * (byte shift s, row), KX positions x = s + 4k per thread */
+#define FS_TW 32 /* widest tile (KX = 8); also the row stride of the packed tile-position index */
 #ifndef FS_TH
-#define FS_TH 16
+#define FS_TH 32
 #endif
-#define FS_THREADS (FS_TH * 8)
+#define FS_THREADS (FS_TH * 4)
 #define FS_CTAS_PER_SM (512 / FS_THREADS) /* 128 registers per thread */
+
+/* positions per thread (x = s + 4k, k < KX) of the tiles of a search area `w` positions wide: a warp covers 4 * KX
+ * columns; the KX in 5..8 that wastes the fewest columns wins (104 -> 7: 4 x 28 = 112 instead of 4 x 32 = 128) */
+__host__ __device__ static inline int fs_choose_kx(int w) {
+    int best = 8, cost = ((w + 31) / 32) * 32;
+    for (int k = 7; k >= 5; k--) {
+        const int c = ((w + 4 * k - 1) / (4 * k)) * 4 * k;
+        if (c < cost) {
+            cost = c;
+            best = k;
+        }
+    }
+    return best;
+}
 
 typedef struct FsTileList {
     unsigned int count; /* tiles appended by k_ctrl */
@@ -20,6 +36,31 @@ typedef struct FsTileList {
     unsigned int overflow;
     FsTile      *tiles;
 } FsTileList;
+
+#ifdef __CUDACC__
+/* append the tiles (4 * KX x FS_TH positions) of a large search area to the work list of k_fullsearch */
+__device__ static inline void fs_emit_tiles(const FsTask &f, FsTileList *list, uint32_t task, uint16_t job) {
+    const uint32_t kx = (uint32_t)fs_choose_kx(f.w), tw = 4 * kx;
+    const uint32_t ntx = ((uint32_t)f.w + tw - 1) / tw, nty = (uint32_t)(f.h + FS_TH - 1) / FS_TH;
+    const uint32_t n = ntx * nty, base = atomicAdd(&list->count, n);
+    if (base + n > list->cap) {
+        atomicExch(&list->overflow, 1u);
+        return;
+    }
+    FsTile *t = list->tiles + base;
+    for (uint32_t ty = 0; ty < nty; ty++)
+        for (uint32_t tx = 0; tx < ntx; tx++, t++) {
+            t->task = task;
+            t->job  = job;
+            t->tx   = (uint16_t)(tx * tw);
+            t->ty   = (uint16_t)(ty * FS_TH);
+            t->ref_slot = f.ref_slot;
+            t->x0 = f.x0; t->y0 = f.y0; t->w = f.w; t->h = f.h;
+            t->probe = f.probe;
+            t->kx    = (uint8_t)kx;
+        }
+}
+#endif
 
 cudaError_t        me_kernels_setup(void);
 unsigned long long me_launch_count(void);

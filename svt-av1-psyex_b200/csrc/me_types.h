@@ -129,7 +129,7 @@ typedef struct FsTile { /* a rectangle of search positions of one FsTask, unit o
     uint16_t tx, ty; /* tile origin inside the search area */
     uint16_t ref_slot;
     int16_t  x0, y0, w, h; /* the task's search area (copied: the FsTask slot is reused by the next round) */
-    uint8_t  probe, pad_[3];
+    uint8_t  probe, kx /* positions per thread: the tile is 4 * kx positions wide */, pad_[2];
 } FsTile;
 
 /* one picture's ME job; an array of these (one per picture of a batch) lives in HBM */

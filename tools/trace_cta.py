@@ -1,11 +1,12 @@
 """Summary of the per-CTA timeline printed by the ME_HME_TRACE build (tools/trace_hme.sh): CTA durations, time per stage,
-co-residency per SM. Usage: python tools/trace_cta.py gpurun_out/trace_cta.txt"""
+co-residency per SM. Usage: python tools/trace_cta.py gpurun_out/trace_cta.txt [b64 per picture]"""
 import collections
 import statistics
 import sys
 
 lines = [l.split() for l in open(sys.argv[1]) if l.startswith("CTA")]
-L = lines[-510:]  # the last picture
+NB = int(sys.argv[2]) if len(sys.argv) > 2 else 510
+L = lines[-NB:]  # the last picture
 t0 = min(int(l[5]) for l in L)
 rows = [(int(l[1]), int(l[3]), int(l[5]) - t0, [int(x) for x in l[7:16]]) for l in L]
 dur = [r[3][8] for r in rows]
