@@ -262,8 +262,20 @@ __global__ void __launch_bounds__(KS_THREADS) k_search(const MeJob *jobs, const 
 #define FS_ROWS (FS_TH + 64) /* FS_TH + 63 window rows (+1) */
 #define FS_KEY_SHIFT 10 /* 32 x 32 tile positions */
 #define FS_BIAS (1u << 17) /* added to the 8x8 SADs of positions outside the tile: they can never win */
-#define FS_SMEM_BYTES ((4 * FS_ROWS * FS_PW + 64 * 16 + 96) * 4)
+#define FS_SBEST 96 /* words per warp: best (sad << 10 | tile position) of the 85 PUs over the warp's 8 search rows */
+#define FS_SMEM_BYTES ((4 * FS_ROWS * FS_PW + 64 * 16 + 4 * FS_SBEST) * 4)
 
+/* a tile visits every PU once per warp and sbest has a row per warp: no atomic is needed */
+#ifndef FS_STORE_MODE
+#define FS_STORE_MODE 2
+#endif
+#if FS_STORE_MODE == 0
+#define FS_STORE(i, m) do { if (lane == 0) atomicMin(&sbest[i], m); } while (0)
+#elif FS_STORE_MODE == 1
+#define FS_STORE(i, m) do { if (lane == 0) sbest[i] = (m); } while (0)
+#else
+#define FS_STORE(i, m) do { sbest[i] = (m); } while (0)
+#endif
 template <bool SUB, int KX>
 __device__ __forceinline__ void fs_compute(const uint32_t *__restrict__ wc, const uint32_t *__restrict__ srcw,
                                            uint32_t *sbest, int xw0, int ly, int s, int wvalid, int hvalid, int lane) {
@@ -329,8 +341,7 @@ __device__ __forceinline__ void fs_compute(const uint32_t *__restrict__ wc, cons
 #pragma unroll
                     for (int k = 0; k < KX; k++) m = min(m, (acc[i][k] << FS_KEY_SHIFT) + idx[k]);
                     m = __reduce_min_sync(0xffffffffu, m);
-                    if (lane == 0)
-                        atomicMin(&sbest[21 + 16 * q + 8 * h + 4 * (i >> 1) + 2 * br + (i & 1)], m);
+                    FS_STORE(21 + 16 * q + 8 * h + 4 * (i >> 1) + 2 * br + (i & 1), m);
 #pragma unroll
                     for (int k = 0; k < KX; k++) s16[i >> 1][k] += acc[i][k];
                 }
@@ -342,8 +353,7 @@ __device__ __forceinline__ void fs_compute(const uint32_t *__restrict__ wc, cons
 #pragma unroll
                 for (int k = 0; k < KX; k++) m = min(m, (s16[i][k] << FS_KEY_SHIFT) + idx[k]);
                 m = __reduce_min_sync(0xffffffffu, m);
-                if (lane == 0)
-                    atomicMin(&sbest[5 + 4 * q + 2 * h + i], m);
+                FS_STORE(5 + 4 * q + 2 * h + i, m);
 #pragma unroll
                 for (int k = 0; k < KX; k++) s32[k] += s16[i][k];
             }
@@ -357,8 +367,7 @@ __device__ __forceinline__ void fs_compute(const uint32_t *__restrict__ wc, cons
                 m                  = min(m, (vmask >> k) & 1u ? key : 0xFFFFFFFFu);
             }
             m = __reduce_min_sync(0xffffffffu, m);
-            if (lane == 0)
-                atomicMin(&sbest[1 + q], m);
+            FS_STORE(1 + q, m);
 #pragma unroll
             for (int k = 0; k < KX; k++) s64[k] += s32[k];
         }
@@ -371,8 +380,7 @@ __device__ __forceinline__ void fs_compute(const uint32_t *__restrict__ wc, cons
             m                  = min(m, (vmask >> k) & 1u ? key : 0xFFFFFFFFu);
         }
         m = __reduce_min_sync(0xffffffffu, m);
-        if (lane == 0)
-            atomicMin(&sbest[0], m);
+        FS_STORE(0, m);
     }
 }
 
@@ -380,7 +388,7 @@ __global__ void __launch_bounds__(FS_THREADS, FS_CTAS_PER_SM) k_fullsearch(MeJob
     extern __shared__ __align__(16) uint32_t fs_smem[];
     uint32_t *win   = fs_smem; /* [4][FS_ROWS][FS_PW] */
     uint32_t *srcw  = fs_smem + 4 * FS_ROWS * FS_PW; /* [64][16] (32 rows used for sub-sampled SAD) */
-    uint32_t *sbest = srcw + 64 * 16; /* [85] packed (sad << 11 | tile position) */
+    uint32_t *sbest = srcw + 64 * 16; /* [4 warps][FS_SBEST] packed (sad << 10 | tile position): a tile visits every PU once per warp, so plain stores */
     __shared__ uint32_t s_tile;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t total = list->count > list->cap ? 0u : list->count;
@@ -413,8 +421,7 @@ __global__ void __launch_bounds__(FS_THREADS, FS_CTAS_PER_SM) k_fullsearch(MeJob
                 const int r = i >> 4, cw = i & 15;
                 srcw[i]     = *(const uint32_t *)(sp + (size_t)(r * rstep) * pl.stride + cw * 4);
             }
-            if (tid < ME_NPU)
-                sbest[tid] = 0xFFFFFFFFu;
+            for (int i = tid; i < 4 * FS_SBEST; i += FS_THREADS) sbest[i] = 0xFFFFFFFFu; /* warps without positions leave it so */
         }
         /* stage: reference window, four copies shifted by 0..3 bytes */
         {
@@ -445,7 +452,7 @@ __global__ void __launch_bounds__(FS_THREADS, FS_CTAS_PER_SM) k_fullsearch(MeJob
             if (xw0 < wvalid && yw0 < hvalid) {
                 const int       s = lane >> 3, ly = yw0 + (lane & 7);
                 const uint32_t *wc = win + s * FS_ROWS * FS_PW;
-#define FS_CALL(SUB, K) fs_compute<SUB, K>(wc, srcw, sbest, xw0, ly, s, wvalid, hvalid, lane)
+#define FS_CALL(SUB, K) fs_compute<SUB, K>(wc, srcw, sbest + warp * FS_SBEST, xw0, ly, s, wvalid, hvalid, lane)
                 if (sub) {
                     if (kx == 8) FS_CALL(true, 8); else if (kx == 7) FS_CALL(true, 7); else if (kx == 6) FS_CALL(true, 6); else FS_CALL(true, 5);
                 } else {
@@ -457,7 +464,7 @@ __global__ void __launch_bounds__(FS_THREADS, FS_CTAS_PER_SM) k_fullsearch(MeJob
         __syncthreads();
         /* merge the tile's best keys into the task's 64-bit (sad, scan order) keys */
         if (tid < ME_NPU) {
-            const uint32_t key = sbest[tid];
+            const uint32_t key = min(min(sbest[tid], sbest[FS_SBEST + tid]), min(sbest[2 * FS_SBEST + tid], sbest[3 * FS_SBEST + tid]));
             if (key != 0xFFFFFFFFu) {
                 const uint32_t raw = key >> FS_KEY_SHIFT, pos = key & ((1u << FS_KEY_SHIFT) - 1u);
                 const uint32_t lx = pos & (FS_TW - 1), ly = pos / FS_TW;
