@@ -72,6 +72,28 @@ def derive(poc):
     return _d(PRESET, W, H, poc, NPIC, force_refs=FORCE_REFS)
 
 
+def bind_to_gpu_numa(index):
+    """Pin this process (and the pinned buffers it is about to allocate: first touch) to the CPUs of the NUMA node the
+    GPU hangs off, as read from sysfs. One process per GPU: without this the 8 ranks' uploads cross the socket link."""
+    try:
+        import torch
+        bdf = torch.cuda.get_device_properties(index).pci_bus_id
+        dom = torch.cuda.get_device_properties(index).pci_domain_id
+        dev = torch.cuda.get_device_properties(index).pci_device_id
+        path = f"/sys/bus/pci/devices/{dom:04x}:{bdf:02x}:{dev:02x}.0/local_cpulist"
+        cpus = set()
+        for part in open(path).read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return sorted(cpus)
+    except Exception:
+        pass
+    return None
+
+
 def rank_info():
     return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 
@@ -263,8 +285,21 @@ def gpu_main(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the engine has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    numa_cpus = bind_to_gpu_numa(local_rank) if world > 1 else None
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # NCCL prints its version banner on stdout when the box sets NCCL_DEBUG=VERSION: stdout carries ONE JSON line,
+        # so fd 1 points at stderr while the communicator comes up (first collective included)
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
 
     def barrier():
         torch.cuda.synchronize()
@@ -441,6 +476,24 @@ def gpu_main(args):
         cpu_baseline = {"value": arm.pictures() * reps / dt, "unit": "frames/s", "cores": threads, "kind": "reference",
                         "sample": f"{arm.sample_text()} x {reps} repetitions, {dt:.1f} s wall on {threads} threads",
                         "cpu": cpu_model(), "simd": "avx2"}
+    extra = None
+    if rank == 0 and world == 1 and args.extra and WORKLOAD == "1080p-m4" and args.kind == "motion":
+        # the same measurement on the configurations where the integer full search dominates (worst-case "iid" input:
+        # no early exits, every search area at its configured size), each in a process of its own, after this one's
+        # engine is closed; they explain the path's integer-SAD roofline, the headline stays the workload above
+        import subprocess
+        extra = []
+        for wl, kind in (("1080p-m4", "iid"), ("4k-m0", "iid")):
+            cmd = [sys.executable, os.path.abspath(__file__), "--workload", wl, "--kind", kind, "--steps", "3", "--warmup", "3",
+                   "--no-cpu", "--no-extra"]
+            try:
+                r = subprocess.run(cmd, capture_output=True, text=True, timeout=400)
+                d = json.loads(r.stdout.strip().splitlines()[-1])
+                extra.append({"workload": wl, "sequence": kind, "value": d["value"], "e2e": d["e2e"]["value"], "unit": "frames/s",
+                              "steps": d["steps"], "warmup": d["warmup"], "clocks": d["clocks"],
+                              "roofline": {k: d["roofline"][k] for k in ("kernel", "achieved", "peak", "unit", "frac", "kernels")}})
+            except Exception as e:  # reported, never silent
+                extra.append({"workload": wl, "sequence": kind, "error": repr(e)[:200]})
     if rank == 0:
         line = {
             "metric": "open-loop ME frames/sec", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
@@ -449,7 +502,8 @@ def gpu_main(args):
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": 1e3 * dt_e2e / args.steps},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
-            "result_checksum": checksum,
+            "result_checksum": checksum, "extra_workloads": extra,
+            "host": {"cpus": os.cpu_count(), "rank0_numa_cpus": len(numa_cpus) if numa_cpus else None},
         }
         print(json.dumps(line))
     if world > 1:
@@ -465,6 +519,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--kind", default="motion", choices=["motion", "iid"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-extra", dest="extra", action="store_false",
+                    help="skip the two short full-search-bound runs (1080p-m4 iid, 4k-m0 iid) appended as extra_workloads at N=1")
     ap.add_argument("--workload", default="1080p-m4", choices=sorted(WORKLOADS),
                     help="BASELINE.json config to run (default: configs[1], the one the metric is quoted on at N=1)")
     args = ap.parse_args()
