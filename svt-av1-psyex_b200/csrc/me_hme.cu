@@ -548,8 +548,10 @@ __device__ __forceinline__ unsigned long long hm_job_search8(const HmJobD &J, co
     const int  ymul = skip ? 2 : 1, rows = t.rows, step = t.row_step;
     const int  pitch4 = hm_map_width(J.map) >> 4; /* window row pitch in 16-byte units */
     const int  nseg = J.nchunk, total = J.total;
-    const uint32_t m_seg = J.m_chunk;
-    unsigned long long key = ((unsigned long long)ME_SAD_LOOP_INIT << 32) | 0xFFFFFFFFull;
+    const uint32_t m_seg = J.m_chunk, pw = (uint32_t)J.pw;
+    /* inside the job a 32-bit key is enough: SAD of a 16-byte-wide block of <= 16 rows < 2^16, and a job has fewer
+       positions than its window has bytes (<= 16384): (sad << 16 | e * pw + x) orders like the 64-bit key */
+    uint32_t best = 0xFFFFFFFFu;
     for (int base = warp * 32; base < total; base += nthr) {
         const int  u  = base + lane;
         const bool on = u < total;
@@ -580,23 +582,20 @@ __device__ __forceinline__ unsigned long long hm_job_search8(const HmJobD &J, co
                 wp += dw;
                 sp += ds;
             }
-            const uint32_t idx0 = (uint32_t)((J.e0 + e) * t.sa_w + J.px0);
-            const int      x0   = 32 * m + c - (int)J.aoff;
+            const int      x0 = 32 * m + c - (int)J.aoff;
+            const uint32_t l0 = (uint32_t)(e * (int)pw + x0); /* wraps for x0 < 0: only used where the position is valid */
 #pragma unroll
             for (int k = 0; k < 8; k++) {
-                const int x = x0 + 4 * k;
-                if (x >= 0 && x < J.pw && acc[k] < ME_SAD_LOOP_INIT) {
-                    const unsigned long long cand = ((unsigned long long)acc[k] << 32) | (idx0 + (uint32_t)x);
-                    key                           = cand < key ? cand : key;
-                }
+                const uint32_t cand = (acc[k] << 16) + l0 + 4u * k;
+                best                = min(best, (uint32_t)(x0 + 4 * k) < pw ? cand : 0xFFFFFFFFu);
             }
         }
     }
-    for (int d = 16; d; d >>= 1) {
-        const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, d);
-        key                            = other < key ? other : key;
-    }
-    return key;
+    best = __reduce_min_sync(0xffffffffu, best);
+    if (best == 0xFFFFFFFFu)
+        return ((unsigned long long)ME_SAD_LOOP_INIT << 32) | 0xFFFFFFFFull;
+    const uint32_t lidx = best & 0xFFFFu, e = lidx / pw, x = lidx - e * pw;
+    return ((unsigned long long)(best >> 16) << 32) | (uint32_t)((J.e0 + (int)e) * t.sa_w + J.px0 + (int)x);
 }
 
 /* ------------------------------------------------------------------------------------------------
