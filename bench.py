@@ -449,13 +449,14 @@ def gpu_main(args):
     except Exception:
         pass
     # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the one `ncu --set full` capture
-    # of this workload kept under profiles/ (ncu_r1_k_hme_final_details.txt, ncu_r1_k_fullsearch_final_details.txt)
-    ncu_traffic = {("1080p-m4", "motion", "k_hme"): 15201536 + 512, ("1080p-m4", "iid", "k_fullsearch"): 13067776}
+    # of this workload kept under profiles/ (ncu_r1_final_<kernel>_<workload>_details.txt)
+    ncu_traffic = {("1080p-m4", "motion", "k_hme"): 15210752 + 4096, ("1080p-m4", "iid", "k_fullsearch"): 13272576,
+                   ("4k-m0", "motion", "k_hme"): 62712832 + 10173952, ("4k-m0", "iid", "k_fullsearch"): 75407104 + 5648640}
     ncu_key = (WORKLOAD, args.kind, dom)
     roofline = {
         "bound": "int_sad", "kernel": dom, "achieved": achieved, "peak": sad_peak / 1e12, "unit": "Tbyte-SAD/s",
         "frac": achieved / (sad_peak / 1e12) if sad_peak else None, "traffic": ncu_traffic.get(ncu_key),
-        "traffic_unit": "DRAM bytes per launch (one picture); the planes a picture's search touches are ~3.3 MB each at 1080p",
+        "traffic_unit": "DRAM bytes per launch (one picture); the three planes of a picture are 3.3 MB at 1080p, 12.4 MB at 4K",
         "hbm_gbs_achieved": (ncu_traffic[ncu_key] * 16 / (dom_ms * 1e-3) / 1e9) if dom_ms > 0 and ncu_key in ncu_traffic else None,
         "peak_source": "VABSDIFF4.U8.ACC issue rate measured live by k_sad_peak on this GPU x 4 bytes",
         "launches_per_step": 16,  # one k_hme, one k_fullsearch and one k_epilogue launch per picture
