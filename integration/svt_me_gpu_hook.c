@@ -1,0 +1,199 @@
+/*
+ * svt_me_gpu_hook.c - see svt_me_gpu_hook.h. Plain C, no CUDA: the engine is a dlopen'ed C-ABI library.
+ */
+#include "svt_me_gpu_hook.h"
+
+#include <dlfcn.h>
+#include <stdlib.h>
+#include <string.h>
+
+int (*svt_me_picture_register)(uint64_t, const uint8_t *, int, int, int, int, int)                                   = NULL;
+int (*svt_me_picture_submit)(uint64_t, const MeGpuParams *, const uint64_t[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS])        = NULL;
+int (*svt_me_picture_wait)(uint64_t, MeGpuOutputs *)                                                                 = NULL;
+int (*svt_me_picture_release)(uint64_t)                                                                              = NULL;
+static void (*hook_shutdown)(void) = NULL;
+static void *hook_lib              = NULL;
+
+static EbErrorType map_error(int rc) {
+    return rc == ME_GPU_OK ? EB_ErrorNone : rc == ME_GPU_ERR_NO_MEMORY ? EB_ErrorInsufficientResources : EB_ErrorUndefined;
+}
+
+EbErrorType svt_me_gpu_hook_init(const char *library_path, int max_width, int max_height, int max_refs_l0, int max_refs_l1,
+                                 int pictures_in_flight) {
+    typedef int (*InitFn)(int, const int *, int, int, int, int, int);
+    void *h = dlopen(library_path ? library_path : "libme_gpu.so", RTLD_NOW | RTLD_LOCAL);
+    if (!h)
+        return EB_ErrorUndefined;
+    InitFn init = (InitFn)dlsym(h, "me_gpu_init");
+    if (!init || init(0, NULL, max_width, max_height, max_refs_l0, max_refs_l1, pictures_in_flight) != ME_GPU_OK) {
+        dlclose(h);
+        return EB_ErrorInsufficientResources;
+    }
+    svt_me_picture_register = (int (*)(uint64_t, const uint8_t *, int, int, int, int, int))dlsym(h, "me_gpu_register_picture");
+    svt_me_picture_submit   = (int (*)(uint64_t, const MeGpuParams *, const uint64_t[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS]))dlsym(h, "me_gpu_submit");
+    svt_me_picture_wait     = (int (*)(uint64_t, MeGpuOutputs *))dlsym(h, "me_gpu_wait");
+    svt_me_picture_release  = (int (*)(uint64_t))dlsym(h, "me_gpu_release_picture");
+    hook_shutdown           = (void (*)(void))dlsym(h, "me_gpu_shutdown");
+    hook_lib                = h;
+    if (!svt_me_picture_register || !svt_me_picture_submit || !svt_me_picture_wait || !svt_me_picture_release || !hook_shutdown) {
+        svt_me_gpu_hook_shutdown();
+        return EB_ErrorUndefined;
+    }
+    return EB_ErrorNone;
+}
+
+void svt_me_gpu_hook_shutdown(void) {
+    if (hook_shutdown)
+        hook_shutdown();
+    svt_me_picture_register = NULL;
+    svt_me_picture_submit   = NULL;
+    svt_me_picture_wait     = NULL;
+    svt_me_picture_release  = NULL;
+    hook_shutdown           = NULL;
+    if (hook_lib)
+        dlclose(hook_lib);
+    hook_lib = NULL;
+}
+
+void svt_me_gpu_params_from_me_ctx(MeGpuParams *p, const MeContext *m) {
+    p->enable_hme_flag            = m->enable_hme_flag;
+    p->enable_hme_level0_flag     = m->enable_hme_level0_flag;
+    p->enable_hme_level1_flag     = m->enable_hme_level1_flag;
+    p->enable_hme_level2_flag     = m->enable_hme_level2_flag;
+    p->hme_search_method          = m->hme_search_method;
+    p->me_search_method           = m->me_search_method;
+    p->use_best_unipred_cand_only = m->use_best_unipred_cand_only;
+    p->reduce_hme_l0_sr_th_min    = m->reduce_hme_l0_sr_th_min;
+    p->reduce_hme_l0_sr_th_max    = m->reduce_hme_l0_sr_th_max;
+    p->num_hme_sa_w               = m->num_hme_sa_w;
+    p->num_hme_sa_h               = m->num_hme_sa_h;
+    memcpy(&p->me_sa, &m->me_sa, sizeof p->me_sa); /* SearchAreaMinMax and MeGpuSearchAreaMinMax share their layout */
+    memcpy(&p->hme_l0_sa, &m->hme_l0_sa, sizeof p->hme_l0_sa);
+    memcpy(&p->hme_l1_sa, &m->hme_l1_sa, sizeof p->hme_l1_sa);
+    memcpy(&p->hme_l2_sa, &m->hme_l2_sa, sizeof p->hme_l2_sa);
+    p->enable_me_hme_ref_pruning               = m->me_hme_prune_ctrls.enable_me_hme_ref_pruning;
+    p->prune_ref_if_hme_sad_dev_bigger_than_th = m->me_hme_prune_ctrls.prune_ref_if_hme_sad_dev_bigger_than_th;
+    p->prune_ref_if_me_sad_dev_bigger_than_th  = m->me_hme_prune_ctrls.prune_ref_if_me_sad_dev_bigger_than_th;
+    p->zz_sad_th                               = m->me_hme_prune_ctrls.zz_sad_th;
+    p->zz_sad_pct                              = m->me_hme_prune_ctrls.zz_sad_pct;
+    p->phme_sad_th                             = m->me_hme_prune_ctrls.phme_sad_th;
+    p->phme_sad_pct                            = m->me_hme_prune_ctrls.phme_sad_pct;
+    p->enable_me_sr_adjustment              = m->me_sr_adjustment_ctrls.enable_me_sr_adjustment;
+    p->reduce_me_sr_based_on_mv_length_th   = m->me_sr_adjustment_ctrls.reduce_me_sr_based_on_mv_length_th;
+    p->stationary_hme_sad_abs_th            = m->me_sr_adjustment_ctrls.stationary_hme_sad_abs_th;
+    p->stationary_me_sr_divisor             = m->me_sr_adjustment_ctrls.stationary_me_sr_divisor;
+    p->reduce_me_sr_based_on_hme_sad_abs_th = m->me_sr_adjustment_ctrls.reduce_me_sr_based_on_hme_sad_abs_th;
+    p->me_sr_divisor_for_low_hme_sad        = m->me_sr_adjustment_ctrls.me_sr_divisor_for_low_hme_sad;
+    p->distance_based_hme_resizing          = m->me_sr_adjustment_ctrls.distance_based_hme_resizing;
+    p->me_8x8_var_enabled = m->me_8x8_var_ctrls.enabled;
+    p->me_sr_div4_th      = m->me_8x8_var_ctrls.me_sr_div4_th;
+    p->me_sr_div2_th      = m->me_8x8_var_ctrls.me_sr_div2_th;
+    p->me_sr_mult2_th     = m->me_8x8_var_ctrls.me_sr_mult2_th;
+    p->mv_sa_adj_enabled          = m->mv_based_sa_adj.enabled;
+    p->mv_sa_adj_nearest_ref_only = m->mv_based_sa_adj.nearest_ref_only;
+    p->mv_sa_adj_mv_size_th       = m->mv_based_sa_adj.mv_size_th;
+    p->mv_sa_adj_sa_multiplier    = m->mv_based_sa_adj.sa_multiplier;
+    p->prehme_enable           = m->prehme_ctrl.enable;
+    p->prehme_skip_search_line = m->prehme_ctrl.skip_search_line;
+    p->prehme_l1_early_exit    = m->prehme_ctrl.l1_early_exit;
+    memcpy(p->prehme_sa_cfg, m->prehme_ctrl.prehme_sa_cfg, sizeof p->prehme_sa_cfg);
+    p->prune_me_candidates_th      = m->prune_me_candidates_th;
+    p->me_early_exit_th            = m->me_early_exit_th;
+    p->me_safe_limit_zz_th         = m->me_safe_limit_zz_th;
+    p->prev_me_stage_based_exit_th = m->prev_me_stage_based_exit_th;
+}
+
+void svt_me_gpu_params_from_ctx(MeGpuParams *p, const PictureParentControlSet *pcs, const MeContext *m) {
+    const SequenceControlSet *scs = pcs->scs;
+    memset(p, 0, sizeof *p);
+    svt_me_gpu_params_from_me_ctx(p, m);
+    /* pcs / scs scalars read by svt_aom_motion_estimation_b64 and its callees */
+    p->picture_number                  = pcs->picture_number;
+    p->input_resolution                = (uint8_t)scs->input_resolution;
+    p->enable_me_8x8                   = pcs->enable_me_8x8;
+    p->enable_me_16x16                 = pcs->enable_me_16x16;
+    p->max_number_of_pus_per_sb        = pcs->max_number_of_pus_per_sb;
+    p->gm_enabled                      = pcs->gm_ctrls.enabled;
+    p->gm_use_distance_based_active_th = pcs->gm_ctrls.use_distance_based_active_th;
+    p->hierarchical_levels             = pcs->hierarchical_levels;
+    p->pcs_temporal_layer_index        = pcs->temporal_layer_index;
+    p->similar_brightness_refs         = pcs->similar_brightness_refs;
+    p->only_l_bwd                      = scs->mrp_ctrls.only_l_bwd;
+    p->max_cand                        = pcs->pa_me_data->max_cand;
+    p->max_refs                        = pcs->pa_me_data->max_refs;
+    p->max_l0                          = pcs->pa_me_data->max_l0;
+    /* per-call MeContext fields, me_process.c:215-262 */
+    p->me_type                     = (uint8_t)m->me_type;
+    p->tf_me_exit_th               = m->tf_me_exit_th;
+    p->num_of_list_to_search       = m->num_of_list_to_search;
+    p->num_of_ref_pic_to_search[0] = m->num_of_ref_pic_to_search[0];
+    p->num_of_ref_pic_to_search[1] = m->num_of_ref_pic_to_search[1];
+    p->temporal_layer_index        = m->temporal_layer_index;
+    p->is_ref                      = m->is_ref;
+}
+
+EbErrorType svt_me_gpu_register_picture(const PictureParentControlSet *pcs, const EbPictureBufferDesc *input_padded_pic) {
+    if (!svt_me_picture_register)
+        return EB_ErrorUndefined;
+    const EbPictureBufferDesc *d = input_padded_pic; /* y8b luma with its 68-pixel border, reference_object.c:251-253 */
+    return map_error(svt_me_picture_register(pcs->picture_number, d->buffer_y, d->stride_y, d->org_x, d->org_y,
+                                             pcs->aligned_width, pcs->aligned_height));
+}
+
+EbErrorType svt_me_gpu_release_picture(uint64_t picture_number) {
+    return svt_me_picture_release ? map_error(svt_me_picture_release(picture_number)) : EB_ErrorUndefined;
+}
+
+EbErrorType svt_me_gpu_picture(PictureParentControlSet *pcs, const MeContext *me_ctx) {
+    if (!svt_me_picture_submit || !svt_me_picture_wait)
+        return EB_ErrorUndefined;
+    MeGpuParams gp;
+    uint64_t    refs[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS] = {{0}};
+    svt_me_gpu_params_from_ctx(&gp, pcs, me_ctx);
+    for (int l = 0; l < me_ctx->num_of_list_to_search; l++)
+        for (int r = 0; r < me_ctx->num_of_ref_pic_to_search[l]; r++)
+            refs[l][r] = me_ctx->me_ds_ref_array[l][r].picture_number; /* me_process.c:248-262 */
+    const int rc = svt_me_picture_submit(pcs->picture_number, &gp, refs);
+    if (rc != ME_GPU_OK)
+        return map_error(rc);
+
+    /* MeGpuOutputs wants one slab per MeSbResults array; the reference allocates me_results[b64] one by one
+       (pcs.c:1425-1444), so the three arrays come back into staging slabs and are copied out per b64. The eight
+       per-b64 pcs arrays are contiguous already and are written in place. */
+    const uint32_t b64_w = (uint32_t)(pcs->aligned_width + 63) / 64, b64_h = (uint32_t)(pcs->aligned_height + 63) / 64;
+    const uint32_t nb = b64_w * b64_h;
+    const uint32_t P  = pcs->enable_me_16x16 ? (pcs->enable_me_8x8 ? pcs->max_number_of_pus_per_sb : MAX_SB64_PU_COUNT_NO_8X8)
+                                             : MAX_SB64_PU_COUNT_WO_16X16; /* pcs.c:108-117 */
+    const size_t n_idx = (size_t)nb * P, n_cand = n_idx * gp.max_cand, n_mv = n_idx * gp.max_refs;
+    uint8_t     *slab  = (uint8_t *)malloc(n_idx + n_cand + n_mv * sizeof(uint32_t) + 16);
+    if (!slab) {
+        MeGpuOutputs none;
+        memset(&none, 0, sizeof none);
+        svt_me_picture_wait(pcs->picture_number, &none); /* retire the job */
+        return EB_ErrorInsufficientResources;
+    }
+    MeGpuOutputs out;
+    memset(&out, 0, sizeof out);
+    out.b64_count                   = nb;
+    out.me_mv_array                 = (uint32_t *)slab; /* first: 4-byte aligned */
+    out.total_me_candidate_index    = slab + n_mv * sizeof(uint32_t);
+    out.me_candidate_array          = out.total_me_candidate_index + n_idx;
+    out.me_64x64_distortion         = pcs->me_64x64_distortion;
+    out.me_32x32_distortion         = pcs->me_32x32_distortion;
+    out.me_16x16_distortion         = pcs->me_16x16_distortion;
+    out.me_8x8_distortion           = pcs->me_8x8_distortion;
+    out.me_8x8_cost_variance        = pcs->me_8x8_cost_variance;
+    out.rc_me_distortion            = pcs->rc_me_distortion;
+    out.stationary_block_present_sb = pcs->stationary_block_present_sb;
+    out.rc_me_allow_gm              = pcs->rc_me_allow_gm;
+    const int rw = svt_me_picture_wait(pcs->picture_number, &out);
+    if (rw == ME_GPU_OK && out.pu_count == P)
+        for (uint32_t b = 0; b < nb; b++) {
+            MeSbResults *res = pcs->pa_me_data->me_results[b];
+            memcpy(res->total_me_candidate_index, out.total_me_candidate_index + (size_t)b * P, P);
+            memcpy(res->me_candidate_array, out.me_candidate_array + (size_t)b * P * gp.max_cand, (size_t)P * gp.max_cand);
+            memcpy(res->me_mv_array, out.me_mv_array + (size_t)b * P * gp.max_refs, (size_t)P * gp.max_refs * sizeof(uint32_t));
+        }
+    free(slab);
+    return rw != ME_GPU_OK ? map_error(rw) : out.pu_count == P ? EB_ErrorNone : EB_ErrorUndefined;
+}

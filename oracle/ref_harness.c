@@ -177,53 +177,10 @@ static void ctx_from_params(MeContext *m, const MeGpuParams *p) {
     m->prev_me_stage_based_exit_th = p->prev_me_stage_based_exit_th;
 }
 
-static void params_from_ctx(MeGpuParams *p, const MeContext *m) {
-    p->enable_hme_flag        = m->enable_hme_flag;
-    p->enable_hme_level0_flag = m->enable_hme_level0_flag;
-    p->enable_hme_level1_flag = m->enable_hme_level1_flag;
-    p->enable_hme_level2_flag = m->enable_hme_level2_flag;
-    p->hme_search_method      = m->hme_search_method;
-    p->me_search_method       = m->me_search_method;
-    p->use_best_unipred_cand_only = m->use_best_unipred_cand_only;
-    p->reduce_hme_l0_sr_th_min = m->reduce_hme_l0_sr_th_min;
-    p->reduce_hme_l0_sr_th_max = m->reduce_hme_l0_sr_th_max;
-    p->num_hme_sa_w = m->num_hme_sa_w;
-    p->num_hme_sa_h = m->num_hme_sa_h;
-    memcpy(&p->me_sa, &m->me_sa, sizeof p->me_sa);
-    memcpy(&p->hme_l0_sa, &m->hme_l0_sa, sizeof p->hme_l0_sa);
-    memcpy(&p->hme_l1_sa, &m->hme_l1_sa, sizeof p->hme_l1_sa);
-    memcpy(&p->hme_l2_sa, &m->hme_l2_sa, sizeof p->hme_l2_sa);
-    p->enable_me_hme_ref_pruning               = m->me_hme_prune_ctrls.enable_me_hme_ref_pruning;
-    p->prune_ref_if_hme_sad_dev_bigger_than_th = m->me_hme_prune_ctrls.prune_ref_if_hme_sad_dev_bigger_than_th;
-    p->prune_ref_if_me_sad_dev_bigger_than_th  = m->me_hme_prune_ctrls.prune_ref_if_me_sad_dev_bigger_than_th;
-    p->zz_sad_th    = m->me_hme_prune_ctrls.zz_sad_th;
-    p->zz_sad_pct   = m->me_hme_prune_ctrls.zz_sad_pct;
-    p->phme_sad_th  = m->me_hme_prune_ctrls.phme_sad_th;
-    p->phme_sad_pct = m->me_hme_prune_ctrls.phme_sad_pct;
-    p->enable_me_sr_adjustment              = m->me_sr_adjustment_ctrls.enable_me_sr_adjustment;
-    p->reduce_me_sr_based_on_mv_length_th   = m->me_sr_adjustment_ctrls.reduce_me_sr_based_on_mv_length_th;
-    p->stationary_hme_sad_abs_th            = m->me_sr_adjustment_ctrls.stationary_hme_sad_abs_th;
-    p->stationary_me_sr_divisor             = m->me_sr_adjustment_ctrls.stationary_me_sr_divisor;
-    p->reduce_me_sr_based_on_hme_sad_abs_th = m->me_sr_adjustment_ctrls.reduce_me_sr_based_on_hme_sad_abs_th;
-    p->me_sr_divisor_for_low_hme_sad        = m->me_sr_adjustment_ctrls.me_sr_divisor_for_low_hme_sad;
-    p->distance_based_hme_resizing          = m->me_sr_adjustment_ctrls.distance_based_hme_resizing;
-    p->me_8x8_var_enabled = m->me_8x8_var_ctrls.enabled;
-    p->me_sr_div4_th      = m->me_8x8_var_ctrls.me_sr_div4_th;
-    p->me_sr_div2_th      = m->me_8x8_var_ctrls.me_sr_div2_th;
-    p->me_sr_mult2_th     = m->me_8x8_var_ctrls.me_sr_mult2_th;
-    p->mv_sa_adj_enabled          = m->mv_based_sa_adj.enabled;
-    p->mv_sa_adj_nearest_ref_only = m->mv_based_sa_adj.nearest_ref_only;
-    p->mv_sa_adj_mv_size_th       = m->mv_based_sa_adj.mv_size_th;
-    p->mv_sa_adj_sa_multiplier    = m->mv_based_sa_adj.sa_multiplier;
-    p->prehme_enable           = m->prehme_ctrl.enable;
-    p->prehme_skip_search_line = m->prehme_ctrl.skip_search_line;
-    p->prehme_l1_early_exit    = m->prehme_ctrl.l1_early_exit;
-    memcpy(p->prehme_sa_cfg, m->prehme_ctrl.prehme_sa_cfg, sizeof p->prehme_sa_cfg);
-    p->prune_me_candidates_th      = m->prune_me_candidates_th;
-    p->me_early_exit_th            = m->me_early_exit_th;
-    p->me_safe_limit_zz_th         = m->me_safe_limit_zz_th;
-    p->prev_me_stage_based_exit_th = m->prev_me_stage_based_exit_th;
-}
+/* MeContext -> MeGpuParams is the reference-side binding's own mapping (integration/svt_me_gpu_hook.c): the derive-params
+ * tests below therefore pin the code a maintainer ships, not a private copy of it */
+#include "../integration/svt_me_gpu_hook.h"
+static void params_from_ctx(MeGpuParams *p, const MeContext *m) { svt_me_gpu_params_from_me_ctx(p, m); }
 
 /* Extra inputs of svt_aom_sig_deriv_me that come from enc_handle.c's static set_mrp_ctrl() and cannot be
  * called from outside the reference: passed in by the caller (the host-side restatement computes them,
@@ -414,6 +371,123 @@ REF_API int ref_me_b64_range(const OraclePicture *src, const OraclePicture *cons
     }
     free(geo); free(rp); free(res); free(md); free(m); free(scs); free(pcs);
     return 0;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * The reference-side binding (integration/svt_me_gpu_hook.c) driven the way the encoder would drive it: a pcs with
+ * individually allocated MeSbResults (pcs.c:1425-1444, me_sb_results_ctor), pictures as EbPictureBufferDesc, controls
+ * in a MeContext. svt_me_gpu_picture() stands where the b64 loop of svt_aom_motion_estimation_kernel stands; what it
+ * leaves in the pcs is copied into `out` (same layout as ref_me_b64_range) for the byte-for-byte comparison with the
+ * CPU loop. Needs a GPU: called from the `-m gpu` tests only.
+ * ---------------------------------------------------------------------------------------------- */
+REF_API int ref_hook_me_picture(const OraclePicture *src, const OraclePicture *const refs[2][4], const MeGpuParams *p,
+                                MeGpuOutputs *out, const char *gpu_library_path) {
+    const int pic_w = (src->full.width + 7) & ~7, pic_h = (src->full.height + 7) & ~7;
+    const uint32_t bw = (pic_w + 63) / 64, bh = (pic_h + 63) / 64, total = bw * bh;
+    if (out->b64_count < total)
+        return -2;
+    PictureParentControlSet *pcs = calloc(1, sizeof *pcs);
+    SequenceControlSet      *scs = calloc(1, sizeof *scs);
+    MeContext               *m   = calloc(1, sizeof *m);
+    MotionEstimationData    *md  = calloc(1, sizeof *md);
+    MeSbResults            **rp  = calloc(total, sizeof *rp);
+    if (!pcs || !scs || !m || !md || !rp)
+        return -1;
+    const uint32_t P = p->enable_me_16x16 ? (p->enable_me_8x8 ? p->max_number_of_pus_per_sb : 21) : 5;
+    ctx_from_params(m, p);
+    pcs->scs                      = scs;
+    pcs->picture_number           = p->picture_number;
+    pcs->aligned_width            = (uint16_t)pic_w;
+    pcs->aligned_height           = (uint16_t)pic_h;
+    pcs->enable_me_8x8            = p->enable_me_8x8;
+    pcs->enable_me_16x16          = p->enable_me_16x16;
+    pcs->max_number_of_pus_per_sb = p->max_number_of_pus_per_sb;
+    pcs->gm_ctrls.enabled         = p->gm_enabled;
+    pcs->gm_ctrls.use_distance_based_active_th = p->gm_use_distance_based_active_th;
+    pcs->hierarchical_levels      = p->hierarchical_levels;
+    pcs->temporal_layer_index     = p->pcs_temporal_layer_index;
+    pcs->similar_brightness_refs  = p->similar_brightness_refs;
+    pcs->pa_me_data               = md;
+    pcs->me_64x64_distortion      = calloc(total, sizeof(uint32_t)); /* pcs.c allocates these per picture, b64_total_count long */
+    pcs->me_32x32_distortion      = calloc(total, sizeof(uint32_t));
+    pcs->me_16x16_distortion      = calloc(total, sizeof(uint32_t));
+    pcs->me_8x8_distortion        = calloc(total, sizeof(uint32_t));
+    pcs->me_8x8_cost_variance     = calloc(total, sizeof(uint32_t));
+    pcs->rc_me_distortion         = calloc(total, sizeof(uint32_t));
+    pcs->stationary_block_present_sb = calloc(total, 1);
+    pcs->rc_me_allow_gm           = calloc(total, 1);
+    scs->mrp_ctrls.only_l_bwd     = p->only_l_bwd;
+    scs->input_resolution         = (EbInputResolution)p->input_resolution;
+    scs->b64_size                 = 64;
+    md->me_results                = rp;
+    md->max_cand                  = p->max_cand;
+    md->max_refs                  = p->max_refs;
+    md->max_l0                    = p->max_l0;
+    for (uint32_t b = 0; b < total; b++) { /* me_sb_results_ctor: three arrays per b64, each its own allocation */
+        rp[b]                           = calloc(1, sizeof(MeSbResults));
+        rp[b]->me_mv_array              = calloc((size_t)P * p->max_refs, sizeof(MvCandidate));
+        rp[b]->me_candidate_array       = calloc((size_t)P * p->max_cand, sizeof(MeCandidate));
+        rp[b]->total_me_candidate_index = calloc(P, 1);
+    }
+    int rc = 0;
+    if (svt_me_gpu_hook_init(gpu_library_path, pic_w, pic_h, 4, 3, 10) != EB_ErrorNone)
+        rc = -10;
+    /* picture analysis side: every picture is registered once, from its padded y8b descriptor */
+    EbPictureBufferDesc d;
+    PictureParentControlSet *rpcs = calloc(1, sizeof *rpcs);
+    uint64_t registered[9];
+    int      nreg = 0;
+    for (int k = -1; !rc && k < 8; k++) {
+        const OraclePicture *pic = k < 0 ? src : refs[k / 4][k % 4];
+        if (k >= 0 && (k / 4 >= p->num_of_list_to_search || k % 4 >= p->num_of_ref_pic_to_search[k / 4]))
+            continue;
+        int seen = 0;
+        for (int i = 0; i < nreg; i++) seen |= registered[i] == pic->picture_number;
+        if (seen)
+            continue;
+        desc_from_plane(&d, &pic->full);
+        rpcs->picture_number = pic->picture_number;
+        rpcs->aligned_width  = (uint16_t)pic_w;
+        rpcs->aligned_height = (uint16_t)pic_h;
+        if (svt_me_gpu_register_picture(rpcs, &d) != EB_ErrorNone)
+            rc = -11;
+        else
+            registered[nreg++] = pic->picture_number;
+    }
+    /* ME kernel side: me_process.c:215-262 */
+    m->me_type = (EbMeType)p->me_type;
+    for (int li = 0; li < p->num_of_list_to_search; li++)
+        for (int ri = 0; ri < p->num_of_ref_pic_to_search[li]; ri++)
+            m->me_ds_ref_array[li][ri].picture_number = refs[li][ri]->picture_number;
+    if (!rc && svt_me_gpu_picture(pcs, m) != EB_ErrorNone)
+        rc = -12;
+    for (int i = 0; i < nreg; i++) svt_me_gpu_release_picture(registered[i]);
+    svt_me_gpu_hook_shutdown();
+
+    for (uint32_t b = 0; b < total; b++) {
+        if (!rc) {
+            memcpy(out->total_me_candidate_index + (size_t)b * P, rp[b]->total_me_candidate_index, P);
+            memcpy(out->me_candidate_array + (size_t)b * P * p->max_cand, rp[b]->me_candidate_array, (size_t)P * p->max_cand);
+            memcpy(out->me_mv_array + (size_t)b * P * p->max_refs, rp[b]->me_mv_array, (size_t)P * p->max_refs * sizeof(uint32_t));
+        }
+        free(rp[b]->total_me_candidate_index); free(rp[b]->me_candidate_array); free(rp[b]->me_mv_array); free(rp[b]);
+    }
+    if (!rc) {
+        memcpy(out->me_64x64_distortion, pcs->me_64x64_distortion, total * sizeof(uint32_t));
+        memcpy(out->me_32x32_distortion, pcs->me_32x32_distortion, total * sizeof(uint32_t));
+        memcpy(out->me_16x16_distortion, pcs->me_16x16_distortion, total * sizeof(uint32_t));
+        memcpy(out->me_8x8_distortion, pcs->me_8x8_distortion, total * sizeof(uint32_t));
+        memcpy(out->me_8x8_cost_variance, pcs->me_8x8_cost_variance, total * sizeof(uint32_t));
+        memcpy(out->rc_me_distortion, pcs->rc_me_distortion, total * sizeof(uint32_t));
+        memcpy(out->stationary_block_present_sb, pcs->stationary_block_present_sb, total);
+        memcpy(out->rc_me_allow_gm, pcs->rc_me_allow_gm, total);
+        out->b64_count = total;
+        out->pu_count  = P;
+    }
+    free(pcs->me_64x64_distortion); free(pcs->me_32x32_distortion); free(pcs->me_16x16_distortion); free(pcs->me_8x8_distortion);
+    free(pcs->me_8x8_cost_variance); free(pcs->rc_me_distortion); free(pcs->stationary_block_present_sb); free(pcs->rc_me_allow_gm);
+    free(rpcs); free(rp); free(md); free(m); free(scs); free(pcs);
+    return rc;
 }
 
 /* static in the reference (temporal_filtering.c:2760): level 0 copies hme_l0_sa_default_tf into hme_l0_sa */

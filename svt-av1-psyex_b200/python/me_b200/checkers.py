@@ -103,6 +103,24 @@ class Reference:
             raise RuntimeError(f"ref_me_b64_range failed: {rc}")
         return out
 
+    def has_hook(self):
+        return hasattr(self.lib, "ref_hook_me_picture")
+
+    def hook_me_picture(self, src: Picture, refs, params, gpu_library_path):
+        """The reference-side binding (integration/svt_me_gpu_hook.c, compiled against the reference's headers) driven
+        like the encoder drives its ME stage: a real pcs / MeContext in, pcs->pa_me_data->me_results and the per-b64
+        pcs arrays out. Runs the CUDA engine through dlopen(gpu_library_path): GPU tests only."""
+        self.lib.ref_hook_me_picture.argtypes = [C.POINTER(abi.OraclePicture), C.POINTER(abi.RefArray),
+                                                 C.POINTER(abi.MeGpuParams), C.POINTER(abi.MeGpuOutputs), C.c_char_p]
+        out = Outputs(src.width, src.height, params, debug=False)
+        arr, keep = _refs_array(refs)
+        s = src.c_struct()
+        rc = self.lib.ref_hook_me_picture(C.byref(s), C.byref(arr), C.byref(params), C.byref(out.c),
+                                          gpu_library_path.encode())
+        if rc != 0:
+            raise RuntimeError(f"ref_hook_me_picture failed: {rc}")
+        return out
+
     def derive_params_tf(self, cfg):
         p = abi.MeGpuParams()
         self.lib.ref_derive_params_tf.argtypes = [C.POINTER(abi.MeGpuTfConfig), C.POINTER(abi.MeGpuParams)]

@@ -73,3 +73,19 @@ def test_product_does_not_reference_the_oracle():
                 if f == "abi.py":  # paths of the checker libraries are only named for checkers.py
                     continue
                 assert "me_oracle" not in txt and "libme_ref" not in txt and "me_emul" not in txt, os.path.join(root, f)
+
+
+def test_reference_side_hook_builds_and_fails_loudly_without_the_engine():
+    """integration/svt_me_gpu_hook.c compiles against the reference's headers (oracle/Makefile) and, with no engine
+    library to dlopen, reports the failure instead of falling back to anything."""
+    from helpers import PictureSet, derive
+    from me_b200.checkers import Reference
+    if not Reference.available():
+        pytest.skip("needs oracle/_ref/libme_ref.so (built where /root/reference exists)")
+    ref = Reference()
+    assert ref.has_hook()
+    w, h, n, poc = 64, 64, 9, 4
+    ps = PictureSet(w, h, n, "iid", ref)
+    cfg, p, l0, l1 = derive(4, w, h, poc, n)
+    with pytest.raises(RuntimeError, match="-10"):
+        ref.hook_me_picture(ps.get(poc), [[ps.get(k) for k in l0], [ps.get(k) for k in l1]], p, "/nonexistent/libme_gpu.so")

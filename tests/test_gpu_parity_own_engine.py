@@ -80,3 +80,27 @@ def test_two_devices_in_one_process(oracle):
         exp = oracle.me_picture(ps.get(poc), [[ps.get(k) for k in l0], [ps.get(k) for k in l1]], p)
         bad = planes.compare_outputs(exp, got[poc], used_refs=used_refs(l0, l1))
         assert not bad, (poc, bad)
+
+
+@pytest.mark.parametrize("w,h,preset,poc,kind", [(320, 192, 4, 4, "motion"), (320, 192, 8, 1, "iid"), (640, 360, 2, 8, "motion"),
+                                                 (200, 136, 0, 2, "motion")])
+def test_reference_side_hook_fills_the_pcs_like_the_cpu_loop(w, h, preset, poc, kind):
+    """integration/svt_me_gpu_hook.c (the binding INTEGRATION.md describes, compiled against the reference's own headers
+    into oracle/_ref/libme_ref.so) in place of the b64 loop of svt_aom_motion_estimation_kernel: the MeSbResults of
+    every b64 and the eight per-b64 pcs arrays equal, byte for byte, what the reference's own
+    svt_aom_motion_estimation_b64 loop leaves in an identical pcs."""
+    from me_b200 import abi
+    from me_b200.checkers import Reference
+    if not Reference.available():
+        pytest.skip("oracle/_ref/libme_ref.so is built where /root/reference exists and travels prebuilt")
+    ref = Reference()
+    assert ref.has_hook()
+    n = 17
+    ps = PictureSet(w, h, n, kind, ref)
+    cfg, p, l0, l1 = derive(preset, w, h, poc, n)
+    refs = [[ps.get(k) for k in l0], [ps.get(k) for k in l1]]
+    exp = ref.me_picture(ps.get(poc), refs, p, simd=0, debug=False)
+    got = ref.hook_me_picture(ps.get(poc), refs, p, abi.GPU_LIB)
+    bad = planes.compare_outputs(exp, got, fields=planes.PRODUCT_FIELDS)
+    assert not bad, bad
+    assert got.c.pu_count == exp.c.pu_count
