@@ -136,6 +136,58 @@ def test_pictures_in_flight_out_of_order(engine, oracle):
         assert not bad, (poc, bad)
 
 
+def test_concurrent_callers(engine, oracle):
+    """SURVEY 8(b) threading: the encoder's ME threads (up to 25) call submit / wait concurrently, keyed by picture, while
+    picture analysis registers new pictures. Four host threads, each with its own pictures of a different preset."""
+    import threading
+    w, h, n = 320, 192, 17
+    ps = PictureSet(w, h, n, "motion", oracle)
+    work = [(4, [16, 8]), (8, [4, 12]), (2, [2, 6]), (0, [1, 10])]
+    jobs, pocs = {}, set()
+    for preset, lst in work:
+        for poc in lst:
+            jobs[poc] = derive(preset, w, h, poc, n)
+            pocs |= set([poc] + jobs[poc][2] + jobs[poc][3])
+    for k in sorted(pocs):
+        ps.get(k)  # synthesise up front: the threads below only talk to the engine
+    base, got, errors = 5000, {}, []
+    barrier = threading.Barrier(len(work))
+
+    def run(tid, lst):
+        try:
+            mine = sorted(set(k for poc in lst for k in [poc] + jobs[poc][2] + jobs[poc][3]))
+            off = base + 100 * tid  # every thread registers its own copies under its own picture numbers
+            barrier.wait()
+            for k in mine:
+                engine.register_picture(off + k, ps.get(k).planes[0], w, h)
+            for rep in range(3):
+                for poc in lst:
+                    _, p, l0, l1 = jobs[poc]
+                    q = type(p).from_buffer_copy(p)
+                    q.picture_number = off + poc
+                    engine.submit(off + poc, q, [[off + k for k in l0], [off + k for k in l1]])
+                for poc in reversed(lst):
+                    out = planes.Outputs(w, h, jobs[poc][1])
+                    engine.wait(off + poc, out)
+                    got[(poc, rep)] = out
+            for k in mine:
+                engine.release_picture(off + k)
+        except Exception as e:  # surfaced in the main thread
+            errors.append((tid, repr(e)))
+
+    threads = [threading.Thread(target=run, args=(i, lst)) for i, (_, lst) in enumerate(work)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    for poc, (_, p, l0, l1) in jobs.items():
+        exp = oracle.me_picture(ps.get(poc), [[ps.get(k) for k in l0], [ps.get(k) for k in l1]], p)
+        for rep in range(3):
+            bad = planes.compare_outputs(exp, got[(poc, rep)], used_refs=used_refs(l0, l1))
+            assert not bad, (poc, rep, bad)
+
+
 def test_dg_detector_parity(engine, oracle):
     """k_dg_hme through me_gpu_dg_detector against the restatement of dg_detector_hme_level0, every metric exact;
     the golden metrics (frozen from the reference itself) are checked on the way."""
