@@ -37,8 +37,13 @@
 #define HM_ALL_THREADS (HM_THREADS + 32) /* + the warp that requests the windows (TMA) */
 #define HM_BUF_WORDS 2048 /* per-warp staging buffer: source block (<= 512 words) + reference window (15 rows x
                              131 words of the widest pre-HME strip fit; taller windows are banded) */
-#define FS_WARP_MAX 256 /* search areas up to this many positions (and <= FS_WARP_MAXW wide) stay in k_hme */
+#ifndef FS_WARP_MAX
+#define FS_WARP_MAX 256
+#endif
+/* FS_WARP_MAX: search areas up to this many positions (and <= FS_WARP_MAXW wide) stay in k_hme */
+#ifndef FS_WARP_MAXW
 #define FS_WARP_MAXW 48
+#endif
 #define HM_ITEM_POS_A 384 /* search positions per work item, lane = position */
 #define HM_ITEM_POS_B 32 /* ... lane = block row */
 #define HM_ITEM_POS_FS 16 /* ... full-search positions */
