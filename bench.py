@@ -328,7 +328,8 @@ def gpu_main(args):
     # Pictures stream through the engine the way they stream through the encoder's ME stage: up to WINDOW pictures
     # are in flight, the oldest one is waited for (its results copied back) before the next is submitted, and a step
     # does not drain the pipeline; drain() (inside the timed region) waits for whatever is left.
-    WINDOW = 12  # < 16: the engine's job contexts, and the pinned result buffer of a POC is reused every 16 pictures
+    # < 16: the engine's job contexts, and the pinned result buffer of a POC is reused every 16 pictures
+    WINDOW = int(os.environ.get("BENCH_WINDOW", 12))
     in_flight = collections.deque()
 
     def retire_oldest():

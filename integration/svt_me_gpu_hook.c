@@ -12,6 +12,7 @@ int (*svt_me_picture_submit)(uint64_t, const MeGpuParams *, const uint64_t[ME_GP
 int (*svt_me_picture_wait)(uint64_t, MeGpuOutputs *)                                                                 = NULL;
 int (*svt_me_picture_release)(uint64_t)                                                                              = NULL;
 static void (*hook_shutdown)(void) = NULL;
+static int (*hook_dg)(uint64_t, uint64_t, uint8_t, MeGpuDgMetrics *) = NULL;
 static void *hook_lib              = NULL;
 
 static EbErrorType map_error(int rc) {
@@ -34,6 +35,7 @@ EbErrorType svt_me_gpu_hook_init(const char *library_path, int max_width, int ma
     svt_me_picture_wait     = (int (*)(uint64_t, MeGpuOutputs *))dlsym(h, "me_gpu_wait");
     svt_me_picture_release  = (int (*)(uint64_t))dlsym(h, "me_gpu_release_picture");
     hook_shutdown           = (void (*)(void))dlsym(h, "me_gpu_shutdown");
+    hook_dg                 = (int (*)(uint64_t, uint64_t, uint8_t, MeGpuDgMetrics *))dlsym(h, "me_gpu_dg_detector");
     hook_lib                = h;
     if (!svt_me_picture_register || !svt_me_picture_submit || !svt_me_picture_wait || !svt_me_picture_release || !hook_shutdown) {
         svt_me_gpu_hook_shutdown();
@@ -50,6 +52,7 @@ void svt_me_gpu_hook_shutdown(void) {
     svt_me_picture_wait     = NULL;
     svt_me_picture_release  = NULL;
     hook_shutdown           = NULL;
+    hook_dg                 = NULL;
     if (hook_lib)
         dlclose(hook_lib);
     hook_lib = NULL;
@@ -196,4 +199,60 @@ EbErrorType svt_me_gpu_picture(PictureParentControlSet *pcs, const MeContext *me
         }
     free(slab);
     return rw != ME_GPU_OK ? map_error(rw) : out.pu_count == P ? EB_ErrorNone : EB_ErrorUndefined;
+}
+
+EbErrorType svt_me_gpu_tf_pair(const PictureParentControlSet *centre_pcs, MeContext *me_ctx, uint64_t neighbour_picture_number,
+                               SvtMeGpuTfPair *pair) {
+    if (!svt_me_picture_submit || !svt_me_picture_wait)
+        return EB_ErrorUndefined;
+    MeGpuParams gp;
+    uint64_t    refs[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS] = {{0}};
+    svt_me_gpu_params_from_ctx(&gp, centre_pcs, me_ctx);
+    gp.me_type                     = ME_GPU_ME_MCTF;
+    gp.num_of_list_to_search       = 1; /* temporal_filtering.c:3150-3152 */
+    gp.num_of_ref_pic_to_search[0] = 1;
+    gp.num_of_ref_pic_to_search[1] = 0;
+    refs[0][0]                     = neighbour_picture_number;
+    int rc = svt_me_picture_submit(centre_pcs->picture_number, &gp, refs);
+    if (rc != ME_GPU_OK)
+        return map_error(rc);
+    MeGpuOutputs out;
+    memset(&out, 0, sizeof out);
+    out.b64_count     = pair->b64_count;
+    out.tf_best_sad   = pair->best_sad;
+    out.tf_best_mv    = pair->best_mv;
+    out.tf_hme_centre = pair->hme_centre;
+    out.tf_hme_sad    = pair->hme_sad;
+    out.tf_early_exit = pair->early_exit;
+    rc = svt_me_picture_wait(centre_pcs->picture_number, &out);
+    if (rc != ME_GPU_OK)
+        return map_error(rc);
+    me_ctx->tf_tot_horz_blks += out.tf_tot_horz_blks; /* motion_estimation.c:2469-2474 */
+    me_ctx->tf_tot_vert_blks += out.tf_tot_vert_blks;
+    return EB_ErrorNone;
+}
+
+void svt_me_gpu_tf_load_block(MeContext *me_ctx, const SvtMeGpuTfPair *pair, uint32_t b) {
+    memcpy(me_ctx->p_sb_best_sad[0][0], pair->best_sad + (size_t)SQUARE_PU_COUNT * b, SQUARE_PU_COUNT * sizeof(uint32_t));
+    memcpy(me_ctx->p_sb_best_mv[0][0], pair->best_mv + (size_t)SQUARE_PU_COUNT * b, SQUARE_PU_COUNT * sizeof(uint32_t));
+    me_ctx->search_results[0][0].hme_sc_x = pair->hme_centre[2 * b];
+    me_ctx->search_results[0][0].hme_sc_y = pair->hme_centre[2 * b + 1];
+    me_ctx->search_results[0][0].hme_sad  = pair->hme_sad[b];
+    if (pair->early_exit[b])
+        me_ctx->tf_use_pred_64x64_only_th = (uint8_t)~0; /* motion_estimation.c:3111 */
+}
+
+EbErrorType svt_me_gpu_dg_detector(PictureParentControlSet *src_pcs) {
+    if (!hook_dg)
+        return EB_ErrorUndefined;
+    MeGpuDgMetrics m;
+    const int      rc = hook_dg(src_pcs->picture_number, src_pcs->dg_detector->ref_pic->picture_number,
+                                (uint8_t)src_pcs->input_resolution, &m);
+    if (rc != ME_GPU_OK)
+        return map_error(rc);
+    src_pcs->dg_detector->metrics.tot_dist       = m.tot_dist; /* then pd_process.c:595-603 unchanged */
+    src_pcs->dg_detector->metrics.tot_cplx       = m.tot_cplx;
+    src_pcs->dg_detector->metrics.tot_active     = m.tot_active;
+    src_pcs->dg_detector->metrics.sum_in_vectors = m.sum_in_vectors;
+    return EB_ErrorNone;
 }

@@ -49,6 +49,30 @@ EbErrorType svt_me_gpu_release_picture(uint64_t picture_number);
  * svt_aom_motion_estimation_b64 does b64 by b64. me_ctx carries the controls and me_ds_ref_array[l][r].picture_number. */
 EbErrorType svt_me_gpu_picture(PictureParentControlSet *pcs, const MeContext *me_ctx);
 
+/* ---- temporal filter (ME_MCTF, temporal_filtering.c:3144-3187) ------------------------------------------------ */
+/* ME results of one (centre, neighbour) pair over all blocks: what the block loop of produce_temporally_filtered_pic
+ * reads from the MeContext after its svt_aom_motion_estimation_b64 call. Arrays are caller-owned, b64_count long. */
+typedef struct SvtMeGpuTfPair {
+    uint32_t  b64_count;
+    uint32_t *best_sad; /* [b64][85] */
+    uint32_t *best_mv; /* [b64][85] */
+    int16_t  *hme_centre; /* [b64][2] */
+    uint32_t *hme_sad; /* [b64] */
+    uint8_t  *early_exit; /* [b64] */
+} SvtMeGpuTfPair;
+/* once per (centre, neighbour), before the block loop; me_ctx set up as at temporal_filtering.c:3144-3181 (controls by
+ * svt_aom_sig_deriv_me_tf, me_type = ME_MCTF, tf_me_exit_th). Adds the pair's tf_tot_horz/vert_blks to me_ctx. */
+EbErrorType svt_me_gpu_tf_pair(const PictureParentControlSet *centre_pcs, MeContext *me_ctx, uint64_t neighbour_picture_number,
+                               SvtMeGpuTfPair *pair);
+/* in the block loop, instead of svt_aom_motion_estimation_b64 (:3182), for block b: puts the block's results where the
+ * filter's readers expect them (p_sb_best_sad/mv[0][0], search_results[0][0], the 64x64-only switch) */
+void svt_me_gpu_tf_load_block(MeContext *me_ctx, const SvtMeGpuTfPair *pair, uint32_t b);
+
+/* ---- dynamic-GOP detector (early_hme, pd_process.c:561-625) ---------------------------------------------------- */
+/* replaces the TASK_DG_DETECTOR_HME segment dispatch + semaphore wait: fills src_pcs->dg_detector->metrics for
+ * (src_pcs, src_pcs->dg_detector->ref_pic); both pictures registered */
+EbErrorType svt_me_gpu_dg_detector(PictureParentControlSet *src_pcs);
+
 #ifdef __cplusplus
 }
 #endif

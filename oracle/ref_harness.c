@@ -490,6 +490,113 @@ REF_API int ref_hook_me_picture(const OraclePicture *src, const OraclePicture *c
     return rc;
 }
 
+/* register one OraclePicture through the binding (needs only picture number and aligned size of a pcs) */
+static int hook_register(const OraclePicture *pic, int pic_w, int pic_h) {
+    EbPictureBufferDesc      d;
+    PictureParentControlSet *rpcs = calloc(1, sizeof *rpcs);
+    if (!rpcs)
+        return -1;
+    desc_from_plane(&d, &pic->full);
+    rpcs->picture_number = pic->picture_number;
+    rpcs->aligned_width  = (uint16_t)pic_w;
+    rpcs->aligned_height = (uint16_t)pic_h;
+    const int rc = svt_me_gpu_register_picture(rpcs, &d) == EB_ErrorNone ? 0 : -11;
+    free(rpcs);
+    return rc;
+}
+
+/* Temporal-filter ME of one (centre, neighbour) pair through the binding: svt_me_gpu_tf_pair before the block loop,
+ * svt_me_gpu_tf_load_block inside it; what the MeContext then holds per block goes to out->tf_* (same layout as
+ * ref_me_b64_range with me_type = ME_MCTF). GPU tests only. */
+REF_API int ref_hook_tf_pair(const OraclePicture *src, const OraclePicture *ref, const MeGpuParams *p, MeGpuOutputs *out,
+                             const char *gpu_library_path) {
+    const int pic_w = (src->full.width + 7) & ~7, pic_h = (src->full.height + 7) & ~7;
+    const uint32_t total = (uint32_t)((pic_w + 63) / 64) * ((pic_h + 63) / 64);
+    if (out->b64_count < total)
+        return -2;
+    PictureParentControlSet *pcs = calloc(1, sizeof *pcs);
+    SequenceControlSet      *scs = calloc(1, sizeof *scs);
+    MeContext               *m   = calloc(1, sizeof *m);
+    MotionEstimationData    *md  = calloc(1, sizeof *md);
+    if (!pcs || !scs || !m || !md)
+        return -1;
+    ctx_from_params(m, p);
+    pcs->scs                      = scs;
+    pcs->picture_number           = p->picture_number;
+    pcs->aligned_width            = (uint16_t)pic_w;
+    pcs->aligned_height           = (uint16_t)pic_h;
+    pcs->enable_me_8x8            = p->enable_me_8x8;
+    pcs->enable_me_16x16          = p->enable_me_16x16;
+    pcs->max_number_of_pus_per_sb = p->max_number_of_pus_per_sb;
+    pcs->hierarchical_levels      = p->hierarchical_levels;
+    pcs->temporal_layer_index     = p->pcs_temporal_layer_index;
+    pcs->pa_me_data               = md;
+    scs->input_resolution         = (EbInputResolution)p->input_resolution;
+    md->max_cand                  = p->max_cand;
+    md->max_refs                  = p->max_refs;
+    md->max_l0                    = p->max_l0;
+    int rc = svt_me_gpu_hook_init(gpu_library_path, pic_w, pic_h, 4, 3, 4) == EB_ErrorNone ? 0 : -10;
+    if (!rc) rc = hook_register(src, pic_w, pic_h);
+    if (!rc && ref->picture_number != src->picture_number) rc = hook_register(ref, pic_w, pic_h);
+    SvtMeGpuTfPair pair = {total, out->tf_best_sad, out->tf_best_mv, out->tf_hme_centre, out->tf_hme_sad, out->tf_early_exit};
+    /* the pair's arrays are filled by the engine; the loop below reads them back through the MeContext, block by block */
+    if (!rc && svt_me_gpu_tf_pair(pcs, m, ref->picture_number, &pair) != EB_ErrorNone)
+        rc = -12;
+    if (!rc) {
+        uint32_t *sad = malloc((size_t)total * 85 * 4), *mv = malloc((size_t)total * 85 * 4);
+        for (uint32_t b = 0; b < total; b++) {
+            m->tf_use_pred_64x64_only_th = 1;
+            svt_me_gpu_tf_load_block(m, &pair, b);
+            memcpy(sad + (size_t)b * 85, m->p_sb_best_sad[0][0], 85 * 4);
+            memcpy(mv + (size_t)b * 85, m->p_sb_best_mv[0][0], 85 * 4);
+            out->tf_hme_centre[2 * b]     = m->search_results[0][0].hme_sc_x;
+            out->tf_hme_centre[2 * b + 1] = m->search_results[0][0].hme_sc_y;
+            out->tf_hme_sad[b]            = (uint32_t)m->search_results[0][0].hme_sad;
+            out->tf_early_exit[b]         = m->tf_use_pred_64x64_only_th == (uint8_t)~0;
+        }
+        memcpy(out->tf_best_sad, sad, (size_t)total * 85 * 4);
+        memcpy(out->tf_best_mv, mv, (size_t)total * 85 * 4);
+        free(sad); free(mv);
+        out->tf_tot_horz_blks = m->tf_tot_horz_blks;
+        out->tf_tot_vert_blks = m->tf_tot_vert_blks;
+        out->b64_count        = total;
+    }
+    svt_me_gpu_release_picture(src->picture_number);
+    if (ref->picture_number != src->picture_number) svt_me_gpu_release_picture(ref->picture_number);
+    svt_me_gpu_hook_shutdown();
+    free(md); free(m); free(scs); free(pcs);
+    return rc;
+}
+
+/* early_hme's detector round trip through the binding: metrics land in src_pcs->dg_detector->metrics. GPU tests only. */
+REF_API int ref_hook_dg_detector(const OraclePicture *src, const OraclePicture *ref, uint8_t input_resolution, MeGpuDgMetrics *out,
+                                 const char *gpu_library_path) {
+    const int pic_w = (src->full.width + 7) & ~7, pic_h = (src->full.height + 7) & ~7;
+    PictureParentControlSet *pcs = calloc(1, sizeof *pcs), *rpcs = calloc(1, sizeof *rpcs);
+    DGDetectorSeg           *dg  = calloc(1, sizeof *dg);
+    if (!pcs || !rpcs || !dg)
+        return -1;
+    pcs->picture_number   = src->picture_number;
+    rpcs->picture_number  = ref->picture_number;
+    pcs->input_resolution = (EbInputResolution)input_resolution;
+    pcs->dg_detector      = dg;
+    dg->ref_pic           = rpcs;
+    int rc = svt_me_gpu_hook_init(gpu_library_path, pic_w, pic_h, 4, 3, 4) == EB_ErrorNone ? 0 : -10;
+    if (!rc) rc = hook_register(src, pic_w, pic_h);
+    if (!rc) rc = hook_register(ref, pic_w, pic_h);
+    if (!rc && svt_me_gpu_dg_detector(pcs) != EB_ErrorNone)
+        rc = -12;
+    out->tot_dist       = dg->metrics.tot_dist;
+    out->tot_cplx       = dg->metrics.tot_cplx;
+    out->tot_active     = dg->metrics.tot_active;
+    out->sum_in_vectors = dg->metrics.sum_in_vectors;
+    svt_me_gpu_release_picture(src->picture_number);
+    svt_me_gpu_release_picture(ref->picture_number);
+    svt_me_gpu_hook_shutdown();
+    free(dg); free(rpcs); free(pcs);
+    return rc;
+}
+
 /* static in the reference (temporal_filtering.c:2760): level 0 copies hme_l0_sa_default_tf into hme_l0_sa */
 static void harness_set_hme_search_params_mctf0(MeContext *m) { m->hme_l0_sa = m->hme_l0_sa_default_tf; }
 

@@ -121,6 +121,26 @@ class Reference:
             raise RuntimeError(f"ref_hook_me_picture failed: {rc}")
         return out
 
+    def hook_tf_pair(self, src: Picture, ref: Picture, params, gpu_library_path):
+        """svt_me_gpu_tf_pair + svt_me_gpu_tf_load_block of the binding for one (centre, neighbour) pair"""
+        self.lib.ref_hook_tf_pair.argtypes = [C.POINTER(abi.OraclePicture), C.POINTER(abi.OraclePicture),
+                                              C.POINTER(abi.MeGpuParams), C.POINTER(abi.MeGpuOutputs), C.c_char_p]
+        out = Outputs(src.width, src.height, params, debug=False)
+        a, b = src.c_struct(), ref.c_struct()
+        rc = self.lib.ref_hook_tf_pair(C.byref(a), C.byref(b), C.byref(params), C.byref(out.c), gpu_library_path.encode())
+        if rc != 0:
+            raise RuntimeError(f"ref_hook_tf_pair failed: {rc}")
+        return out
+
+    def hook_dg_detector(self, src: Picture, ref: Picture, input_resolution, gpu_library_path):
+        self.lib.ref_hook_dg_detector.argtypes = [C.POINTER(abi.OraclePicture), C.POINTER(abi.OraclePicture), abi.u8,
+                                                  C.POINTER(abi.MeGpuDgMetrics), C.c_char_p]
+        a, b, m = src.c_struct(), ref.c_struct(), abi.MeGpuDgMetrics()
+        rc = self.lib.ref_hook_dg_detector(C.byref(a), C.byref(b), input_resolution, C.byref(m), gpu_library_path.encode())
+        if rc != 0:
+            raise RuntimeError(f"ref_hook_dg_detector failed: {rc}")
+        return m.as_tuple()
+
     def derive_params_tf(self, cfg):
         p = abi.MeGpuParams()
         self.lib.ref_derive_params_tf.argtypes = [C.POINTER(abi.MeGpuTfConfig), C.POINTER(abi.MeGpuParams)]

@@ -104,3 +104,27 @@ def test_reference_side_hook_fills_the_pcs_like_the_cpu_loop(w, h, preset, poc, 
     bad = planes.compare_outputs(exp, got, fields=planes.PRODUCT_FIELDS)
     assert not bad, bad
     assert got.c.pu_count == exp.c.pu_count
+
+
+def test_reference_side_hook_temporal_filter_and_dg_detector():
+    """The binding's temporal-filter pair (svt_me_gpu_tf_pair + svt_me_gpu_tf_load_block: what the block loop of
+    produce_temporally_filtered_pic then finds in its MeContext) and its dynamic-GOP detector call
+    (dg_detector->metrics), against the reference's own code on the same inputs."""
+    from helpers import DgPictures, derive_tf
+    from me_b200 import abi
+    from me_b200.checkers import Reference
+    if not Reference.available():
+        pytest.skip("oracle/_ref/libme_ref.so is built where /root/reference exists and travels prebuilt")
+    ref = Reference()
+    for w, h, lvl, kind, c, nb, th in [(320, 192, 1, "motion", 8, 11, 400), (264, 200, 0, "iid", 4, 5, 20000),
+                                       (320, 192, 3, "motion", 8, 9, 6000)]:
+        ps = PictureSet(w, h, 20, kind, ref)
+        _, p = derive_tf(lvl, w, h, c, me_exit_th=th)
+        exp = ref.me_picture(ps.get(c), [[ps.get(nb)], []], p, simd=0, debug=False)
+        got = ref.hook_tf_pair(ps.get(c), ps.get(nb), p, abi.GPU_LIB)
+        bad = planes.compare_outputs(exp, got, fields=planes.TF_FIELDS)
+        assert not bad, (lvl, bad)
+        assert exp.tf_blocks == got.tf_blocks
+    for w, h, res, kind, a, b in [(320, 192, 4, "motion", 4, 3), (640, 360, 2, "motion", 8, 0), (320, 192, 4, "blocks", 2, 1)]:
+        ps = DgPictures(w, h, kind, ref)
+        assert ref.hook_dg_detector(ps.get(a), ps.get(b), res, abi.GPU_LIB) == ref.dg_detector(ps.get(a), ps.get(b), res)
