@@ -80,7 +80,7 @@ __device__ unsigned g_trace_cnt;
 #endif
 /* search areas at least this wide / with at least this many 8-position units take hm_job_search8 (tunable by
    ME_HME_K8_MIN_PW / ME_HME_K8_MIN_UNITS for experiments) */
-__device__ int g_k8_min_pw = 64, g_k8_min_units = 64, g_team1_units = 16, g_lanes_target = 96;
+__device__ int g_k8_min_pw = 64, g_k8_min_units = 64, g_team1_units = 16, g_lanes_target = 96, g_tall_min_rows = 32;
 
 struct HmeShared {
     B64State           s;
@@ -395,12 +395,22 @@ __device__ void hm_plan_task(const SearchTask &t, const MeJob *j, int org_x, int
         kx    = 8;
         units = 4 * (((15 + pwb - 1) >> 5) + 1) * neb;
     }
+    /* tall thin areas (pre-HME region 0: 8 positions wide, hundreds of rows) of 16x8-row blocks: hm_job_search_tall */
+    const bool tall = !wide && g_tall_min_rows > 0 && t.bw == 16 && t.rows == 8 && nxb == 1 && pwb <= 8 && neb >= g_tall_min_rows &&
+                      t.row_step % ymul == 0;
+    if (tall) {
+        const int ys = t.row_step / ymul;
+        kx    = 1;
+        units = 4 * ys * ((neb + 4 * ys - 1) / (4 * ys));
+    }
     const int win     = pitch * (((neb - 1) * ymul + span + 1 + hm_map_rows(map) - 1) / hm_map_rows(map) * hm_map_rows(map));
     /* jobs of few units are searched by one warp each, four at a time per CTA, when four windows fit the ring (measured:
        two warps per job with the next batch in flight is slower than one warp per job and no prefetch of the next batch) */
-    pl.team = (uint8_t)(!wide && units <= g_team1_units && win <= HM_RING_BYTES / 4 ? 1 : 4);
+    pl.team = (uint8_t)(!wide && !tall && units <= g_team1_units && win <= HM_RING_BYTES / 4 ? 1 : 4);
     int g_log2 = 2 - lv; /* lanes per unit: the 16-byte column segments of the block row ... */
-    while (!wide && g_log2 < 5 && (pl.team < 4 ? (units << (g_log2 + 1)) <= 32 * pl.team : (units << g_log2) < g_lanes_target) &&
+    if (tall)
+        g_log2 = 0;
+    while (!wide && !tall && g_log2 < 5 && (pl.team < 4 ? (units << (g_log2 + 1)) <= 32 * pl.team : (units << g_log2) < g_lanes_target) &&
            ((2 << g_log2) >> (2 - lv)) <= (int)t.rows)
         g_log2++; /* ... x row groups: up to the team's worth of lanes */
     pl.pwb = (int16_t)pwb;
@@ -446,6 +456,12 @@ __device__ void hm_job_decode(const SearchTask *tasks, const HmPlan *plans, cons
     J.dep    = -1;
     J.m_chunk = hm_magic((uint32_t)nchunk);
     J.m_cls   = hm_magic((uint32_t)ncls);
+    if (pl.kx == 1) { /* hm_job_search_tall: (byte class, row parity, group of 4 * ys search rows) */
+        const int ys = t.row_step / ymul, ng = (ne + 4 * ys - 1) / (4 * ys);
+        J.ncls    = (uint8_t)ys;
+        J.nchunk  = (uint8_t)ng;
+        J.total   = (uint16_t)(4 * ys * ng);
+    }
     if (pl.kx == 8) { /* hm_job_search8: (byte class, 32-byte segment of the window row, search row) */
         const int nseg = (((int)J.aoff + pw - 1) >> 5) + 1;
         J.ncls    = 4;
@@ -593,6 +609,72 @@ __device__ __forceinline__ unsigned long long hm_job_search8(const HmJobD &J, co
             for (int k = 0; k < 8; k++) {
                 const uint32_t cand = (acc[k] << 16) + l0 + 4u * k;
                 best                = min(best, (uint32_t)(x0 + 4 * k) < pw ? cand : 0xFFFFFFFFu);
+            }
+        }
+    }
+    best = __reduce_min_sync(0xffffffffu, best);
+    if (best == 0xFFFFFFFFu)
+        return ((unsigned long long)ME_SAD_LOOP_INIT << 32) | 0xFFFFFFFFull;
+    const uint32_t lidx = best & 0xFFFFu, e = lidx / pw, x = lidx - e * pw;
+    return ((unsigned long long)(best >> 16) << 32) | (uint32_t)((J.e0 + (int)e) * t.sa_w + J.px0 + (int)x);
+}
+
+/* Tall thin search areas (<= 8 positions wide) of 16-byte x 8-row blocks: pre-HME region 0 (8 x 100..400). A lane owns
+ * the two positions x = c, c + 4 of FOUR search rows whose block rows fall on the same window rows (e, e + ys, e + 2 ys,
+ * e + 3 ys with ys = row_step / ymul: block row r of search row e + i ys is window row (e ymul) + (i + r) row_step), so
+ * 11 window rows - 6 words and 5 funnel shifts each - feed the 8 x 32 VABSDIFF4 of eight positions, where one lane per
+ * search row loads 8 window rows for two. 32-bit keys as in hm_job_search8. */
+__device__ __forceinline__ unsigned long long hm_job_search_tall(const HmJobD &J, const SearchTask &t, const uint32_t *raw,
+                                                                 const uint32_t *src, int src_pitch4, int warp, int nthr, int lane) {
+    const bool skip = t.bw == 16 && t.rows <= 16 && t.skip_line;
+    const int  ymul = skip ? 2 : 1, step = t.row_step, ys = J.ncls /* row_step / ymul: 1 or 2 */;
+    const int  pitchw = hm_map_width(J.map) >> 2, total = J.total, ne = J.ne, maxrow = (int)J.nrows - 1;
+    const uint32_t pw = (uint32_t)J.pw;
+    uint32_t   best = 0xFFFFFFFFu;
+    for (int base = warp * 32; base < total; base += nthr) {
+        const int u = base + lane;
+        if (u < total) {
+            const int c = u & 3, v = u >> 2;
+            const int par = v & (ys - 1), g = ys == 2 ? v >> 1 : v;
+            const int e0 = 4 * ys * g + par, o = (int)J.aoff + c, sh = (o & 3) * 8;
+            const uint32_t *wbase = raw + (o >> 2);
+            const uint4    *sp = reinterpret_cast<const uint4 *>(src);
+            uint32_t acc[4][2];
+#pragma unroll
+            for (int i = 0; i < 4; i++) acc[i][0] = acc[i][1] = 0;
+            uint4 S[8];
+#pragma unroll
+            for (int k = 0; k < 11; k++) {
+                const uint32_t *q = wbase + min(e0 * ymul + k * step, maxrow) * pitchw; /* rows past the window: dropped positions only */
+                uint32_t w[6];
+#pragma unroll
+                for (int i = 0; i < 6; i++) w[i] = q[i];
+#pragma unroll
+                for (int i = 0; i < 5; i++) w[i] = __funnelshift_r(w[i], w[i + 1], sh);
+                if (k < 8)
+                    S[k] = sp[k * step * src_pitch4];
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const int r = k - i;
+                    if (r >= 0 && r < 8) {
+#pragma unroll
+                        for (int h = 0; h < 2; h++) {
+                            acc[i][h] = hm_vsad4(S[r].x, w[h], acc[i][h]);
+                            acc[i][h] = hm_vsad4(S[r].y, w[h + 1], acc[i][h]);
+                            acc[i][h] = hm_vsad4(S[r].z, w[h + 2], acc[i][h]);
+                            acc[i][h] = hm_vsad4(S[r].w, w[h + 3], acc[i][h]);
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const int e = e0 + i * ys;
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const uint32_t x = (uint32_t)(c + 4 * h), cand = (acc[i][h] << 16) + (uint32_t)e * pw + x;
+                    best = min(best, x < pw && e < ne ? cand : 0xFFFFFFFFu);
+                }
             }
         }
     }
@@ -932,6 +1014,8 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
                     unsigned long long key;
                     if (pl.kx == 8)
                         key = hm_job_search8(J, t, raw, srcb, sp4, widx, nthr, lane);
+                    else if (pl.kx == 1)
+                        key = hm_job_search_tall(J, t, raw, srcb, sp4, widx, nthr, lane);
                     else if (pl.kx == 4)
                         key = hm_job_search<4>(J, t, pl.g_log2, raw, srcb, sp4, widx, nthr, lane);
                     else
@@ -1046,6 +1130,10 @@ cudaError_t me_hme_setup(void) {
     if (getenv("ME_HME_LANES_TARGET")) {
         const int v = atoi(getenv("ME_HME_LANES_TARGET"));
         cudaMemcpyToSymbol(g_lanes_target, &v, sizeof(v));
+    }
+    if (getenv("ME_HME_TALL_MIN_ROWS")) {
+        const int v = atoi(getenv("ME_HME_TALL_MIN_ROWS"));
+        cudaMemcpyToSymbol(g_tall_min_rows, &v, sizeof(v));
     }
     if (getenv("ME_HME_K8_MIN_UNITS")) {
         const int v = atoi(getenv("ME_HME_K8_MIN_UNITS"));
