@@ -410,9 +410,22 @@ __device__ void hm_plan_task(const SearchTask &t, const MeJob *j, int org_x, int
     int g_log2 = 2 - lv; /* lanes per unit: the 16-byte column segments of the block row ... */
     if (tall)
         g_log2 = 0;
-    while (!wide && !tall && g_log2 < 5 && (pl.team < 4 ? (units << (g_log2 + 1)) <= 32 * pl.team : (units << g_log2) < g_lanes_target) &&
-           ((2 << g_log2) >> (2 - lv)) <= (int)t.rows)
-        g_log2++; /* ... x row groups: up to the team's worth of lanes */
+    else if (!wide && pl.team < 4) {
+        /* one warp per job: the split with the fewest (passes over the warp) x (block rows per lane); ties keep the
+           smaller group (fewer shuffles). HME level 2 (12 units of 32 rows x 4 segments): 8 lanes per unit, 3 x 16
+           row iterations instead of 2 x 32 */
+        int best_cost = 1 << 30;
+        for (int gl = 2 - lv; gl <= 5 && ((1 << gl) >> (2 - lv)) <= (int)t.rows; gl++) {
+            const int rg = (1 << gl) >> (2 - lv);
+            const int cost = (((units << gl) + 31) >> 5) * (((int)t.rows + rg - 1) / rg);
+            if (cost < best_cost) {
+                best_cost = cost;
+                g_log2    = gl;
+            }
+        }
+    } else
+        while (!wide && g_log2 < 5 && (units << g_log2) < g_lanes_target && ((2 << g_log2) >> (2 - lv)) <= (int)t.rows)
+            g_log2++; /* ... x row groups: up to the team's worth of lanes */
     pl.pwb = (int16_t)pwb;
     pl.neb = (int16_t)neb;
     pl.nxb = (uint8_t)nxb;
