@@ -451,8 +451,8 @@ def gpu_main(args):
         pass
     # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the one `ncu --set full` capture
     # of this workload kept under profiles/ (ncu_r1_final_<kernel>_<workload>_details.txt)
-    ncu_traffic = {("1080p-m4", "motion", "k_hme"): 15210752 + 4096, ("1080p-m4", "iid", "k_fullsearch"): 13272576,
-                   ("4k-m0", "motion", "k_hme"): 62712832 + 10173952, ("4k-m0", "iid", "k_fullsearch"): 75407104 + 5648640}
+    ncu_traffic = {("1080p-m4", "motion", "k_hme"): 15221760 + 1024, ("1080p-m4", "iid", "k_fullsearch"): 13271552 + 768,
+                   ("4k-m0", "motion", "k_hme"): 62639872 + 9188096, ("4k-m0", "iid", "k_fullsearch"): 75336960 + 4834048}
     ncu_key = (WORKLOAD, args.kind, dom)
     roofline = {
         "bound": "int_sad", "kernel": dom, "achieved": achieved, "peak": sad_peak / 1e12, "unit": "Tbyte-SAD/s",

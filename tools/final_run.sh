@@ -27,5 +27,4 @@ ncu --set full --clock-control none --import-source on -k k_hme -s 2 -c 1 -f -o 
 ncu --set full --clock-control none --import-source on -k k_fullsearch -s 2 -c 1 -f -o $O/final_k_fullsearch_1080p_iid python tools/profile_step.py 3 iid > $O/final_ncu2.log 2>&1
 ncu --set full --clock-control none --import-source on -k k_hme -s 1 -c 1 -f -o $O/final_k_hme_4k_m0 python tools/profile_step.py 2 motion 4k-m0 > $O/final_ncu3.log 2>&1
 ncu --set full --clock-control none --import-source on -k k_fullsearch -s 1 -c 1 -f -o $O/final_k_fullsearch_4k_m0_iid python tools/profile_step.py 2 iid 4k-m0 > $O/final_ncu4.log 2>&1
-timeout 600 compute-sanitizer --tool memcheck python __graft_entry__.py smoke > $O/final_memcheck.log 2>&1; tail -3 $O/final_memcheck.log
 ls -la $O | grep final_
