@@ -88,13 +88,14 @@ struct HmeShared {
     SearchResult       r[ME_SLOTS];
     FsTask             f[ME_NREF];
     unsigned long long tkey[ME_SLOTS]; /* best (sad << 32 | scan index) of each search task */
-    int                item_first[ME_SLOTS + 1]; /* prefix sums: items of task i are [first[i], first[i+1]) */
-    int                item_rows[ME_SLOTS]; /* search rows per item */
+    uint16_t           item_first[ME_SLOTS + 1]; /* prefix sums: items of task i are [first[i], first[i+1]) */
+    uint16_t           item_rows[ME_SLOTS]; /* search rows per item */
     int                next_item;
     int                team; /* warps per window job in this round (4 / team jobs are searched at a time) */
     int                next_lo; /* first task of the next round of window jobs */
     HmPlan             plan[ME_SLOTS];
-    int                job_first[ME_SLOTS + 1]; /* prefix sums of the window jobs */
+    uint16_t           job_first[ME_SLOTS + 1]; /* prefix sums of the window jobs */
+    MeGpuParams        p; /* the picture's controls: the control stages read them hundreds of times, one dependent load each */
     alignas(8) unsigned long long mbar[HM_NBAR]; /* TMA completion of the windows in flight */
     HmJobD             jobs[HM_MAXJOBS];
     alignas(16) uint32_t src0[64 * HM_SRC0_PITCH], src1[32 * HM_SRC1_PITCH], src2[16 * HM_SRC2_PITCH]; /* the b64's source block on the three planes (padded pitches) */
@@ -437,7 +438,7 @@ __device__ void hm_plan_task(const SearchTask &t, const MeJob *j, int org_x, int
 }
 
 /* job number -> job descriptor (one thread per job) */
-__device__ void hm_job_decode(const SearchTask *tasks, const HmPlan *plans, const int *job_first, const MeJob *j, int jb, HmJobD &J) {
+__device__ void hm_job_decode(const SearchTask *tasks, const HmPlan *plans, const uint16_t *job_first, const MeJob *j, int jb, HmJobD &J) {
     int task = 0;
     for (int step = 16; step; step >>= 1) /* last task with job_first[task] <= jb */
         if (job_first[task + step] <= jb)
@@ -811,7 +812,7 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
 
     CtrlCtx c;
     c.j     = j;
-    c.p     = &j->p;
+    c.p     = &sm.p;
     c.s     = &sm.s;
     c.t     = sm.t;
     c.r     = sm.r;
@@ -828,6 +829,8 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
     c.nlanes = 32;
     const bool sub = j->p.me_search_method == ME_GPU_SUB_SAD_SEARCH;
 
+    for (int i = tid; i < (int)(sizeof(MeGpuParams) / 4); i += HM_THREADS)
+        reinterpret_cast<uint32_t *>(&sm.p)[i] = reinterpret_cast<const uint32_t *>(&j->p)[i];
     mc_init_keys(keys, tid, HM_THREADS);
     for (int i = tid; i < ME_SLOTS; i += HM_THREADS) {
         sm.t[i].valid = 0;
@@ -858,7 +861,7 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
     int       fetched = 0; /* producer: jobs of the stage whose windows have been requested */
 
 #ifdef ME_HME_TRACE
-    long long tr[ST_COUNT][4];
+    long long tr[ST_COUNT][8];
     long long t_begin = clock64();
     unsigned long long gt_begin, gt_stage[ST_COUNT];
     unsigned smid;
@@ -868,6 +871,8 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
     for (int st = 0; st < ST_COUNT; st++) {
 #ifdef ME_HME_TRACE
         long long tr0 = clock64();
+        long long tr_wait = 0, tr_search = 0, tr_bar = 0;
+        int       tr_jobs = 0;
 #endif
         if (warp == 0) {
             mc_run_stage(&c, st);
@@ -921,8 +926,8 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
                 if (lane >= o)
                     incl += v;
             }
-            sm.item_first[lane + 1] = incl;
-            sm.item_rows[lane]      = rows_per;
+            sm.item_first[lane + 1] = (uint16_t)incl;
+            sm.item_rows[lane]      = (uint16_t)rows_per;
             if (lane == 0)
                 sm.item_first[0] = sm.job_first[0] = 0;
         }
@@ -944,7 +949,7 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
                 const int      kept = __reduce_max_sync(0xffffffffu, over ? 0 : inclj);
                 /* warps per job in this round: the largest team any of its window jobs needs */
                 const int team = __reduce_max_sync(0xffffffffu, nj > 0 && !over ? (int)pl.team : 1);
-                sm.job_first[lane + 1] = over ? kept : inclj;
+                sm.job_first[lane + 1] = (uint16_t)(over ? kept : inclj);
                 if (lane == 0) {
                     sm.job_first[0] = 0;
                     sm.team         = team;
@@ -958,8 +963,21 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
                 break;
             for (int jb = tid; jb < njobs; jb += HM_THREADS) hm_job_decode(sm.t, sm.plan, sm.job_first, j, jb, sm.jobs[jb]);
             __syncthreads();
+            fetched = 0;
             if (producer) {
                 if (lane == 0) { /* ring placement, in job order (FIFO): depends on the sizes only, never on timing */
+                    { /* job 0 sits at the start of the ring whatever follows: its window is requested before the others are placed */
+                        HmJobD &J0 = sm.jobs[0];
+                        J0.off128  = 0;
+                        J0.dep     = -1;
+                        const uint32_t bar = hm_smem(&sm.mbar[seq % HM_NBAR]);
+                        const int      pitch = hm_map_width(J0.map), br = hm_map_rows(J0.map);
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); /* generic-proxy accesses to the ring come first */
+                        hm_mbar_expect(bar, (uint32_t)((int)J0.nrows * pitch));
+                        for (int y = 0; y < (int)J0.nrows; y += br)
+                            hm_tma_box(hm_smem(raw0) + (uint32_t)(y * pitch), maps.m[J0.map], J0.xt, J0.y0 + y, sm.t[J0.task].ref_slot, bar);
+                        fetched = 1;
+                    }
                     int cur = 0;
                     if (sm.team < HM_WARPS) {
                         /* the jobs of a batch are searched together: batches alternate between the ring halves when they
@@ -997,7 +1015,6 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
                 }
                 __syncwarp();
             }
-            fetched = 0;
             /* searched while the TMA transfers of the following jobs are in flight: large jobs by the whole CTA one after
                the other, small ones by one warp each, four at a time */
             const uint32_t seq0 = seq;
@@ -1016,7 +1033,13 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
                 if (jb < njobs) {
                     const uint32_t    slot = (seq0 + (uint32_t)jb) % HM_NBAR, par = ((seq0 + (uint32_t)jb) / HM_NBAR) & 1;
                     __syncwarp();
+#ifdef ME_HME_TRACE
+                    const long long tw0 = clock64();
+#endif
                     hm_mbar_wait(hm_smem(&sm.mbar[slot]), par); /* also orders the producer's ring placement before the read */
+#ifdef ME_HME_TRACE
+                    const long long tw1 = clock64();
+#endif
                     const HmJobD      J    = sm.jobs[jb];
                     const SearchTask &t    = sm.t[J.task];
                     const HmPlan     &pl   = sm.plan[J.task];
@@ -1035,8 +1058,19 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
                         key = hm_job_search<2>(J, t, pl.g_log2, raw, srcb, sp4, widx, nthr, lane);
                     if (lane == 0)
                         atomicMin(&sm.tkey[J.task], key);
+#ifdef ME_HME_TRACE
+                    tr_wait += tw1 - tw0;
+                    tr_search += clock64() - tw1;
+                    tr_jobs++;
+#endif
                 }
+#ifdef ME_HME_TRACE
+                const long long tb0 = clock64();
+#endif
                 __syncthreads(); /* the windows' ring bytes are free again */
+#ifdef ME_HME_TRACE
+                tr_bar += clock64() - tb0;
+#endif
             }
             seq += (uint32_t)njobs;
         }
@@ -1083,6 +1117,7 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
 #ifdef ME_HME_TRACE
         long long tr3 = clock64();
         tr[st][0] = tr1 - tr0; tr[st][1] = tr2 - tr1; tr[st][2] = tr3 - tr2; tr[st][3] = tr3w - tr2;
+        tr[st][4] = tr_wait; tr[st][5] = tr_search; tr[st][6] = tr_bar; tr[st][7] = tr_jobs;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_stage[st]));
 #endif
         if (search_stage && tid < ME_SLOTS && sm.t[tid].valid) {
@@ -1107,8 +1142,9 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
 #ifdef ME_HME_TRACE
     if (blockIdx.y == 0 && b == 100 && tid == 0) {
         for (int st = 0; st < ST_COUNT; st++)
-            printf("b %d tid %d stage %d: ctrl %lld partition %lld items+barrier %lld (own items %lld) cycles\n", b, tid, st,
-                   tr[st][0], tr[st][1], tr[st][2], tr[st][3]);
+            printf("b %d tid %d stage %d: ctrl %lld plan+jobs %lld items+barrier %lld (own items %lld) cycles; warp 0's window jobs: %lld "
+                   "of them, TMA wait %lld, SAD loop %lld, barrier %lld\n", b, tid, st, tr[st][0], tr[st][1], tr[st][2], tr[st][3],
+                   tr[st][7], tr[st][4], tr[st][5], tr[st][6]);
         printf("b %d tid %d total %lld cycles\n", b, tid, clock64() - t_begin);
     }
     if (tid == 0) { /* print only once every CTA of the launch is past its last stage (bounded wait): printf stalls the SM */
