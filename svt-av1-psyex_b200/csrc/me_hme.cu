@@ -861,7 +861,7 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
     int       fetched = 0; /* producer: jobs of the stage whose windows have been requested */
 
 #ifdef ME_HME_TRACE
-    long long tr[ST_COUNT][8];
+    long long tr[ST_COUNT][12];
     long long t_begin = clock64();
     unsigned long long gt_begin, gt_stage[ST_COUNT];
     unsigned smid;
@@ -871,7 +871,7 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
     for (int st = 0; st < ST_COUNT; st++) {
 #ifdef ME_HME_TRACE
         long long tr0 = clock64();
-        long long tr_wait = 0, tr_search = 0, tr_bar = 0;
+        long long tr_wait = 0, tr_search = 0, tr_bar = 0, tr_round = 0, tr_decode = 0, tr_first = 0, tr_mark = 0;
         int       tr_jobs = 0;
 #endif
         if (warp == 0) {
@@ -931,10 +931,19 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
             if (lane == 0)
                 sm.item_first[0] = sm.job_first[0] = 0;
         }
+#ifdef ME_HME_TRACE
+        const long long tr_pa = clock64();
+#endif
         __syncthreads();
+#ifdef ME_HME_TRACE
+        const long long tr_pb = clock64();
+#endif
         /* window jobs, in rounds of up to HM_MAXJOBS jobs (whole tasks; the 4K presets' HME level 0 cuts a b64's 28
            quadrant searches into ~280 jobs) */
         for (int task_lo = 0; search_stage && task_lo < ME_SLOTS;) {
+#ifdef ME_HME_TRACE
+            tr_mark = clock64();
+#endif
             if (warp == 0) {
                 const HmPlan pl = sm.plan[lane];
                 const int    nj = lane >= task_lo && pl.new_path ? (int)pl.nxb * (int)pl.nyb : 0;
@@ -959,10 +968,18 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
             __syncthreads();
             const int njobs = sm.job_first[ME_SLOTS];
             task_lo         = sm.next_lo;
+#ifdef ME_HME_TRACE
+            tr_round += clock64() - tr_mark;
+            tr_mark = clock64();
+#endif
             if (njobs == 0)
                 break;
             for (int jb = tid; jb < njobs; jb += HM_THREADS) hm_job_decode(sm.t, sm.plan, sm.job_first, j, jb, sm.jobs[jb]);
             __syncthreads();
+#ifdef ME_HME_TRACE
+            tr_decode += clock64() - tr_mark;
+            tr_mark = clock64();
+#endif
             fetched = 0;
             if (producer) {
                 if (lane == 0) { /* ring placement, in job order (FIFO): depends on the sizes only, never on timing */
@@ -1039,6 +1056,8 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
                     hm_mbar_wait(hm_smem(&sm.mbar[slot]), par); /* also orders the producer's ring placement before the read */
 #ifdef ME_HME_TRACE
                     const long long tw1 = clock64();
+                    if (jb0 == 0)
+                        tr_first += tw1 - tr_mark;
 #endif
                     const HmJobD      J    = sm.jobs[jb];
                     const SearchTask &t    = sm.t[J.task];
@@ -1118,6 +1137,7 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
         long long tr3 = clock64();
         tr[st][0] = tr1 - tr0; tr[st][1] = tr2 - tr1; tr[st][2] = tr3 - tr2; tr[st][3] = tr3w - tr2;
         tr[st][4] = tr_wait; tr[st][5] = tr_search; tr[st][6] = tr_bar; tr[st][7] = tr_jobs;
+        tr[st][8] = tr_round; tr[st][9] = tr_decode; tr[st][10] = tr_first; tr[st][11] = tr_pa - tr1; tr[st][3] = tr_pb - tr_pa;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_stage[st]));
 #endif
         if (search_stage && tid < ME_SLOTS && sm.t[tid].valid) {
@@ -1143,8 +1163,8 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
     if (blockIdx.y == 0 && b == 100 && tid == 0) {
         for (int st = 0; st < ST_COUNT; st++)
             printf("b %d tid %d stage %d: ctrl %lld plan+jobs %lld items+barrier %lld (own items %lld) cycles; warp 0's window jobs: %lld "
-                   "of them, TMA wait %lld, SAD loop %lld, barrier %lld\n", b, tid, st, tr[st][0], tr[st][1], tr[st][2], tr[st][3],
-                   tr[st][7], tr[st][4], tr[st][5], tr[st][6]);
+                   "of them, TMA wait %lld, SAD loop %lld, barrier %lld; round planning %lld, decode %lld, decode -> first window there %lld; task planning %lld (+ barrier %lld)\n", b, tid, st, tr[st][0], tr[st][1], tr[st][2], tr[st][3],
+                   tr[st][7], tr[st][4], tr[st][5], tr[st][6], tr[st][8], tr[st][9], tr[st][10], tr[st][11], tr[st][3]);
         printf("b %d tid %d total %lld cycles\n", b, tid, clock64() - t_begin);
     }
     if (tid == 0) { /* print only once every CTA of the launch is past its last stage (bounded wait): printf stalls the SM */
