@@ -922,8 +922,9 @@ ME_HD void me_epi_decode(EpiCtx *e, int k, int n) {
     e->best_mv[k][n]  = mv;
 }
 
-/* ME:1522-1565 me_prune_ref */
-ME_HD void me_epi_prune(EpiCtx *e) {
+/* ME:1522-1565 me_prune_ref, first half: hme_sad = sum of the 64 best 8x8 SADs (the device sums them with a warp per
+ * reference, me_kernels.cu) */
+ME_HD void me_epi_prune_sums(EpiCtx *e) {
     const MeGpuParams *p = e->p;
     B64State          *s = e->s;
     for (int li = 0; li < p->num_of_list_to_search; li++)
@@ -936,6 +937,12 @@ ME_HD void me_epi_prune(EpiCtx *e) {
             for (int k = 0; k < 64; k++) v += e->best_sad[li * ME_NR + ri][21 + k];
             s->hme_sad[li][ri] = v;
         }
+}
+
+/* second half: the deviation test over all 2x4 slots */
+ME_HD void me_epi_prune_decide(EpiCtx *e) {
+    const MeGpuParams *p = e->p;
+    B64State          *s = e->s;
     uint16_t th = p->prune_ref_if_me_sad_dev_bigger_than_th;
     if (p->enable_me_hme_ref_pruning && th != (uint16_t)~0) {
         uint64_t best = ~(uint64_t)0;
@@ -946,6 +953,11 @@ ME_HD void me_epi_prune(EpiCtx *e) {
                 if (((uint64_t)s->hme_sad[li][ri] - best) * 100 > (uint64_t)th * best)
                     s->do_ref[li][ri] = 0;
     }
+}
+
+ME_HD void me_epi_prune(EpiCtx *e) {
+    me_epi_prune_sums(e);
+    me_epi_prune_decide(e);
 }
 
 /* z-order PU index (MeContext order) -> raster PU index (output order), ME:2520-2531 */

@@ -516,15 +516,32 @@ __global__ void __launch_bounds__(EP_THREADS) k_epilogue(MeJob *jobs) {
             atomicAdd(&j->ops_total[1], (unsigned long long)e.s->ops_fs);
         }
     } else {
-        if (tid == 0 && j->p.enable_hme_flag && j->p.enable_me_hme_ref_pruning)
-            me_epi_prune(&e);
+        const int lane = tid & 31, warp = tid >> 5;
+        if (j->p.enable_hme_flag && j->p.enable_me_hme_ref_pruning) {
+            /* me_prune_ref: the 64 best 8x8 SADs of a reference summed by a warp (two per lane), then the test on thread 0 */
+            for (int k = warp; k < ME_NREF; k += EP_THREADS / 32) {
+                const int li = k / ME_NR, ri = k % ME_NR;
+                if (li < (int)j->p.num_of_list_to_search && ri < (int)j->p.num_of_ref_pic_to_search[li]) {
+                    const bool     on = st.do_ref[li][ri] != 0;
+                    const uint32_t v  = __reduce_add_sync(0xffffffffu, on ? best_sad[k][21 + lane] + best_sad[k][53 + lane] : 0u);
+                    if (lane == 0)
+                        st.hme_sad[li][ri] = on ? v : ME_MAX_SAD_VALUE * 64u;
+                }
+            }
+            __syncthreads();
+            if (tid == 0)
+                me_epi_prune_decide(&e);
+        }
         __syncthreads();
         if (tid < j->p.max_number_of_pus_per_sb)
             me_epi_candidates(&e, tid);
         __syncthreads();
-        if (tid == 0) {
+        /* the three serial tails are independent of each other: one warp each */
+        if (tid == 0)
             me_epi_distortion(&e);
+        else if (tid == 32)
             me_epi_gm(&e);
+        else if (tid == 64) {
             me_epi_taps(&e);
             atomicAdd(&j->ops_total[0], (unsigned long long)e.s->ops);
             atomicAdd(&j->ops_total[1], (unsigned long long)e.s->ops_fs);
