@@ -674,6 +674,14 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
     j.flags                    = jc->out_slab + L.off[9];
     j.dbg_best_sad = jc->dbg_sad; j.dbg_best_mv = jc->dbg_mv; j.dbg_centre = jc->dbg_centre; j.dbg_hme_sad = jc->dbg_hme;
     j.dbg_do_ref = jc->dbg_do_ref; j.dbg_area = jc->dbg_area;
+    if (out) { /* destinations known up front (me_gpu_submit_out): taps nobody asked for are not written at all */
+        if (!out->p_sb_best_sad) j.dbg_best_sad = nullptr;
+        if (!out->p_sb_best_mv) j.dbg_best_mv = nullptr;
+        if (!out->hme_search_centre) j.dbg_centre = nullptr;
+        if (!out->hme_sad) j.dbg_hme_sad = nullptr;
+        if (!out->do_ref) j.dbg_do_ref = nullptr;
+        if (!out->search_area) j.dbg_area = nullptr;
+    }
     j.ops_total = jc->d_head->tail.ops;
     {
         const TfLayout T = tf_layout(nb); /* far below the open-loop layout's size */
