@@ -451,8 +451,8 @@ def gpu_main(args):
         pass
     # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the one `ncu --set full` capture
     # of this workload kept under profiles/ (ncu_r1_final_<kernel>_<workload>_details.txt)
-    ncu_traffic = {("1080p-m4", "motion", "k_hme"): 15221760 + 1024, ("1080p-m4", "iid", "k_fullsearch"): 13271552 + 768,
-                   ("4k-m0", "motion", "k_hme"): 62639872 + 9188096, ("4k-m0", "iid", "k_fullsearch"): 75336960 + 4834048}
+    ncu_traffic = {("1080p-m4", "motion", "k_hme"): 15215360 + 1792, ("1080p-m4", "iid", "k_fullsearch"): 13270528,
+                   ("4k-m0", "motion", "k_hme"): 63624960 + 7126784, ("4k-m0", "iid", "k_fullsearch"): 75603456 + 5817856}
     ncu_key = (WORKLOAD, args.kind, dom)
     roofline = {
         "bound": "int_sad", "kernel": dom, "achieved": achieved, "peak": sad_peak / 1e12, "unit": "Tbyte-SAD/s",
