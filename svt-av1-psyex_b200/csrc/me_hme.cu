@@ -80,7 +80,7 @@ __device__ unsigned g_trace_cnt;
 #endif
 /* search areas at least this wide / with at least this many 8-position units take hm_job_search8 (tunable by
    ME_HME_K8_MIN_PW / ME_HME_K8_MIN_UNITS for experiments) */
-__device__ int g_k8_min_pw = 64, g_k8_min_units = 64, g_team1_units = 16, g_lanes_target = 96, g_tall_min_rows = 32;
+__device__ int g_k8_min_pw = 32, g_k8_min_units = 64, g_team1_units = 16, g_lanes_target = 96, g_tall_min_rows = 32;
 
 struct HmeShared {
     B64State           s;
