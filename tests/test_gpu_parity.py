@@ -136,6 +136,27 @@ def test_pictures_in_flight_out_of_order(engine, oracle):
         assert not bad, (poc, bad)
 
 
+@pytest.mark.parametrize("debug", [True, False])
+def test_submit_out_with_and_without_taps(engine, oracle, debug):
+    """me_gpu_submit_out: destinations known at submit. With parity taps requested they come back exact; without them the
+    engine does not write them at all and the product arrays are unchanged."""
+    w, h, n, preset, poc = 320, 192, 17, 4, 8
+    ps = PictureSet(w, h, n, "motion", oracle)
+    cfg, p, l0, l1 = derive(preset, w, h, poc, n)
+    pocs = sorted(set([poc] + l0 + l1))
+    _register(engine, ps, pocs)
+    try:
+        got = planes.Outputs(w, h, p, debug=debug)
+        engine.submit_out(poc, p, [l0, l1], got)
+        engine.wait(poc, got)
+    finally:
+        _release(engine, pocs)
+    exp = oracle.me_picture(ps.get(poc), [[ps.get(k) for k in l0], [ps.get(k) for k in l1]], p)
+    fields = planes.PRODUCT_FIELDS + (planes.DEBUG_FIELDS if debug else [])
+    bad = planes.compare_outputs(exp, got, fields=fields, used_refs=used_refs(l0, l1))
+    assert not bad, bad
+
+
 def test_concurrent_callers(engine, oracle):
     """SURVEY 8(b) threading: the encoder's ME threads (up to 25) call submit / wait concurrently, keyed by picture, while
     picture analysis registers new pictures. Four host threads, each with its own pictures of a different preset."""
