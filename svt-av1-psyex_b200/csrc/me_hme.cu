@@ -706,7 +706,7 @@ __device__ __forceinline__ unsigned long long hm_job_search_tall(const HmJobD &J
  * ---------------------------------------------------------------------------------------------- */
 template <bool SUB>
 __device__ void fullsearch_item(const FsTask &f, int y_lo, int y_hi, const MeJob *j, const uint8_t *pool, uint32_t *win,
-                                unsigned long long *keys, int org_x, int org_y, int lane) {
+                                unsigned long long *keys, int org_x, int org_y, int lane, const uint32_t *src0) {
     constexpr int      NR = SUB ? 4 : 8, RSTEP = SUB ? 2 : 1;
     const MePlaneGeom &pl = j->g.plane[0];
     const int          stride_words = pl.stride >> 2;
@@ -715,14 +715,14 @@ __device__ void fullsearch_item(const FsTask &f, int y_lo, int y_hi, const MeJob
     const int by = ((lane >> 1) & 1) | ((lane >> 2) & 2); /* + 4 for the second block */
     uint32_t  sw[2][NR][2];
     {
-        const uint8_t *sp = hm_plane(pool, j->g, j->src_slot, 0) + (size_t)(pl.pad + org_y) * pl.stride + pl.pad + org_x;
+        /* the b64's source block is resident in shared memory (HmeShared.src0, pitch HM_SRC0_PITCH words) */
 #pragma unroll
         for (int b = 0; b < 2; b++)
 #pragma unroll
             for (int r = 0; r < NR; r++) {
-                const uint32_t *q = (const uint32_t *)(sp + (size_t)(8 * (by + 4 * b) + r * RSTEP) * pl.stride + 8 * bx);
-                sw[b][r][0]       = __ldg(q);
-                sw[b][r][1]       = __ldg(q + 1);
+                const uint2 v = *reinterpret_cast<const uint2 *>(src0 + (8 * (by + 4 * b) + r * RSTEP) * HM_SRC0_PITCH + 2 * bx);
+                sw[b][r][0]   = v.x;
+                sw[b][r][1]   = v.y;
             }
     }
     const uint8_t *w00   = hm_plane(pool, j->g, f.ref_slot, 0) + (size_t)(pl.pad + org_y + f.y0) * pl.stride + pl.pad + org_x + f.x0;
@@ -1120,10 +1120,10 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
                 const FsTask &f = sm.f[task];
                 if (sub)
                     fullsearch_item<true>(f, lo, min((int)f.h, lo + rows_per), j, pool, sm.buf[warp], keys + task * ME_NPU,
-                                          c.org_x, c.org_y, lane);
+                                          c.org_x, c.org_y, lane, sm.src0);
                 else
                     fullsearch_item<false>(f, lo, min((int)f.h, lo + rows_per), j, pool, sm.buf[warp], keys + task * ME_NPU,
-                                           c.org_x, c.org_y, lane);
+                                           c.org_x, c.org_y, lane, sm.src0);
             }
         }
         if (!search_stage)
