@@ -417,6 +417,7 @@ __global__ void __launch_bounds__(FS_THREADS, FS_CTAS_PER_SM) k_fullsearch(MeJob
         {
             const uint8_t *sp = plane_ptr(pool, j->g, j->src_slot, 0) + (size_t)(pl.pad + org_y) * pl.stride + pl.pad + org_x;
             const int      nrows = sub ? 32 : 64, rstep = sub ? 2 : 1;
+#pragma unroll 4
             for (int i = tid; i < nrows * 16; i += FS_THREADS) {
                 const int r = i >> 4, cw = i & 15;
                 srcw[i]     = *(const uint32_t *)(sp + (size_t)(r * rstep) * pl.stride + cw * 4);
@@ -430,6 +431,7 @@ __global__ void __launch_bounds__(FS_THREADS, FS_CTAS_PER_SM) k_fullsearch(MeJob
             const int      a   = (int)((uintptr_t)w00 & 3);
             const uint32_t *g0 = (const uint32_t *)(w00 - a);
             const int      nrows = hvalid + (sub ? 62 : 63) + 1;
+#pragma unroll 4 /* the loads of four iterations in flight: the staging phase is L2-latency bound */
             for (int i = tid; i < nrows * FS_PW; i += FS_THREADS) {
                 const int       r = i / FS_PW, cw = i - r * FS_PW;
                 const uint32_t *g = g0 + (size_t)r * (pl.stride >> 2) + cw;
