@@ -455,7 +455,8 @@ def gpu_main(args):
                    ("4k-m0", "motion", "k_hme"): 63624960 + 7126784, ("4k-m0", "iid", "k_fullsearch"): 75603456 + 5817856}
     ncu_key = (WORKLOAD, args.kind, dom)
     roofline = {
-        "bound": "int_sad", "kernel": dom, "achieved": achieved, "peak": sad_peak / 1e12, "unit": "Tbyte-SAD/s",
+        "bound": "int_sad", "bound_note": "integer ALU (packed byte-SAD issue rate, SURVEY 8(d)): the path is neither HBM- nor "
+        "tensor-bound; its HBM side is in traffic / hbm_gbs_achieved against hbm_peak_gbs", "kernel": dom, "achieved": achieved, "peak": sad_peak / 1e12, "unit": "Tbyte-SAD/s",
         "frac": achieved / (sad_peak / 1e12) if sad_peak else None, "traffic": ncu_traffic.get(ncu_key),
         "traffic_unit": "DRAM bytes per launch (one picture); the three planes of a picture are 3.3 MB at 1080p, 12.4 MB at 4K",
         "hbm_gbs_achieved": (ncu_traffic[ncu_key] * 16 / (dom_ms * 1e-3) / 1e9) if dom_ms > 0 and ncu_key in ncu_traffic else None,
