@@ -80,7 +80,7 @@ __device__ unsigned g_trace_cnt;
 #endif
 /* search areas at least this wide / with at least this many 8-position units take hm_job_search8 (tunable by
    ME_HME_K8_MIN_PW / ME_HME_K8_MIN_UNITS for experiments) */
-__device__ int g_k8_min_pw = 32, g_k8_min_units = 64, g_team1_units = 16, g_lanes_target = 96, g_tall_min_rows = 32;
+__device__ int g_k8_min_pw = 32, g_k8_min_units = 64, g_team1_units = 16, g_lanes_target = 96, g_tall_min_rows = 32, g_l2_prefetch = 0;
 
 struct HmeShared {
     B64State           s;
@@ -342,6 +342,10 @@ __device__ __forceinline__ void hm_tma_box(uint32_t dst, const void *map, int x,
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
                  ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(z), "r"(bar)
                  : "memory");
+}
+
+__device__ __forceinline__ void hm_tma_prefetch_l2(const void *map, int x, int y, int z) {
+    asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(map), "r"(x), "r"(y), "r"(z) : "memory");
 }
 
 /* box widths of the tensor maps, by plane: sixteenth {48, 80, 224}, quarter {80}, full {96, 128} */
@@ -996,6 +1000,14 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
                         fetched = 1;
                     }
                     int cur = 0;
+                    if (g_l2_prefetch && sm.team < HM_WARPS) /* one-warp batches cannot be fetched ahead (ring space): at least bring
+                                                                the windows of the later batches into L2 while the first is searched */
+                        for (int jb = HM_WARPS / sm.team; jb < njobs; jb++) {
+                            const HmJobD &Jn = sm.jobs[jb];
+                            const int     br = hm_map_rows(Jn.map);
+                            for (int y = 0; y < (int)Jn.nrows; y += br)
+                                hm_tma_prefetch_l2(maps.m[Jn.map], Jn.xt, Jn.y0 + y, sm.t[Jn.task].ref_slot);
+                        }
                     if (sm.team < HM_WARPS) {
                         /* the jobs of a batch are searched together: batches alternate between the ring halves when they
                            fit one, else every batch starts at 0 (then the next batch is fetched after this one) */
@@ -1203,6 +1215,10 @@ cudaError_t me_hme_setup(void) {
     if (getenv("ME_HME_TALL_MIN_ROWS")) {
         const int v = atoi(getenv("ME_HME_TALL_MIN_ROWS"));
         cudaMemcpyToSymbol(g_tall_min_rows, &v, sizeof(v));
+    }
+    if (getenv("ME_HME_L2_PREFETCH")) {
+        const int v = atoi(getenv("ME_HME_L2_PREFETCH"));
+        cudaMemcpyToSymbol(g_l2_prefetch, &v, sizeof(v));
     }
     if (getenv("ME_HME_K8_MIN_UNITS")) {
         const int v = atoi(getenv("ME_HME_K8_MIN_UNITS"));
