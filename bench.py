@@ -34,19 +34,9 @@ sys.path.insert(0, os.path.join(REPO, "tests"))
 
 from me_b200 import abi, planes, synth  # noqa: E402
 
-# BASELINE.json configs -> concrete workloads. `refs` None = what the preset's mrp level gives (4 + 3 at presets <= 5).
-# `sets` = resident copies of the sequence used in rotation (inputs larger than the 126 MB L2 either way);
-# `cpu_every` = the CPU arms time every n-th chunk of 6 b64s of each picture (a bounded sample, scaled back up).
-WORKLOADS = {
-    "1080p-m4": dict(w=1920, h=1080, preset=4, refs=(2, 2), sets=3, cpu_every=1, baseline_config=1,
-                     text="1080p 8-bit preset 4, mini-GOP 16, 2 refs/list, default HME + integer search areas"),
-    "1080p-m8": dict(w=1920, h=1080, preset=8, refs=(1, 1), sets=3, cpu_every=1, baseline_config=0,
-                     text="1080p 8-bit preset 8, mini-GOP 16, 1 ref/list (configs[3] = this workload, one stream per GPU)"),
-    "4k-m2": dict(w=3840, h=2160, preset=2, refs=None, sets=2, cpu_every=8, baseline_config=2,
-                  text="4K 10-bit source (8-bit ME planes) preset 2, mini-GOP 16, 4 + 3 refs, search areas up to 128x128 (x2 by MV)"),
-    "4k-m0": dict(w=3840, h=2160, preset=0, refs=None, sets=2, cpu_every=48, baseline_config=4,
-                  text="4K 8-bit preset 0, mini-GOP 16, 4 + 3 refs, HME-L0 up to 480x480, integer search up to 256x256 (x2 by MV)"),
-}
+import workloads  # noqa: E402  (tests/workloads.py: the BASELINE.json configs as concrete workloads + golden digests)
+
+WORKLOADS = workloads.WORKLOADS
 WORKLOAD = "1080p-m4"
 W, H, PRESET, NPIC, FORCE_REFS = 1920, 1080, 4, 33, (2, 2)
 NSETS, SET_STRIDE = 3, 1000  # copies of the sequence in the pool (distinct picture numbers: poc + 1000 * set)
@@ -63,8 +53,7 @@ def b64_count():
     return ((W + 63) // 64) * ((H + 63) // 64)
 
 
-# decode order of mini-GOP 2 (POC 17..32)
-STEP_POCS = [32 if g == 0 else 16 + g for g in synth.RA5_DECODE_ORDER]
+STEP_POCS = workloads.STEP_POCS  # decode order of mini-GOP 2 (POC 17..32)
 
 
 def derive(poc):
@@ -426,6 +415,17 @@ def gpu_main(args):
     dt_e2e, _, _ = timed(step_e2e, args.steps, args.warmup)
 
     checksum = int(sum(int(outs[p]["me_mv_array"].astype(np.uint64).sum()) for p in STEP_POCS) & 0xFFFFFFFF)
+    # parity gate: the product arrays of the step's 16 pictures, as the e2e arm left them in host memory, against the
+    # digests frozen from the reference's own AVX2 path on the same synthetic inputs (tests/golden/picture_hashes.json)
+    gold = workloads.load_hashes()
+    keys = [workloads.hash_key(WORKLOAD, args.kind, poc) for poc in STEP_POCS]
+    if all(k in gold for k in keys):
+        wrong = [poc for poc, k in zip(STEP_POCS, keys) if workloads.picture_hashes(outs[poc]) != gold[k]]
+        parity = {"pictures": len(keys), "equal": not wrong, "mismatched_pocs": wrong,
+                  "against": "tests/golden/picture_hashes.json (reference svt_aom_motion_estimation_b64 + AVX2 kernels, all b64s, "
+                             "every product array)"}
+    else:
+        parity = {"pictures": 0, "equal": None, "against": "no golden digests for this workload"}
     eng.close()
 
     n_frames = 16 * args.steps * world
@@ -505,13 +505,13 @@ def gpu_main(args):
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": 1e3 * dt_e2e / args.steps},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
-            "result_checksum": checksum, "extra_workloads": extra,
+            "result_checksum": checksum, "parity": parity, "extra_workloads": extra,
             "host": {"cpus": os.cpu_count(), "rank0_numa_cpus": len(numa_cpus) if numa_cpus else None},
         }
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
-    return 0
+    return 0 if parity["equal"] is not False else 3  # results that differ from the reference's are not a benchmark
 
 
 def main():
