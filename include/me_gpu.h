@@ -305,6 +305,8 @@ typedef struct MeGpuTimings {
     float k_fullsearch_main_ms; /* the main-round k_fullsearch launch alone */
     float k_ctrl_ms; /* sum over the k_ctrl launches */
     float k_epilogue_ms;
+    uint64_t byte_sad_ops_fullsearch_inline; /* the part of byte_sad_ops_fullsearch searched inside k_hme (8x8-variance probe, areas
+                                                of <= 256 positions) instead of as k_fullsearch tiles */
 } MeGpuTimings;
 int me_gpu_get_timings(MeGpuTimings *t);
 /* profiling mode: bracket every kernel launch of a job with CUDA events (adds ~30 event records per picture) */

@@ -189,6 +189,7 @@ ME_HD void mc_stage_init(CtrlCtx *c) {
     if (c->lane == 0) {
         s->ops        = 0;
         s->ops_fs     = 0;
+        s->ops_fs_inline = 0;
         s->tf_exit    = 0;
         c->s->pending = PEND_NONE;
     }

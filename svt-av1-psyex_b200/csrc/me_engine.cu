@@ -41,7 +41,7 @@ struct Slot {
 /* uploaded in one copy at submit; the tail (list header + counters) comes back in one copy */
 struct JobTail {
     FsTileList         list;
-    unsigned long long ops[4]; /* byte-SADs, full-search byte-SADs, tf_tot_horz_blks, tf_tot_vert_blks */
+    unsigned long long ops[5]; /* byte-SADs, full-search byte-SADs, tf_tot_horz_blks, tf_tot_vert_blks, full-search byte-SADs inside k_hme */
 };
 struct JobHead {
     MeJob   job;
@@ -697,7 +697,7 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
     tl.list.count = tl.list.next = tl.list.overflow = 0;
     tl.list.cap   = jc->tile_cap;
     tl.list.tiles = jc->tiles;
-    tl.ops[0] = tl.ops[1] = tl.ops[2] = tl.ops[3] = 0;
+    tl.ops[0] = tl.ops[1] = tl.ops[2] = tl.ops[3] = tl.ops[4] = 0;
 
     CU(cudaSetDevice(d.id));
     cudaStream_t st = jc->stream;
@@ -752,7 +752,8 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
             maps = &d.mapsets.back().maps;
         }
         pbegin(1);
-        me_launch_hme(jc->d_job, 1, nbi, jc->d_list, d.pool, maps, st);
+        me_launch_hme(jc->d_job, 1, nbi, (int)p.num_of_ref_pic_to_search[0] + (p.num_of_list_to_search > 1 ? (int)p.num_of_ref_pic_to_search[1] : 0),
+                      jc->d_list, d.pool, maps, st);
         pend();
         if (prof) CU(cudaEventRecord(jc->ev[1], st));
         if (jc->tail != st) { /* the rest of the picture goes to the higher-priority stream */
@@ -918,6 +919,7 @@ int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out) {
     t.kernel_launches = me_launch_count() + me_hme_launch_count() + me_dg_launch_count();
     t.byte_sad_ops    = jc->h_tail->ops[0];
     t.byte_sad_ops_fullsearch = jc->h_tail->ops[1];
+    t.byte_sad_ops_fullsearch_inline = jc->h_tail->ops[4];
     g.last            = t;
     out->b64_count    = (uint32_t)nb;
     out->pu_count     = j.pu_count;

@@ -516,6 +516,7 @@ __global__ void __launch_bounds__(EP_THREADS) k_epilogue(MeJob *jobs) {
             me_epi_taps(&e);
             atomicAdd(&j->ops_total[0], (unsigned long long)e.s->ops);
             atomicAdd(&j->ops_total[1], (unsigned long long)e.s->ops_fs);
+            atomicAdd(&j->ops_total[4], (unsigned long long)e.s->ops_fs_inline);
         }
     } else {
         const int lane = tid & 31, warp = tid >> 5;
@@ -547,6 +548,7 @@ __global__ void __launch_bounds__(EP_THREADS) k_epilogue(MeJob *jobs) {
             me_epi_taps(&e);
             atomicAdd(&j->ops_total[0], (unsigned long long)e.s->ops);
             atomicAdd(&j->ops_total[1], (unsigned long long)e.s->ops_fs);
+            atomicAdd(&j->ops_total[4], (unsigned long long)e.s->ops_fs_inline);
         }
     }
     if (j->dbg_best_sad)

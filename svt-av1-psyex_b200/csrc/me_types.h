@@ -89,6 +89,7 @@ typedef struct B64State {
     uint8_t  tf_exit; /* ME_MCTF: hme_sad < tf_me_exit_th, the integer search is skipped (ME:3109-3113) */
     uint64_t ops; /* algorithmic byte-SAD count, SURVEY 8(d) */
     uint64_t ops_fs; /* part of ops spent in the integer full search */
+    uint64_t ops_fs_inline; /* part of ops_fs searched inside k_hme (probe, areas of <= 256 positions) rather than as k_fullsearch tiles */
 } B64State;
 
 /* one svt_sad_loop_kernel call. Coordinates are in the plane's own interior coordinate system (may be
@@ -158,7 +159,7 @@ typedef struct MeJob {
     uint64_t *dbg_hme_sad;
     uint8_t  *dbg_do_ref;
     int16_t  *dbg_area;
-    unsigned long long *ops_total; /* [4] per job: all byte-SADs, full-search byte-SADs, tf_tot_horz_blks, tf_tot_vert_blks */
+    unsigned long long *ops_total; /* [5] per job: all byte-SADs, full-search byte-SADs, tf_tot_horz_blks, tf_tot_vert_blks, full-search byte-SADs done inside k_hme */
     /* ME_MCTF outputs (device mirrors of MeGpuOutputs.tf_*) */
     uint32_t *tf_best_sad; /* [b64_count][ME_NPU] */
     uint32_t *tf_best_mv;

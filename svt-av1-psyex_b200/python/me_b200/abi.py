@@ -122,7 +122,7 @@ class MeGpuTimings(C.Structure):
                 ("epilogue_ms", C.c_float), ("total_ms", C.c_float), ("kernel_launches", u64),
                 ("byte_sad_ops", u64), ("byte_sad_ops_fullsearch", u64), ("k_search_ms", C.c_float),
                 ("k_fullsearch_ms", C.c_float), ("k_fullsearch_main_ms", C.c_float), ("k_ctrl_ms", C.c_float),
-                ("k_epilogue_ms", C.c_float)]
+                ("k_epilogue_ms", C.c_float), ("byte_sad_ops_fullsearch_inline", u64)]
 
 
 class MeGpuDgMetrics(C.Structure):
@@ -149,7 +149,7 @@ class RefMrpInputs(C.Structure):
 RefArray = (C.POINTER(OraclePicture) * MAX_REFS) * MAX_LISTS
 RefNumbers = (u64 * MAX_REFS) * MAX_LISTS
 
-GPU_LIB = os.path.join(PKG, "libme_gpu.so")
+GPU_LIB = os.environ.get("ME_B200_TRACE_LIB") or os.path.join(PKG, "libme_gpu.so")  # tools/trace_hme.py points at the instrumented build
 HOST_LIB = os.path.join(PKG, "libme_host.so")
 ORACLE_LIB = os.path.join(REPO, "oracle", "libme_oracle.so")
 REF_LIB = os.path.join(REPO, "oracle", "_ref", "libme_ref.so")
