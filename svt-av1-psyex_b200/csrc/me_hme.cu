@@ -59,11 +59,11 @@ struct HmPlan { /* how a task is cut into window jobs */
 struct HmJobD { /* one window job, 32 bytes */
     int16_t  px0, pw, e0, ne; /* band of search positions: columns [px0, px0 + pw), evaluated rows [e0, e0 + ne) */
     int16_t  xt, y0; /* TMA column (multiple of 16) and row of the window */
-    uint16_t pad0_;
+    uint16_t pitch; /* bytes per window row = box width of the job's tensor map */
     uint16_t nrows; /* window rows (whole boxes) */
     uint16_t total; /* lanes' worth of work of the SAD loop: units x lanes per unit */
     uint8_t  task, map, aoff /* byte offset of position px0 in a window row */, ncls, nchunk;
-    int8_t   pad1_;
+    uint8_t  brows; /* rows per TMA box */
     uint32_t m_chunk, m_cls;
 };
 #define HM_ROUND 16 /* window jobs decoded at a time (one lane each) */
@@ -91,10 +91,14 @@ struct HmeShared {
     unsigned long long tkey[ME_SLOTS]; /* best (sad << 32 | scan index) of each search task */
     MeGpuParams        p; /* the picture's controls: the control code reads them hundreds of times */
     alignas(16) uint32_t src0[64 * HM_SRC0_PITCH], src1[32 * HM_SRC1_PITCH], src2[16 * HM_SRC2_PITCH]; /* the b64's source block on the three planes (padded pitches) */
-    HmWarp             w[HM_MAXW];
-    /* the warps' window rings follow (ring_bytes each, 128-byte aligned) */
+    /* HmWarp[nwarps] and then the warps' window rings follow (ring_bytes each, 128-byte aligned) */
 };
 #define HM_FIXED_BYTES ((sizeof(HmeShared) + 127) & ~(size_t)127)
+#define HM_WARP_BYTES(nw) ((sizeof(HmWarp) * (size_t)(nw) + 127) & ~(size_t)127)
+/* registers per thread. Measured (1080p preset 4, frames/s): 128 -> 4530, 96 -> 4260, 80 -> 4250, 64 -> 3990: the spills cost more than the extra resident CTAs bring */
+#ifndef HM_MAXREG
+#define HM_MAXREG 128
+#endif
 
 __device__ __forceinline__ uint32_t hm_vsad4(uint32_t a, uint32_t b, uint32_t c) {
     uint32_t d;
@@ -448,8 +452,8 @@ __device__ void hm_job_decode(const SearchTask *tasks, const HmPlan *plans, cons
     J.aoff   = (uint8_t)(x0 & 15);
     J.y0     = (int16_t)(g.pad + t.ry + ymul * e0 + (skip ? 1 : 0));
     J.nrows  = (uint16_t)(((ne - 1) * ymul + (t.rows - 1) * t.row_step + 1 + br - 1) / br * br); /* whole boxes */
-    J.pad0_  = 0;
-    J.pad1_  = 0;
+    J.pitch  = (uint16_t)hm_map_width(pl.map);
+    J.brows  = (uint8_t)br;
     J.ncls   = (uint8_t)ncls;
     J.nchunk = (uint8_t)nchunk;
     J.total  = (uint16_t)((ncls * nchunk * ne) << pl.g_log2);
@@ -477,7 +481,7 @@ __device__ __forceinline__ unsigned long long hm_job_search(const HmJobD &J, con
                                                             const uint32_t *src, int src_pitch4, int warp, int nthr, int lane) {
     const bool skip = t.bw == 16 && t.rows <= 16 && t.skip_line;
     const int  ymul = skip ? 2 : 1, rows = t.rows, step = t.row_step;
-    const int  pitchw = hm_map_width(J.map) >> 2, G = 1 << g_log2;
+    const int  pitchw = (int)J.pitch >> 2, G = 1 << g_log2;
     const int  ncs_log2 = 2 - t.level, RG = G >> ncs_log2; /* column segments: 1 / 2 / 4 on the sixteenth / quarter / full plane */
     const int  ncls = J.ncls, nchunk = J.nchunk, total = J.total;
     const uint32_t m_chunk = J.m_chunk, m_cls = J.m_cls;
@@ -548,7 +552,7 @@ __device__ __forceinline__ unsigned long long hm_job_search8(const HmJobD &J, co
                                                              const uint32_t *src, int src_pitch4, int warp, int nthr, int lane) {
     const bool skip = t.bw == 16 && t.rows <= 16 && t.skip_line;
     const int  ymul = skip ? 2 : 1, rows = t.rows, step = t.row_step;
-    const int  pitch4 = hm_map_width(J.map) >> 4; /* window row pitch in 16-byte units */
+    const int  pitch4 = (int)J.pitch >> 4; /* window row pitch in 16-byte units */
     const int  nseg = J.nchunk, total = J.total;
     const uint32_t m_seg = J.m_chunk, pw = (uint32_t)J.pw;
     /* inside the job a 32-bit key is enough: SAD of a 16-byte-wide block of <= 16 rows < 2^16, and a job has fewer
@@ -609,7 +613,7 @@ __device__ __forceinline__ unsigned long long hm_job_search_tall(const HmJobD &J
                                                                  const uint32_t *src, int src_pitch4, int warp, int nthr, int lane) {
     const bool skip = t.bw == 16 && t.rows <= 16 && t.skip_line;
     const int  ymul = skip ? 2 : 1, step = t.row_step, ys = J.ncls /* row_step / ymul: 1 or 2 */;
-    const int  pitchw = hm_map_width(J.map) >> 2, total = J.total, ne = J.ne, maxrow = (int)J.nrows - 1;
+    const int  pitchw = (int)J.pitch >> 2, total = J.total, ne = J.ne, maxrow = (int)J.nrows - 1;
     const uint32_t pw = (uint32_t)J.pw;
     uint32_t   best = 0xFFFFFFFFu;
     for (int base = warp * 32; base < total; base += nthr) {
@@ -785,7 +789,7 @@ struct HmWarpCtx {
     int      lane;
 };
 
-__device__ __forceinline__ int hm_job_bytes(const HmJobD &J) { return (int)J.nrows * hm_map_width(J.map); }
+__device__ __forceinline__ int hm_job_bytes(const HmJobD &J) { return (int)J.nrows * (int)J.pitch; }
 __device__ __forceinline__ int hm_job_offset(const HmJobD &J, uint32_t q, int ring_bytes) {
     return (q & 1) ? (ring_bytes - hm_job_bytes(J)) & ~127 : 0;
 }
@@ -793,13 +797,13 @@ __device__ __forceinline__ int hm_job_offset(const HmJobD &J, uint32_t q, int ri
 /* lane 0: request the window of job J (sequence number q) */
 __device__ __forceinline__ void hm_issue(const HmWarpCtx &wc, const HmeMaps &maps, const HmJobD &J, uint32_t q, uint32_t ref_slot) {
     const uint32_t bar   = hm_smem(&wc.w->mbar[q & 1]);
-    const int      pitch = hm_map_width(J.map), br = hm_map_rows(J.map), off = hm_job_offset(J, q, wc.ring_bytes);
+    const int      pitch = J.pitch, br = J.brows, off = hm_job_offset(J, q, wc.ring_bytes);
     const uint32_t dst   = hm_smem(wc.ring) + (uint32_t)off;
     hm_mbar_expect(bar, (uint32_t)hm_job_bytes(J));
     for (int y = 0; y < (int)J.nrows; y += br) hm_tma_box(dst + (uint32_t)(y * pitch), maps.m[J.map], J.xt, J.y0 + y, (int)ref_slot, bar);
 }
 
-__device__ void hm_run_tasks(HmeShared &sm, HmWarpCtx &wc, int first, int n, const MeJob *j, const uint8_t *pool, const HmeMaps &maps,
+__device__ __noinline__ void hm_run_tasks(HmeShared &sm, HmWarpCtx &wc, int first, int n, const MeJob *j, const uint8_t *pool, const HmeMaps &maps,
                              int org_x, int org_y, FsTileList *list) {
     const int                lane = wc.lane;
     const unsigned long long none = ((unsigned long long)ME_SAD_LOOP_INIT << 32) | 0xFFFFFFFFull;
@@ -925,7 +929,7 @@ __device__ void hm_run_tasks(HmeShared &sm, HmWarpCtx &wc, int first, int n, con
 }
 
 /* the integer search task sm.f[k] of this warp's reference: searched here when small, else cut into tiles for k_fullsearch */
-__device__ void hm_run_fs(HmeShared &sm, HmWarpCtx &wc, int k, const MeJob *j, const uint8_t *pool, unsigned long long *keys, int org_x,
+__device__ __noinline__ void hm_run_fs(HmeShared &sm, HmWarpCtx &wc, int k, const MeJob *j, const uint8_t *pool, unsigned long long *keys, int org_x,
                           int org_y, FsTileList *list, uint32_t b, bool sub) {
     const FsTask f = sm.f[k];
     if (!f.valid)
@@ -977,7 +981,7 @@ __device__ __forceinline__ void hm_clear_slots(SearchTask *t, int first, int n) 
     for (int i = 0; i < n; i++) t[first + i].valid = 0;
 }
 
-__global__ void __launch_bounds__(HM_MAXW * 32, 2)
+__global__ void __maxnreg__(HM_MAXREG)
     k_hme(MeJob *jobs, FsTileList *list, const uint8_t *pool, const __grid_constant__ HmeMaps maps, int ring_bytes) {
     extern __shared__ __align__(1024) unsigned char hm_raw[];
     long long      tp  = TR_T();
@@ -1013,8 +1017,8 @@ __global__ void __launch_bounds__(HM_MAXW * 32, 2)
     c.nlanes = 1;
 
     HmWarpCtx wc;
-    wc.w          = &sm.w[warp];
-    wc.ring       = hm_raw + HM_FIXED_BYTES + (size_t)warp * (size_t)ring_bytes;
+    wc.w          = reinterpret_cast<HmWarp *>(hm_raw + HM_FIXED_BYTES) + warp;
+    wc.ring       = hm_raw + HM_FIXED_BYTES + HM_WARP_BYTES(blockDim.x >> 5) + (size_t)warp * (size_t)ring_bytes;
     wc.ring_bytes = ring_bytes;
     wc.seq        = 0;
     wc.lane       = lane;
@@ -1035,15 +1039,29 @@ __global__ void __launch_bounds__(HM_MAXW * 32, 2)
     }
     /* the b64's source block on the three planes stays in shared memory for the whole chain (rows below a short
        picture-edge block are padding: loaded, never summed) */
-    for (int i = tid; i < 64 * 16 + 32 * 8 + 16 * 4; i += nthr) {
-        const int lv = i < 64 * 16 ? 0 : i < 64 * 16 + 32 * 8 ? 1 : 2;
-        const int q  = i - (lv == 0 ? 0 : lv == 1 ? 64 * 16 : 64 * 16 + 32 * 8);
-        const int wr = 16 >> lv, r = q / wr, cw = q - r * wr;
-        const MePlaneGeom &pl = j->g.plane[lv];
-        const uint8_t     *sp = hm_plane(pool, j->g, j->src_slot, lv) + (size_t)(pl.pad + (c.org_y >> lv) + r) * pl.stride + pl.pad +
-                            (c.org_x >> lv);
-        const int sp_w = lv == 0 ? HM_SRC0_PITCH : lv == 1 ? HM_SRC1_PITCH : HM_SRC2_PITCH;
-        (lv == 0 ? sm.src0 : lv == 1 ? sm.src1 : sm.src2)[r * sp_w + cw] = __ldg((const uint32_t *)sp + cw);
+    for (int base = 0; base < 64 * 16 + 32 * 8 + 16 * 4; base += 4 * nthr) { /* four loads in flight per thread: the set-up is HBM latency */
+        uint32_t  v[4];
+        uint32_t *dst[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int i = base + u * nthr + tid;
+            dst[u]      = nullptr;
+            if (i < 64 * 16 + 32 * 8 + 16 * 4) {
+                const int lv = i < 64 * 16 ? 0 : i < 64 * 16 + 32 * 8 ? 1 : 2;
+                const int q  = i - (lv == 0 ? 0 : lv == 1 ? 64 * 16 : 64 * 16 + 32 * 8);
+                const int r = q >> (4 - lv), cw = q & ((16 >> lv) - 1);
+                const MePlaneGeom &pl = j->g.plane[lv];
+                const uint8_t     *sp = hm_plane(pool, j->g, j->src_slot, lv) + (size_t)(pl.pad + (c.org_y >> lv) + r) * pl.stride + pl.pad +
+                                    (c.org_x >> lv);
+                const int sp_w = lv == 0 ? HM_SRC0_PITCH : lv == 1 ? HM_SRC1_PITCH : HM_SRC2_PITCH;
+                dst[u]         = (lv == 0 ? sm.src0 : lv == 1 ? sm.src1 : sm.src2) + r * sp_w + cw;
+                v[u]           = __ldg((const uint32_t *)sp + cw);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+            if (dst[u])
+                *dst[u] = v[u];
     }
     __threadfence();
     __syncthreads();
@@ -1175,25 +1193,29 @@ int me_hme_make_maps(HmeMaps *maps, const uint8_t *pool, const MePicGeom *g, int
 }
 
 /* Shared memory of a CTA of `nwarps` search warps: the fixed part + a window ring per warp. The ring is what is left of
- * the SM's 227 KB when `target` CTAs are resident: 4 for up to 4 references (a 1080p picture's 510 CTAs are then
- * co-resident on 148 SMs), 2 for 5..8 (the 4K presets: 7 references), never above 32 KB (the in-job keys of
- * hm_job_search8 index positions with 16 bits) nor below the largest single window (128 x 72 bytes). */
+ * the SM's 227 KB when `target` CTAs are resident - as many as the registers allow (HM_MAXREG) - never above 32 KB (the
+ * in-job keys of hm_job_search8 index positions with 16 bits) nor below the largest single window (128 x 72 bytes). */
 int me_hme_ring_bytes(int nwarps) {
-    const int target = nwarps <= 4 ? 4 : 2;
-    const int budget = (227 * 1024) / target - 1024 /* per-CTA reservation */ - (int)HM_FIXED_BYTES - 128 /* over-read slack */;
-    int       ring   = (budget / nwarps) & ~127;
-    if (ring > 32768)
-        ring = 32768;
-    if (ring < 9216)
-        ring = 9216;
-    return ring;
+    int target = (65536 / HM_MAXREG) / (32 * nwarps);
+    if (target > 8)
+        target = 8;
+    if (target < 1)
+        target = 1;
+    for (;; target--) {
+        const int budget = (227 * 1024) / target - 1024 /* per-CTA reservation */ - (int)HM_FIXED_BYTES - (int)HM_WARP_BYTES(nwarps) - 128 /* over-read slack */;
+        int       ring   = (budget / nwarps) & ~127;
+        if (ring > 32768)
+            ring = 32768;
+        if (ring >= 7168 || target == 1) /* 96 x 72: the whole window of an HME level 2 / centre search */
+            return ring < 9216 && target == 1 ? 9216 : ring;
+    }
 }
 
 void me_launch_hme(MeJob *jobs, int njobs, int max_b64, int nwarps, FsTileList *list, const uint8_t *pool, const HmeMaps *maps,
                    cudaStream_t st) {
     dim3         grid(max_b64, njobs);
     const int    ring = me_hme_ring_bytes(nwarps);
-    const size_t smem = HM_FIXED_BYTES + (size_t)nwarps * (size_t)ring + 128;
+    const size_t smem = HM_FIXED_BYTES + HM_WARP_BYTES(nwarps) + (size_t)nwarps * (size_t)ring + 128;
     k_hme<<<grid, 32 * nwarps, smem, st>>>(jobs, list, pool, *maps, ring);
     g_hme_launches++;
 }
