@@ -284,6 +284,24 @@ typedef struct MeGpuDgMetrics { /* DGDetectorMetrics, pcs.h:731-737 (seg_complet
 int me_gpu_dg_detector(uint64_t src_picture_number, uint64_t ref_picture_number, uint8_t input_resolution,
                        MeGpuDgMetrics *metrics);
 
+/* The same search with NO allocation of any kind behind the call (no cudaMalloc / cudaFree, no stream or event creation,
+ * no engine pool): for callers that cannot allocate - code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc. It has NO counterpart in the reference.
+ * Works without me_gpu_init, on the current CUDA device. The caller passes the two PADDED sixteenth planes (host pointers
+ * at the first byte of the padded plane, padding 16 on every side, stride >= width / 4 + 32; what me_gpu_read_pyramid
+ * returns as `sixteenth`) and the luma size of the pictures (multiples of 8). Scratch - both planes and the accumulator -
+ * is a file-scope device array of ME_GPU_DG_NOALLOC_MAX_BYTES that every GPU loading the library holds until exit: pictures
+ * up to 3840x2160; anything larger is rejected with ME_GPU_ERR_NO_MEMORY. All calls share that array: calls from one
+ * process are serialised, calls that overlap on the GPU from several processes' contexts do not share it, and a caller
+ * that drives the GPU work itself must not overlap two of them. me_gpu_dg_detector_noalloc_setup() (optional; once per
+ * device, that device current, outside any graph capture) resolves the array's device address and loads the kernel;
+ * me_gpu_dg_detector_noalloc_error() is the (static) text of this entry point's last error. */
+#define ME_GPU_DG_NOALLOC_MAX_BYTES (1280 * 1024)
+int me_gpu_dg_detector_noalloc_setup(void);
+int me_gpu_dg_detector_noalloc(const uint8_t *src_sixteenth, int src_stride, const uint8_t *ref_sixteenth, int ref_stride,
+                               int width, int height, uint8_t input_resolution, MeGpuDgMetrics *metrics);
+const char *me_gpu_dg_detector_noalloc_error(void);
+
 /* host-side restatement of svt_aom_sig_deriv_me and the pcs/scs settings it depends on */
 int me_gpu_derive_params(const MeGpuEncoderConfig *cfg, MeGpuParams *params);
 

@@ -151,3 +151,108 @@ void me_launch_dg(const uint8_t *pool, const MePicGeom *g, uint32_t src_slot, ui
     k_dg_hme<<<g->b64_count, DG_THREADS, 0, st>>>(pool, *g, src_slot, ref_slot, sa, acc);
     g_dg_launches++;
 }
+
+/* ------------------------------------------------------------------------------------------------
+ * me_gpu_dg_detector_noalloc: the same kernel for callers that may not allocate (CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc). No counterpart in the reference.
+ *
+ * Scratch (the two sixteenth planes at the pool's pitch + the metric accumulator) lives in ONE file-scope device array
+ * of ME_GPU_DG_NOALLOC_MAX_BYTES that every GPU loading this library holds until exit. In host code `g_dg_scratch` is a
+ * host-side stand-in for the symbol, not a device address: its device address is fetched once per device with
+ * cudaGetSymbolAddress (that device current) and only that pointer is handed to the kernel.
+ * All calls share the array and it keeps the last call's contents: the accumulator is cleared on every call, the planes
+ * are overwritten in full. Calls that overlap on the GPU race; calls from one process are serialised here by a mutex.
+ * ---------------------------------------------------------------------------------------------- */
+#include <mutex>
+
+static __device__ __align__(256) uint8_t g_dg_scratch[ME_GPU_DG_NOALLOC_MAX_BYTES];
+
+#define DG_NOALLOC_ACC_BYTES 256 /* the accumulator's share at the head of the scratch (keeps the planes 256-byte aligned) */
+#define DG_NOALLOC_MAX_DEVICES 64
+
+static std::mutex  g_dg_noalloc_mu;
+static uint8_t    *g_dg_scratch_ptr[DG_NOALLOC_MAX_DEVICES]; /* device address of g_dg_scratch, per device */
+static const char *g_dg_noalloc_err = "";
+
+static int dg_noalloc_fail(int code, const char *msg) {
+    g_dg_noalloc_err = msg; /* string literals only: nothing is allocated on this path either */
+    return code;
+}
+
+/* once per device, with that device current: the symbol's device address (and the module's load, which the first use of
+ * any kernel of the library triggers). Call it outside a graph capture; the entry point calls it when needed. */
+extern "C" int me_gpu_dg_detector_noalloc_setup(void) {
+    std::lock_guard<std::mutex> lk(g_dg_noalloc_mu);
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0)
+        return dg_noalloc_fail(ME_GPU_ERR_NO_DEVICE, "no CUDA device (this engine has no CPU fallback)");
+    if (dev >= DG_NOALLOC_MAX_DEVICES)
+        return dg_noalloc_fail(ME_GPU_ERR_BAD_ARG, "device ordinal beyond the table of scratch addresses");
+    if (!g_dg_scratch_ptr[dev]) {
+        void *p = nullptr;
+        if (cudaGetSymbolAddress(&p, g_dg_scratch) != cudaSuccess || !p) {
+            cudaGetLastError();
+            return dg_noalloc_fail(ME_GPU_ERR_CUDA, "cudaGetSymbolAddress(g_dg_scratch) failed");
+        }
+        cudaFuncAttributes fa;
+        if (cudaFuncGetAttributes(&fa, k_dg_hme) != cudaSuccess) {
+            cudaGetLastError();
+            return dg_noalloc_fail(ME_GPU_ERR_CUDA, "k_dg_hme is not loadable on this device (sm_100a required)");
+        }
+        g_dg_scratch_ptr[dev] = (uint8_t *)p;
+    }
+    return ME_GPU_OK;
+}
+
+extern "C" const char *me_gpu_dg_detector_noalloc_error(void) { return g_dg_noalloc_err; }
+
+extern "C" int me_gpu_dg_detector_noalloc(const uint8_t *src_sixteenth, int src_stride, const uint8_t *ref_sixteenth, int ref_stride,
+                                          int width, int height, uint8_t input_resolution, MeGpuDgMetrics *metrics) {
+    if (!src_sixteenth || !ref_sixteenth || !metrics)
+        return dg_noalloc_fail(ME_GPU_ERR_BAD_ARG, "null argument");
+    if (width <= 0 || height <= 0 || (width & 7) || (height & 7))
+        return dg_noalloc_fail(ME_GPU_ERR_BAD_ARG, "luma size must be a positive multiple of 8");
+    MePicGeom g;
+    me_make_geom(&g, width, height);
+    const MePlaneGeom pl        = g.plane[2];
+    const int         row_bytes = pl.width + 2 * pl.pad;
+    const size_t      slot      = ((size_t)pl.stride * (size_t)pl.rows + 255) & ~(size_t)255;
+    if (DG_NOALLOC_ACC_BYTES + 2 * slot > (size_t)ME_GPU_DG_NOALLOC_MAX_BYTES)
+        return dg_noalloc_fail(ME_GPU_ERR_NO_MEMORY,
+                               "picture too large for the static scratch of me_gpu_dg_detector_noalloc (ME_GPU_DG_NOALLOC_MAX_BYTES: "
+                               "two sixteenth planes of up to 3840x2160 pictures)");
+    if (src_stride < row_bytes || ref_stride < row_bytes)
+        return dg_noalloc_fail(ME_GPU_ERR_BAD_ARG, "stride smaller than the padded sixteenth plane's row (width / 4 + 32)");
+    int rc = me_gpu_dg_detector_noalloc_setup();
+    if (rc != ME_GPU_OK)
+        return rc;
+    std::lock_guard<std::mutex> lk(g_dg_noalloc_mu);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    uint8_t        *base = g_dg_scratch_ptr[dev]; /* the DEVICE address; never g_dg_scratch itself */
+    MeGpuDgMetrics *acc  = reinterpret_cast<MeGpuDgMetrics *>(base);
+    uint8_t        *pool = base + DG_NOALLOC_ACC_BYTES;
+    /* the kernel addresses planes as pool + slot * slot_bytes + plane[2].offset: slot 0 = source, slot 1 = reference */
+    g.plane[2].offset = 0;
+    g.slot_bytes      = slot;
+    const int sa = input_resolution <= 1 ? 16 : input_resolution <= 2 ? 64 : 128; /* pd_process.c:497-498 */
+    cudaStream_t st = 0; /* the default stream: no stream is created either */
+    cudaError_t  e  = cudaMemsetAsync(acc, 0, DG_NOALLOC_ACC_BYTES, st); /* the array keeps the last call's sums */
+    if (e == cudaSuccess)
+        e = cudaMemcpy2DAsync(pool, pl.stride, src_sixteenth, src_stride, row_bytes, pl.rows, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess)
+        e = cudaMemcpy2DAsync(pool + slot, pl.stride, ref_sixteenth, ref_stride, row_bytes, pl.rows, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) {
+        me_launch_dg(pool, &g, 0u, 1u, sa, acc, st);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(metrics, acc, sizeof(MeGpuDgMetrics), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return dg_noalloc_fail(ME_GPU_ERR_CUDA, "me_gpu_dg_detector_noalloc: a CUDA call failed");
+    }
+    return ME_GPU_OK;
+}

@@ -160,6 +160,7 @@ GPU_SYMBOLS = [
     "me_gpu_register_picture_unpadded", "me_gpu_release_picture", "me_gpu_read_pyramid", "me_gpu_plane_geometry",
     "me_gpu_submit", "me_gpu_wait", "me_gpu_derive_params", "me_gpu_get_timings", "me_gpu_measure_sad_peak", "me_gpu_set_profiling", "me_gpu_submit_out", "me_gpu_output_layout",
     "me_gpu_dg_detector", "me_gpu_derive_params_tf",
+    "me_gpu_dg_detector_noalloc", "me_gpu_dg_detector_noalloc_setup", "me_gpu_dg_detector_noalloc_error",
 ]
 
 
@@ -185,6 +186,9 @@ def load_gpu_lib():
     lib.me_gpu_get_timings.argtypes = [C.POINTER(MeGpuTimings)]
     lib.me_gpu_dg_detector.argtypes = [u64, u64, u8, C.POINTER(MeGpuDgMetrics)]
     lib.me_gpu_measure_sad_peak.restype = C.c_double
+    lib.me_gpu_dg_detector_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, u8,
+                                               C.POINTER(MeGpuDgMetrics)]
+    lib.me_gpu_dg_detector_noalloc_error.restype = C.c_char_p
     return lib
 
 
