@@ -122,10 +122,11 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
-def make_pictures(kind, pinned):
-    """padded full-resolution planes of the 33 pictures, in pinned host memory when torch+CUDA are there"""
+def make_pictures(kind, pinned, padded=True):
+    """full-resolution luma planes of the 33 pictures (with or without the 68-pixel border: the engine generates it on the
+    device for unpadded input), in pinned host memory when torch+CUDA are there"""
     seq = synth.Sequence(W, H, NPIC, kind=kind)
-    rows, stride = H + 136, W + 136
+    rows, stride = (H + 136, W + 136) if padded else (H, W)
     out = {}
     for poc in range(NPIC):
         if pinned:
@@ -135,7 +136,7 @@ def make_pictures(kind, pinned):
             out[poc] = (a, t)
         else:
             out[poc] = (np.empty((rows, stride), dtype=np.uint8), None)
-        out[poc][0][...] = np.pad(seq.luma(poc), 68, mode="edge")
+        out[poc][0][...] = np.pad(seq.luma(poc), 68, mode="edge") if padded else seq.luma(poc)
     return out
 
 
@@ -163,7 +164,7 @@ class CpuArm:
     """The reference's ME (svt_aom_motion_estimation_b64 + AVX2 kernels, oracle/_ref) on host threads."""
 
     def __init__(self, kind, pocs, threads, simd=1):
-        from me_b200 import checkers
+        import checkers
         self.ref = checkers.Reference()
         self.threads, self.simd, self.pocs = threads, simd, pocs
         seq = synth.Sequence(W, H, NPIC, kind=kind)
@@ -295,7 +296,7 @@ def gpu_main(args):
         if world > 1:
             dist.barrier()
 
-    pics = make_pictures(args.kind, pinned=True)
+    pics = make_pictures(args.kind, pinned=True, padded=False)
     jobs = {poc: derive(poc) for poc in STEP_POCS}
     eng = Engine(W, H, 4, 3, pictures_in_flight=NSETS * NPIC + 4, devices=[local_rank])
     outs = {poc: pinned_outputs(jobs[poc][1], eng) for poc in STEP_POCS}
@@ -304,7 +305,7 @@ def gpu_main(args):
 
     def reg(poc, st):
         a, _ = pics[poc]
-        eng.register_picture_ptr(poc + SET_STRIDE * st, a.ctypes.data, a.strides[0], W, H)
+        eng.register_picture_unpadded_ptr(poc + SET_STRIDE * st, a.ctypes.data, a.strides[0], W, H)
 
     def submit(poc, st):
         # picture numbers of a set are offset by a constant: distances (all ME reads) are unchanged
@@ -391,7 +392,7 @@ def gpu_main(args):
     # roofline pass: one picture at a time, every launch bracketed by events on its stream
     eng.set_profiling(True)
     prof = {"k_search_ms": 0.0, "k_fullsearch_ms": 0.0, "k_fullsearch_main_ms": 0.0, "k_ctrl_ms": 0.0, "k_epilogue_ms": 0.0,
-            "total_ms": 0.0, "ops": 0, "ops_fs": 0}
+            "total_ms": 0.0, "ops": 0, "ops_fs": 0, "ops_fs_inline": 0}
     for rep in range(2):
         for k in prof:
             prof[k] = 0 if k.startswith("ops") else 0.0
@@ -405,6 +406,7 @@ def gpu_main(args):
                 prof[k] += getattr(t, k)
             prof["ops"] += t.byte_sad_ops
             prof["ops_fs"] += t.byte_sad_ops_fullsearch
+            prof["ops_fs_inline"] += t.byte_sad_ops_fullsearch_inline
     eng.set_profiling(False)
     sad_peak = 4.0 * eng.sad_peak()  # byte-SADs / s
 
@@ -431,13 +433,16 @@ def gpu_main(args):
     n_frames = 16 * args.steps * world
     value = n_frames / dt_res
     e2e = n_frames / dt_e2e
-    h2d = 16 * (W + 136) * (H + 136)
+    h2d = 16 * W * H  # the luma planes without their border: me_gpu_register_picture_unpadded pads on the device
     d2h = sum(sum(a.nbytes for a in outs[p].arrays.values()) for p in STEP_POCS)
 
-    ops_hme = prof["ops"] - prof["ops_fs"]
+    # byte-SADs where they are executed: the 8x8-variance probes and the integer searches of <= 256 positions run inside k_hme,
+    # only the tiled areas in k_fullsearch
+    ops_tiles = prof["ops_fs"] - prof["ops_fs_inline"]
+    ops_hme = prof["ops"] - ops_tiles
     kernels = {
         "k_hme": {"ms_per_step": prof["k_search_ms"], "byte_sads_per_step": ops_hme},
-        "k_fullsearch": {"ms_per_step": prof["k_fullsearch_ms"], "byte_sads_per_step": prof["ops_fs"]},
+        "k_fullsearch": {"ms_per_step": prof["k_fullsearch_ms"], "byte_sads_per_step": ops_tiles},
         "k_ctrl": {"ms_per_step": prof["k_ctrl_ms"]},
         "k_epilogue": {"ms_per_step": prof["k_epilogue_ms"]},
     }
@@ -449,17 +454,21 @@ def gpu_main(args):
         peaks = json.load(open(os.path.join(REPO, "MEASURED_PEAKS.json")))
     except Exception:
         pass
-    # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the one `ncu --set full` capture
-    # of this workload kept under profiles/ (ncu_r1_final_<kernel>_<workload>_details.txt)
-    ncu_traffic = {("1080p-m4", "motion", "k_hme"): 15215360 + 1792, ("1080p-m4", "iid", "k_fullsearch"): 13270528,
-                   ("4k-m0", "motion", "k_hme"): 63624960 + 7126784, ("4k-m0", "iid", "k_fullsearch"): 75603456 + 5817856}
-    ncu_key = (WORKLOAD, args.kind, dom)
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel: NOT measured by this run (it needs ncu);
+    # read from profiles/ncu_traffic.json, which names the capture and the commit each figure comes from
+    traffic, traffic_source = None, None
+    try:
+        e = json.load(open(os.path.join(REPO, "profiles", "ncu_traffic.json")))["entries"].get(f"{WORKLOAD}/{args.kind}/{dom}")
+        if e:
+            traffic, traffic_source = e["dram_bytes_per_launch"], f"profiles/{e['capture']} (commit {e['commit']})"
+    except Exception:
+        pass
     roofline = {
         "bound": "int_sad", "bound_note": "integer ALU (packed byte-SAD issue rate, SURVEY 8(d)): the path is neither HBM- nor "
         "tensor-bound; its HBM side is in traffic / hbm_gbs_achieved against hbm_peak_gbs", "kernel": dom, "achieved": achieved, "peak": sad_peak / 1e12, "unit": "Tbyte-SAD/s",
-        "frac": achieved / (sad_peak / 1e12) if sad_peak else None, "traffic": ncu_traffic.get(ncu_key),
+        "frac": achieved / (sad_peak / 1e12) if sad_peak else None, "traffic": traffic, "traffic_source": traffic_source,
         "traffic_unit": "DRAM bytes per launch (one picture); the three planes of a picture are 3.3 MB at 1080p, 12.4 MB at 4K",
-        "hbm_gbs_achieved": (ncu_traffic[ncu_key] * 16 / (dom_ms * 1e-3) / 1e9) if dom_ms > 0 and ncu_key in ncu_traffic else None,
+        "hbm_gbs_achieved": (traffic * 16 / (dom_ms * 1e-3) / 1e9) if dom_ms > 0 and traffic else None,
         "peak_source": "VABSDIFF4.U8.ACC issue rate measured live by k_sad_peak on this GPU x 4 bytes",
         "launches_per_step": 16,  # one k_hme, one k_fullsearch and one k_epilogue launch per picture
         "kernels": kernels, "serial_ms_per_step": prof["total_ms"],
@@ -486,14 +495,14 @@ def gpu_main(args):
         # engine is closed; they explain the path's integer-SAD roofline, the headline stays the workload above
         import subprocess
         extra = []
-        for wl, kind in (("1080p-m4", "iid"), ("4k-m0", "iid")):
-            cmd = [sys.executable, os.path.abspath(__file__), "--workload", wl, "--kind", kind, "--steps", "3", "--warmup", "3",
+        for wl, kind in (("1080p-m4", "iid"), ("4k-m2", "motion"), ("4k-m0", "iid")):
+            cmd = [sys.executable, os.path.abspath(__file__), "--workload", wl, "--kind", kind, "--steps", "10", "--warmup", "3",
                    "--no-cpu", "--no-extra"]
             try:
-                r = subprocess.run(cmd, capture_output=True, text=True, timeout=400)
+                r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
                 d = json.loads(r.stdout.strip().splitlines()[-1])
                 extra.append({"workload": wl, "sequence": kind, "value": d["value"], "e2e": d["e2e"]["value"], "unit": "frames/s",
-                              "steps": d["steps"], "warmup": d["warmup"], "clocks": d["clocks"],
+                              "steps": d["steps"], "warmup": d["warmup"], "clocks": d["clocks"], "parity": d["parity"],
                               "roofline": {k: d["roofline"][k] for k in ("kernel", "achieved", "peak", "unit", "frac", "kernels")}})
             except Exception as e:  # reported, never silent
                 extra.append({"workload": wl, "sequence": kind, "error": repr(e)[:200]})
@@ -523,7 +532,7 @@ def main():
     ap.add_argument("--kind", default="motion", choices=["motion", "iid"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-extra", dest="extra", action="store_false",
-                    help="skip the two short full-search-bound runs (1080p-m4 iid, 4k-m0 iid) appended as extra_workloads at N=1")
+                    help="skip the runs of the other configurations (1080p-m4 iid, 4k-m2 motion, 4k-m0 iid) appended as extra_workloads at N=1")
     ap.add_argument("--workload", default="1080p-m4", choices=sorted(WORKLOADS),
                     help="BASELINE.json config to run (default: configs[1], the one the metric is quoted on at N=1)")
     args = ap.parse_args()

@@ -241,7 +241,21 @@ int me_gpu_plane_geometry(int width, int height, int level, int *plane_w, int *p
 /* motion estimation ----------------------------------------------------------------------- */
 int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
                   const uint64_t ref_picture_numbers[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS]);
+/* Blocks until the oldest job in flight of the picture is complete, copies its results into *out and retires the job. ONE
+ * thread retires a job: a second me_gpu_wait on it while the first is blocked returns ME_GPU_ERR_STATE (threads that only
+ * need to know that the results have been delivered call me_gpu_wait_done). After a successful submit EVERY outcome of the
+ * wait retires the job - device errors included - except ME_GPU_ERR_BAD_ARG for a too small *out, which leaves it in
+ * flight (come back with a larger buffer, or me_gpu_cancel). */
 int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out);
+/* same, for exactly the job submitted with this me_type and first reference (ref_picture_numbers[0][0]): the open-loop ME
+ * of a picture and its temporal-filter pairs may be in flight together */
+int me_gpu_wait_pair(uint64_t picture_number, uint8_t me_type, uint64_t first_ref_picture_number, MeGpuOutputs *out);
+/* waits until the device is done with the picture's oldest job and retires it without delivering anything */
+int me_gpu_cancel(uint64_t picture_number);
+/* blocks until no job of the picture submitted before this call is in flight any more, i.e. until another thread's
+ * me_gpu_wait has the results (the segment threads of svt_aom_motion_estimation_kernel); ME_GPU_OK also when
+ * the job was retired already (one of the last 64) */
+int me_gpu_wait_done(uint64_t picture_number);
 /* Same as me_gpu_submit, with the destination of the results known up front: the device->host copies are queued
  * on the job's stream right behind the last kernel, so that me_gpu_wait(picture_number, out) only has to wait.
  * `out` (the struct and the arrays it points to) must stay valid and unchanged until that wait returns. */

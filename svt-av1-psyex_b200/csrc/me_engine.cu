@@ -15,6 +15,7 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <condition_variable>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -90,7 +91,11 @@ TfLayout tf_layout(size_t nb) {
 
 struct JobCtx {
     bool         busy = false;
+    bool         retiring = false; /* a waiter has taken this job and dropped the lock to wait for the device */
     uint64_t     picture_number = 0;
+    uint64_t     ticket = 0; /* submission order */
+    uint8_t      me_type = 0; /* (picture, me_type, first reference) identifies a job: a picture's open-loop ME and its */
+    uint64_t     ref00 = 0; /*  temporal-filter pairs can be in flight together */
     int          device = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t  ev[5] = {}; /* start, hme done, search done, end, (spare) */
@@ -144,15 +149,19 @@ struct Engine {
     std::mutex          dg_mu; /* one detector call at a time (they share the per-device accumulator) */
     MeGpuTimings        last{};
     std::mutex          mu;
+    std::condition_variable cv; /* a job was retired */
     bool                profiling = false;
-    bool                legacy = false; /* ME_GPU_LEGACY=1: one launch per stage instead of k_hme (debugging) */
-    std::string         err;
+    uint64_t            ticket = 0; /* submissions so far: orders the jobs of one picture */
+    uint64_t            done_ring[64] = {}; /* picture numbers of the last retired jobs (me_gpu_wait_done after the retirement) */
+    bool                done_valid[64] = {};
+    unsigned            done_next = 0;
 };
 
 Engine g;
+thread_local std::string t_err; /* every calling thread reads back its own last error */
 
 int fail(int code, const std::string &msg) {
-    g.err = msg;
+    t_err = msg;
     return code;
 }
 #define CU(x)                                                                                              \
@@ -201,10 +210,14 @@ int alloc_job(Device &d, JobCtx &jc, const MePicGeom &gm, int max_l0, int max_l1
     jc.tile_cap  = (uint32_t)(nb * ME_NREF * 128); /* >= max_tiles_per_b64 of every preset (832 at preset 0) */
     CU(cudaStreamCreateWithFlags(&jc.stream, cudaStreamNonBlocking));
     {
-        /* ME_GPU_SPLIT=1 (experiment): the tail of a picture (tiled full search, epilogue, result copies) on a stream of
-           higher priority than the k_hme launches of the pictures behind it, so that its CTAs get the SM resources that
-           free up first. Measured: within +-3 % on the 1080p workloads, -6 % end to end at 4K preset 2: off by default */
+        /* ME_GPU_DEBUG builds, ME_GPU_SPLIT=1 (experiment): the tail of a picture (tiled full search, epilogue, result copies)
+           on a stream of higher priority than the k_hme launches of the pictures behind it. Measured: within +-3 % on the
+           1080p workloads, -6 % end to end at 4K preset 2 */
+#ifdef ME_GPU_DEBUG
         static const int split = getenv("ME_GPU_SPLIT") ? atoi(getenv("ME_GPU_SPLIT")) : 0;
+#else
+        const int split = 0;
+#endif
         int lo = 0, hi = 0;
         CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
         if (split && hi < lo) {
@@ -343,7 +356,7 @@ int register_common(uint64_t picture_number, const uint8_t *src, int stride, int
 
 extern "C" {
 
-const char *me_gpu_last_error(void) { return g.err.c_str(); }
+const char *me_gpu_last_error(void) { return t_err.c_str(); }
 
 int me_gpu_device_count(void) {
     int n = 0;
@@ -374,6 +387,7 @@ void me_gpu_shutdown(void) {
     g.slots.clear();
     g.by_number.clear();
     g.initialised = false;
+    g.cv.notify_all();
 }
 
 int me_gpu_init(int device_count, const int *device_ids, int max_width, int max_height, int max_refs_l0, int max_refs_l1,
@@ -447,7 +461,6 @@ int me_gpu_init(int device_count, const int *device_ids, int max_width, int max_
             CU(cudaSetDevice(ids[i]));
             CU(cudaEventCreateWithFlags(&s.ready[i], cudaEventDisableTiming));
         }
-    g.legacy      = getenv("ME_GPU_LEGACY") && atoi(getenv("ME_GPU_LEGACY")) != 0;
     g.initialised = true;
     return ME_GPU_OK;
 }
@@ -482,18 +495,33 @@ int me_gpu_register_picture_unpadded(uint64_t picture_number, const uint8_t *y8b
 }
 
 int me_gpu_release_picture(uint64_t picture_number) {
-    std::lock_guard<std::mutex> lk(g.mu);
+    std::unique_lock<std::mutex> lk(g.mu);
     if (!g.initialised)
         return fail(ME_GPU_ERR_STATE, "not initialised");
     auto it = g.by_number.find(picture_number);
     if (it == g.by_number.end())
         return fail(ME_GPU_ERR_NOT_FOUND, "picture not registered");
     const int s = it->second;
-    /* uploads / peer copies into this slot must finish before the slot can be handed out again */
-    for (size_t i = 0; i < g.dev.size(); i++) {
-        cudaSetDevice(g.dev[i].id);
-        cudaEventSynchronize(g.slots[s].ready[i]);
+    /* uploads / peer copies into this slot must finish before the slot can be handed out again; the wait happens outside
+       the lock (other ME threads keep submitting and waiting meanwhile). The slot cannot change hands during it: it is
+       still registered, and registering the same number again fails until it is released. */
+    cudaEvent_t ev[8];
+    int         ids[8];
+    size_t      n = 0;
+    for (size_t i = 0; i < g.dev.size(); i++)
+        if (!g.slots[s].ready_seen[i]) {
+            ev[n]    = g.slots[s].ready[i];
+            ids[n++] = g.dev[i].id;
+        }
+    lk.unlock();
+    for (size_t i = 0; i < n; i++) {
+        cudaSetDevice(ids[i]);
+        cudaEventSynchronize(ev[i]);
     }
+    lk.lock();
+    it = g.by_number.find(picture_number);
+    if (!g.initialised || it == g.by_number.end() || it->second != s)
+        return fail(ME_GPU_ERR_NOT_FOUND, "picture released twice");
     g.slots[s].release_pending = true;
     free_slot_if_idle(s);
     return ME_GPU_OK;
@@ -632,8 +660,8 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
         return fail(ME_GPU_ERR_STATE, "too many pictures in flight: call me_gpu_wait first");
     for (auto &dv : g.dev)
         for (auto &c : dv.jobs)
-            if (c.busy && c.picture_number == picture_number)
-                return fail(ME_GPU_ERR_STATE, "picture already submitted");
+            if (c.busy && c.picture_number == picture_number && c.me_type == p.me_type && c.ref00 == ref_picture_numbers[0][0])
+                return fail(ME_GPU_ERR_STATE, "picture already submitted (same me_type and first reference)");
 
     MeJob &j = *jc->h_job;
     memset(jc->h_head, 0, sizeof(JobHead));
@@ -733,7 +761,7 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
             jc->npairs++;
         }
     };
-    if (!g.legacy) {
+    {
         /* the whole per-b64 chain in one launch; large search areas come back as tiles */
         const HmeMaps *maps = nullptr;
         for (auto &ms : d.mapsets)
@@ -761,67 +789,28 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
             CU(cudaStreamWaitEvent(jc->tail, jc->ev_mid, 0));
             st = jc->tail;
         }
+#ifdef ME_GPU_DEBUG
         static const int skip = getenv("ME_GPU_SKIP") ? atoi(getenv("ME_GPU_SKIP")) : 0; /* timing experiments only: results wrong */
+#else
+        const int skip = 0;
+#endif
         pbegin(3);
         if (!(skip & 1))
             me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, d.sms * FS_CTAS_PER_SM, st);
         pend();
-    } else {
-        const bool zz   = p.me_early_exit_th || p.me_safe_limit_zz_th;
-        const bool phme = p.prehme_enable != 0;
-        const bool l1ee = phme && p.prehme_l1_early_exit && p.num_of_list_to_search == 2;
-        const bool l0 = p.enable_hme_flag && p.enable_hme_level0_flag, l1 = p.enable_hme_flag && p.enable_hme_level1_flag,
-                   l2 = p.enable_hme_flag && p.enable_hme_level2_flag;
-        /* one launch per stage (debug path): ctrl launches run the stages between two search launches */
-        uint32_t mask = 1u << ST_INIT;
-        auto flush = [&](int slots) {
-            pbegin(0);
-            me_launch_ctrl(jc->d_job, 1, nbi, mask, jc->d_list, st);
-            pend();
-            pbegin(1);
-            me_launch_search(jc->d_job, 1, nbi, slots, d.pool, st);
-            pend();
-            mask = 0;
-        };
-        if (zz) flush(ME_NREF);
-        mask |= 1u << ST_PREHME0;
-        if (phme) flush(ME_NREF * 2);
-        if (l1ee) {
-            mask |= 1u << ST_PREHME1;
-            flush(ME_NREF * 2);
-        }
-        mask |= 1u << ST_HME_L0;
-        if (l0) flush(ME_NREF * 4);
-        mask |= 1u << ST_HME_L1;
-        if (l1) flush(ME_NREF * 4);
-        mask |= 1u << ST_HME_L2;
-        if (l2) flush(ME_NREF * 4);
-        mask |= 1u << ST_CENTRE;
-        flush(ME_NREF * 2);
-        if (prof) CU(cudaEventRecord(jc->ev[1], st));
-        const int fs_ctas = d.sms * FS_CTAS_PER_SM;
-        pbegin(0);
-        me_launch_ctrl(jc->d_job, 1, nbi, 1u << ST_PROBE, jc->d_list, st);
-        pend();
-        pbegin(2);
-        me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, fs_ctas, st);
-        pend();
-        CU(cudaMemsetAsync(jc->d_list, 0, 2 * sizeof(unsigned int), st)); /* count = next = 0 */
-        pbegin(0);
-        me_launch_ctrl(jc->d_job, 1, nbi, 1u << ST_MAIN, jc->d_list, st);
-        pend();
-        pbegin(3);
-        me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, fs_ctas, st);
-        pend();
     }
-    if (jc->tail != st) { /* legacy path: everything up to here ran on the job's first stream */
+    if (jc->tail != st) {
         CU(cudaEventRecord(jc->ev_mid, st));
         CU(cudaStreamWaitEvent(jc->tail, jc->ev_mid, 0));
         st = jc->tail;
     }
     if (prof) CU(cudaEventRecord(jc->ev[2], st));
     pbegin(4);
+#ifdef ME_GPU_DEBUG
     static const int skip_epi = getenv("ME_GPU_SKIP") ? atoi(getenv("ME_GPU_SKIP")) & 2 : 0; /* timing experiments only */
+#else
+    const int skip_epi = 0;
+#endif
     if (!skip_epi)
         me_launch_epilogue(jc->d_job, 1, nbi, st);
     pend();
@@ -835,7 +824,11 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
             return rc;
     }
     jc->busy           = true;
+    jc->retiring       = false;
     jc->picture_number = picture_number;
+    jc->me_type        = p.me_type;
+    jc->ref00          = ref_picture_numbers[0][0];
+    jc->ticket         = ++g.ticket;
     for (int s : jc->slots_used) g.slots[s].refcount++;
     g.submit_counter++;
     return ME_GPU_OK;
@@ -865,38 +858,72 @@ int me_gpu_output_layout(int width, int height, const MeGpuParams *params, size_
     return ME_GPU_OK;
 }
 
-int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out) {
+/* the oldest job in flight of a picture (any me_type / reference when !exact) */
+static JobCtx *find_job(uint64_t picture_number, bool exact, uint8_t me_type, uint64_t ref00, Device **dv) {
+    JobCtx *jc = nullptr;
+    for (auto &d : g.dev)
+        for (auto &c : d.jobs)
+            if (c.busy && c.picture_number == picture_number && (!exact || (c.me_type == me_type && c.ref00 == ref00)) &&
+                (!jc || c.ticket < jc->ticket)) {
+                jc  = &c;
+                *dv = &d;
+            }
+    return jc;
+}
+
+/* a job leaves the engine: on success and on EVERY failure after its submission succeeded */
+static void retire_locked(JobCtx *jc) {
+    jc->busy     = false;
+    jc->retiring = false;
+    for (int s : jc->slots_used) {
+        g.slots[s].refcount--;
+        free_slot_if_idle(s);
+    }
+    g.done_ring[g.done_next % 64]  = jc->picture_number;
+    g.done_valid[g.done_next % 64] = true;
+    g.done_next++;
+    g.cv.notify_all();
+}
+
+/* out == nullptr: cancel (wait for the device to be done with the job, deliver nothing) */
+static int wait_impl(uint64_t picture_number, bool exact, uint8_t me_type, uint64_t ref00, MeGpuOutputs *out) {
     std::unique_lock<std::mutex> lk(g.mu);
     if (!g.initialised)
         return fail(ME_GPU_ERR_STATE, "not initialised");
-    if (!out)
-        return fail(ME_GPU_ERR_BAD_ARG, "null outputs");
-    JobCtx *jc = nullptr;
     Device *dv = nullptr;
-    for (auto &d : g.dev)
-        for (auto &c : d.jobs)
-            if (c.busy && c.picture_number == picture_number) {
-                jc = &c;
-                dv = &d;
-            }
+    JobCtx *jc = find_job(picture_number, exact, me_type, ref00, &dv);
     if (!jc)
         return fail(ME_GPU_ERR_NOT_FOUND, "picture was not submitted");
+    if (jc->retiring)
+        return fail(ME_GPU_ERR_STATE, "another thread is already waiting for this job's results (me_gpu_wait_done blocks until it has them)");
     const MeJob   &j  = *jc->h_job;
     const size_t   nb = (size_t)j.g.b64_count;
-    if (out->b64_count < nb)
+    if (out && out->b64_count < nb) /* nothing has been touched: the caller may come back with a large enough buffer, or cancel */
         return fail(ME_GPU_ERR_BAD_ARG, "MeGpuOutputs.b64_count is smaller than the picture's b64 count");
-    CU(cudaSetDevice(dv->id));
-    if (!jc->d2h_enqueued) {
-        int rc = enqueue_d2h(jc, out);
-        if (rc)
-            return rc;
-    }
-    cudaEvent_t done = jc->ev[4];
+    jc->retiring = true; /* from here on this thread owns the job's retirement, whatever happens */
+    cudaError_t e = cudaSetDevice(dv->id);
+    int         rc = ME_GPU_OK;
+    if (e == cudaSuccess && out && !jc->d2h_enqueued)
+        rc = enqueue_d2h(jc, out);
+    cudaStream_t tail = jc->tail;
+    cudaEvent_t  done = jc->ev[4];
+    const bool   have_event = jc->d2h_enqueued;
     lk.unlock();
-    cudaError_t e = cudaEventSynchronize(done);
+    if (e == cudaSuccess) /* without result copies (cancel of a plain submit, or a failed enqueue): the stream itself */
+        e = have_event && rc == ME_GPU_OK ? cudaEventSynchronize(done) : cudaStreamSynchronize(tail);
     lk.lock();
-    if (e != cudaSuccess)
-        return fail(ME_GPU_ERR_CUDA, std::string("job failed: ") + cudaGetErrorString(e));
+    if (e != cudaSuccess || rc != ME_GPU_OK) {
+        retire_locked(jc);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            return fail(ME_GPU_ERR_CUDA, std::string("job failed: ") + cudaGetErrorString(e));
+        }
+        return rc;
+    }
+    if (!out) {
+        retire_locked(jc);
+        return ME_GPU_OK;
+    }
     const unsigned overflow = jc->h_tail->list.overflow;
     MeGpuTimings t{};
     cudaEventElapsedTime(&t.total_ms, jc->ev[0], jc->ev[4]);
@@ -909,9 +936,7 @@ int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out) {
         float ms = 0.f;
         cudaEventElapsedTime(&ms, jc->pev[2 * i], jc->pev[2 * i + 1]);
         switch (jc->pkind[i]) {
-        case 0: t.k_ctrl_ms += ms; break;
         case 1: t.k_search_ms += ms; break;
-        case 2: t.k_fullsearch_ms += ms; break;
         case 3: t.k_fullsearch_ms += ms; t.k_fullsearch_main_ms += ms; break;
         default: t.k_epilogue_ms += ms; break;
         }
@@ -927,14 +952,41 @@ int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out) {
         out->tf_tot_horz_blks = (uint32_t)jc->h_tail->ops[2];
         out->tf_tot_vert_blks = (uint32_t)jc->h_tail->ops[3];
     }
-    jc->busy          = false;
-    for (int s : jc->slots_used) {
-        g.slots[s].refcount--;
-        free_slot_if_idle(s);
-    }
+    retire_locked(jc);
     if (overflow)
         return fail(ME_GPU_ERR_UNSUPPORTED, overflow == 2 ? "a search window exceeds the staging buffer of k_hme"
                                                            : "full-search tile list overflowed");
+    return ME_GPU_OK;
+}
+
+int me_gpu_wait(uint64_t picture_number, MeGpuOutputs *out) {
+    if (!out)
+        return fail(ME_GPU_ERR_BAD_ARG, "null outputs");
+    return wait_impl(picture_number, false, 0, 0, out);
+}
+
+int me_gpu_wait_pair(uint64_t picture_number, uint8_t me_type, uint64_t first_ref_picture_number, MeGpuOutputs *out) {
+    if (!out)
+        return fail(ME_GPU_ERR_BAD_ARG, "null outputs");
+    return wait_impl(picture_number, true, me_type, first_ref_picture_number, out);
+}
+
+int me_gpu_cancel(uint64_t picture_number) { return wait_impl(picture_number, false, 0, 0, nullptr); }
+
+int me_gpu_wait_done(uint64_t picture_number) {
+    std::unique_lock<std::mutex> lk(g.mu);
+    if (!g.initialised)
+        return fail(ME_GPU_ERR_STATE, "not initialised");
+    Device *dv   = nullptr;
+    JobCtx *jc   = find_job(picture_number, false, 0, 0, &dv);
+    if (!jc) {
+        for (int i = 0; i < 64; i++)
+            if (g.done_valid[i] && g.done_ring[i] == picture_number)
+                return ME_GPU_OK;
+        return fail(ME_GPU_ERR_NOT_FOUND, "picture was not submitted (or was retired more than 64 jobs ago)");
+    }
+    const uint64_t ticket = jc->ticket;
+    g.cv.wait(lk, [&] { return !g.initialised || !jc->busy || jc->ticket != ticket; });
     return ME_GPU_OK;
 }
 

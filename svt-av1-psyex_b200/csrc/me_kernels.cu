@@ -4,10 +4,7 @@
  *   k_downsample_pad   svt_aom_downsample_2d_c + svt_aom_generate_padding   (pic_analysis_process.c:130-160,
  *                      pic_operators.c:397-443): one pass writes a whole padded plane of the pyramid
  *   k_pad_full         edge replication of the full-resolution plane (svt_aom_pad_input_pictures)
- *   k_ctrl             one thread per 64x64 block runs the integer control stages of me_ctrl.h and emits
- *                      search tasks / full-search tiles
- *   k_search           svt_sad_loop_kernel_c (C_DEFAULT/compute_sad_c.c:58-101) for every task of a stage:
- *                      zero-MV SADs, pre-HME, HME level 0/1/2, check_00_center SADs
+ *   (me_hme.cu: k_hme, the per-b64 chain up to the small integer searches; me_dg.cu: k_dg_hme)
  *   k_fullsearch       open_loop_me_fullpel_search_sblock (motion_estimation.c:781-817) with the 85 square
  *                      PU SADs per position (motion_estimation.c:210-425): persistent CTAs pull 64x32-position
  *                      tiles, stage the reference window into four byte-shifted shared-memory copies, keep 8
@@ -99,160 +96,6 @@ __global__ void __launch_bounds__(256) k_pad_full(uint8_t *pool, size_t slot_off
         out |= (uint32_t)row[ix] << (8 * i);
     }
     *(uint32_t *)(base + (size_t)py * pl.stride + px) = out;
-}
-
-/* ------------------------------------------------------------------------------------------------
- * control stages
- * ---------------------------------------------------------------------------------------------- */
-__global__ void __launch_bounds__(64) k_ctrl(MeJob *jobs, uint32_t stage_mask, FsTileList *list) {
-    MeJob    *j = &jobs[blockIdx.y];
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= j->g.b64_count)
-        return;
-    CtrlCtx c;
-    c.j     = j;
-    c.p     = &j->p;
-    c.s     = &j->state[b];
-    c.t     = &j->tasks[(size_t)b * ME_SLOTS];
-    c.r     = &j->results[(size_t)b * ME_SLOTS];
-    c.f     = &j->fs_tasks[(size_t)b * ME_NREF];
-    c.keys  = &j->keys[(size_t)b * ME_NREF * ME_NPU];
-    c.org_x = (b % j->g.b64_cols) * 64;
-    c.org_y = (b / j->g.b64_cols) * 64;
-    c.b64_w = (uint32_t)min(64, j->g.width - c.org_x);
-    c.b64_h = (uint32_t)min(64, j->g.height - c.org_y);
-    c.pic_w = j->g.width;
-    c.pic_h = j->g.height;
-    c.only = -1; /* one thread runs the whole stage */
-    c.lane = 0;
-    c.nlanes = 1;
-    if (stage_mask & (1u << ST_INIT))
-        mc_init_keys(c.keys, 0, 1);
-    for (int st = 0; st < ST_COUNT; st++)
-        if (stage_mask & (1u << st))
-            mc_run_stage(&c, st);
-    if (stage_mask & ((1u << ST_PROBE) | (1u << ST_MAIN))) {
-        /* cut every full-search task of this b64 into tiles and append them to the work list */
-        for (int k = 0; k < ME_NREF; k++) {
-            const FsTask f = c.f[k];
-            if (!f.valid)
-                continue;
-            fs_emit_tiles(f, list, (uint32_t)b * ME_NREF + (uint32_t)k, (uint16_t)blockIdx.y);
-        }
-    }
-}
-
-/* ------------------------------------------------------------------------------------------------
- * k_search: one CTA per svt_sad_loop_kernel task
- * ---------------------------------------------------------------------------------------------- */
-#define KS_THREADS 128
-#define KS_SMEM_WORDS (22 * 1024) /* 88 KB of dynamic shared memory */
-
-__global__ void __launch_bounds__(KS_THREADS) k_search(const MeJob *jobs, const uint8_t *pool) {
-    extern __shared__ uint32_t ks_smem[];
-    __shared__ unsigned long long ks_red[KS_THREADS / 32];
-    const MeJob     *j    = &jobs[blockIdx.z];
-    const uint32_t   b    = blockIdx.y;
-    const uint32_t   slot = blockIdx.x;
-    const SearchTask t    = j->tasks[(size_t)b * ME_SLOTS + slot];
-    if (!t.valid)
-        return;
-    const MePlaneGeom pl   = j->g.plane[t.level];
-    const uint8_t    *srcp = plane_ptr(pool, j->g, j->src_slot, t.level);
-    const uint8_t    *refp = plane_ptr(pool, j->g, t.ref_slot, t.level);
-    const int         tid  = threadIdx.x;
-    const int         nw   = (t.bw + 3) >> 2; /* words per block row */
-    const uint32_t    last_mask = (t.bw & 3) ? ((1u << (8 * (t.bw & 3))) - 1u) : 0xFFFFFFFFu;
-    const int         rows = t.rows, step = t.row_step;
-
-    /* source block -> shared memory words (bytes beyond the block width masked to 0) */
-    uint32_t *srcw = ks_smem;
-    for (int i = tid; i < rows * nw; i += KS_THREADS) {
-        const int      r = i / nw, cw = i % nw;
-        const uint8_t *g = srcp + (size_t)(pl.pad + t.sy + r * step) * pl.stride + pl.pad + t.sx + cw * 4;
-        uint32_t       v = 0;
-        for (int k = 0; k < 4; k++)
-            if (cw * 4 + k < t.bw)
-                v |= (uint32_t)g[k] << (8 * k);
-        srcw[i] = v;
-    }
-    uint32_t *win = ks_smem + ((rows * nw + 3) & ~3);
-
-    /* window geometry: search point (x, y) reads ref rows y + r*step, bytes [x, x + bw) */
-    const uint8_t *w00   = refp + (size_t)(pl.pad + t.ry) * pl.stride + pl.pad + t.rx; /* search point (0,0) */
-    const int      a     = (int)((uintptr_t)w00 & 3);
-    const int      pitch = ((a + t.sa_w - 1 + t.bw + 3) >> 2) + 1; /* words per window row (+1 for the funnel read) */
-    const bool     skip  = t.bw == 16 && t.rows <= 16 && t.skip_line;
-    const int      erows = skip ? (t.sa_h >> 1) : t.sa_h; /* search rows that are evaluated */
-    const int      span  = (rows - 1) * step; /* extra window rows below a search row */
-    const int      rows_avail = (KS_SMEM_WORDS - ((rows * nw + 3) & ~3)) / pitch;
-    int            band  = skip ? ((rows_avail - span - 1) / 2 + 1) : (rows_avail - span);
-    if (band < 1)
-        band = 1;
-
-    unsigned long long best = ((unsigned long long)ME_SAD_LOOP_INIT << 32) | 0xFFFFFFFFull;
-    for (int e0 = 0; e0 < erows; e0 += band) {
-        const int e1   = min(erows, e0 + band);
-        const int ymin = skip ? 2 * e0 + 1 : e0;
-        const int ymax = skip ? 2 * (e1 - 1) + 1 : e1 - 1;
-        const int wrows = ymax - ymin + span + 1;
-        __syncthreads();
-        /* stage the window with aligned 32-bit loads */
-        const uint32_t *g0 = (const uint32_t *)(w00 - a + (ptrdiff_t)ymin * pl.stride);
-        for (int i = tid; i < wrows * pitch; i += KS_THREADS) {
-            const int r = i / pitch, cw = i % pitch;
-            win[i]      = g0[(size_t)r * (pl.stride >> 2) + cw];
-        }
-        __syncthreads();
-        const int npos = (e1 - e0) * t.sa_w;
-        for (int p = tid; p < npos; p += KS_THREADS) {
-            const int ee = p / t.sa_w, x = p - ee * t.sa_w;
-            const int yl = skip ? 2 * ee : ee; /* row inside the band window */
-            const int o  = a + x;
-            const int sh = (o & 3) * 8;
-            const uint32_t *wp = win + yl * pitch + (o >> 2);
-            const uint32_t *sp = srcw;
-            uint32_t        sad = 0;
-            for (int r = 0; r < rows; r++) {
-                uint32_t prev = wp[0];
-                for (int cw = 0; cw < nw; cw++) {
-                    const uint32_t next = wp[cw + 1];
-                    uint32_t       v    = __funnelshift_r(prev, next, sh);
-                    prev                = next;
-                    if (cw == nw - 1)
-                        v &= last_mask;
-                    sad = vsad4(sp[cw], v, sad);
-                }
-                wp += pitch * step;
-                sp += nw;
-            }
-            const unsigned long long key = ((unsigned long long)sad << 32) | (uint32_t)((e0 + ee) * t.sa_w + x);
-            best                         = key < best ? key : best;
-        }
-    }
-    /* CTA minimum of (sad, scan index): the first minimum in scan order wins, as in the reference */
-    for (int off = 16; off; off >>= 1) {
-        const unsigned long long o = __shfl_xor_sync(0xffffffffu, best, off);
-        best                       = o < best ? o : best;
-    }
-    if ((tid & 31) == 0)
-        ks_red[tid >> 5] = best;
-    __syncthreads();
-    if (tid == 0) {
-        for (int i = 1; i < KS_THREADS / 32; i++) best = ks_red[i] < best ? ks_red[i] : best;
-        SearchResult r;
-        r.sad   = (uint32_t)(best >> 32);
-        r.found = r.sad < ME_SAD_LOOP_INIT;
-        r.x = r.y = 0;
-        r.pad_[0] = r.pad_[1] = r.pad_[2] = 0;
-        if (r.found) {
-            const uint32_t idx = (uint32_t)best;
-            const uint32_t ee  = idx / (uint32_t)t.sa_w;
-            r.x                = (int16_t)(idx - ee * (uint32_t)t.sa_w);
-            r.y                = (int16_t)(skip ? 2 * ee + 1 : ee);
-        }
-        j->results[(size_t)b * ME_SLOTS + slot] = r;
-    }
 }
 
 /* ------------------------------------------------------------------------------------------------
@@ -594,9 +437,6 @@ static unsigned long long g_launches = 0;
 unsigned long long me_launch_count(void) { return g_launches; }
 
 cudaError_t me_kernels_setup(void) {
-    cudaError_t e = cudaFuncSetAttribute(k_search, cudaFuncAttributeMaxDynamicSharedMemorySize, KS_SMEM_WORDS * 4);
-    if (e != cudaSuccess)
-        return e;
     return cudaFuncSetAttribute(k_fullsearch, cudaFuncAttributeMaxDynamicSharedMemorySize, FS_SMEM_BYTES);
 }
 
@@ -609,18 +449,6 @@ void me_launch_pad_full(uint8_t *pool, size_t slot_off, const MePlaneGeom *pl, c
 void me_launch_downsample(uint8_t *pool, size_t slot_off, const MePlaneGeom *src, const MePlaneGeom *dst, cudaStream_t st) {
     dim3 grid((dst->stride / 4 + 255) / 256, dst->rows);
     k_downsample_pad<<<grid, 256, 0, st>>>(pool, slot_off, *src, *dst);
-    g_launches++;
-}
-
-void me_launch_ctrl(MeJob *jobs, int njobs, int max_b64, uint32_t stage_mask, FsTileList *list, cudaStream_t st) {
-    dim3 grid((max_b64 + 63) / 64, njobs);
-    k_ctrl<<<grid, 64, 0, st>>>(jobs, stage_mask, list);
-    g_launches++;
-}
-
-void me_launch_search(const MeJob *jobs, int njobs, int max_b64, int slots, const uint8_t *pool, cudaStream_t st) {
-    dim3 grid(slots, max_b64, njobs);
-    k_search<<<grid, KS_THREADS, KS_SMEM_WORDS * 4, st>>>(jobs, pool);
     g_launches++;
 }
 

@@ -30,7 +30,7 @@ __host__ __device__ static inline int fs_choose_kx(int w) {
 }
 
 typedef struct FsTileList {
-    unsigned int count; /* tiles appended by k_ctrl */
+    unsigned int count; /* tiles appended by k_hme */
     unsigned int next; /* next tile to hand out (k_fullsearch) */
     unsigned int cap;
     unsigned int overflow;
@@ -67,8 +67,6 @@ unsigned long long me_launch_count(void);
 void   me_launch_pad_full(uint8_t *pool, size_t slot_off, const MePlaneGeom *pl, cudaStream_t st);
 void   me_launch_repitch(const uint8_t *src, int src_pitch, uint8_t *dst, int dst_pitch, int row_bytes, int rows, cudaStream_t st);
 void   me_launch_downsample(uint8_t *pool, size_t slot_off, const MePlaneGeom *src, const MePlaneGeom *dst, cudaStream_t st);
-void   me_launch_ctrl(MeJob *jobs, int njobs, int max_b64, uint32_t stage_mask, FsTileList *list, cudaStream_t st);
-void   me_launch_search(const MeJob *jobs, int njobs, int max_b64, int slots, const uint8_t *pool, cudaStream_t st);
 void   me_launch_fullsearch(MeJob *jobs, FsTileList *list, const uint8_t *pool, int ctas, cudaStream_t st);
 void   me_launch_epilogue(MeJob *jobs, int njobs, int max_b64, cudaStream_t st);
 double me_measure_sad_peak(cudaStream_t st);

@@ -260,8 +260,9 @@ int me_gpu_derive_params(const MeGpuEncoderConfig *c, MeGpuParams *p) {
         if (c->force_ref_l0 > 0) {
             n0 = (uint8_t)c->force_ref_l0;
             n1 = (uint8_t)DMAX(0, c->force_ref_l1);
-            l0 = DMAX(l0, n0);
-            l1 = DMAX(l1, n1);
+            /* a sequence configured with these counts sizes its ME result pool by them (pcs.c:91-96 from the mrp maxima) */
+            l0 = n0;
+            l1 = n1;
         }
         p->max_refs = (uint8_t)(l0 + l1);
         p->max_cand = (uint8_t)(l0 + l1 + l0 * l1 + (l0 - 1) + (l1 == 3 ? 1 : 0));

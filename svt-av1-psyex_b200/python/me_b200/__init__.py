@@ -4,5 +4,5 @@ abi      ctypes mirror of include/me_gpu.h
 planes   padded picture planes and result slabs
 synth    synthetic sequences and the random-access prediction structure
 engine   the product: thin wrapper over libme_gpu.so (CUDA); no CPU fallback
-checkers oracle / reference wrappers - imported ONLY by tests, smoke() and bench.py's CPU baseline legs
+(the wrappers of the CPU oracle and of the compiled reference are test infrastructure and live under tests/)
 """

@@ -1,4 +1,4 @@
-"""ctypes mirror of include/me_gpu.h and oracle/me_oracle.h.
+"""ctypes mirror of include/me_gpu.h (and of the plain picture descriptor the CPU checkers under tests/ take).
 
 Harness plumbing only: the product is libme_gpu.so (CUDA behind a C-ABI); Python is used by tests and
 bench.py to feed it host buffers. Field order must match the C headers exactly (checked by
@@ -151,8 +151,6 @@ RefNumbers = (u64 * MAX_REFS) * MAX_LISTS
 
 GPU_LIB = os.environ.get("ME_B200_TRACE_LIB") or os.path.join(PKG, "libme_gpu.so")  # tools/trace_hme.py points at the instrumented build
 HOST_LIB = os.path.join(PKG, "libme_host.so")
-ORACLE_LIB = os.path.join(REPO, "oracle", "libme_oracle.so")
-REF_LIB = os.path.join(REPO, "oracle", "_ref", "libme_ref.so")
 
 # every symbol include/me_gpu.h declares (tests/test_abi.py checks the .so exports all of them)
 GPU_SYMBOLS = [
@@ -160,6 +158,7 @@ GPU_SYMBOLS = [
     "me_gpu_register_picture_unpadded", "me_gpu_release_picture", "me_gpu_read_pyramid", "me_gpu_plane_geometry",
     "me_gpu_submit", "me_gpu_wait", "me_gpu_derive_params", "me_gpu_get_timings", "me_gpu_measure_sad_peak", "me_gpu_set_profiling", "me_gpu_submit_out", "me_gpu_output_layout",
     "me_gpu_dg_detector", "me_gpu_derive_params_tf",
+    "me_gpu_wait_pair", "me_gpu_cancel", "me_gpu_wait_done",
     "me_gpu_dg_detector_noalloc", "me_gpu_dg_detector_noalloc_setup", "me_gpu_dg_detector_noalloc_error",
 ]
 
@@ -178,6 +177,9 @@ def load_gpu_lib():
     lib.me_gpu_plane_geometry.argtypes = [C.c_int, C.c_int, C.c_int] + [C.POINTER(C.c_int)] * 5
     lib.me_gpu_submit.argtypes = [u64, C.POINTER(MeGpuParams), C.POINTER(RefNumbers)]
     lib.me_gpu_wait.argtypes = [u64, C.POINTER(MeGpuOutputs)]
+    lib.me_gpu_wait_pair.argtypes = [u64, u8, u64, C.POINTER(MeGpuOutputs)]
+    lib.me_gpu_cancel.argtypes = [u64]
+    lib.me_gpu_wait_done.argtypes = [u64]
     lib.me_gpu_submit_out.argtypes = [u64, C.POINTER(MeGpuParams), C.POINTER(RefNumbers), C.POINTER(MeGpuOutputs)]
     lib.me_gpu_output_layout.argtypes = [C.c_int, C.c_int, C.POINTER(MeGpuParams), C.POINTER(C.c_size_t * 11),
                                          C.POINTER(C.c_size_t)]

@@ -60,6 +60,9 @@ class Engine:
         self._check(self.lib.me_gpu_register_picture_unpadded(picture_number, a.ctypes.data, a.strides[0], a.shape[1],
                                                               a.shape[0]))
 
+    def register_picture_unpadded_ptr(self, picture_number, ptr, stride, width, height):
+        self._check(self.lib.me_gpu_register_picture_unpadded(picture_number, ptr, stride, width, height))
+
     def release_picture(self, picture_number):
         self._check(self.lib.me_gpu_release_picture(picture_number))
 

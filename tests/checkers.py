@@ -1,11 +1,15 @@
 """CPU checkers: the plain-C restatement (oracle/libme_oracle.so) and the reference's own sources
-(oracle/_ref/libme_ref.so). TEST INFRASTRUCTURE: only tests/, __graft_entry__.smoke() and bench.py's
-cpu_baseline / --impl reference legs import this module. The product (engine.py) never does."""
+(oracle/_ref/libme_ref.so). TEST INFRASTRUCTURE, kept outside the product package: only tests/,
+__graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this module."""
 import ctypes as C
 import os
 
-from . import abi
-from .planes import Outputs, Picture
+from me_b200 import abi
+from me_b200.planes import Outputs, Picture
+
+REPO = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+ORACLE_LIB = os.path.join(REPO, "oracle", "libme_oracle.so")
+REF_LIB = os.path.join(REPO, "oracle", "_ref", "libme_ref.so")
 
 
 def _refs_array(refs):
@@ -21,9 +25,9 @@ def _refs_array(refs):
 
 class Oracle:
     def __init__(self):
-        if not os.path.exists(abi.ORACLE_LIB):
-            raise RuntimeError(f"{abi.ORACLE_LIB} missing: run make -C oracle")
-        self.lib = C.CDLL(abi.ORACLE_LIB)
+        if not os.path.exists(ORACLE_LIB):
+            raise RuntimeError(f"{ORACLE_LIB} missing: run make -C oracle")
+        self.lib = C.CDLL(ORACLE_LIB)
         self.lib.oracle_me_b64_range.argtypes = [C.POINTER(abi.OraclePicture), C.POINTER(abi.RefArray),
                                                  C.POINTER(abi.MeGpuParams), C.POINTER(abi.MeGpuOutputs),
                                                  abi.u32, abi.u32, C.POINTER(abi.u64)]
@@ -63,9 +67,9 @@ class Reference:
     """The reference's own C (simd=0) or AVX2 / AVX-512 (simd=1/2) ME, via oracle/ref_harness.c."""
 
     def __init__(self):
-        if not os.path.exists(abi.REF_LIB):
-            raise RuntimeError(f"{abi.REF_LIB} missing: run make -C oracle (needs /root/reference)")
-        self.lib = C.CDLL(abi.REF_LIB)
+        if not os.path.exists(REF_LIB):
+            raise RuntimeError(f"{REF_LIB} missing: run make -C oracle (needs /root/reference)")
+        self.lib = C.CDLL(REF_LIB)
         self.lib.ref_me_b64_range.argtypes = [C.POINTER(abi.OraclePicture), C.POINTER(abi.RefArray),
                                               C.POINTER(abi.MeGpuParams), C.POINTER(abi.MeGpuOutputs), abi.u32,
                                               abi.u32, C.c_int]
@@ -88,7 +92,7 @@ class Reference:
 
     @staticmethod
     def available():
-        return os.path.exists(abi.REF_LIB)
+        return os.path.exists(REF_LIB)
 
     def build_pyramid(self, pic: Picture):
         s = pic.c_struct()

@@ -20,16 +20,17 @@ def _make(path, target=None):
 
 @pytest.fixture(scope="session", autouse=True)
 def built_libs():
-    """CPU-side checkers and the host library; the CUDA library is only (re)built when missing."""
+    """CPU-side checkers, the host library and - where nvcc exists - the CUDA library: `make` every time (incremental), so
+    that the tests never run against a library older than the sources. A box without the toolchain or without
+    /root/reference (the GPU box for oracle/_ref) uses the prebuilt files that travelled with the snapshot."""
     pkg = os.path.join(REPO, "svt-av1-psyex_b200")
-    if not os.path.exists(os.path.join(REPO, "oracle", "libme_oracle.so")):
+    have_cc = any(os.access(os.path.join(d, "gcc"), os.X_OK) for d in os.environ.get("PATH", "").split(os.pathsep))
+    if have_cc:
         _make(os.path.join(REPO, "oracle"), "libme_oracle.so")
-    if os.path.isdir("/root/reference/Source") and not os.path.exists(os.path.join(REPO, "oracle", "_ref", "libme_ref.so")):
-        _make(os.path.join(REPO, "oracle"))
-    if not os.path.exists(os.path.join(pkg, "libme_host.so")):
+        if os.path.isdir("/root/reference/Source"):
+            _make(os.path.join(REPO, "oracle"))
         _make(pkg, "libme_host.so")
-    if not os.path.exists(os.path.join(REPO, "tests", "emul", "libme_emul.so")):
         _make(os.path.join(REPO, "tests", "emul"))
-    if not os.path.exists(os.path.join(pkg, "libme_gpu.so")) and os.path.exists("/usr/local/cuda/bin/nvcc"):
-        _make(pkg, "libme_gpu.so")
+        if os.path.exists("/usr/local/cuda/bin/nvcc"):
+            _make(pkg, "libme_gpu.so")
     yield

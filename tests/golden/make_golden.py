@@ -21,7 +21,7 @@ sys.path.insert(0, os.path.join(HERE, ".."))
 from helpers import DG_CASES, TF_CASES, DgPictures, PictureSet, derive, derive_tf, host_lib  # noqa: E402
 from me_b200 import planes  # noqa: E402
 from me_b200 import abi  # noqa: E402
-from me_b200.checkers import Reference  # noqa: E402
+from checkers import Reference  # noqa: E402
 
 ME_CASES = [  # (width, height, preset, poc, kind)
     (320, 192, 8, 8, "motion"), (320, 192, 8, 1, "iid"), (320, 192, 4, 4, "motion"), (320, 192, 4, 7, "iid"),

@@ -24,7 +24,7 @@ sys.path.insert(0, os.path.join(HERE, ".."))
 import workloads  # noqa: E402
 from helpers import PictureSet  # noqa: E402
 from me_b200 import planes  # noqa: E402
-from me_b200.checkers import Oracle, Reference  # noqa: E402
+from checkers import Oracle, Reference  # noqa: E402
 
 SAMPLE_B64 = 30
 

@@ -69,7 +69,7 @@ class Emulator:
                                              C.POINTER(abi.u64)]
 
     def me_picture(self, src, refs, params):
-        from me_b200 import checkers
+        import checkers
         out = planes.Outputs(src.width, src.height, params)
         arr, keep = checkers._refs_array(refs)
         s = src.c_struct()

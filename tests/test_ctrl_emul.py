@@ -5,7 +5,7 @@ import pytest
 
 from helpers import TF_CASES, Emulator, PictureSet, derive, derive_tf, used_refs
 from me_b200 import planes
-from me_b200.checkers import Oracle
+from checkers import Oracle
 
 CASES = [(preset, poc, kind) for preset in (8, 4, 2, 6, 10, 5) for poc in (16, 8, 4, 1, 7) for kind in ("motion", "iid")]
 

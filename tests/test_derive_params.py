@@ -9,7 +9,7 @@ import pytest
 
 from helpers import host_lib
 from me_b200 import abi
-from me_b200.checkers import Reference
+from checkers import Reference
 
 SKIP = {"max_cand", "max_refs", "max_l0", "num_of_list_to_search", "num_of_ref_pic_to_search", "only_l_bwd"}
 GOLD = os.path.join(os.path.dirname(__file__), "golden", "derive_params.json")

@@ -11,7 +11,7 @@ pytestmark = pytest.mark.gpu
 
 @pytest.fixture(scope="module")
 def oracle():
-    from me_b200.checkers import Oracle
+    from checkers import Oracle
     return Oracle()
 
 
@@ -307,3 +307,69 @@ def test_tf_me_rejects_bad_reference_counts(engine, oracle):
             engine.submit(4, p, [[5], []])
     finally:
         _release(engine, [4, 5])
+
+
+def test_wait_protocol_with_several_threads(engine, oracle):
+    """SURVEY 8(b) threading: every segment thread of a picture blocks on the same job. One thread retires it
+    (me_gpu_wait), the others block in me_gpu_wait_done until the results have been delivered; a second me_gpu_wait while
+    the first is blocked is refused with a defined code; me_gpu_cancel retires a job nobody wants; a too small output
+    buffer leaves the job in flight; the temporal-filter pair of a picture can be in flight beside its open-loop ME."""
+    import threading
+    from helpers import derive_tf
+    from me_b200.engine import MeGpuError
+    w, h, n, preset, poc = 320, 192, 17, 4, 8
+    ps = PictureSet(w, h, n, "motion", oracle)
+    cfg, p, l0, l1 = derive(preset, w, h, poc, n)
+    pocs = sorted(set([poc] + l0 + l1))
+    _register(engine, ps, pocs)
+    lib = engine.lib
+    try:
+        exp = oracle.me_picture(ps.get(poc), [[ps.get(k) for k in l0], [ps.get(k) for k in l1]], p)
+        for rep in range(4):
+            engine.submit(poc, p, [l0, l1])
+            got = planes.Outputs(w, h, p)
+            rcs, order = [], []
+            gate = threading.Barrier(6)
+
+            def seg(i):
+                gate.wait()
+                if i == 0:
+                    rcs.append(("wait", lib.me_gpu_wait(poc, got.c)))
+                    order.append("retired")
+                else:
+                    rc = lib.me_gpu_wait_done(poc)
+                    order.append("done")
+                    rcs.append(("done", rc))
+
+            ts = [threading.Thread(target=seg, args=(i,)) for i in range(6)]
+            for t in ts:
+                t.start()
+            for t in ts:
+                t.join()
+            assert all(rc == 0 for _, rc in rcs), rcs
+            bad = planes.compare_outputs(exp, got, used_refs=used_refs(l0, l1))
+            assert not bad, (rep, bad)
+            assert lib.me_gpu_wait_done(poc) == 0  # already retired: still a defined answer
+        assert lib.me_gpu_wait_done(987654) == -3  # ME_GPU_ERR_NOT_FOUND
+        # too small a buffer: refused, the job stays; cancel retires it and frees its picture references
+        engine.submit(poc, p, [l0, l1])
+        small = planes.Outputs(w, h, p)
+        small.c.b64_count = 1
+        assert lib.me_gpu_wait(poc, small.c) == -2
+        assert lib.me_gpu_cancel(poc) == 0
+        assert lib.me_gpu_cancel(poc) == -3
+        # open-loop ME and a temporal-filter pair of the same picture in flight together, waited for by identity
+        _, ptf = derive_tf(1, w, h, poc, me_exit_th=400)
+        engine.submit(poc, p, [l0, l1])
+        engine.submit(poc, ptf, [[l0[0]], []])
+        with pytest.raises(MeGpuError):
+            engine.submit(poc, ptf, [[l0[0]], []])  # the same job twice
+        tf = planes.Outputs(w, h, ptf)
+        assert lib.me_gpu_wait_pair(poc, ptf.me_type, l0[0], tf.c) == 0
+        got = planes.Outputs(w, h, p)
+        engine.wait(poc, got)
+        assert not planes.compare_outputs(exp, got, used_refs=used_refs(l0, l1))
+        exp_tf = oracle.me_picture(ps.get(poc), [[ps.get(l0[0])], []], ptf)
+        assert not planes.compare_outputs(exp_tf, tf, fields=planes.TF_FIELDS)
+    finally:
+        _release(engine, pocs)

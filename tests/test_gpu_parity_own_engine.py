@@ -11,7 +11,7 @@ pytestmark = pytest.mark.gpu
 
 @pytest.fixture(scope="module")
 def oracle():
-    from me_b200.checkers import Oracle
+    from checkers import Oracle
     return Oracle()
 
 
@@ -90,7 +90,7 @@ def test_reference_side_hook_fills_the_pcs_like_the_cpu_loop(w, h, preset, poc, 
     every b64 and the eight per-b64 pcs arrays equal, byte for byte, what the reference's own
     svt_aom_motion_estimation_b64 loop leaves in an identical pcs."""
     from me_b200 import abi
-    from me_b200.checkers import Reference
+    from checkers import Reference
     if not Reference.available():
         pytest.skip("oracle/_ref/libme_ref.so is built where /root/reference exists and travels prebuilt")
     ref = Reference()
@@ -112,7 +112,7 @@ def test_reference_side_hook_temporal_filter_and_dg_detector():
     (dg_detector->metrics), against the reference's own code on the same inputs."""
     from helpers import DgPictures, derive_tf
     from me_b200 import abi
-    from me_b200.checkers import Reference
+    from checkers import Reference
     if not Reference.available():
         pytest.skip("oracle/_ref/libme_ref.so is built where /root/reference exists and travels prebuilt")
     ref = Reference()

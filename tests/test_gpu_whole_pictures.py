@@ -21,12 +21,12 @@ pytestmark = pytest.mark.gpu
 
 @pytest.fixture(scope="module")
 def oracle():
-    from me_b200.checkers import Oracle
+    from checkers import Oracle
     return Oracle()
 
 
 def _reference():
-    from me_b200.checkers import Reference
+    from checkers import Reference
     return Reference() if Reference.available() else None
 
 

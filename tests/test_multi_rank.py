@@ -11,7 +11,7 @@ import torch.multiprocessing as mp
 
 from helpers import Emulator, PictureSet, derive
 from me_b200 import shard, synth
-from me_b200.checkers import Oracle
+from checkers import Oracle
 
 W, H, N, PRESET = 136, 72, 33, 8
 POCS = [32 if g == 0 else 16 + g for g in synth.RA5_DECODE_ORDER]

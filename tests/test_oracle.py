@@ -13,7 +13,7 @@ import json
 
 from helpers import DG_CASES, TF_CASES, DgPictures, PictureSet, derive, derive_tf, used_refs
 from me_b200 import abi, planes
-from me_b200.checkers import Oracle, Reference
+from checkers import Oracle, Reference
 
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
 have_ref = pytest.mark.skipif(not Reference.available(), reason="oracle/_ref not built (needs /root/reference)")

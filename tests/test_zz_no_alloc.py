@@ -27,7 +27,7 @@ def _noalloc(lib, src, ref, w, h, res):
 
 
 def test_noalloc_entry_point_equals_the_existing_one():
-    from me_b200.checkers import Oracle
+    from checkers import Oracle
     from me_b200.engine import Engine
     oracle = Oracle()
     lib = abi.load_gpu_lib()

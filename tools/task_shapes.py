@@ -13,7 +13,7 @@ from me_b200 import synth  # noqa: E402
 
 poc = int(sys.argv[1]) if len(sys.argv) > 1 else 24
 kind = sys.argv[2] if len(sys.argv) > 2 else "motion"
-from me_b200 import checkers  # noqa: E402
+import checkers  # noqa: E402
 
 _, p, l0, l1 = bench.derive(poc)
 ps = helpers.PictureSet(bench.W, bench.H, bench.NPIC, kind, checkers.Oracle())

@@ -20,7 +20,8 @@ sys.path.insert(0, os.path.join(REPO, "tests"))
 import bench  # noqa: E402  (sets sys.path for me_b200)
 import torch  # noqa: E402
 from helpers import derive_tf  # noqa: E402
-from me_b200 import checkers, planes, synth  # noqa: E402
+import checkers  # noqa: E402
+from me_b200 import planes, synth  # noqa: E402
 from me_b200.engine import Engine  # noqa: E402
 
 W, H, NPIC = bench.W, bench.H, 16
