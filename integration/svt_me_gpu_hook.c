@@ -4,18 +4,26 @@
 #include "svt_me_gpu_hook.h"
 
 #include <dlfcn.h>
+#include <pthread.h>
 #include <stdlib.h>
 #include <string.h>
+
+#include "reference_object.h"
 
 int (*svt_me_picture_register)(uint64_t, const uint8_t *, int, int, int, int, int)                                   = NULL;
 int (*svt_me_picture_submit)(uint64_t, const MeGpuParams *, const uint64_t[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS])        = NULL;
 int (*svt_me_picture_wait)(uint64_t, MeGpuOutputs *)                                                                 = NULL;
 int (*svt_me_picture_release)(uint64_t)                                                                              = NULL;
+static int (*hook_cancel)(uint64_t) = NULL;
+static const char *(*hook_last_error)(void) = NULL;
 static void (*hook_shutdown)(void) = NULL;
 static int (*hook_dg)(uint64_t, uint64_t, uint8_t, MeGpuDgMetrics *) = NULL;
 static void *hook_lib              = NULL;
 
+#include <stdio.h>
 static EbErrorType map_error(int rc) {
+    if (rc != ME_GPU_OK) /* the engine's own words, once, where the failure happens: the caller only sees an EbErrorType */
+        fprintf(stderr, "svt_me_gpu_hook: engine error %d: %s\n", rc, hook_last_error ? hook_last_error() : "?");
     return rc == ME_GPU_OK ? EB_ErrorNone : rc == ME_GPU_ERR_NO_MEMORY ? EB_ErrorInsufficientResources : EB_ErrorUndefined;
 }
 
@@ -34,6 +42,8 @@ EbErrorType svt_me_gpu_hook_init(const char *library_path, int max_width, int ma
     svt_me_picture_submit   = (int (*)(uint64_t, const MeGpuParams *, const uint64_t[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS]))dlsym(h, "me_gpu_submit");
     svt_me_picture_wait     = (int (*)(uint64_t, MeGpuOutputs *))dlsym(h, "me_gpu_wait");
     svt_me_picture_release  = (int (*)(uint64_t))dlsym(h, "me_gpu_release_picture");
+    hook_cancel             = (int (*)(uint64_t))dlsym(h, "me_gpu_cancel");
+    hook_last_error         = (const char *(*)(void))dlsym(h, "me_gpu_last_error");
     hook_shutdown           = (void (*)(void))dlsym(h, "me_gpu_shutdown");
     hook_dg                 = (int (*)(uint64_t, uint64_t, uint8_t, MeGpuDgMetrics *))dlsym(h, "me_gpu_dg_detector");
     hook_lib                = h;
@@ -52,6 +62,7 @@ void svt_me_gpu_hook_shutdown(void) {
     svt_me_picture_wait     = NULL;
     svt_me_picture_release  = NULL;
     hook_shutdown           = NULL;
+    hook_cancel             = NULL;
     hook_dg                 = NULL;
     if (hook_lib)
         dlclose(hook_lib);
@@ -147,16 +158,21 @@ EbErrorType svt_me_gpu_release_picture(uint64_t picture_number) {
     return svt_me_picture_release ? map_error(svt_me_picture_release(picture_number)) : EB_ErrorUndefined;
 }
 
-EbErrorType svt_me_gpu_picture(PictureParentControlSet *pcs, const MeContext *me_ctx) {
+/* src_id / ref_ids: the numbers the pictures were registered under (their picture numbers, possibly tagged: see
+ * svt_me_gpu_segment); NULL ref_ids = the plain picture numbers of me_ctx->me_ds_ref_array */
+static EbErrorType hook_picture(PictureParentControlSet *pcs, const MeContext *me_ctx, uint64_t src_id,
+                                const uint64_t ref_ids[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS]) {
     if (!svt_me_picture_submit || !svt_me_picture_wait)
         return EB_ErrorUndefined;
     MeGpuParams gp;
     uint64_t    refs[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS] = {{0}};
     svt_me_gpu_params_from_ctx(&gp, pcs, me_ctx);
+    gp.picture_number = src_id; /* ME only reads differences of picture numbers, truncated to 16 bits (motion_estimation.c:1232) */
     for (int l = 0; l < me_ctx->num_of_list_to_search; l++)
         for (int r = 0; r < me_ctx->num_of_ref_pic_to_search[l]; r++)
-            refs[l][r] = me_ctx->me_ds_ref_array[l][r].picture_number; /* me_process.c:248-262 */
-    const int rc = svt_me_picture_submit(pcs->picture_number, &gp, refs);
+            refs[l][r] = ref_ids ? ref_ids[l][r] : me_ctx->me_ds_ref_array[l][r].picture_number; /* me_process.c:248-262 */
+    const uint64_t job = src_id;
+    const int rc = svt_me_picture_submit(job, &gp, refs);
     if (rc != ME_GPU_OK)
         return map_error(rc);
 
@@ -170,9 +186,8 @@ EbErrorType svt_me_gpu_picture(PictureParentControlSet *pcs, const MeContext *me
     const size_t n_idx = (size_t)nb * P, n_cand = n_idx * gp.max_cand, n_mv = n_idx * gp.max_refs;
     uint8_t     *slab  = (uint8_t *)malloc(n_idx + n_cand + n_mv * sizeof(uint32_t) + 16);
     if (!slab) {
-        MeGpuOutputs none;
-        memset(&none, 0, sizeof none);
-        svt_me_picture_wait(pcs->picture_number, &none); /* retire the job */
+        if (hook_cancel)
+            hook_cancel(job); /* retire the job: nothing is delivered */
         return EB_ErrorInsufficientResources;
     }
     MeGpuOutputs out;
@@ -189,7 +204,7 @@ EbErrorType svt_me_gpu_picture(PictureParentControlSet *pcs, const MeContext *me
     out.rc_me_distortion            = pcs->rc_me_distortion;
     out.stationary_block_present_sb = pcs->stationary_block_present_sb;
     out.rc_me_allow_gm              = pcs->rc_me_allow_gm;
-    const int rw = svt_me_picture_wait(pcs->picture_number, &out);
+    const int rw = svt_me_picture_wait(job, &out);
     if (rw == ME_GPU_OK && out.pu_count == P)
         for (uint32_t b = 0; b < nb; b++) {
             MeSbResults *res = pcs->pa_me_data->me_results[b];
@@ -199,6 +214,127 @@ EbErrorType svt_me_gpu_picture(PictureParentControlSet *pcs, const MeContext *me
         }
     free(slab);
     return rw != ME_GPU_OK ? map_error(rw) : out.pu_count == P ? EB_ErrorNone : EB_ErrorUndefined;
+}
+
+EbErrorType svt_me_gpu_picture(PictureParentControlSet *pcs, const MeContext *me_ctx) {
+    return hook_picture(pcs, me_ctx, pcs->picture_number, NULL);
+}
+
+/* ---- per-picture once-logic and lazy registration ------------------------------------------------------------- */
+#define HOOK_MAX_REGS 512 /* PA reference objects alive at once (pa_reference_picture_buffer_init_count is < 100) */
+#define HOOK_MAX_PICS 128 /* pictures whose segment items are in flight */
+typedef struct HookReg {
+    const void *obj; /* EbPaReferenceObject the pyramid was uploaded from */
+    uint64_t    number; /* its picture number at the time */
+    uint64_t    id; /* what the engine knows it as: (registration count << 32) | low 32 bits of the picture number. An alt-ref
+                       picture and its overlay share a picture number but not their pixels: identities must not collide, and
+                       ME only ever reads 16-bit differences of the numbers */
+    int         used;
+} HookReg;
+typedef struct HookPic {
+    const void *pcs; /* the picture's control set: an alt-ref and its overlay are two pictures with one number */
+    uint64_t    number;
+    uint64_t    src_id, ref_ids[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS];
+    int         used, done;
+    uint32_t    arrivals;
+    EbErrorType rc;
+} HookPic;
+static HookReg         hook_regs[HOOK_MAX_REGS];
+static HookPic         hook_pics[HOOK_MAX_PICS];
+static pthread_mutex_t hook_mu = PTHREAD_MUTEX_INITIALIZER;
+static pthread_cond_t  hook_cv = PTHREAD_COND_INITIALIZER;
+static uint64_t        hook_n_reg, hook_n_rel, hook_n_pic;
+
+int svt_me_gpu_live(void) { return svt_me_picture_submit != NULL; }
+
+void svt_me_gpu_stats(uint64_t *registered, uint64_t *released, uint64_t *pictures) {
+    pthread_mutex_lock(&hook_mu);
+    if (registered) *registered = hook_n_reg;
+    if (released) *released = hook_n_rel;
+    if (pictures) *pictures = hook_n_pic;
+    pthread_mutex_unlock(&hook_mu);
+}
+
+/* hook_mu held. The device holds the pyramid of `obj`'s current picture after this; *id = its engine identity. */
+static EbErrorType hook_ensure_registered(const PictureParentControlSet *pcs, const EbPaReferenceObject *obj, uint64_t *id) {
+    HookReg *slot = NULL, *free_slot = NULL;
+    for (int i = 0; i < HOOK_MAX_REGS; i++) {
+        if (hook_regs[i].used && hook_regs[i].obj == (const void *)obj)
+            slot = &hook_regs[i];
+        else if (!hook_regs[i].used && !free_slot)
+            free_slot = &hook_regs[i];
+    }
+    if (slot && slot->number == obj->picture_number) {
+        *id = slot->id;
+        return EB_ErrorNone;
+    }
+    if (slot) { /* the pool handed the object to a new picture: the old one is done with (reference_object.c:406) */
+        svt_me_picture_release(slot->id);
+        hook_n_rel++;
+        slot->used = 0;
+        if (!free_slot)
+            free_slot = slot;
+    }
+    if (!free_slot)
+        return EB_ErrorInsufficientResources;
+    const EbPictureBufferDesc *d  = (const EbPictureBufferDesc *)obj->input_padded_pic;
+    const uint64_t             nid = ((hook_n_reg + 1) << 32) | (obj->picture_number & 0xFFFFFFFFull);
+    const int rc = svt_me_picture_register(nid, d->buffer_y, d->stride_y, d->org_x, d->org_y, pcs->aligned_width, pcs->aligned_height);
+    if (rc != ME_GPU_OK)
+        return map_error(rc);
+    free_slot->obj    = obj;
+    free_slot->number = obj->picture_number;
+    free_slot->id     = nid;
+    free_slot->used   = 1;
+    hook_n_reg++;
+    *id = nid;
+    return EB_ErrorNone;
+}
+
+EbErrorType svt_me_gpu_segment(PictureParentControlSet *pcs, MeContext *me_ctx) {
+    if (!svt_me_gpu_live())
+        return EB_ErrorUndefined;
+    HookPic *e = NULL;
+    int      leader = 0;
+    pthread_mutex_lock(&hook_mu);
+    for (int i = 0; i < HOOK_MAX_PICS; i++)
+        if (hook_pics[i].used && hook_pics[i].pcs == (const void *)pcs && hook_pics[i].number == pcs->picture_number)
+            e = &hook_pics[i];
+    if (!e) {
+        for (int i = 0; i < HOOK_MAX_PICS && !e; i++)
+            if (!hook_pics[i].used)
+                e = &hook_pics[i];
+        if (!e) {
+            pthread_mutex_unlock(&hook_mu);
+            return EB_ErrorInsufficientResources;
+        }
+        e->used = 1; e->done = 0; e->arrivals = 0; e->rc = EB_ErrorNone; e->number = pcs->picture_number; e->pcs = pcs;
+        leader  = 1;
+        hook_n_pic++;
+        /* the pyramids this picture reads: its own and its references' (me_process.c:248-262) */
+        EbErrorType rc = hook_ensure_registered(pcs, (const EbPaReferenceObject *)pcs->pa_ref_pic_wrapper->object_ptr, &e->src_id);
+        for (int l = 0; rc == EB_ErrorNone && l < me_ctx->num_of_list_to_search; l++)
+            for (int r = 0; rc == EB_ErrorNone && r < me_ctx->num_of_ref_pic_to_search[l]; r++)
+                rc = hook_ensure_registered(pcs, (const EbPaReferenceObject *)pcs->ref_pa_pic_ptr_array[l][r]->object_ptr,
+                                            &e->ref_ids[l][r]);
+        e->rc = rc;
+    }
+    pthread_mutex_unlock(&hook_mu);
+    if (leader) {
+        EbErrorType rc = e->rc == EB_ErrorNone ? hook_picture(pcs, me_ctx, e->src_id, e->ref_ids) : e->rc;
+        pthread_mutex_lock(&hook_mu);
+        e->rc   = rc;
+        e->done = 1;
+        pthread_cond_broadcast(&hook_cv);
+    } else {
+        pthread_mutex_lock(&hook_mu);
+        while (!e->done) pthread_cond_wait(&hook_cv, &hook_mu);
+    }
+    const EbErrorType rc = e->rc;
+    if (++e->arrivals == pcs->me_segments_total_count)
+        e->used = 0; /* TASK_SUPERRES_RE_ME of the same picture later starts a fresh entry */
+    pthread_mutex_unlock(&hook_mu);
+    return rc;
 }
 
 EbErrorType svt_me_gpu_tf_pair(const PictureParentControlSet *centre_pcs, MeContext *me_ctx, uint64_t neighbour_picture_number,

@@ -49,6 +49,22 @@ EbErrorType svt_me_gpu_release_picture(uint64_t picture_number);
  * svt_aom_motion_estimation_b64 does b64 by b64. me_ctx carries the controls and me_ds_ref_array[l][r].picture_number. */
 EbErrorType svt_me_gpu_picture(PictureParentControlSet *pcs, const MeContext *me_ctx);
 
+/* What svt_aom_motion_estimation_kernel calls for one TASK_PAME segment item of a picture in place of its b64 loop
+ * (me_process.c:174-290). The picture's 48 segment items arrive on up to 25 ME threads in any order: the FIRST thread to
+ * arrive registers whatever pyramids the device does not hold yet (the picture's own PA reference object and those of its
+ * references, lazily, keyed by the object: a recycled object releases the picture it held before), submits the whole
+ * picture, waits and scatters the results into the pcs; every other segment's thread blocks here until that is done.
+ * When this returns EB_ErrorNone the pcs holds the results of ALL b64s; the caller then adds its segment's b64 count to
+ * pcs->me_processed_b64_count under me_processed_b64_mutex and the thread that completes the count runs
+ * svt_aom_global_motion_estimation, exactly as at me_process.c:274-287. me_ctx: controls by svt_aom_sig_deriv_me, the
+ * per-call fields of me_process.c:219-262 filled for the picture. Not for super-res / resize pictures (their references
+ * are rescaled planes): the caller keeps the CPU loop for those. */
+EbErrorType svt_me_gpu_segment(PictureParentControlSet *pcs, MeContext *me_ctx);
+/* non-zero when svt_me_gpu_hook_init succeeded: the ME kernel takes the device path */
+int svt_me_gpu_live(void);
+/* pictures the hook has registered / released so far (diagnostics) */
+void svt_me_gpu_stats(uint64_t *registered, uint64_t *released, uint64_t *pictures);
+
 /* ---- temporal filter (ME_MCTF, temporal_filtering.c:3144-3187) ------------------------------------------------ */
 /* ME results of one (centre, neighbour) pair over all blocks: what the block loop of produce_temporally_filtered_pic
  * reads from the MeContext after its svt_aom_motion_estimation_b64 call. Arrays are caller-owned, b64_count long. */

@@ -86,8 +86,10 @@ ME_HD uint16_t mc_scaled_distance(uint16_t dist) { return (uint16_t)(((dist * 5)
 
 /* ME:1232-1234: ABS((int16_t)(pcs->picture_number - ref picture_number)) */
 ME_HD uint16_t mc_ref_distance(const CtrlCtx *c, int li, int ri) {
-    int64_t d = (int64_t)c->p->picture_number - (int64_t)c->j->ref_picture_number[li][ri];
-    return (uint16_t)(int16_t)MC_ABS(d);
+    /* truncated to 16 bits BEFORE the absolute value, as the reference writes it: only the low 16 bits of the numbers count,
+       so a caller may keep an identity tag in the high bits of the picture numbers it hands to the engine */
+    const int16_t d = (int16_t)(c->p->picture_number - c->j->ref_picture_number[li][ri]);
+    return (uint16_t)MC_ABS(d);
 }
 
 /* window clamp shared by ME:848-880, 949-982, 1050-1078, 1585-1629, 1445-1491. The left/top clamp moves the
