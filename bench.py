@@ -24,7 +24,6 @@ import os
 import sys
 import threading
 import time
-from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
 
@@ -161,14 +160,19 @@ def pinned_outputs(params, eng):
 # reference CPU arm (oracle/_ref: the reference's own sources compiled in place)
 # --------------------------------------------------------------------------------------------------
 class CpuArm:
-    """The reference's ME (svt_aom_motion_estimation_b64 + AVX2 kernels, oracle/_ref) on host threads."""
+    """The reference's own open-loop ME (svt_aom_motion_estimation_b64 + its SIMD kernels, oracle/_ref = the reference's
+    sources compiled in place) over the step's pictures, on host threads, in C: every picture cut into the encoder's ME
+    segments, all items in one queue, a MeContext per thread (oracle/ref_harness.c: ref_me_step_mt). Controls come from
+    the reference's own svt_aom_sig_deriv_me (workloads.reference_params): no product library is loaded on this arm."""
 
-    def __init__(self, kind, pocs, threads, simd=1):
+    SIMD = {"avx2": 1, "avx512": 2, "c": 0}
+
+    def __init__(self, kind, pocs):
         import checkers
         self.ref = checkers.Reference()
-        self.threads, self.simd, self.pocs = threads, simd, pocs
+        self.pocs = pocs
         seq = synth.Sequence(W, H, NPIC, kind=kind)
-        pics = self.pics = {}  # keeps the planes alive: the C structs built below point into them
+        pics = self.pics = {}
 
         def get(k):
             if k not in pics:
@@ -178,42 +182,43 @@ class CpuArm:
                 pics[k] = p
             return pics[k]
 
-        self.work, self.keep, self.b64_done = [], [], 0
+        self.jobs = []
         for poc in pocs:
-            cfg, p, l0, l1 = derive(poc)
-            refs = [[get(k) for k in l0], [get(k) for k in l1]]
-            out = planes.Outputs(W, H, p, debug=False)
-            arr, keep = checkers._refs_array(refs)
-            s = get(poc).c_struct()
-            self.keep.append((refs, out, arr, keep, s, p))
-            chunks = list(range(0, b64_count(), 6))  # the picture's b64s in chunks of 6 ...
-            for first in chunks[(7 * len(self.keep)) % CPU_EVERY::CPU_EVERY]:  # ... every CPU_EVERY-th of them
-                count = min(6, b64_count() - first)
-                self.work.append((s, arr, p, out, first, count))
-                self.b64_done += count
-        # fill the RTCD table on one thread before fanning out
-        s, arr, p, out, _, _ = self.work[0]
-        self.ref.lib.ref_me_b64_range(C.byref(s), C.byref(arr), C.byref(p), C.byref(out.c), 0, 1, simd)
-        self.pool = ThreadPoolExecutor(threads)
+            p, l0, l1 = workloads.reference_params(WORKLOAD, poc, self.ref)
+            self.jobs.append((get(poc), [[get(k) for k in l0], [get(k) for k in l1]], p, planes.Outputs(W, H, p, debug=False)))
+        self.b64_done = 0
 
-    def _run(self, item):
-        s, arr, p, out, first, count = item
-        rc = self.ref.lib.ref_me_b64_range(C.byref(s), C.byref(arr), C.byref(p), C.byref(out.c), first, count, self.simd)
-        assert rc == 0
-
-    def step(self):
-        """ME of the sampled b64s of every picture of the arm once; returns seconds"""
+    def step(self, threads, simd="avx2", every=None):
+        """ME of (a sample of) every picture of the step once; returns seconds"""
         t0 = time.perf_counter()
-        list(self.pool.map(self._run, self.work))
+        self.b64_done = self.ref.me_step_mt(self.jobs, threads, self.SIMD[simd], CPU_EVERY if every is None else every)
         return time.perf_counter() - t0
 
     def pictures(self):
-        """whole pictures' worth of b64s one step() covers"""
+        """whole pictures' worth of b64s the last step() covered"""
         return self.b64_done / b64_count()
+
+    def measure(self, threads, simd, budget_s, max_reps=20):
+        self.step(threads, simd)
+        reps, dt, pics = 0, 0.0, 0.0
+        while dt < budget_s and reps < max_reps:
+            dt += self.step(threads, simd)
+            pics += self.pictures()
+            reps += 1
+        return {"value": pics / dt, "unit": "frames/s", "cores": threads, "kind": "reference", "simd": simd,
+                "sample": f"{self.sample_text()} x {reps} repetitions, {dt:.1f} s wall on {threads} threads"}
+
+    def parity(self, kind):
+        """the arm's own outputs against the frozen digests (only when whole pictures were searched)"""
+        gold = workloads.load_hashes()
+        keys = [workloads.hash_key(WORKLOAD, kind, poc) for poc in self.pocs]
+        if CPU_EVERY != 1 or not all(k in gold for k in keys):
+            return None
+        return all(workloads.picture_hashes(j[3]) == gold[k] for j, k in zip(self.jobs, keys))
 
     def sample_text(self):
         return (f"all {b64_count()} b64 of each of the step's {len(self.pocs)} pictures" if CPU_EVERY == 1 else
-                f"every {CPU_EVERY}th chunk of 6 b64s of each of the step's {len(self.pocs)} pictures "
+                f"every {CPU_EVERY}th ME segment (of 48) of each of the step's {len(self.pocs)} pictures "
                 f"({self.b64_done} of {len(self.pocs) * b64_count()} b64, frames/s scaled by the b64 count)")
 
 
@@ -227,27 +232,53 @@ def cpu_model():
     return "unknown"
 
 
+def physical_cores():
+    """distinct (physical id, core id) pairs of /proc/cpuinfo; None when the VM does not tell"""
+    try:
+        seen, phys, core = set(), None, None
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("physical id"):
+                phys = line.split(":")[1].strip()
+            elif line.startswith("core id"):
+                core = line.split(":")[1].strip()
+            elif not line.strip() and phys is not None and core is not None:
+                seen.add((phys, core))
+                phys = core = None
+        return len(seen) or None
+    except Exception:
+        return None
+
+
+def host_info():
+    return {"cpu": cpu_model(), "logical_cpus": os.cpu_count(), "physical_cores": physical_cores(),
+            "note": "a small host for a baseline: the GPU box's VM exposes 16 vCPUs of an unnamed Xeon; every ratio against "
+                    "this arm is a ratio against THESE cores"}
+
+
 def reference_main(args):
     rank, _, world = rank_info()
     if rank != 0:
         return 0
     threads = os.cpu_count() or 1
-    arm = CpuArm(args.kind, STEP_POCS, threads)
+    arm = CpuArm(args.kind, STEP_POCS)
     for _ in range(args.warmup):
-        arm.step()
-    t_total = 0.0
+        arm.step(threads)
+    t_total, pics = 0.0, 0.0
     for _ in range(args.steps):
-        t_total += arm.step()
-    value = arm.pictures() * args.steps / t_total
+        t_total += arm.step(threads)
+        pics += arm.pictures()
+    value = pics / t_total
     sample = f"{arm.sample_text()}, per step; {threads} threads"
+    others = [arm.measure(threads, "avx512", 3.0), arm.measure(1, "avx2", 3.0, max_reps=3)]
     line = {
         "impl": "reference", "metric": "open-loop ME frames/sec", "value": value, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_total / max(1, args.steps),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": workload_config(args.kind),
         "cpu_baseline": {"value": value, "unit": "frames/s", "cores": threads, "kind": "reference", "sample": sample,
-                         "cpu": cpu_model(), "simd": "avx2 (svt_*_avx2 kernels behind the reference's RTCD pointers)"},
+                         "simd": "avx2 (svt_*_avx2 kernels behind the reference's RTCD pointers)", "other_arms": others},
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "parity": {"equal": arm.parity(args.kind), "against": "tests/golden/picture_hashes.json"}, "host": host_info(),
     }
     print(json.dumps(line))
     return 0
@@ -479,15 +510,11 @@ def gpu_main(args):
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
-        arm = CpuArm(args.kind, STEP_POCS, threads)
-        arm.step()
-        reps, dt = 0, 0.0
-        while dt < 4.0 and reps < 20:
-            dt += arm.step()
-            reps += 1
-        cpu_baseline = {"value": arm.pictures() * reps / dt, "unit": "frames/s", "cores": threads, "kind": "reference",
-                        "sample": f"{arm.sample_text()} x {reps} repetitions, {dt:.1f} s wall on {threads} threads",
-                        "cpu": cpu_model(), "simd": "avx2"}
+        arm = CpuArm(args.kind, STEP_POCS)
+        cpu_baseline = arm.measure(threads, "avx2", 4.0)
+        cpu_baseline["other_arms"] = [arm.measure(threads, "avx512", 3.0), arm.measure(1, "avx2", 3.0, max_reps=3)]
+        cpu_baseline["parity_equal"] = arm.parity(args.kind)
+        cpu_baseline["host"] = host_info()
     extra = None
     if rank == 0 and world == 1 and args.extra and WORKLOAD == "1080p-m4" and args.kind == "motion":
         # the same measurement on the configurations where the integer full search dominates (worst-case "iid" input:

@@ -244,27 +244,51 @@ REF_API int ref_derive_params(const MeGpuEncoderConfig *cfg, const RefMrpInputs 
     return 0;
 }
 
-/* ME of b64s [first, first+count) with the reference's own svt_aom_motion_estimation_b64.
- * simd: 0 = C kernels (the specification), 1 = AVX2, 2 = AVX-512 sad_loop on top of AVX2. */
-REF_API int ref_me_b64_range(const OraclePicture *src, const OraclePicture *const refs[2][4], const MeGpuParams *p,
-                     MeGpuOutputs *out, uint32_t first, uint32_t count, int simd) {
-    set_rtcd(simd);
+/* ------------------------------------------------------------------------------------------------
+ * One picture's ME state as the encoder holds it: pcs / scs / pa_me_data / MeSbResults / b64 geometry / picture
+ * descriptors, built ONCE per picture; the blocks are then run against it by any number of threads, each with its own
+ * MeContext (me_process.c:75-88: one MeContext per ME thread).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct RefPicCtx {
+    PictureParentControlSet *pcs;
+    SequenceControlSet      *scs;
+    MotionEstimationData    *md;
+    MeSbResults             *res;
+    MeSbResults            **rp;
+    B64Geom                 *geo;
+    EbPictureBufferDesc      sf, sq, ss, rf[2][4], rq[2][4], rs[2][4];
+    const OraclePicture     *refs[2][4];
+    const MeGpuParams       *p;
+    MeGpuOutputs            *out;
+    uint32_t                 total, P;
+} RefPicCtx;
+
+static void ref_pic_ctx_free(RefPicCtx *c) {
+    if (!c)
+        return;
+    free(c->geo); free(c->rp); free(c->res); free(c->md); free(c->scs); free(c->pcs); free(c);
+}
+
+static RefPicCtx *ref_pic_ctx_new(const OraclePicture *src, const OraclePicture *const refs[2][4], const MeGpuParams *p, MeGpuOutputs *out) {
     const int pic_w = (src->full.width + 7) & ~7, pic_h = (src->full.height + 7) & ~7;
     const uint32_t bw = (pic_w + 63) / 64, bh = (pic_h + 63) / 64, total = bw * bh;
     if (out->b64_count < total)
-        return -2;
-    PictureParentControlSet *pcs = calloc(1, sizeof *pcs);
-    SequenceControlSet      *scs = calloc(1, sizeof *scs);
-    MeContext               *m   = calloc(1, sizeof *m);
-    MotionEstimationData    *md  = calloc(1, sizeof *md);
-    MeSbResults             *res = calloc(total, sizeof *res);
-    MeSbResults            **rp  = calloc(total, sizeof *rp);
-    B64Geom                 *geo = calloc(total, sizeof *geo);
-    if (!pcs || !scs || !m || !md || !res || !rp || !geo)
-        return -1;
+        return NULL;
+    RefPicCtx *c = calloc(1, sizeof *c);
+    if (!c)
+        return NULL;
+    PictureParentControlSet *pcs = c->pcs = calloc(1, sizeof *pcs);
+    SequenceControlSet      *scs = c->scs = calloc(1, sizeof *scs);
+    MotionEstimationData    *md  = c->md  = calloc(1, sizeof *md);
+    MeSbResults             *res = c->res = calloc(total, sizeof *res);
+    MeSbResults            **rp  = c->rp  = calloc(total, sizeof *rp);
+    B64Geom                 *geo = c->geo = calloc(total, sizeof *geo);
+    if (!pcs || !scs || !md || !res || !rp || !geo) {
+        ref_pic_ctx_free(c);
+        return NULL;
+    }
     const uint32_t P = p->enable_me_16x16 ? (p->enable_me_8x8 ? p->max_number_of_pus_per_sb : 21) : 5;
-
-    ctx_from_params(m, p);
+    c->total = total; c->P = P; c->p = p; c->out = out;
     pcs->scs                      = scs;
     pcs->picture_number           = p->picture_number;
     pcs->aligned_width            = (uint16_t)pic_w;
@@ -304,41 +328,60 @@ REF_API int ref_me_b64_range(const OraclePicture *src, const OraclePicture *cons
         geo[b].width                 = (uint8_t)((pic_w - geo[b].org_x) < 64 ? pic_w - geo[b].org_x : 64);
         geo[b].height                = (uint8_t)((pic_h - geo[b].org_y) < 64 ? pic_h - geo[b].org_y : 64);
     }
-    EbPictureBufferDesc sf, sq, ss, rf[2][4], rq[2][4], rs[2][4];
-    desc_from_plane(&sf, &src->full);
-    desc_from_plane(&sq, &src->quarter);
-    desc_from_plane(&ss, &src->sixteenth);
+    desc_from_plane(&c->sf, &src->full);
+    desc_from_plane(&c->sq, &src->quarter);
+    desc_from_plane(&c->ss, &src->sixteenth);
     for (int li = 0; li < p->num_of_list_to_search; li++)
         for (int ri = 0; ri < p->num_of_ref_pic_to_search[li]; ri++) {
-            desc_from_plane(&rf[li][ri], &refs[li][ri]->full);
-            desc_from_plane(&rq[li][ri], &refs[li][ri]->quarter);
-            desc_from_plane(&rs[li][ri], &refs[li][ri]->sixteenth);
-            m->me_ds_ref_array[li][ri].picture_ptr           = &rf[li][ri];
-            m->me_ds_ref_array[li][ri].quarter_picture_ptr   = &rq[li][ri];
-            m->me_ds_ref_array[li][ri].sixteenth_picture_ptr = &rs[li][ri];
-            m->me_ds_ref_array[li][ri].picture_number        = refs[li][ri]->picture_number;
+            c->refs[li][ri] = refs[li][ri];
+            desc_from_plane(&c->rf[li][ri], &refs[li][ri]->full);
+            desc_from_plane(&c->rq[li][ri], &refs[li][ri]->quarter);
+            desc_from_plane(&c->rs[li][ri], &refs[li][ri]->sixteenth);
         }
+    return c;
+}
 
-    for (uint32_t b = first; b < first + count && b < total; b++) {
-        const uint32_t ox = geo[b].org_x, oy = geo[b].org_y;
+/* what svt_aom_motion_estimation_kernel does when it takes an item of this picture (me_process.c:121, 219-262) */
+static void ref_pic_ctx_bind(RefPicCtx *c, MeContext *m) {
+    const MeGpuParams *p = c->p;
+    ctx_from_params(m, p);
+    for (int li = 0; li < p->num_of_list_to_search; li++)
+        for (int ri = 0; ri < p->num_of_ref_pic_to_search[li]; ri++) {
+            m->me_ds_ref_array[li][ri].picture_ptr           = &c->rf[li][ri];
+            m->me_ds_ref_array[li][ri].quarter_picture_ptr   = &c->rq[li][ri];
+            m->me_ds_ref_array[li][ri].sixteenth_picture_ptr = &c->rs[li][ri];
+            m->me_ds_ref_array[li][ri].picture_number        = c->refs[li][ri]->picture_number;
+        }
+}
+
+/* blocks [first, first + count) of the picture on MeContext m (bound to it). canonical: reset the state the reference
+ * leaves stale between blocks (never read for an output) so that the parity taps are reproducible; the timed arm
+ * leaves it as the encoder does. */
+static void ref_pic_ctx_run(RefPicCtx *c, MeContext *m, uint32_t first, uint32_t count, int canonical) {
+    const MeGpuParams *p   = c->p;
+    MeGpuOutputs      *out = c->out;
+    EbPictureBufferDesc *sf = &c->sf, *sq = &c->sq, *ss = &c->ss;
+    for (uint32_t b = first; b < first + count && b < c->total; b++) {
+        const uint32_t ox = c->geo[b].org_x, oy = c->geo[b].org_y;
         /* me_process.c:183-214 */
-        m->b64_src_ptr                 = &sf.buffer_y[(sf.org_y + oy) * sf.stride_y + sf.org_x + ox];
-        m->b64_src_stride              = sf.stride_y;
-        m->quarter_b64_buffer          = &sq.buffer_y[(sq.org_y + (oy >> 1)) * sq.stride_y + sq.org_x + (ox >> 1)];
-        m->quarter_b64_buffer_stride   = sq.stride_y;
-        m->sixteenth_b64_buffer        = &ss.buffer_y[(ss.org_y + (oy >> 2)) * ss.stride_y + ss.org_x + (ox >> 2)];
-        m->sixteenth_b64_buffer_stride = ss.stride_y;
+        m->b64_src_ptr                 = &sf->buffer_y[(sf->org_y + oy) * sf->stride_y + sf->org_x + ox];
+        m->b64_src_stride              = sf->stride_y;
+        m->quarter_b64_buffer          = &sq->buffer_y[(sq->org_y + (oy >> 1)) * sq->stride_y + sq->org_x + (ox >> 1)];
+        m->quarter_b64_buffer_stride   = sq->stride_y;
+        m->sixteenth_b64_buffer        = &ss->buffer_y[(ss->org_y + (oy >> 2)) * ss->stride_y + ss->org_x + (ox >> 2)];
+        m->sixteenth_b64_buffer_stride = ss->stride_y;
         m->me_type                     = (EbMeType)p->me_type;
         m->tf_use_pred_64x64_only_th   = 1; /* temporal_filtering.c:3174 sets tf_ctrls.use_pred_64x64_only_th; 0xFF marks the exit */
-        /* canonical state for data the reference leaves stale between blocks (never read for an output) */
-        for (int li = 0; li < 2; li++)
-            for (int ri = 0; ri < 4; ri++)
-                for (int k = 0; k < SQUARE_PU_COUNT; k++) m->p_sb_best_sad[li][ri][k] = MAX_SAD_VALUE;
-        memset(m->prehme_data, 0, sizeof m->prehme_data);
-        for (int li = 0; li < 2; li++)
-            for (int ri = 0; ri < 4; ri++) m->search_results[li][ri].hme_sc_x = m->search_results[li][ri].hme_sc_y = 0;
+        if (canonical) {
+            for (int li = 0; li < 2; li++)
+                for (int ri = 0; ri < 4; ri++)
+                    for (int k = 0; k < SQUARE_PU_COUNT; k++) m->p_sb_best_sad[li][ri][k] = MAX_SAD_VALUE;
+            memset(m->prehme_data, 0, sizeof m->prehme_data);
+            for (int li = 0; li < 2; li++)
+                for (int ri = 0; ri < 4; ri++) m->search_results[li][ri].hme_sc_x = m->search_results[li][ri].hme_sc_y = 0;
+        }
 
-        svt_aom_motion_estimation_b64(pcs, b, ox, oy, m, &sf);
+        svt_aom_motion_estimation_b64(c->pcs, b, ox, oy, m, sf);
 
         if (p->me_type == ME_GPU_ME_MCTF) {
             if (out->tf_best_sad) memcpy(out->tf_best_sad + (size_t)b * 85, m->p_sb_best_sad[0][0], 85 * sizeof(uint32_t));
@@ -352,25 +395,134 @@ REF_API int ref_me_b64_range(const OraclePicture *src, const OraclePicture *cons
         }
         if (out->p_sb_best_sad) memcpy(out->p_sb_best_sad + (size_t)b * 2 * 4 * 85, m->p_sb_best_sad, sizeof m->p_sb_best_sad);
         if (out->p_sb_best_mv) memcpy(out->p_sb_best_mv + (size_t)b * 2 * 4 * 85, m->p_sb_best_mv, sizeof m->p_sb_best_mv);
-        for (int li = 0; li < 2; li++)
-            for (int ri = 0; ri < 4; ri++) {
-                size_t k = ((size_t)b * 2 + li) * 4 + ri;
-                if (out->hme_search_centre) {
-                    out->hme_search_centre[2 * k]     = m->search_results[li][ri].hme_sc_x;
-                    out->hme_search_centre[2 * k + 1] = m->search_results[li][ri].hme_sc_y;
+        if (out->hme_search_centre || out->hme_sad || out->do_ref)
+            for (int li = 0; li < 2; li++)
+                for (int ri = 0; ri < 4; ri++) {
+                    size_t k = ((size_t)b * 2 + li) * 4 + ri;
+                    if (out->hme_search_centre) {
+                        out->hme_search_centre[2 * k]     = m->search_results[li][ri].hme_sc_x;
+                        out->hme_search_centre[2 * k + 1] = m->search_results[li][ri].hme_sc_y;
+                    }
+                    if (out->hme_sad) out->hme_sad[k] = m->search_results[li][ri].hme_sad;
+                    if (out->do_ref) out->do_ref[k] = m->search_results[li][ri].do_ref;
                 }
-                if (out->hme_sad) out->hme_sad[k] = m->search_results[li][ri].hme_sad;
-                if (out->do_ref) out->do_ref[k] = m->search_results[li][ri].do_ref;
-            }
     }
-    out->b64_count = total;
-    out->pu_count  = P;
+}
+
+/* ME of b64s [first, first+count) with the reference's own svt_aom_motion_estimation_b64.
+ * simd: 0 = C kernels (the specification), 1 = AVX2, 2 = AVX-512 sad_loop on top of AVX2. */
+REF_API int ref_me_b64_range(const OraclePicture *src, const OraclePicture *const refs[2][4], const MeGpuParams *p,
+                     MeGpuOutputs *out, uint32_t first, uint32_t count, int simd) {
+    set_rtcd(simd);
+    RefPicCtx *c = ref_pic_ctx_new(src, refs, p, out);
+    MeContext *m = calloc(1, sizeof *m);
+    if (!c || !m) {
+        ref_pic_ctx_free(c);
+        free(m);
+        return c ? -1 : -2;
+    }
+    ref_pic_ctx_bind(c, m);
+    ref_pic_ctx_run(c, m, first, count, 1);
+    out->b64_count = c->total;
+    out->pu_count  = c->P;
     if (p->me_type == ME_GPU_ME_MCTF) { /* counted by hme_b64 (ME:2469-2474) over the blocks of this call */
         out->tf_tot_horz_blks = m->tf_tot_horz_blks;
         out->tf_tot_vert_blks = m->tf_tot_vert_blks;
     }
-    free(geo); free(rp); free(res); free(md); free(m); free(scs); free(pcs);
+    ref_pic_ctx_free(c);
+    free(m);
     return 0;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * The timed CPU arm (bench.py --impl reference, cpu_baseline): open-loop ME of a whole step of pictures on `nthreads`
+ * threads, the way the encoder's ME stage runs it - every picture cut into its ME segments (enc_handle.c:396-410:
+ * 6 x 8 = 48 at 1080p and above), the items of all pictures in one queue (pd_process.c:3545-3557), each thread with a
+ * private MeContext taking the next item (enc_handle.c:731-773) - minus the FIFO and object-pool overhead. The picture
+ * state is built once per picture per step, outside the b64 loop. every > 1: only every `every`-th segment of a picture
+ * is run (a bounded sample for the slow configurations); *b64_done = blocks actually searched.
+ * ---------------------------------------------------------------------------------------------- */
+#include <pthread.h>
+typedef struct RefStepJob {
+    const OraclePicture *src;
+    const OraclePicture *const (*refs)[4];
+    const MeGpuParams   *p;
+    MeGpuOutputs        *out;
+} RefStepJob;
+typedef struct RefStepShared {
+    RefPicCtx **ctx;
+    int         njobs, seg_cols, seg_rows, every;
+    volatile int next; /* next (picture, segment) item */
+    volatile long b64_done;
+} RefStepShared;
+
+static void *ref_step_thread(void *arg) {
+    RefStepShared *sh = (RefStepShared *)arg;
+    MeContext     *m  = calloc(1, sizeof *m);
+    int            bound = -1;
+    const int      nseg = sh->seg_cols * sh->seg_rows;
+    for (;;) {
+        const int item = __sync_fetch_and_add(&sh->next, 1);
+        if (item >= sh->njobs * nseg)
+            break;
+        const int pic = item / nseg, seg = item % nseg;
+        if (sh->every > 1 && (seg + 7 * pic) % sh->every)
+            continue;
+        RefPicCtx *c = sh->ctx[pic];
+        if (bound != pic) {
+            ref_pic_ctx_bind(c, m);
+            bound = pic;
+        }
+        const uint32_t bw = (c->pcs->aligned_width + 63) / 64, bh = (c->pcs->aligned_height + 63) / 64;
+        const uint32_t sx = seg % sh->seg_cols, sy = seg / sh->seg_cols;
+        /* SEGMENT_START_IDX / SEGMENT_END_IDX, Codec/definitions.h */
+        const uint32_t x0 = (sx * bw) / sh->seg_cols, x1 = ((sx + 1) * bw) / sh->seg_cols;
+        const uint32_t y0 = (sy * bh) / sh->seg_rows, y1 = ((sy + 1) * bh) / sh->seg_rows;
+        for (uint32_t y = y0; y < y1; y++) ref_pic_ctx_run(c, m, y * bw + x0, x1 - x0, 0);
+        __sync_fetch_and_add(&sh->b64_done, (long)((x1 - x0) * (y1 - y0)));
+    }
+    free(m);
+    return NULL;
+}
+
+REF_API int ref_me_step_mt(const RefStepJob *jobs, int njobs, int nthreads, int simd, int every, long *b64_done) {
+    set_rtcd(simd);
+    if (njobs <= 0 || nthreads <= 0 || nthreads > 256)
+        return -3;
+    RefStepShared sh;
+    memset(&sh, 0, sizeof sh);
+    sh.ctx   = calloc((size_t)njobs, sizeof *sh.ctx);
+    sh.njobs = njobs;
+    sh.every = every < 1 ? 1 : every;
+    int rc   = 0;
+    for (int i = 0; i < njobs && !rc; i++) {
+        sh.ctx[i] = ref_pic_ctx_new(jobs[i].src, jobs[i].refs, jobs[i].p, jobs[i].out);
+        if (!sh.ctx[i])
+            rc = -1;
+    }
+    if (!rc) {
+        /* enc_handle.c:394-397: me_seg_h = ((h + 32) / 64 < 6) ? 1 : 8, me_seg_w = ((w + 32) / 64 < 10) ? 1 : 6 */
+        const uint32_t w = sh.ctx[0]->pcs->aligned_width, h = sh.ctx[0]->pcs->aligned_height;
+        sh.seg_cols = ((w + 32) / 64) < 10 ? 1 : 6;
+        sh.seg_rows = ((h + 32) / 64) < 6 ? 1 : 8;
+        pthread_t th[256];
+        int       started = 0;
+        for (; started < nthreads; started++)
+            if (pthread_create(&th[started], NULL, ref_step_thread, &sh))
+                break;
+        for (int i = 0; i < started; i++) pthread_join(th[i], NULL);
+        if (!started)
+            rc = -4;
+        for (int i = 0; i < njobs; i++) {
+            jobs[i].out->b64_count = sh.ctx[i]->total;
+            jobs[i].out->pu_count  = sh.ctx[i]->P;
+        }
+    }
+    if (b64_done)
+        *b64_done = sh.b64_done;
+    for (int i = 0; i < njobs; i++) ref_pic_ctx_free(sh.ctx[i]);
+    free(sh.ctx);
+    return rc;
 }
 
 /* ------------------------------------------------------------------------------------------------

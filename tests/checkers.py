@@ -107,6 +107,26 @@ class Reference:
             raise RuntimeError(f"ref_me_b64_range failed: {rc}")
         return out
 
+    def me_step_mt(self, jobs, threads, simd=1, every=1):
+        """jobs: [(src Picture, refs, params, Outputs)]: open-loop ME of all of them on `threads` threads (the timed CPU
+        arm: segments of all pictures in one queue, a MeContext per thread). Returns the b64s searched."""
+        class RefStepJob(C.Structure):
+            _fields_ = [("src", C.POINTER(abi.OraclePicture)), ("refs", C.POINTER(abi.RefArray)),
+                        ("p", C.POINTER(abi.MeGpuParams)), ("out", C.POINTER(abi.MeGpuOutputs))]
+        arr = (RefStepJob * len(jobs))()
+        keep = []
+        for i, (src, refs, p, out) in enumerate(jobs):
+            ra, k = _refs_array(refs)
+            s = src.c_struct()
+            keep.append((ra, k, s))
+            arr[i].src, arr[i].refs, arr[i].p, arr[i].out = C.pointer(s), C.pointer(ra), C.pointer(p), C.pointer(out.c)
+        done = C.c_long(0)
+        self.lib.ref_me_step_mt.argtypes = [C.POINTER(RefStepJob), C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_long)]
+        rc = self.lib.ref_me_step_mt(arr, len(jobs), threads, simd, every, C.byref(done))
+        if rc != 0:
+            raise RuntimeError(f"ref_me_step_mt failed: {rc}")
+        return done.value
+
     def has_hook(self):
         return hasattr(self.lib, "ref_hook_me_picture")
 

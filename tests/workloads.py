@@ -54,3 +54,30 @@ def load_hashes():
 
 def hash_key(name, kind, poc):
     return f"{name}/{kind}/{poc}"
+
+
+# What enc_handle.c's static set_mrp_ctrl() (Source/Lib/Globals/enc_handle.c:3397-3560, mrp levels 2 / 5 / 10) gives the
+# workloads' presets - or what their forced reference counts stand for: (max refs list 0, max refs list 1,
+# mrp_ctrls.safe_limit_nref, mrp_ctrls.safe_limit_zz_th, mrp_ctrls.only_l_bwd). The reference arm needs them to call the
+# reference's own svt_aom_sig_deriv_me without going through the product's host library; tests/test_bench_contract.py
+# checks that the two routes give the same MeGpuParams, byte for byte.
+MRP = {"1080p-m4": (2, 2, 0, 0, 1), "1080p-m8": (1, 1, 2, 0, 1), "4k-m2": (4, 3, 0, 0, 1), "4k-m0": (4, 3, 0, 0, 1)}
+
+
+def reference_params(name, poc, ref):
+    """(MeGpuParams, list0 pocs, list1 pocs) of picture `poc` of workload `name`, controls by the REFERENCE's own
+    svt_aom_sig_deriv_me (`ref`: checkers.Reference); no product library involved."""
+    from me_b200 import abi
+    wl = WORKLOADS[name]
+    l0max, l1max, nref, zz, only_l_bwd = MRP[name]
+    tl = synth.RA5_RPS[poc % 16][0]
+    cfg = abi.MeGpuEncoderConfig(enc_mode=wl["preset"], qp=35, hierarchical_levels=4, width=wl["w"], height=wl["h"],
+                                 picture_number=poc, temporal_layer_index=tl, is_ref=1 if tl < 4 else 0)
+    p = ref.derive_params(cfg, nref, zz)
+    _, l0, l1 = synth.ref_lists(poc, NPIC, l0max, l1max)
+    p.only_l_bwd = only_l_bwd
+    p.max_l0, p.max_refs = l0max, l0max + l1max
+    p.max_cand = l0max + l1max + l0max * l1max + (l0max - 1) + (1 if l1max == 3 else 0)  # pcs.c:91-96
+    p.num_of_list_to_search = 2 if l1 else 1
+    p.num_of_ref_pic_to_search[0], p.num_of_ref_pic_to_search[1] = len(l0), len(l1)
+    return p, l0, l1
