@@ -297,54 +297,84 @@ def workload_config(kind):
 # --------------------------------------------------------------------------------------------------
 # B200 arm
 # --------------------------------------------------------------------------------------------------
-def gpu_main(args):
-    import torch
-    import torch.distributed as dist
-    from me_b200.engine import Engine
-
-    rank, local_rank, world = rank_info()
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; the engine has no CPU fallback")
-    torch.cuda.set_device(local_rank)
-    numa_cpus = bind_to_gpu_numa(local_rank) if world > 1 else None
-    if world > 1:
-        # NCCL prints its version banner on stdout when the box sets NCCL_DEBUG=VERSION: stdout carries ONE JSON line,
-        # so fd 1 points at stderr while the communicator comes up (first collective included)
+def init_dist(torch, dist, local_rank, world):
+    """NCCL for the timer's all_reduce(MAX) (the contract's launch), gloo for the sharded mode's control plane (which
+    picture sits in which pool slot: a few bytes per picture). Neither carries a pixel."""
+    if world <= 1:
+        return None
+    # NCCL prints its version banner on stdout when the box sets NCCL_DEBUG=VERSION: stdout carries ONE JSON line,
+    # so fd 1 points at stderr while the communicator comes up (first collective included)
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist.barrier()
+        torch.cuda.synchronize()
+        ctl = dist.new_group(backend="gloo")
+    finally:
         sys.stdout.flush()
-        saved = os.dup(1)
-        os.dup2(2, 1)
-        try:
-            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-            dist.barrier()
-            torch.cuda.synchronize()
-        finally:
-            sys.stdout.flush()
-            os.dup2(saved, 1)
-            os.close(saved)
+        os.dup2(saved, 1)
+        os.close(saved)
+    return ctl
+
+
+def measure(args, kind, mode, steps, warmup, torch, dist, ctl, with_cpu):
+    """One measurement of the current workload (set_workload) on this rank's GPU.
+    mode "replicas": every rank runs the whole step on its own copy of the stream (weak scaling; configs[3]).
+    mode "sharded":  ONE stream; the pictures of the step are dealt round-robin in decode order over the ranks; a picture
+                     is uploaded by its owner only and reaches the ranks that reference it GPU to GPU (CUDA IPC mapping of
+                     the owner's pool, device-to-device copy over NVLink); strong scaling; no collective on the data path."""
+    from me_b200 import shard
+    from me_b200.engine import Engine
+    rank, local_rank, world = rank_info()
+    sharded = mode == "sharded" and world > 1
 
     def barrier():
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
 
-    pics = make_pictures(args.kind, pinned=True, padded=False)
-    jobs = {poc: derive(poc) for poc in STEP_POCS}
+    pics = make_pictures(kind, pinned=True, padded=False)
+    owner = shard.owners(synth.decode_order(NPIC), world) if sharded else {poc: rank for poc in range(NPIC)}
+    my_pocs = [poc for poc in STEP_POCS if owner[poc] == rank]
+    jobs = {poc: derive(poc) for poc in my_pocs}
+    needed = shard.pyramids_needed(my_pocs, lambda poc: jobs[poc][2:])  # what this rank's pictures read
     eng = Engine(W, H, 4, 3, pictures_in_flight=NSETS * NPIC + 4, devices=[local_rank])
-    outs = {poc: pinned_outputs(jobs[poc][1], eng) for poc in STEP_POCS}
+    outs = {poc: pinned_outputs(jobs[poc][1], eng) for poc in my_pocs}
     state = {"k": 0}
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # profiling pass only
+    num = lambda poc, st: poc + SET_STRIDE * st  # noqa: E731  picture numbers of a set are offset by a constant: distances are unchanged
+
+    if sharded:
+        handles = [None] * world
+        dist.all_gather_object(handles, eng.ipc_export_pool(), group=ctl)
+        for r, (h, sb) in enumerate(handles):
+            if r != rank:
+                eng.ipc_open_peer(r, h, sb)
 
     def reg(poc, st):
         a, _ = pics[poc]
-        eng.register_picture_unpadded_ptr(poc + SET_STRIDE * st, a.ctypes.data, a.strides[0], W, H)
+        eng.register_picture_unpadded_ptr(num(poc, st), a.ctypes.data, a.strides[0], W, H)
+
+    def exchange(pocs, st):
+        """owners publish (slot, event) of the pictures they have just registered; everybody pulls the ones it reads"""
+        mine = {poc: eng.ipc_picture(num(poc, st)) for poc in pocs if owner[poc] == rank}
+        infos = [None] * world
+        dist.all_gather_object(infos, mine, group=ctl)
+        for poc in pocs:
+            if owner[poc] != rank and poc in needed:
+                slot, evh = infos[owner[poc]][poc]
+                eng.register_picture_from_peer(num(poc, st), owner[poc], slot, evh, W, H)
+
+    def held(poc):
+        return owner[poc] == rank or poc in needed
 
     def submit(poc, st):
-        # picture numbers of a set are offset by a constant: distances (all ME reads) are unchanged
         _, p, l0, l1 = jobs[poc]
         q = abi.MeGpuParams.from_buffer_copy(p)
-        q.picture_number = poc + SET_STRIDE * st
-        eng.submit_out(poc + SET_STRIDE * st, q, [[k + SET_STRIDE * st for k in l0], [k + SET_STRIDE * st for k in l1]],
-                       outs[poc])
+        q.picture_number = num(poc, st)
+        eng.submit_out(num(poc, st), q, [[num(k, st) for k in l0], [num(k, st) for k in l1]], outs[poc])
 
     # Pictures stream through the engine the way they stream through the encoder's ME stage: up to WINDOW pictures
     # are in flight, the oldest one is waited for (its results copied back) before the next is submitted, and a step
@@ -355,7 +385,7 @@ def gpu_main(args):
 
     def retire_oldest():
         poc, st = in_flight.popleft()
-        eng.wait(poc + SET_STRIDE * st, outs[poc])
+        eng.wait(num(poc, st), outs[poc])
 
     def enqueue(poc, st):
         while len(in_flight) >= WINDOW:
@@ -370,7 +400,7 @@ def gpu_main(args):
     def step_resident():
         st = state["k"] % NSETS
         state["k"] += 1
-        for poc in STEP_POCS:
+        for poc in my_pocs:
             enqueue(poc, st)
 
     uploaded = set()
@@ -378,15 +408,24 @@ def gpu_main(args):
     def step_e2e():
         st = state["k"] % NSETS
         state["k"] += 1
-        if st in uploaded:  # the set was used NSETS steps ago: its jobs are long done
+        if st in uploaded:  # the set was used NSETS steps ago: its jobs are long done, here and (a rendezvous per step) on the peers
             for poc in STEP_POCS:
-                eng.release_picture(poc + SET_STRIDE * st)
+                if held(poc):
+                    eng.release_picture(num(poc, st))
         uploaded.add(st)
-        for poc in STEP_POCS:
-            while len(in_flight) >= WINDOW:
-                retire_oldest()
-            reg(poc, st)
-            enqueue(poc, st)
+        if sharded:
+            drain()  # result buffers of this rank's pictures are reused; and the pulls below need the pool slots
+            for poc in my_pocs:
+                reg(poc, st)
+            exchange(STEP_POCS, st)
+            for poc in my_pocs:
+                enqueue(poc, st)
+        else:
+            for poc in my_pocs:
+                while len(in_flight) >= WINDOW:
+                    retire_oldest()
+                reg(poc, st)
+                enqueue(poc, st)
 
     def timed(step_fn, steps, warmup):
         for _ in range(warmup):
@@ -409,16 +448,32 @@ def gpu_main(args):
             sampler.join()
         launches = eng.timings().kernel_launches - l0
         if world > 1:
-            t = torch.tensor([dt], dtype=torch.float64, device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            dt = float(t.item())
+            t = torch.tensor([dt, float(launches)], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t[:1], op=dist.ReduceOp.MAX)
+            dist.all_reduce(t[1:], op=dist.ReduceOp.SUM)
+            dt, launches = float(t[0].item()), int(t[1].item())
         return dt, launches, sampler.summary()
 
-    # resident arm: everything registered once
+    # resident arm: every pyramid where it is read before the clock starts (sharded: uploaded by its owner, pulled by the rest)
     for st in range(NSETS):
         for poc in range(NPIC):
-            reg(poc, st)
-    dt_res, launches, clocks = timed(step_resident, args.steps, args.warmup)
+            if owner[poc] == rank:
+                reg(poc, st)
+        if sharded:
+            exchange(list(range(NPIC)), st)
+    peer_verified = None
+    if sharded:
+        pulled = [poc for poc in needed if owner[poc] != rank]
+        if pulled:  # one replicated pyramid read back and compared with the one this device builds from the same luma
+            poc = pulled[0]
+            got = eng.read_pyramid(num(poc, 0), W, H)
+            a, _ = pics[poc]
+            eng.register_picture_unpadded_ptr(999999, a.ctypes.data, a.strides[0], W, H)
+            own = eng.read_pyramid(999999, W, H)
+            eng.release_picture(999999)
+            peer_verified = all(np.array_equal(x, y) for x, y in zip(got, own))
+    bytes0 = eng.ipc_bytes_pulled() if sharded else 0
+    dt_res, launches, clocks = timed(step_resident, steps, warmup)
 
     # roofline pass: one picture at a time, every launch bracketed by events on its stream
     eng.set_profiling(True)
@@ -427,11 +482,11 @@ def gpu_main(args):
     for rep in range(2):
         for k in prof:
             prof[k] = 0 if k.startswith("ops") else 0.0
-        for poc in STEP_POCS:
+        for poc in my_pocs:
             flush_buf.zero_()
             torch.cuda.synchronize()
             submit(poc, rep)
-            eng.wait(poc + SET_STRIDE * rep, outs[poc])
+            eng.wait(num(poc, rep), outs[poc])
             t = eng.timings()
             for k in ("k_search_ms", "k_fullsearch_ms", "k_fullsearch_main_ms", "k_ctrl_ms", "k_epilogue_ms", "total_ms"):
                 prof[k] += getattr(t, k)
@@ -441,31 +496,39 @@ def gpu_main(args):
     eng.set_profiling(False)
     sad_peak = 4.0 * eng.sad_peak()  # byte-SADs / s
 
-    # e2e arm: sources of the step uploaded every step
+    # e2e arm: sources of the step uploaded every step (by their owner), pulled by the ranks that read them
     for st in range(NSETS):
         for poc in STEP_POCS:
-            eng.release_picture(poc + SET_STRIDE * st)
-    dt_e2e, _, _ = timed(step_e2e, args.steps, args.warmup)
+            if held(poc):
+                eng.release_picture(num(poc, st))
+    barrier()
+    bytes1 = eng.ipc_bytes_pulled() if sharded else 0
+    dt_e2e, _, _ = timed(step_e2e, steps, warmup)
+    bytes2 = eng.ipc_bytes_pulled() if sharded else 0
 
-    checksum = int(sum(int(outs[p]["me_mv_array"].astype(np.uint64).sum()) for p in STEP_POCS) & 0xFFFFFFFF)
-    # parity gate: the product arrays of the step's 16 pictures, as the e2e arm left them in host memory, against the
+    # parity gate: the product arrays of this rank's pictures, as the e2e arm left them in host memory, against the
     # digests frozen from the reference's own AVX2 path on the same synthetic inputs (tests/golden/picture_hashes.json)
     gold = workloads.load_hashes()
-    keys = [workloads.hash_key(WORKLOAD, args.kind, poc) for poc in STEP_POCS]
-    if all(k in gold for k in keys):
-        wrong = [poc for poc, k in zip(STEP_POCS, keys) if workloads.picture_hashes(outs[poc]) != gold[k]]
-        parity = {"pictures": len(keys), "equal": not wrong, "mismatched_pocs": wrong,
-                  "against": "tests/golden/picture_hashes.json (reference svt_aom_motion_estimation_b64 + AVX2 kernels, all b64s, "
-                             "every product array)"}
+    keys = {poc: workloads.hash_key(WORKLOAD, kind, poc) for poc in my_pocs}
+    have = all(k in gold for k in keys.values())
+    wrong = [poc for poc in my_pocs if have and workloads.picture_hashes(outs[poc]) != gold[keys[poc]]]
+    checked = len(my_pocs) if have else 0
+    nvlink = [bytes1 - bytes0, bytes2 - bytes1]
+    if world > 1:
+        t = torch.tensor([len(wrong), checked, nvlink[0], nvlink[1]], dtype=torch.int64, device="cuda")
+        dist.all_reduce(t)
+        n_wrong, checked, nvlink = int(t[0]), int(t[1]), [int(t[2]), int(t[3])]
     else:
-        parity = {"pictures": 0, "equal": None, "against": "no golden digests for this workload"}
+        n_wrong = len(wrong)
+    parity = {"pictures": checked, "equal": (n_wrong == 0) if checked else None, "mismatched_pocs_rank0": wrong,
+              "against": "tests/golden/picture_hashes.json (reference svt_aom_motion_estimation_b64 + AVX2 kernels, all b64s, "
+                         "every product array)" if checked else "no golden digests for this workload"}
+    d2h = sum(sum(a.nbytes for a in outs[p].arrays.values()) for p in my_pocs)
     eng.close()
 
-    n_frames = 16 * args.steps * world
-    value = n_frames / dt_res
-    e2e = n_frames / dt_e2e
-    h2d = 16 * W * H  # the luma planes without their border: me_gpu_register_picture_unpadded pads on the device
-    d2h = sum(sum(a.nbytes for a in outs[p].arrays.values()) for p in STEP_POCS)
+    n_frames = 16 * steps * (1 if sharded else world)
+    value, e2e = n_frames / dt_res, n_frames / dt_e2e
+    h2d = len(my_pocs) * W * H  # luma planes without their border: me_gpu_register_picture_unpadded pads on the device
 
     # byte-SADs where they are executed: the 8x8-variance probes and the integer searches of <= 256 positions run inside k_hme,
     # only the tiled areas in k_fullsearch
@@ -474,7 +537,6 @@ def gpu_main(args):
     kernels = {
         "k_hme": {"ms_per_step": prof["k_search_ms"], "byte_sads_per_step": ops_hme},
         "k_fullsearch": {"ms_per_step": prof["k_fullsearch_ms"], "byte_sads_per_step": ops_tiles},
-        "k_ctrl": {"ms_per_step": prof["k_ctrl_ms"]},
         "k_epilogue": {"ms_per_step": prof["k_epilogue_ms"]},
     }
     dom = "k_hme" if prof["k_search_ms"] >= prof["k_fullsearch_ms"] else "k_fullsearch"
@@ -489,37 +551,82 @@ def gpu_main(args):
     # read from profiles/ncu_traffic.json, which names the capture and the commit each figure comes from
     traffic, traffic_source = None, None
     try:
-        e = json.load(open(os.path.join(REPO, "profiles", "ncu_traffic.json")))["entries"].get(f"{WORKLOAD}/{args.kind}/{dom}")
+        e = json.load(open(os.path.join(REPO, "profiles", "ncu_traffic.json")))["entries"].get(f"{WORKLOAD}/{kind}/{dom}")
         if e:
             traffic, traffic_source = e["dram_bytes_per_launch"], f"profiles/{e['capture']} (commit {e['commit']})"
     except Exception:
         pass
     roofline = {
         "bound": "int_sad", "bound_note": "integer ALU (packed byte-SAD issue rate, SURVEY 8(d)): the path is neither HBM- nor "
-        "tensor-bound; its HBM side is in traffic / hbm_gbs_achieved against hbm_peak_gbs", "kernel": dom, "achieved": achieved, "peak": sad_peak / 1e12, "unit": "Tbyte-SAD/s",
-        "frac": achieved / (sad_peak / 1e12) if sad_peak else None, "traffic": traffic, "traffic_source": traffic_source,
+        "tensor-bound; its HBM side is in traffic / hbm_gbs_achieved against hbm_peak_gbs", "kernel": dom, "achieved": achieved,
+        "peak": sad_peak / 1e12, "unit": "Tbyte-SAD/s", "frac": achieved / (sad_peak / 1e12) if sad_peak else None,
+        "traffic": traffic, "traffic_source": traffic_source,
         "traffic_unit": "DRAM bytes per launch (one picture); the three planes of a picture are 3.3 MB at 1080p, 12.4 MB at 4K",
         "hbm_gbs_achieved": (traffic * 16 / (dom_ms * 1e-3) / 1e9) if dom_ms > 0 and traffic else None,
         "peak_source": "VABSDIFF4.U8.ACC issue rate measured live by k_sad_peak on this GPU x 4 bytes",
-        "launches_per_step": 16,  # one k_hme, one k_fullsearch and one k_epilogue launch per picture
+        "launches_per_step": len(my_pocs),  # one k_hme, one k_fullsearch and one k_epilogue launch per picture (rank 0's pictures)
         "kernels": kernels, "serial_ms_per_step": prof["total_ms"],
         "whole_path_frac": (prof["ops"] / (prof["total_ms"] * 1e-3)) / sad_peak if sad_peak and prof["total_ms"] else None,
         "hbm_peak_gbs": peaks.get("hbm_gbs"),
     }
-
     cpu_baseline = None
-    if rank == 0 and world == 1 and not args.no_cpu:
+    if rank == 0 and world == 1 and with_cpu:
         threads = os.cpu_count() or 1
-        arm = CpuArm(args.kind, STEP_POCS)
+        arm = CpuArm(kind, STEP_POCS)
         cpu_baseline = arm.measure(threads, "avx2", 4.0)
         cpu_baseline["other_arms"] = [arm.measure(threads, "avx512", 3.0), arm.measure(1, "avx2", 3.0, max_reps=3)]
-        cpu_baseline["parity_equal"] = arm.parity(args.kind)
+        cpu_baseline["parity_equal"] = arm.parity(kind)
         cpu_baseline["host"] = host_info()
+    cfg = workload_config(kind)
+    cfg["mode"] = ("sharded: one stream, the step's pictures dealt round-robin in decode order over the ranks; owners upload, "
+                   "the others pull pyramids GPU to GPU (CUDA IPC + device-to-device copy over NVLink), no collective on the data path"
+                   if sharded else "replicas: every rank runs the whole step on its own copy of the stream" if world > 1 else "one GPU")
+    line = {
+        "metric": "open-loop ME frames/sec", "value": value, "unit": "frames/s", "n_gpus": world, "steps": steps,
+        "warmup": warmup, "ms_per_step": 1e3 * dt_res / steps, "higher_is_better": True,
+        "scaling": "strong" if sharded else "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": cfg,
+        "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": 16 * W * H * (1 if sharded else world),
+                "d2h_bytes_per_step": d2h * (world if not sharded else 1), "ms_per_step": 1e3 * dt_e2e / steps,
+                "h2d_gbs_per_rank": h2d / (dt_e2e / steps) / 1e9, "d2h_gbs_per_rank": d2h / (dt_e2e / steps) / 1e9},
+        "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline, "parity": parity,
+        "host": {"cpus": os.cpu_count()},
+    }
+    if sharded:
+        line["nvlink_bytes_per_step"] = nvlink[1] / (steps + warmup)  # all ranks, e2e arm, warm-up steps counted on both sides
+        line["peer_copy_verified"] = peer_verified
+        line["pictures_per_rank_per_step"] = len(my_pocs)
+    return line
+
+
+def gpu_main(args):
+    import torch
+    import torch.distributed as dist
+
+    rank, local_rank, world = rank_info()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the engine has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    numa_cpus = bind_to_gpu_numa(local_rank) if world > 1 else None
+    ctl = init_dist(torch, dist, local_rank, world)
+    mode = args.mode or ("sharded" if world > 1 and WORKLOAD.startswith("4k") else "replicas")
+    line = measure(args, args.kind, mode, args.steps, args.warmup, torch, dist, ctl, with_cpu=not args.no_cpu)
+    line["host"]["rank0_numa_cpus"] = len(numa_cpus) if numa_cpus else None
+    ok = line["parity"]["equal"] is not False
+    if world > 1 and mode == "replicas" and args.extra:
+        # the multi-GPU path north_star describes, on BASELINE configs[2], in the same launch: one 4K stream sharded over the ranks
+        main_wl = WORKLOAD
+        set_workload("4k-m2")
+        sh = measure(args, "motion", "sharded", max(3, args.steps), args.warmup, torch, dist, ctl, with_cpu=False)
+        set_workload(main_wl)
+        line["sharded_4k"] = {k: sh[k] for k in ("value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "scaling", "config", "e2e",
+                                                  "parity", "nvlink_bytes_per_step", "peer_copy_verified", "pictures_per_rank_per_step",
+                                                  "clocks")}
+        ok = ok and sh["parity"]["equal"] is not False
     extra = None
     if rank == 0 and world == 1 and args.extra and WORKLOAD == "1080p-m4" and args.kind == "motion":
-        # the same measurement on the configurations where the integer full search dominates (worst-case "iid" input:
-        # no early exits, every search area at its configured size), each in a process of its own, after this one's
-        # engine is closed; they explain the path's integer-SAD roofline, the headline stays the workload above
+        # the same measurement on the other configurations (worst-case "iid" input: no early exits, every search area at its
+        # configured size - the cases where the integer full search dominates - and BASELINE configs[2]), each in a process of
+        # its own after this one's engine is closed; the headline stays the workload above
         import subprocess
         extra = []
         for wl, kind in (("1080p-m4", "iid"), ("4k-m2", "motion"), ("4k-m0", "iid")):
@@ -533,21 +640,12 @@ def gpu_main(args):
                               "roofline": {k: d["roofline"][k] for k in ("kernel", "achieved", "peak", "unit", "frac", "kernels")}})
             except Exception as e:  # reported, never silent
                 extra.append({"workload": wl, "sequence": kind, "error": repr(e)[:200]})
+    line["extra_workloads"] = extra
     if rank == 0:
-        line = {
-            "metric": "open-loop ME frames/sec", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * dt_res / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": workload_config(args.kind),
-            "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": 1e3 * dt_e2e / args.steps},
-            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
-            "result_checksum": checksum, "parity": parity, "extra_workloads": extra,
-            "host": {"cpus": os.cpu_count(), "rank0_numa_cpus": len(numa_cpus) if numa_cpus else None},
-        }
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
-    return 0 if parity["equal"] is not False else 3  # results that differ from the reference's are not a benchmark
+    return 0 if ok else 3  # results that differ from the reference's are not a benchmark
 
 
 def main():
@@ -560,6 +658,9 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-extra", dest="extra", action="store_false",
                     help="skip the runs of the other configurations (1080p-m4 iid, 4k-m2 motion, 4k-m0 iid) appended as extra_workloads at N=1")
+    ap.add_argument("--mode", default=None, choices=["replicas", "sharded"],
+                    help="N > 1: replicas = every rank its own copy of the stream (weak scaling; default at 1080p, configs[3]); sharded = "
+                         "one stream, pictures dealt over the ranks, pyramids pulled GPU to GPU (strong scaling; default for the 4K workloads)")
     ap.add_argument("--workload", default="1080p-m4", choices=sorted(WORKLOADS),
                     help="BASELINE.json config to run (default: configs[1], the one the metric is quoted on at N=1)")
     args = ap.parse_args()

@@ -238,6 +238,23 @@ int me_gpu_read_pyramid(uint64_t picture_number, uint8_t *full, uint8_t *quarter
 int me_gpu_plane_geometry(int width, int height, int level, int *plane_w, int *plane_h, int *pad, int *stride,
                           int *rows);
 
+/* one process per GPU ---------------------------------------------------------
+ * Every process runs its own engine on its own GPU and owns the pictures it registered. A picture another process needs
+ * as a reference is pulled from the owner's pool over NVLink: device-to-device through a CUDA IPC mapping of that pool,
+ * ordered by the owner's (interprocess) pyramid-complete event. No collective, no host copy. The encoder's equivalent is
+ * nothing (one process, shared memory): pictures are simply visible to all ME threads (me_process.c:248-262).
+ *   owner:    me_gpu_ipc_export_pool once; per picture me_gpu_ipc_picture AFTER me_gpu_register_picture returned
+ *   consumer: me_gpu_ipc_open_peer once per owner; per picture me_gpu_register_picture_from_peer with what the owner's
+ *             me_gpu_ipc_picture returned (carried between the processes by any means: 4 + 64 bytes)
+ * The owner must keep the picture registered until the consumer's copy has run (the consumer's me_gpu_wait of any job that
+ * reads the picture, or its me_gpu_release_picture, implies it). Both pools must be created with the same maximum size. */
+int me_gpu_ipc_export_pool(unsigned char handle[64], uint64_t *slot_bytes);
+int me_gpu_ipc_open_peer(int peer, const unsigned char handle[64], uint64_t slot_bytes);
+int me_gpu_ipc_picture(uint64_t picture_number, int *slot, unsigned char event_handle[64]);
+int me_gpu_register_picture_from_peer(uint64_t picture_number, int peer, int peer_slot, const unsigned char event_handle[64],
+                                      int width, int height);
+uint64_t me_gpu_ipc_bytes_pulled(void); /* bytes copied from peers' pools so far */
+
 /* motion estimation ----------------------------------------------------------------------- */
 int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
                   const uint64_t ref_picture_numbers[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS]);

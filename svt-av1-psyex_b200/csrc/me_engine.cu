@@ -37,6 +37,9 @@ struct Slot {
     bool        release_pending = false;
     bool        ready_seen[8] = {}; /* the host has observed ready[dev] complete: no stream wait needed */
     cudaEvent_t ready[8] = {}; /* per device: pyramid complete on that device */
+    cudaEvent_t ipc_ready = nullptr; /* interprocess twin of ready[0], created when the picture is first exported to another process
+                                        (a stream of another device of THIS process must not wait on an interprocess event:
+                                        the driver faults) */
 };
 
 /* uploaded in one copy at submit; the tail (list header + counters) comes back in one copy */
@@ -152,6 +155,9 @@ struct Engine {
     std::condition_variable cv; /* a job was retired */
     bool                profiling = false;
     uint64_t            ticket = 0; /* submissions so far: orders the jobs of one picture */
+    struct Peer { bool open = false; uint8_t *base = nullptr; uint64_t slot_bytes = 0; std::map<int, cudaEvent_t> ev; };
+    Peer                peers[16]; /* picture pools of other processes (one per GPU) mapped through CUDA IPC */
+    uint64_t            peer_bytes = 0; /* bytes pulled from peers so far (NVLink) */
     uint64_t            done_ring[64] = {}; /* picture numbers of the last retired jobs (me_gpu_wait_done after the retirement) */
     bool                done_valid[64] = {};
     unsigned            done_next = 0;
@@ -380,9 +386,17 @@ void me_gpu_shutdown(void) {
         cudaFree(d.pool);
         cudaFree(d.stage);
     }
-    for (auto &s : g.slots)
+    for (auto &pr : g.peers) {
+        for (auto &kv : pr.ev) cudaEventDestroy(kv.second);
+        pr.ev.clear();
+        if (pr.open) cudaIpcCloseMemHandle(pr.base);
+        pr = Engine::Peer();
+    }
+    for (auto &s : g.slots) {
         for (auto &e : s.ready)
             if (e) cudaEventDestroy(e);
+        if (s.ipc_ready) cudaEventDestroy(s.ipc_ready);
+    }
     g.dev.clear();
     g.slots.clear();
     g.by_number.clear();
@@ -525,6 +539,127 @@ int me_gpu_release_picture(uint64_t picture_number) {
     g.slots[s].release_pending = true;
     free_slot_if_idle(s);
     return ME_GPU_OK;
+}
+
+/* ---- one process per GPU: pyramids travel between the processes' pools over NVLink (CUDA IPC), no collective ---------- */
+int me_gpu_ipc_export_pool(unsigned char handle[64], uint64_t *slot_bytes) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.initialised)
+        return fail(ME_GPU_ERR_STATE, "not initialised");
+    if (!handle || !slot_bytes)
+        return fail(ME_GPU_ERR_BAD_ARG, "null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64 && sizeof(cudaIpcEventHandle_t) == 64, "IPC handles are 64 bytes");
+    CU(cudaSetDevice(g.dev[0].id));
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, g.dev[0].pool));
+    memcpy(handle, &h, 64);
+    *slot_bytes = g.gmax.slot_bytes;
+    return ME_GPU_OK;
+}
+
+int me_gpu_ipc_open_peer(int peer, const unsigned char handle[64], uint64_t slot_bytes) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.initialised)
+        return fail(ME_GPU_ERR_STATE, "not initialised");
+    if (peer < 0 || peer >= 16 || !handle)
+        return fail(ME_GPU_ERR_BAD_ARG, "peer index out of range");
+    if (slot_bytes != g.gmax.slot_bytes)
+        return fail(ME_GPU_ERR_BAD_ARG, "the peer's pool was sized for another maximum picture size");
+    if (g.peers[peer].open)
+        return fail(ME_GPU_ERR_STATE, "peer already open");
+    CU(cudaSetDevice(g.dev[0].id));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    void *base = nullptr;
+    CU(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+    g.peers[peer].open       = true;
+    g.peers[peer].base       = (uint8_t *)base;
+    g.peers[peer].slot_bytes = slot_bytes;
+    return ME_GPU_OK;
+}
+
+int me_gpu_ipc_picture(uint64_t picture_number, int *slot, unsigned char event_handle[64]) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.initialised)
+        return fail(ME_GPU_ERR_STATE, "not initialised");
+    auto it = g.by_number.find(picture_number);
+    if (it == g.by_number.end() || !slot || !event_handle)
+        return fail(ME_GPU_ERR_NOT_FOUND, "picture not registered");
+    CU(cudaSetDevice(g.dev[0].id));
+    Slot &sl = g.slots[it->second];
+    if (!sl.ipc_ready)
+        CU(cudaEventCreateWithFlags(&sl.ipc_ready, cudaEventDisableTiming | cudaEventInterprocess));
+    /* everything that fills this device's copy of the slot went through the upload stream: a marker behind it */
+    CU(cudaEventRecord(sl.ipc_ready, g.dev[0].upload));
+    cudaIpcEventHandle_t h;
+    CU(cudaIpcGetEventHandle(&h, sl.ipc_ready));
+    memcpy(event_handle, &h, 64);
+    *slot = it->second;
+    return ME_GPU_OK;
+}
+
+int me_gpu_register_picture_from_peer(uint64_t picture_number, int peer, int peer_slot, const unsigned char event_handle[64],
+                                      int width, int height) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    if (!g.initialised)
+        return fail(ME_GPU_ERR_STATE, "not initialised");
+    if (peer < 0 || peer >= 16 || !g.peers[peer].open || peer_slot < 0 || !event_handle)
+        return fail(ME_GPU_ERR_BAD_ARG, "peer not open");
+    if (width <= 0 || height <= 0 || (width & 7) || (height & 7) || width > g.gmax.width || height > g.gmax.height)
+        return fail(ME_GPU_ERR_BAD_ARG, "bad picture geometry");
+    if (g.by_number.count(picture_number))
+        return fail(ME_GPU_ERR_STATE, "picture already registered");
+    int s = -1;
+    for (int i = 0; i < g.nslots; i++)
+        if (!g.slots[i].used) {
+            s = i;
+            break;
+        }
+    if (s < 0)
+        return fail(ME_GPU_ERR_NO_MEMORY, "picture pool is full (raise pictures_in_flight or release pictures)");
+    Engine::Peer &pr = g.peers[peer];
+    Device       &d  = g.dev[0];
+    CU(cudaSetDevice(d.id));
+    cudaEvent_t ev = nullptr;
+    auto        f  = pr.ev.find(peer_slot);
+    if (f == pr.ev.end()) { /* one event per peer slot for the life of the engine */
+        cudaIpcEventHandle_t h;
+        memcpy(&h, event_handle, 64);
+        CU(cudaIpcOpenEventHandle(&ev, h));
+        pr.ev[peer_slot] = ev;
+    } else
+        ev = f->second;
+    MePicGeom gm;
+    me_make_geom(&gm, width, height);
+    /* the owner recorded the event behind its pyramid kernels before it handed out the handle: the copy starts after them */
+    CU(cudaStreamWaitEvent(d.upload, ev, 0));
+    CU(cudaMemcpyAsync(d.pool + (size_t)s * g.gmax.slot_bytes, pr.base + (size_t)peer_slot * pr.slot_bytes, gm.slot_bytes,
+                       cudaMemcpyDeviceToDevice, d.upload));
+    g.peer_bytes += gm.slot_bytes;
+    Slot &sl          = g.slots[s];
+    sl.used           = true;
+    sl.picture_number = picture_number;
+    sl.width          = width;
+    sl.height         = height;
+    sl.refcount       = 0;
+    sl.release_pending = false;
+    for (auto &v : sl.ready_seen) v = false;
+    g.by_number[picture_number] = s;
+    CU(cudaEventRecord(sl.ready[0], d.upload));
+    for (size_t o = 1; o < g.dev.size(); o++) { /* several devices in this process as well: replicate as usual */
+        Device &p2 = g.dev[o];
+        CU(cudaSetDevice(p2.id));
+        CU(cudaStreamWaitEvent(p2.upload, sl.ready[0], 0));
+        CU(cudaMemcpyPeerAsync(p2.pool + (size_t)s * g.gmax.slot_bytes, p2.id, d.pool + (size_t)s * g.gmax.slot_bytes, d.id,
+                               g.gmax.slot_bytes, p2.upload));
+        CU(cudaEventRecord(sl.ready[o], p2.upload));
+    }
+    return ME_GPU_OK;
+}
+
+uint64_t me_gpu_ipc_bytes_pulled(void) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    return g.peer_bytes;
 }
 
 int me_gpu_read_pyramid(uint64_t picture_number, uint8_t *full, uint8_t *quarter, uint8_t *sixteenth) {

@@ -159,6 +159,8 @@ GPU_SYMBOLS = [
     "me_gpu_submit", "me_gpu_wait", "me_gpu_derive_params", "me_gpu_get_timings", "me_gpu_measure_sad_peak", "me_gpu_set_profiling", "me_gpu_submit_out", "me_gpu_output_layout",
     "me_gpu_dg_detector", "me_gpu_derive_params_tf",
     "me_gpu_wait_pair", "me_gpu_cancel", "me_gpu_wait_done",
+    "me_gpu_ipc_export_pool", "me_gpu_ipc_open_peer", "me_gpu_ipc_picture", "me_gpu_register_picture_from_peer",
+    "me_gpu_ipc_bytes_pulled",
     "me_gpu_dg_detector_noalloc", "me_gpu_dg_detector_noalloc_setup", "me_gpu_dg_detector_noalloc_error",
 ]
 
@@ -179,6 +181,11 @@ def load_gpu_lib():
     lib.me_gpu_wait.argtypes = [u64, C.POINTER(MeGpuOutputs)]
     lib.me_gpu_wait_pair.argtypes = [u64, u8, u64, C.POINTER(MeGpuOutputs)]
     lib.me_gpu_cancel.argtypes = [u64]
+    lib.me_gpu_ipc_export_pool.argtypes = [C.c_char_p, C.POINTER(u64)]
+    lib.me_gpu_ipc_open_peer.argtypes = [C.c_int, C.c_char_p, u64]
+    lib.me_gpu_ipc_picture.argtypes = [u64, C.POINTER(C.c_int), C.c_char_p]
+    lib.me_gpu_register_picture_from_peer.argtypes = [u64, C.c_int, C.c_int, C.c_char_p, C.c_int, C.c_int]
+    lib.me_gpu_ipc_bytes_pulled.restype = u64
     lib.me_gpu_wait_done.argtypes = [u64]
     lib.me_gpu_submit_out.argtypes = [u64, C.POINTER(MeGpuParams), C.POINTER(RefNumbers), C.POINTER(MeGpuOutputs)]
     lib.me_gpu_output_layout.argtypes = [C.c_int, C.c_int, C.POINTER(MeGpuParams), C.POINTER(C.c_size_t * 11),

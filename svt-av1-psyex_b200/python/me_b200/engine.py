@@ -63,6 +63,26 @@ class Engine:
     def register_picture_unpadded_ptr(self, picture_number, ptr, stride, width, height):
         self._check(self.lib.me_gpu_register_picture_unpadded(picture_number, ptr, stride, width, height))
 
+    # one process per GPU: pyramids pulled from the owner's pool over NVLink (CUDA IPC) ---------------
+    def ipc_export_pool(self):
+        h, sb = C.create_string_buffer(64), abi.u64(0)
+        self._check(self.lib.me_gpu_ipc_export_pool(h, C.byref(sb)))
+        return h.raw, sb.value
+
+    def ipc_open_peer(self, peer, handle, slot_bytes):
+        self._check(self.lib.me_gpu_ipc_open_peer(peer, handle, slot_bytes))
+
+    def ipc_picture(self, picture_number):
+        slot, h = C.c_int(0), C.create_string_buffer(64)
+        self._check(self.lib.me_gpu_ipc_picture(picture_number, C.byref(slot), h))
+        return slot.value, h.raw
+
+    def register_picture_from_peer(self, picture_number, peer, peer_slot, event_handle, width, height):
+        self._check(self.lib.me_gpu_register_picture_from_peer(picture_number, peer, peer_slot, event_handle, width, height))
+
+    def ipc_bytes_pulled(self):
+        return int(self.lib.me_gpu_ipc_bytes_pulled())
+
     def release_picture(self, picture_number):
         self._check(self.lib.me_gpu_release_picture(picture_number))
 

@@ -15,3 +15,8 @@ def pyramids_needed(pocs, ref_lists_of):
         l0, l1 = ref_lists_of(poc)
         need.update([poc], l0, l1)
     return sorted(need)
+
+
+def owners(decode_order_pocs, world):
+    """picture -> rank that uploads it and runs its ME: the sequence's decode order dealt round-robin"""
+    return {poc: i % world for i, poc in enumerate(decode_order_pocs)}
