@@ -2,30 +2,26 @@
  * me_hme.cu - k_hme: the whole per-b64 chain of open-loop ME up to (and including) the small integer
  * searches, in ONE launch per picture.
  *
- * One CTA per 64x64 block, ONE WARP PER SEARCHED REFERENCE. The reference's per-b64 algorithm
- * (motion_estimation.c:3076-3153) is a chain of searches per (list, reference) - zero-MV SAD, pre-HME, HME level
- * 0 / 1 / 2, check_00_center, 8x8-variance probe, integer search - in which every search window depends on the
- * previous search of the SAME reference, and only four steps look across references (zero-MV pruning, pre-HME
- * pruning, final centre + HME pruning, and the epilogue). So a warp owns the chain of its reference from end to
- * end: it runs the control code of me_ctrl.h for its reference (lane 0), fetches its own search windows by TMA
- * into its own double-buffered slice of shared memory, searches them with all 32 lanes, and meets the other
- * warps of the block only at the (at most four) CTA barriers where the reference's code looks across references.
- * No warp ever waits for another reference's search, for a planning step, or for a producer warp.
+ * One CTA (4 warps) per 64x64 block. The block's MeContext state (B64State), its search tasks and their
+ * results live in shared memory for the whole chain; nothing goes through HBM between stages and there is
+ * no launch boundary between them (b64s are independent of each other: motion_estimation.c keeps no
+ * cross-b64 state):
  *
- * The block's MeContext state (B64State), the search tasks and results and the block's source pixels on the three
- * planes live in shared memory for the whole chain; nothing goes through HBM between stages.
+ *   for every stage of me_ctrl.h (init/zz, pre-HME, HME L0, L1, L2, centre, probe, main):
+ *       thread 0   runs the integer control stage on the shared-memory state -> up to 32 tasks
+ *       warp 0     cuts the tasks into work items (bands of search rows) of similar cost
+ *       4 warps    pull items from a shared counter, execute them on their own 8 KB staging buffer and
+ *                  merge (sad, scan index) keys with a shared-memory atomicMin per task
  *
- * Search executors (all SADs are VABSDIFF4.U8.ACC on 32-bit words; the window arrives 16-byte aligned from TMA and
- * unaligned reference words are built with funnel shifts):
- *   hm_job_search8      wide areas of 16-byte block rows (pre-HME region 1, HME level 0): lane = 8 positions of one
- *                       32-byte window segment
- *   hm_job_search_tall  8-wide, hundreds of rows (pre-HME region 0): lane = 2 positions x 4 search rows
- *   hm_job_search<KX>   everything else (HME level 1 / 2, zero-MV and centre SADs): unit = KX positions, spread
- *                       over column segments x row groups of lanes
- *   search_item         generic fallback (picture-edge blocks of odd widths): window staged with LDG
- *   fullsearch_item     open_loop_me_fullpel_search_sblock for the probe and for search areas of up to
- *                       FS_WARP_MAX positions: lane = two 8x8 blocks (z-order), the 85 square-PU SADs by butterflies
- * Larger integer-search areas are cut into tiles and appended to the work list of k_fullsearch.
+ * Item executors (all SADs are VABSDIFF4.U8.ACC on 32-bit words; unaligned reference words are built with
+ * funnel shifts from the aligned shared-memory words):
+ *   lane = search position, whole block per lane: the 16x8 blocks of pre-HME / HME-L0
+ *   lane = (block row, 16-byte chunk), positions in sequence, redux.sync.add per position: big blocks with
+ *          few positions (HME-L1/L2, zero-MV and centre SADs)
+ *   fullsearch_item: lane = two 8x8 blocks (z-order): the 85 square-PU SADs of a position by shuffle
+ *          butterflies, 7 running (sad, position) bests per lane in scan order (8x8-variance probe and search
+ *          areas of up to FS_WARP_MAX positions)
+ * Larger search areas are cut into 64x32-position tiles and appended to the work list of k_fullsearch.
  */
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -36,7 +32,11 @@
 #include "me_ctrl.h"
 #include "me_kernels.h"
 
-#define HM_MAXW ME_NREF /* warps per CTA: one per searched (list, reference) */
+#define HM_WARPS 4
+#define HM_THREADS (HM_WARPS * 32) /* search threads */
+#define HM_ALL_THREADS (HM_THREADS + 32) /* + the warp that requests the windows (TMA) */
+#define HM_BUF_WORDS 2048 /* per-warp staging buffer: source block (<= 512 words) + reference window (15 rows x
+                             131 words of the widest pre-HME strip fit; taller windows are banded) */
 #ifndef FS_WARP_MAX
 #define FS_WARP_MAX 256
 #endif
@@ -44,44 +44,48 @@
 #ifndef FS_WARP_MAXW
 #define FS_WARP_MAXW 48
 #endif
+#define HM_ITEM_POS_A 384 /* search positions per work item, lane = position */
+#define HM_ITEM_POS_B 32 /* ... lane = block row */
+#define HM_ITEM_POS_FS 16 /* ... full-search positions */
+
+#define HM_RAW_BYTES 16384 /* largest window of a job: half of the ring */
 
 /* source-block pitches in shared memory (words): padded so that lanes on different block rows hit different banks */
 #define HM_SRC0_PITCH 24
 #define HM_SRC1_PITCH 12
 #define HM_SRC2_PITCH 4
 
-struct HmPlan { /* how a task is cut into window jobs */
+struct HmPlan { /* how a task is cut into jobs (written by warp 0 at the start of a stage) */
     int16_t pwb, neb; /* positions per x band, evaluated rows per y band */
     uint8_t nxb, nyb, map, kx;
-    uint8_t g_log2, new_path, pad_[2];
+    uint8_t g_log2, new_path, team /* warps that search a job: 1 or 2 for jobs of few units, else 4 */, pad_;
 };
 
 struct HmJobD { /* one window job, 32 bytes */
     int16_t  px0, pw, e0, ne; /* band of search positions: columns [px0, px0 + pw), evaluated rows [e0, e0 + ne) */
     int16_t  xt, y0; /* TMA column (multiple of 16) and row of the window */
-    uint16_t pitch; /* bytes per window row = box width of the job's tensor map */
+    uint16_t off128; /* window offset in the ring, in 128-byte units */
     uint16_t nrows; /* window rows (whole boxes) */
     uint16_t total; /* lanes' worth of work of the SAD loop: units x lanes per unit */
     uint8_t  task, map, aoff /* byte offset of position px0 in a window row */, ncls, nchunk;
-    uint8_t  brows; /* rows per TMA box */
+    int8_t   dep; /* last earlier job of the stage whose window overlaps this one (-1: none) */
     uint32_t m_chunk, m_cls;
 };
-#define HM_ROUND 16 /* window jobs decoded at a time (one lane each) */
-#define HM_TASKS 4 /* search tasks of one reference in one stage: 4 quadrants / 2 regions / 2 centre SADs */
+#define HM_MAXJOBS 32 /* window jobs per stage; tasks beyond go to the per-warp path */
+#define HM_NBAR 8 /* window jobs in flight (ring of job descriptors and mbarriers) */
+#define HM_RING_BYTES (2 * HM_RAW_BYTES)
 
-/* planner thresholds (measured in round 1): areas at least this wide / with at least this many 8-position units take
- * hm_job_search8; 8-wide areas of at least this many rows take hm_job_search_tall */
+#ifdef ME_HME_TRACE
+__device__ unsigned g_trace_cnt;
+#endif
+/* planner thresholds (swept in round 1, +-1 % around these): search areas at least this wide / with at least this many
+   8-position units take hm_job_search8; jobs of up to HM_TEAM1_UNITS units are searched by one warp each; 8-wide areas
+   of at least HM_TALL_MIN_ROWS rows take hm_job_search_tall */
 #define HM_K8_MIN_PW 32
 #define HM_K8_MIN_UNITS 64
+#define HM_TEAM1_UNITS 16
+#define HM_LANES_TARGET 96
 #define HM_TALL_MIN_ROWS 32
-
-struct HmWarp { /* private to one warp */
-    alignas(8) unsigned long long mbar[2]; /* TMA completion of the two windows in flight */
-    HmJobD   jobs[HM_ROUND];
-    HmPlan   plan[HM_TASKS];
-    uint16_t job_first[HM_TASKS + 1]; /* prefix sums of the window jobs over the stage's tasks */
-    uint16_t pad_[3];
-};
 
 struct HmeShared {
     B64State           s;
@@ -89,16 +93,22 @@ struct HmeShared {
     SearchResult       r[ME_SLOTS];
     FsTask             f[ME_NREF];
     unsigned long long tkey[ME_SLOTS]; /* best (sad << 32 | scan index) of each search task */
-    MeGpuParams        p; /* the picture's controls: the control code reads them hundreds of times */
+    uint16_t           item_first[ME_SLOTS + 1]; /* prefix sums: items of task i are [first[i], first[i+1]) */
+    uint16_t           item_rows[ME_SLOTS]; /* search rows per item */
+    int                next_item;
+    int                team; /* warps per window job in this round (4 / team jobs are searched at a time) */
+    int                next_lo; /* first task of the next round of window jobs */
+    HmPlan             plan[ME_SLOTS];
+    uint16_t           job_first[ME_SLOTS + 1]; /* prefix sums of the window jobs */
+    MeGpuParams        p; /* the picture's controls: the control stages read them hundreds of times, one dependent load each */
+    alignas(8) unsigned long long mbar[HM_NBAR]; /* TMA completion of the windows in flight */
+    HmJobD             jobs[HM_MAXJOBS];
     alignas(16) uint32_t src0[64 * HM_SRC0_PITCH], src1[32 * HM_SRC1_PITCH], src2[16 * HM_SRC2_PITCH]; /* the b64's source block on the three planes (padded pitches) */
-    /* HmWarp[nwarps] and then the warps' window rings follow (ring_bytes each, 128-byte aligned) */
+    /* per-warp staging buffers of the item path; the two window buffers of the job path alias them
+       (2 x HM_RAW_BYTES + 128 bytes of slack for masked over-reads) */
+    alignas(128) uint32_t buf[HM_WARPS][HM_BUF_WORDS + 8];
 };
-#define HM_FIXED_BYTES ((sizeof(HmeShared) + 127) & ~(size_t)127)
-#define HM_WARP_BYTES(nw) ((sizeof(HmWarp) * (size_t)(nw) + 127) & ~(size_t)127)
-/* registers per thread. Measured (1080p preset 4, frames/s): 128 -> 4530, 96 -> 4260, 80 -> 4250, 64 -> 3990: the spills cost more than the extra resident CTAs bring */
-#ifndef HM_MAXREG
-#define HM_MAXREG 128
-#endif
+static_assert(sizeof(uint32_t) * HM_WARPS * (HM_BUF_WORDS + 8) >= 2 * HM_RAW_BYTES + 128, "window buffers alias the warp buffers");
 
 __device__ __forceinline__ uint32_t hm_vsad4(uint32_t a, uint32_t b, uint32_t c) {
     uint32_t d;
@@ -125,12 +135,13 @@ __device__ __forceinline__ void hm_stage_window(uint32_t *win, const uint32_t *g
         win[i]      = __ldg(g0 + (size_t)r * stride_words + cw);
     }
 }
+
 /* ------------------------------------------------------------------------------------------------
  * svt_sad_loop_kernel_c over the evaluated search rows [e_lo, e_hi) of one task, executed by one warp.
  * Returns the warp's best (sad << 32 | scan index) key (the same value in every lane).
  * ---------------------------------------------------------------------------------------------- */
 __device__ unsigned long long search_item(const SearchTask &t, int e_lo, int e_hi, const MeJob *j, const uint8_t *pool,
-                                          uint32_t *buf, int buf_words, unsigned int *overflow, int lane) {
+                                          uint32_t *buf, unsigned int *overflow, int lane) {
     const MePlaneGeom &pl   = j->g.plane[t.level];
     const uint8_t     *srcp = hm_plane(pool, j->g, j->src_slot, t.level);
     const uint8_t     *refp = hm_plane(pool, j->g, t.ref_slot, t.level);
@@ -140,7 +151,7 @@ __device__ unsigned long long search_item(const SearchTask &t, int e_lo, int e_h
     const int          stride_words = pl.stride >> 2;
     const int          src_words = rows * nwp;
     uint32_t          *srcw = buf, *win = buf + src_words;
-    const int          win_cap = buf_words - src_words;
+    const int          win_cap = HM_BUF_WORDS - src_words;
     const unsigned long long none = ((unsigned long long)ME_SAD_LOOP_INIT << 32) | 0xFFFFFFFFull;
 
     /* source block -> shared words, zero beyond the block width (source rows are 4-byte aligned) */
@@ -301,6 +312,21 @@ __device__ unsigned long long search_item(const SearchTask &t, int e_lo, int e_h
         }
     return key;
 }
+
+/* ------------------------------------------------------------------------------------------------
+ * Window jobs: the whole CTA works on one search window at a time.
+ *
+ * A job is a band of a task's search area (all of it when the window fits). Its reference window is
+ * fetched by TMA (cp.async.bulk.tensor: one box, or a few stacked ones, form a dense row-major window whose
+ * row pitch is the box width) one job ahead of the SAD loop, into one of two buffers, and completes on the
+ * buffer's mbarrier. TMA boxes start on 16-byte columns, so search position x sits at byte
+ * aoff + x of a window row; unaligned words are funnel-shifted in registers.
+ *
+ * SAD loop: a unit = KX positions of one search row that share their byte alignment (x = ca + 4k), so
+ * that the NW + KX - 1 shifted reference words of a block row feed NW * KX VABSDIFF4; units of small
+ * search areas are split over G lanes by block rows and joined by shuffles. Results merge as
+ * (sad << 32 | scan index) keys: the minimum key is the first minimum of the reference's scan.
+ * ---------------------------------------------------------------------------------------------- */
 __device__ __forceinline__ uint32_t hm_smem(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void hm_mbar_init(uint32_t bar, uint32_t count) {
@@ -338,19 +364,18 @@ __host__ __device__ __forceinline__ int hm_map_rows(int m) {
     return m == 0 ? 64 : m == 1 ? 56 : m == 2 ? 24 : m == 3 ? 40 : 72;
 }
 
-/* cut one task into window jobs of at most `cap` bytes each; false when it cannot be done (picture-edge blocks of odd
- * widths, windows taller than the budget): the task then takes the generic path */
-__device__ bool hm_plan_try(const SearchTask &t, const MeJob *j, int org_x, int org_y, int cap, HmPlan &pl) {
+/* cut one task into window jobs (or leave it to the per-warp path: picture-edge blocks) */
+__device__ void hm_plan_task(const SearchTask &t, const MeJob *j, int org_x, int org_y, HmPlan &pl) {
     pl.new_path = 0;
     pl.nxb = pl.nyb = 0;
     const int lv = t.level, full = 64 >> lv;
     if (t.bw != full || t.sx != (org_x >> lv) || t.sy != (org_y >> lv) || (int)t.rows * t.row_step > full || t.sa_w < 1)
-        return false;
+        return;
     const MePlaneGeom &g    = j->g.plane[lv];
     const bool         skip = t.bw == 16 && t.rows <= 16 && t.skip_line;
     const int          ymul = skip ? 2 : 1, erows = skip ? (t.sa_h >> 1) : t.sa_h;
     if (erows < 1)
-        return false;
+        return;
     const int span = (t.rows - 1) * t.row_step;
     const int a16  = (g.pad + t.rx) & 15;
     const int first = lv == 2 ? 0 : lv == 1 ? 3 : 4, last = lv == 2 ? 2 : lv == 1 ? 3 : 5;
@@ -364,29 +389,39 @@ __device__ bool hm_plan_try(const SearchTask &t, const MeJob *j, int org_x, int 
     int       map  = first;
     while (map < last && hm_map_width(map) < need) map++;
     const int pitch    = hm_map_width(map);
-    const int rows_cap = (cap / pitch) / hm_map_rows(map) * hm_map_rows(map);
+    const int rows_cap = (HM_RAW_BYTES / pitch) / hm_map_rows(map) * hm_map_rows(map);
     const int ne_max   = (rows_cap - span - 1) / ymul + 1;
     if (rows_cap < span + 1 || ne_max < 1 || nxb > 255)
-        return false;
+        return;
     int       kx      = (t.bw == 16 && pwb >= 16) ? 4 : 2;
     const int ncls    = min(4, pwb), per_cls = (pwb + 3) >> 2, nchunk = (per_cls + kx - 1) / kx;
     const int nyb = (erows + ne_max - 1) / ne_max, neb = (erows + nyb - 1) / nyb;
     if (nyb > 255)
-        return false;
+        return;
     int       units   = ncls * nchunk * neb;
     /* wide areas of 16-byte block rows: units of 8 positions on 32-byte window segments (hm_job_search8), one lane each */
     const bool wide = t.bw == 16 && pwb >= HM_K8_MIN_PW && 4 * ((pwb + 31) >> 5) * neb >= HM_K8_MIN_UNITS;
-    if (wide)
-        kx = 8;
+    if (wide) {
+        kx    = 8;
+        units = 4 * (((15 + pwb - 1) >> 5) + 1) * neb;
+    }
     /* tall thin areas (pre-HME region 0: 8 positions wide, hundreds of rows) of 16x8-row blocks: hm_job_search_tall */
-    const bool tall = !wide && t.bw == 16 && t.rows == 8 && nxb == 1 && pwb <= 8 && neb >= HM_TALL_MIN_ROWS && t.row_step % ymul == 0;
-    if (tall)
-        kx = 1;
+    const bool tall = !wide && HM_TALL_MIN_ROWS > 0 && t.bw == 16 && t.rows == 8 && nxb == 1 && pwb <= 8 && neb >= HM_TALL_MIN_ROWS &&
+                      t.row_step % ymul == 0;
+    if (tall) {
+        const int ys = t.row_step / ymul;
+        kx    = 1;
+        units = 4 * ys * ((neb + 4 * ys - 1) / (4 * ys));
+    }
+    const int win     = pitch * (((neb - 1) * ymul + span + 1 + hm_map_rows(map) - 1) / hm_map_rows(map) * hm_map_rows(map));
+    /* jobs of few units are searched by one warp each, four at a time per CTA, when four windows fit the ring (measured:
+       two warps per job with the next batch in flight is slower than one warp per job and no prefetch of the next batch) */
+    pl.team = (uint8_t)(!wide && !tall && units <= HM_TEAM1_UNITS && win <= HM_RING_BYTES / 4 ? 1 : 4);
     int g_log2 = 2 - lv; /* lanes per unit: the 16-byte column segments of the block row ... */
     if (tall)
         g_log2 = 0;
-    else if (!wide) {
-        /* ... x row groups: the split with the fewest (passes over the warp) x (block rows per lane); ties keep the
+    else if (!wide && pl.team < 4) {
+        /* one warp per job: the split with the fewest (passes over the warp) x (block rows per lane); ties keep the
            smaller group (fewer shuffles). HME level 2 (12 units of 32 rows x 4 segments): 8 lanes per unit, 3 x 16
            row iterations instead of 2 x 32 */
         int best_cost = 1 << 30;
@@ -398,7 +433,9 @@ __device__ bool hm_plan_try(const SearchTask &t, const MeJob *j, int org_x, int 
                 g_log2    = gl;
             }
         }
-    }
+    } else
+        while (!wide && g_log2 < 5 && (units << g_log2) < HM_LANES_TARGET && ((2 << g_log2) >> (2 - lv)) <= (int)t.rows)
+            g_log2++; /* ... x row groups: up to the team's worth of lanes */
     pl.pwb = (int16_t)pwb;
     pl.neb = (int16_t)neb;
     pl.nxb = (uint8_t)nxb;
@@ -407,31 +444,14 @@ __device__ bool hm_plan_try(const SearchTask &t, const MeJob *j, int org_x, int 
     pl.kx  = (uint8_t)kx;
     pl.g_log2   = (uint8_t)g_log2;
     pl.new_path = 1;
-    return true;
 }
 
-/* A warp's ring holds two windows so that the next one arrives while this one is searched: jobs are planned for half
- * the ring; a task whose whole search area fits the ring in ONE window takes that instead (HME level 2 and the centre
- * SADs: 64-pixel blocks, a window of 96 x 72 bytes) */
-__device__ void hm_plan_task(const SearchTask &t, const MeJob *j, int org_x, int org_y, int ring_bytes, HmPlan &pl) {
-    HmPlan whole;
-    const bool ok_half  = hm_plan_try(t, j, org_x, org_y, (ring_bytes / 2) & ~127, pl);
-    if (ok_half && pl.nyb == 1)
-        return;
-    const bool ok_whole = hm_plan_try(t, j, org_x, org_y, ring_bytes, whole);
-    if (ok_whole && (whole.nyb == 1 || !ok_half))
-        pl = whole;
-    else if (!ok_half)
-        pl.new_path = 0;
-}
-
-/* job number (over the stage's tasks of this warp) -> job descriptor (one lane per job) */
-__device__ void hm_job_decode(const SearchTask *tasks, const HmPlan *plans, const uint16_t *job_first, int ntasks, const MeJob *j, int jb,
-                              HmJobD &J) {
+/* job number -> job descriptor (one thread per job) */
+__device__ void hm_job_decode(const SearchTask *tasks, const HmPlan *plans, const uint16_t *job_first, const MeJob *j, int jb, HmJobD &J) {
     int task = 0;
-    for (int i = 1; i < ntasks; i++) /* last task with job_first[task] <= jb */
-        if (job_first[i] <= jb)
-            task = i;
+    for (int step = 16; step; step >>= 1) /* last task with job_first[task] <= jb */
+        if (job_first[task + step] <= jb)
+            task += step;
     const SearchTask  &t  = tasks[task];
     const HmPlan      &pl = plans[task];
     const MePlaneGeom &g  = j->g.plane[t.level];
@@ -452,11 +472,11 @@ __device__ void hm_job_decode(const SearchTask *tasks, const HmPlan *plans, cons
     J.aoff   = (uint8_t)(x0 & 15);
     J.y0     = (int16_t)(g.pad + t.ry + ymul * e0 + (skip ? 1 : 0));
     J.nrows  = (uint16_t)(((ne - 1) * ymul + (t.rows - 1) * t.row_step + 1 + br - 1) / br * br); /* whole boxes */
-    J.pitch  = (uint16_t)hm_map_width(pl.map);
-    J.brows  = (uint8_t)br;
+    J.off128 = 0;
     J.ncls   = (uint8_t)ncls;
     J.nchunk = (uint8_t)nchunk;
     J.total  = (uint16_t)((ncls * nchunk * ne) << pl.g_log2);
+    J.dep    = -1;
     J.m_chunk = hm_magic((uint32_t)nchunk);
     J.m_cls   = hm_magic((uint32_t)ncls);
     if (pl.kx == 1) { /* hm_job_search_tall: (byte class, row parity, group of 4 * ys search rows) */
@@ -473,6 +493,24 @@ __device__ void hm_job_decode(const SearchTask *tasks, const HmPlan *plans, cons
         J.m_chunk = hm_magic((uint32_t)nseg);
     }
 }
+
+/* Thread 0, before the CTA searches job `jb`: request the windows of the following jobs while the ring has room.
+ * Jobs are searched in order with a CTA barrier after each, so the jobs before `jb` are done: job n can go as soon as
+ * the last earlier job on its ring bytes (dep) is one of them. Job n (N = seq0 + n over the whole kernel) completes
+ * on mbarrier N % HM_NBAR; at most HM_NBAR jobs are in flight, so the previous user of the mbarrier is done too. */
+__device__ __forceinline__ void hm_fetch_ahead(const HmeMaps &maps, const SearchTask *tasks, const HmJobD *jobs, unsigned long long *full,
+                                               uint32_t ring, int njobs, uint32_t seq0, int jb, int &fetched) {
+    while (fetched < njobs && fetched - jb < HM_NBAR && jobs[fetched].dep < jb) {
+        const HmJobD  &Jn  = jobs[fetched];
+        const uint32_t bar = hm_smem(&full[(seq0 + (uint32_t)fetched) % HM_NBAR]);
+        const int      pitch = hm_map_width(Jn.map), off = (int)Jn.off128 * 128, br = hm_map_rows(Jn.map);
+        hm_mbar_expect(bar, (uint32_t)((int)Jn.nrows * pitch));
+        for (int y = 0; y < (int)Jn.nrows; y += br)
+            hm_tma_box(ring + (uint32_t)(off + y * pitch), maps.m[Jn.map], Jn.xt, Jn.y0 + y, tasks[Jn.task].ref_slot, bar);
+        fetched++;
+    }
+}
+
 /* the SAD loop of one job over the CTA; returns this warp's best key (same value in every lane).
  * A unit (KX positions) is spread over G = 2^g_log2 lanes: the 16-byte column segments of the block row (bw / 16 of
  * them, adjacent lanes -> adjacent banks) times row groups; partial sums are joined by shuffles. */
@@ -481,7 +519,7 @@ __device__ __forceinline__ unsigned long long hm_job_search(const HmJobD &J, con
                                                             const uint32_t *src, int src_pitch4, int warp, int nthr, int lane) {
     const bool skip = t.bw == 16 && t.rows <= 16 && t.skip_line;
     const int  ymul = skip ? 2 : 1, rows = t.rows, step = t.row_step;
-    const int  pitchw = (int)J.pitch >> 2, G = 1 << g_log2;
+    const int  pitchw = hm_map_width(J.map) >> 2, G = 1 << g_log2;
     const int  ncs_log2 = 2 - t.level, RG = G >> ncs_log2; /* column segments: 1 / 2 / 4 on the sixteenth / quarter / full plane */
     const int  ncls = J.ncls, nchunk = J.nchunk, total = J.total;
     const uint32_t m_chunk = J.m_chunk, m_cls = J.m_cls;
@@ -552,7 +590,7 @@ __device__ __forceinline__ unsigned long long hm_job_search8(const HmJobD &J, co
                                                              const uint32_t *src, int src_pitch4, int warp, int nthr, int lane) {
     const bool skip = t.bw == 16 && t.rows <= 16 && t.skip_line;
     const int  ymul = skip ? 2 : 1, rows = t.rows, step = t.row_step;
-    const int  pitch4 = (int)J.pitch >> 4; /* window row pitch in 16-byte units */
+    const int  pitch4 = hm_map_width(J.map) >> 4; /* window row pitch in 16-byte units */
     const int  nseg = J.nchunk, total = J.total;
     const uint32_t m_seg = J.m_chunk, pw = (uint32_t)J.pw;
     /* inside the job a 32-bit key is enough: SAD of a 16-byte-wide block of <= 16 rows < 2^16, and a job has fewer
@@ -613,7 +651,7 @@ __device__ __forceinline__ unsigned long long hm_job_search_tall(const HmJobD &J
                                                                  const uint32_t *src, int src_pitch4, int warp, int nthr, int lane) {
     const bool skip = t.bw == 16 && t.rows <= 16 && t.skip_line;
     const int  ymul = skip ? 2 : 1, step = t.row_step, ys = J.ncls /* row_step / ymul: 1 or 2 */;
-    const int  pitchw = (int)J.pitch >> 2, total = J.total, ne = J.ne, maxrow = (int)J.nrows - 1;
+    const int  pitchw = hm_map_width(J.map) >> 2, total = J.total, ne = J.ne, maxrow = (int)J.nrows - 1;
     const uint32_t pw = (uint32_t)J.pw;
     uint32_t   best = 0xFFFFFFFFu;
     for (int base = warp * 32; base < total; base += nthr) {
@@ -669,13 +707,14 @@ __device__ __forceinline__ unsigned long long hm_job_search_tall(const HmJobD &J
     const uint32_t lidx = best & 0xFFFFu, e = lidx / pw, x = lidx - e * pw;
     return ((unsigned long long)(best >> 16) << 32) | (uint32_t)((J.e0 + (int)e) * t.sa_w + J.px0 + (int)x);
 }
+
 /* ------------------------------------------------------------------------------------------------
  * open_loop_me_fullpel_search_sblock over the search rows [y_lo, y_hi) of a small area (or the single
  * probe position), one warp. Lane z owns the 8x8 blocks with z-order index z and z + 32; the 16x16 /
  * 32x32 / 64x64 sums are butterflies over lanes (z-order: 4 consecutive lanes = one 16x16, 16 = one 32x32).
  * ---------------------------------------------------------------------------------------------- */
 template <bool SUB>
-__device__ void fullsearch_item(const FsTask &f, int y_lo, int y_hi, const MeJob *j, const uint8_t *pool, uint32_t *win, int win_words,
+__device__ void fullsearch_item(const FsTask &f, int y_lo, int y_hi, const MeJob *j, const uint8_t *pool, uint32_t *win,
                                 unsigned long long *keys, int org_x, int org_y, int lane, const uint32_t *src0) {
     constexpr int      NR = SUB ? 4 : 8, RSTEP = SUB ? 2 : 1;
     const MePlaneGeom &pl = j->g.plane[0];
@@ -699,7 +738,7 @@ __device__ void fullsearch_item(const FsTask &f, int y_lo, int y_hi, const MeJob
     const int      a     = (int)((uintptr_t)w00 & 3);
     const int      pitch = (((a + f.w - 1 + 64 + 3) >> 2) + 1) | 1; /* <= 31 words for w <= FS_WARP_MAXW */
     const int      span  = SUB ? 62 : 63;
-    const int      band  = win_words / pitch - span; /* >= 5 rows of positions (the ring is at least 9 KB) */
+    const int      band  = HM_BUF_WORDS / pitch - span; /* >= 5 rows of positions */
     uint32_t bs8[2] = {0xFFFFFFFFu, 0xFFFFFFFFu}, bs16[2] = {0xFFFFFFFFu, 0xFFFFFFFFu}, bs32[2] = {0xFFFFFFFFu, 0xFFFFFFFFu},
              bs64 = 0xFFFFFFFFu;
     uint32_t bi8[2] = {0, 0}, bi16[2] = {0, 0}, bi32[2] = {0, 0}, bi64 = 0;
@@ -766,237 +805,19 @@ __device__ void fullsearch_item(const FsTask &f, int y_lo, int y_hi, const MeJob
 }
 
 /* ------------------------------------------------------------------------------------------------
- * one warp, one stage: the (up to HM_TASKS) search tasks sm.t[first .. first + n) of this warp's reference
- * ---------------------------------------------------------------------------------------------- */
-#ifdef ME_HME_TRACE
-/* per-phase cycle sums over all warps of all launches (lane 0's clock64), read back by me_hme_trace_read(): experiments only */
-enum { TR_SETUP, TR_ZZ, TR_PHME, TR_CROSS, TR_L0, TR_L1, TR_L2, TR_CENTRE, TR_PROBE, TR_MAIN, TR_END, TR_PLAN, TR_DECODE, TR_WAIT, TR_SEARCH,
-       TR_GENERIC, TR_CTRL, TR_JOBS, TR_WARPS, TR_TOTAL, TR_N };
-__device__ unsigned long long g_trace[TR_N];
-#define TR_ADD(i, v) do { if ((threadIdx.x & 31) == 0) atomicAdd(&g_trace[i], (unsigned long long)(v)); } while (0)
-#define TR_T() clock64()
-#else
-#define TR_ADD(i, v) ((void)0)
-#define TR_T() 0ll
-#endif
-
-struct HmWarpCtx {
-    HmWarp  *w;
-    uint8_t *ring; /* this warp's window ring */
-    int      ring_bytes;
-    uint32_t seq; /* window jobs of this warp so far: job q lands at the ring's low (even q) or high (odd q) end and completes on
-                     mbarrier q & 1, phase (q >> 1) & 1 */
-    int      lane;
-};
-
-__device__ __forceinline__ int hm_job_bytes(const HmJobD &J) { return (int)J.nrows * (int)J.pitch; }
-__device__ __forceinline__ int hm_job_offset(const HmJobD &J, uint32_t q, int ring_bytes) {
-    return (q & 1) ? (ring_bytes - hm_job_bytes(J)) & ~127 : 0;
-}
-
-/* lane 0: request the window of job J (sequence number q) */
-__device__ __forceinline__ void hm_issue(const HmWarpCtx &wc, const HmeMaps &maps, const HmJobD &J, uint32_t q, uint32_t ref_slot) {
-    const uint32_t bar   = hm_smem(&wc.w->mbar[q & 1]);
-    const int      pitch = J.pitch, br = J.brows, off = hm_job_offset(J, q, wc.ring_bytes);
-    const uint32_t dst   = hm_smem(wc.ring) + (uint32_t)off;
-    hm_mbar_expect(bar, (uint32_t)hm_job_bytes(J));
-    for (int y = 0; y < (int)J.nrows; y += br) hm_tma_box(dst + (uint32_t)(y * pitch), maps.m[J.map], J.xt, J.y0 + y, (int)ref_slot, bar);
-}
-
-__device__ __noinline__ void hm_run_tasks(HmeShared &sm, HmWarpCtx &wc, int first, int n, const MeJob *j, const uint8_t *pool, const HmeMaps &maps,
-                             int org_x, int org_y, FsTileList *list) {
-    const int                lane = wc.lane;
-    const unsigned long long none = ((unsigned long long)ME_SAD_LOOP_INIT << 32) | 0xFFFFFFFFull;
-    HmWarp                  &W    = *wc.w;
-    /* plan: lane i cuts task i into window jobs */
-    long long tr0 = TR_T();
-    int  nj = 0;
-    bool generic = false;
-    if (lane < n) {
-        const SearchTask t = sm.t[first + lane];
-        HmPlan           pl;
-        pl.new_path = 0;
-        pl.nxb = pl.nyb = 0;
-        if (t.valid) {
-            hm_plan_task(t, j, org_x, org_y, wc.ring_bytes, pl);
-            if (pl.new_path)
-                nj = (int)pl.nxb * (int)pl.nyb;
-            else
-                generic = true;
-        }
-        W.plan[lane]         = pl;
-        sm.tkey[first + lane] = none;
-    }
-    int incl = nj;
-#pragma unroll
-    for (int o = 1; o < HM_TASKS; o <<= 1) {
-        const int v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o)
-            incl += v;
-    }
-    if (lane < HM_TASKS)
-        W.job_first[lane + 1] = (uint16_t)incl;
-    if (lane == 0)
-        W.job_first[0] = 0;
-    const int      total = __shfl_sync(0xffffffffu, incl, HM_TASKS - 1);
-    const unsigned gmask = __ballot_sync(0xffffffffu, generic);
-    __syncwarp();
-    TR_ADD(TR_PLAN, TR_T() - tr0);
-    TR_ADD(TR_JOBS, total);
-    for (int base = 0; base < total; base += HM_ROUND) {
-        const int nr = min(HM_ROUND, total - base);
-        tr0 = TR_T();
-        if (lane < nr)
-            hm_job_decode(sm.t + first, W.plan, W.job_first, n, j, base + lane, W.jobs[lane]);
-        __syncwarp();
-        TR_ADD(TR_DECODE, TR_T() - tr0);
-        if (lane == 0)
-            hm_issue(wc, maps, W.jobs[0], wc.seq, sm.t[first + W.jobs[0].task].ref_slot);
-        for (int i = 0; i < nr; i++) {
-            const uint32_t q = wc.seq + (uint32_t)i;
-            const HmJobD   J = W.jobs[i];
-            /* the next window can come in while this one is searched when the two do not overlap in the ring */
-            bool ahead = false;
-            if (i + 1 < nr) {
-                const HmJobD &Jn   = W.jobs[i + 1];
-                const int     off  = hm_job_offset(J, q, wc.ring_bytes), offn = hm_job_offset(Jn, q + 1, wc.ring_bytes);
-                ahead              = (q & 1) ? hm_job_bytes(Jn) <= off : hm_job_bytes(J) <= offn;
-                if (ahead && lane == 0)
-                    hm_issue(wc, maps, Jn, q + 1, sm.t[first + Jn.task].ref_slot);
-            }
-            tr0 = TR_T();
-            hm_mbar_wait(hm_smem(&W.mbar[q & 1]), (q >> 1) & 1);
-            TR_ADD(TR_WAIT, TR_T() - tr0);
-            tr0 = TR_T();
-            const SearchTask &t    = sm.t[first + J.task];
-            const HmPlan     &pl   = W.plan[J.task];
-            const uint32_t   *raw  = reinterpret_cast<const uint32_t *>(wc.ring + hm_job_offset(J, q, wc.ring_bytes));
-            const uint32_t   *srcb = t.level == 2 ? sm.src2 : t.level == 1 ? sm.src1 : sm.src0;
-            const int sp4 = (t.level == 2 ? HM_SRC2_PITCH : t.level == 1 ? HM_SRC1_PITCH : HM_SRC0_PITCH) / 4;
-            unsigned long long key;
-            if (pl.kx == 8)
-                key = hm_job_search8(J, t, raw, srcb, sp4, 0, 32, lane);
-            else if (pl.kx == 1)
-                key = hm_job_search_tall(J, t, raw, srcb, sp4, 0, 32, lane);
-            else if (pl.kx == 4)
-                key = hm_job_search<4>(J, t, pl.g_log2, raw, srcb, sp4, 0, 32, lane);
-            else
-                key = hm_job_search<2>(J, t, pl.g_log2, raw, srcb, sp4, 0, 32, lane);
-            if (lane == 0 && key < sm.tkey[first + J.task]) /* the task's keys are this warp's alone */
-                sm.tkey[first + J.task] = key;
-            __syncwarp(); /* every lane is done with the window before its bytes are requested again */
-            TR_ADD(TR_SEARCH, TR_T() - tr0);
-            if (i + 1 < nr && !ahead && lane == 0)
-                hm_issue(wc, maps, W.jobs[i + 1], q + 1, sm.t[first + W.jobs[i + 1].task].ref_slot);
-        }
-        wc.seq += (uint32_t)nr;
-        __syncwarp();
-    }
-    /* tasks that cannot be window jobs: the generic path, staged with plain loads into the ring */
-    tr0 = TR_T();
-    for (unsigned m = gmask; m; m &= m - 1) {
-        const int         i = __ffs(m) - 1;
-        const SearchTask &t = sm.t[first + i];
-        const bool skip  = t.bw == 16 && t.rows <= 16 && t.skip_line;
-        const int  erows = skip ? (t.sa_h >> 1) : t.sa_h;
-        const unsigned long long key = search_item(t, 0, erows, j, pool, reinterpret_cast<uint32_t *>(wc.ring), wc.ring_bytes / 4 - 8,
-                                                   &list->overflow, lane);
-        if (lane == 0)
-            sm.tkey[first + i] = key;
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); /* ring bytes written here are TMA targets later */
-        __syncwarp();
-    }
-    __syncwarp();
-    TR_ADD(TR_GENERIC, TR_T() - tr0);
-    if (lane < n && sm.t[first + lane].valid) {
-        /* key -> what the callers of svt_sad_loop_kernel see */
-        const SearchTask        &t   = sm.t[first + lane];
-        const unsigned long long key = sm.tkey[first + lane];
-        SearchResult             r;
-        r.sad   = (uint32_t)(key >> 32);
-        r.found = r.sad < ME_SAD_LOOP_INIT;
-        r.x = r.y = 0;
-        r.pad_[0] = r.pad_[1] = r.pad_[2] = 0;
-        if (r.found) {
-            const bool     skip = t.bw == 16 && t.rows <= 16 && t.skip_line;
-            const uint32_t idx = (uint32_t)key, ee = idx / (uint32_t)t.sa_w;
-            r.x                = (int16_t)(idx - ee * (uint32_t)t.sa_w);
-            r.y                = (int16_t)(skip ? 2 * ee + 1 : ee);
-        }
-        sm.r[first + lane] = r;
-    }
-    __syncwarp();
-}
-
-/* the integer search task sm.f[k] of this warp's reference: searched here when small, else cut into tiles for k_fullsearch */
-__device__ __noinline__ void hm_run_fs(HmeShared &sm, HmWarpCtx &wc, int k, const MeJob *j, const uint8_t *pool, unsigned long long *keys, int org_x,
-                          int org_y, FsTileList *list, uint32_t b, bool sub) {
-    const FsTask f = sm.f[k];
-    if (!f.valid)
-        return;
-    if (f.w <= FS_WARP_MAXW && (int)f.w * (int)f.h <= FS_WARP_MAX) {
-        if (wc.lane == 0)
-            atomicAdd(reinterpret_cast<unsigned long long *>(&sm.s.ops_fs_inline), (unsigned long long)f.w * f.h * (sub ? 64 * 32 : 64 * 64));
-        if (sub)
-            fullsearch_item<true>(f, 0, f.h, j, pool, reinterpret_cast<uint32_t *>(wc.ring), wc.ring_bytes / 4, keys + k * ME_NPU, org_x, org_y,
-                                  wc.lane, sm.src0);
-        else
-            fullsearch_item<false>(f, 0, f.h, j, pool, reinterpret_cast<uint32_t *>(wc.ring), wc.ring_bytes / 4, keys + k * ME_NPU, org_x, org_y,
-                                   wc.lane, sm.src0);
-        __threadfence(); /* the probe keys are read back (at L2) by this warp's lane 0 */
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); /* ring bytes written here are TMA targets later */
-    } else if (wc.lane == 0)
-        fs_emit_tiles(f, list, b * ME_NREF + (uint32_t)k, (uint16_t)blockIdx.y);
-    __syncwarp();
-}
-
-/* ------------------------------------------------------------------------------------------------
  * k_hme
  * ---------------------------------------------------------------------------------------------- */
-#define HM_LANE0(stmt)                    \
-    do {                                  \
-        const long long tc_ = TR_T();     \
-        if (lane == 0) {                  \
-            stmt;                         \
-        }                                 \
-        __syncwarp();                     \
-        TR_ADD(TR_CTRL, TR_T() - tc_);    \
-    } while (0)
-/* a step of the reference's code that looks across references: one thread, between two CTA barriers */
-#define HM_CROSS(stmt)                                            \
-    do {                                                          \
-        const long long tx_ = TR_T();                             \
-        __syncthreads();                                          \
-        if (threadIdx.x == 0) {                                   \
-            c.only = -1;                                          \
-            stmt;                                                 \
-            c.only = k;                                           \
-            for (int i_ = 0; i_ < ME_SLOTS; i_++) sm.t[i_].valid = 0; /* the next stage numbers the task slots its own way */ \
-        }                                                         \
-        __syncthreads();                                          \
-        TR_ADD(TR_CROSS, TR_T() - tx_);                           \
-    } while (0)
-
-__device__ __forceinline__ void hm_clear_slots(SearchTask *t, int first, int n) {
-    for (int i = 0; i < n; i++) t[first + i].valid = 0;
-}
-
-__global__ void __maxnreg__(HM_MAXREG)
-    k_hme(MeJob *jobs, FsTileList *list, const uint8_t *pool, const __grid_constant__ HmeMaps maps, int ring_bytes) {
+__global__ void __launch_bounds__(HM_ALL_THREADS, 5)
+    k_hme(MeJob *jobs, FsTileList *list, const uint8_t *pool, const __grid_constant__ HmeMaps maps) {
     extern __shared__ __align__(1024) unsigned char hm_raw[];
-    long long      tp  = TR_T();
-    const long long t_begin = tp;
-#define TR_PHASE(i) do { const long long tn_ = TR_T(); TR_ADD(i, tn_ - tp); tp = tn_; } while (0)
     HmeShared     &sm  = *reinterpret_cast<HmeShared *>(hm_raw);
     MeJob         *j   = &jobs[blockIdx.y];
-    const uint32_t b   = blockIdx.x;
-    const int      lane = threadIdx.x & 31, warp = threadIdx.x >> 5, tid = (int)threadIdx.x, nthr = (int)blockDim.x;
+    const int      b   = blockIdx.x;
+    const int      lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool     producer = warp == HM_WARPS; /* warp 4 only requests windows; it takes no part in strided loops */
+    const int      tid = producer ? (1 << 28) : (int)threadIdx.x;
     unsigned long long *keys = &j->keys[(size_t)b * ME_NREF * ME_NPU];
-
-    /* warp -> (list, reference): the searched references in the reference's loop order */
-    const int n0 = j->p.num_of_ref_pic_to_search[0];
-    const int li = warp < n0 ? 0 : 1, ri = warp < n0 ? warp : warp - n0;
-    const int k  = li * ME_NR + ri;
+    const unsigned long long none = ((unsigned long long)ME_SAD_LOOP_INIT << 32) | 0xFFFFFFFFull;
 
     CtrlCtx c;
     c.j     = j;
@@ -1006,166 +827,392 @@ __global__ void __maxnreg__(HM_MAXREG)
     c.r     = sm.r;
     c.f     = sm.f;
     c.keys  = keys;
-    c.org_x = (int)(b % (uint32_t)j->g.b64_cols) * 64;
-    c.org_y = (int)(b / (uint32_t)j->g.b64_cols) * 64;
+    c.org_x = (b % j->g.b64_cols) * 64;
+    c.org_y = (b / j->g.b64_cols) * 64;
     c.b64_w = (uint32_t)min(64, j->g.width - c.org_x);
     c.b64_h = (uint32_t)min(64, j->g.height - c.org_y);
     c.pic_w = j->g.width;
     c.pic_h = j->g.height;
-    c.only   = k; /* this warp's lane 0 runs the control code of its own reference */
-    c.lane   = 0;
-    c.nlanes = 1;
+    c.only = min(lane, ME_NREF); /* warp 0 runs the control stages: lane = (list, reference) slot, lanes >= ME_NREF only help clearing */
+    c.lane = lane;
+    c.nlanes = 32;
+    const bool sub = j->p.me_search_method == ME_GPU_SUB_SAD_SEARCH;
 
-    HmWarpCtx wc;
-    wc.w          = reinterpret_cast<HmWarp *>(hm_raw + HM_FIXED_BYTES) + warp;
-    wc.ring       = hm_raw + HM_FIXED_BYTES + HM_WARP_BYTES(blockDim.x >> 5) + (size_t)warp * (size_t)ring_bytes;
-    wc.ring_bytes = ring_bytes;
-    wc.seq        = 0;
-    wc.lane       = lane;
-
-    for (int i = tid; i < (int)(sizeof(MeGpuParams) / 4); i += nthr)
+    for (int i = tid; i < (int)(sizeof(MeGpuParams) / 4); i += HM_THREADS)
         reinterpret_cast<uint32_t *>(&sm.p)[i] = reinterpret_cast<const uint32_t *>(&j->p)[i];
-    mc_init_keys(keys, tid, nthr);
-    for (int i = tid; i < ME_SLOTS; i += nthr) {
+    mc_init_keys(keys, tid, HM_THREADS);
+    for (int i = tid; i < ME_SLOTS; i += HM_THREADS) {
         sm.t[i].valid = 0;
         sm.r[i].sad   = 0;
         sm.r[i].found = 0;
         sm.r[i].x = sm.r[i].y = 0;
     }
-    if (lane == 0) {
-        hm_mbar_init(hm_smem(&wc.w->mbar[0]), 1);
-        hm_mbar_init(hm_smem(&wc.w->mbar[1]), 1);
+    if (tid == 0) {
+        for (int i = 0; i < HM_NBAR; i++) hm_mbar_init(hm_smem(&sm.mbar[i]), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     /* the b64's source block on the three planes stays in shared memory for the whole chain (rows below a short
        picture-edge block are padding: loaded, never summed) */
-    for (int base = 0; base < 64 * 16 + 32 * 8 + 16 * 4; base += 4 * nthr) { /* four loads in flight per thread: the set-up is HBM latency */
-        uint32_t  v[4];
-        uint32_t *dst[4];
+    if (!producer)
+        for (int base = 0; base < 64 * 16 + 32 * 8 + 16 * 4; base += 4 * HM_THREADS) { /* four loads in flight per thread: HBM latency */
+            uint32_t  v[4];
+            uint32_t *dst[4];
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
-            const int i = base + u * nthr + tid;
-            dst[u]      = nullptr;
-            if (i < 64 * 16 + 32 * 8 + 16 * 4) {
-                const int lv = i < 64 * 16 ? 0 : i < 64 * 16 + 32 * 8 ? 1 : 2;
-                const int q  = i - (lv == 0 ? 0 : lv == 1 ? 64 * 16 : 64 * 16 + 32 * 8);
-                const int r = q >> (4 - lv), cw = q & ((16 >> lv) - 1);
-                const MePlaneGeom &pl = j->g.plane[lv];
-                const uint8_t     *sp = hm_plane(pool, j->g, j->src_slot, lv) + (size_t)(pl.pad + (c.org_y >> lv) + r) * pl.stride + pl.pad +
-                                    (c.org_x >> lv);
-                const int sp_w = lv == 0 ? HM_SRC0_PITCH : lv == 1 ? HM_SRC1_PITCH : HM_SRC2_PITCH;
-                dst[u]         = (lv == 0 ? sm.src0 : lv == 1 ? sm.src1 : sm.src2) + r * sp_w + cw;
-                v[u]           = __ldg((const uint32_t *)sp + cw);
+            for (int u = 0; u < 4; u++) {
+                const int i = base + u * HM_THREADS + tid;
+                dst[u]      = nullptr;
+                if (i < 64 * 16 + 32 * 8 + 16 * 4) {
+                    const int lv = i < 64 * 16 ? 0 : i < 64 * 16 + 32 * 8 ? 1 : 2;
+                    const int q  = i - (lv == 0 ? 0 : lv == 1 ? 64 * 16 : 64 * 16 + 32 * 8);
+                    const int r = q >> (4 - lv), cw = q & ((16 >> lv) - 1);
+                    const MePlaneGeom &pl = j->g.plane[lv];
+                    const uint8_t     *sp = hm_plane(pool, j->g, j->src_slot, lv) + (size_t)(pl.pad + (c.org_y >> lv) + r) * pl.stride + pl.pad +
+                                        (c.org_x >> lv);
+                    const int sp_w = lv == 0 ? HM_SRC0_PITCH : lv == 1 ? HM_SRC1_PITCH : HM_SRC2_PITCH;
+                    dst[u]         = (lv == 0 ? sm.src0 : lv == 1 ? sm.src1 : sm.src2) + r * sp_w + cw;
+                    v[u]           = __ldg((const uint32_t *)sp + cw);
+                }
             }
-        }
 #pragma unroll
-        for (int u = 0; u < 4; u++)
-            if (dst[u])
-                *dst[u] = v[u];
-    }
+            for (int u = 0; u < 4; u++)
+                if (dst[u])
+                    *dst[u] = v[u];
+        }
     __threadfence();
     __syncthreads();
-    const MeGpuParams &p   = sm.p;
-    const bool         sub = p.me_search_method == ME_GPU_SUB_SAD_SEARCH;
-    const bool         hme = p.enable_hme_flag != 0;
-#define HM_RUN(first, n) hm_run_tasks(sm, wc, (first), (n), j, pool, maps, c.org_x, c.org_y, list)
+    uint32_t  seq  = 0; /* window jobs so far: job n uses mbarrier n % HM_NBAR, parity (n / HM_NBAR) & 1 */
+    uint8_t  *raw0 = reinterpret_cast<uint8_t *>(&sm.buf[0][0]);
+    int       fetched = 0; /* producer: jobs of the stage whose windows have been requested */
 
-    /* init_me_hme_data: all 2 x 4 (list, reference) slots, searched or not (the pruning steps loop over all of them) */
-    if (tid < ME_NREF) {
-        CtrlCtx ci = c;
-        ci.only    = tid;
-        mc_stage_init(&ci);
-    }
-    __syncthreads();
-    TR_PHASE(TR_SETUP);
-
-    /* zero-MV SADs (ME:2382-2437); the pruning that follows looks across references */
-    if (p.me_early_exit_th || p.me_safe_limit_zz_th) {
-        HM_LANE0(mc_zz_emit(&c));
-        HM_RUN(k, 1);
-        HM_CROSS(mc_zz_consume(&c));
-    }
-    TR_PHASE(TR_ZZ);
-    /* pre-HME (ME:1722-1796): with l1_early_exit list 1 reads list 0's results, so the lists go one after the other */
-    if (p.prehme_enable) {
-        const bool two = p.prehme_l1_early_exit && p.num_of_list_to_search > 1;
-        for (int pass = 0; pass < (two ? 2 : 1); pass++) {
-            if (!two || li == pass) {
-                HM_LANE0(hm_clear_slots(sm.t, 2 * k, 2); mc_prehme_emit_list(&c, li));
-                HM_RUN(2 * k, 2);
-                HM_LANE0(mc_prehme_consume_tasks(&c));
+#ifdef ME_HME_TRACE
+    long long tr[ST_COUNT][12];
+    long long t_begin = clock64();
+    unsigned long long gt_begin, gt_stage[ST_COUNT];
+    unsigned smid;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_begin));
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+#endif
+    for (int st = 0; st < ST_COUNT; st++) {
+#ifdef ME_HME_TRACE
+        long long tr0 = clock64();
+        long long tr_wait = 0, tr_search = 0, tr_bar = 0, tr_round = 0, tr_decode = 0, tr_first = 0, tr_mark = 0;
+        int       tr_jobs = 0;
+#endif
+        if (warp == 0) {
+            mc_run_stage(&c, st);
+            if (lane == 0)
+                sm.next_item = 0;
+        }
+        __syncthreads();
+#ifdef ME_HME_TRACE
+        long long tr1 = clock64();
+#endif
+        const bool search_stage = st <= ST_CENTRE;
+        /* warp 0: cut the tasks into work items (bands of search rows) */
+        if (warp == 0) {
+            int n = 0, rows_per = 1, nj = 0;
+            if (search_stage) {
+                const SearchTask t = sm.t[lane];
+                HmPlan           pl;
+                pl.new_path = 0;
+                if (t.valid)
+                    hm_plan_task(t, j, c.org_x, c.org_y, pl);
+                if (pl.new_path)
+                    nj = (int)pl.nxb * (int)pl.nyb;
+                if (t.valid) { /* the per-warp split, used when the task cannot be a window job */
+                    const bool skip  = t.bw == 16 && t.rows <= 16 && t.skip_line;
+                    const int  erows = skip ? (t.sa_h >> 1) : t.sa_h;
+                    const bool modeB = t.rows * ((((t.bw + 3) >> 2) + 3) >> 2) >= 32;
+                    rows_per         = max(1, (modeB ? HM_ITEM_POS_B : HM_ITEM_POS_A) / max(1, (int)t.sa_w));
+                    n                = (erows + rows_per - 1) / rows_per;
+                }
+                if (nj > HM_MAXJOBS) { /* a task that overflows the job table on its own goes to the per-warp path */
+                    pl.new_path = 0;
+                    nj          = 0;
+                }
+                if (pl.new_path)
+                    n = 0;
+                sm.plan[lane] = pl;
+                sm.tkey[lane] = none;
+            } else if (lane < ME_NREF) {
+                const FsTask f = sm.f[lane];
+                if (f.valid) {
+                    if (f.w <= FS_WARP_MAXW && (int)f.w * (int)f.h <= FS_WARP_MAX) {
+                        atomicAdd(reinterpret_cast<unsigned long long *>(&sm.s.ops_fs_inline), (unsigned long long)f.w * f.h * (sub ? 64 * 32 : 64 * 64));
+                        rows_per = max(1, HM_ITEM_POS_FS / max(1, (int)f.w));
+                        n        = (f.h + rows_per - 1) / rows_per;
+                    } else
+                        fs_emit_tiles(f, list, (uint32_t)b * ME_NREF + (uint32_t)lane, (uint16_t)blockIdx.y);
+                }
             }
-            if (two && pass == 0)
-                __syncthreads();
+            int incl = n;
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o)
+                    incl += v;
+            }
+            sm.item_first[lane + 1] = (uint16_t)incl;
+            sm.item_rows[lane]      = (uint16_t)rows_per;
+            if (lane == 0)
+                sm.item_first[0] = sm.job_first[0] = 0;
         }
-        HM_CROSS(mc_prehme_finish(&c));
-    }
-    TR_PHASE(TR_PHME);
-    /* HME level 0 / 1 / 2 (ME:1906-2177): a chain per reference */
-    if (hme && p.enable_hme_level0_flag) {
-        HM_LANE0(hm_clear_slots(sm.t, 4 * k, 4); mc_l0_emit(&c));
-        HM_RUN(4 * k, 4);
-        HM_LANE0(mc_l0_consume(&c));
-    }
-    TR_PHASE(TR_L0);
-    if (hme && p.enable_hme_level1_flag) {
-        HM_LANE0(hm_clear_slots(sm.t, 4 * k, 4); mc_l1_emit(&c));
-        HM_RUN(4 * k, 4);
-        HM_LANE0(mc_refine_consume(&c, 1));
-    }
-    TR_PHASE(TR_L1);
-    if (hme && p.enable_hme_level2_flag) {
-        HM_LANE0(hm_clear_slots(sm.t, 4 * k, 4); mc_l2_emit(&c));
-        HM_RUN(4 * k, 4);
-        HM_LANE0(mc_refine_consume(&c, 2));
-    }
-    TR_PHASE(TR_L2);
-    /* final centre + HME-based pruning (ME:2182-2380, 2477-2518): across references */
-    HM_CROSS(mc_final_centre(&c); if (p.me_type == ME_GPU_ME_MCTF) sm.s.tf_exit = sm.s.hme_sad[0][0] < p.tf_me_exit_th; /* ME:3109-3113 */
-             else if (hme) mc_hme_prune(&c) /* prune_ref = enable_hme_flag && me_type != ME_MCTF, ME:3103 */);
-    /* integer search (ME:1249-1516): check_00_center SADs, 8x8-variance probe, main search; per reference */
-    tp = TR_T();
-    if (!sm.s.tf_exit) {
-        HM_LANE0(mc_centre_emit(&c));
-        HM_RUN(2 * k, 2);
-        TR_PHASE(TR_CENTRE);
-        HM_LANE0(mc_probe_emit(&c));
-        hm_run_fs(sm, wc, k, j, pool, keys, c.org_x, c.org_y, list, b, sub);
-        TR_PHASE(TR_PROBE);
-        if (sm.s.probed[li][ri]) {
-            HM_LANE0(mc_main_emit_after_probe(&c));
-            hm_run_fs(sm, wc, k, j, pool, keys, c.org_x, c.org_y, list, b, sub);
+#ifdef ME_HME_TRACE
+        const long long tr_pa = clock64();
+#endif
+        __syncthreads();
+#ifdef ME_HME_TRACE
+        const long long tr_pb = clock64();
+#endif
+        /* window jobs, in rounds of up to HM_MAXJOBS jobs (whole tasks; the 4K presets' HME level 0 cuts a b64's 28
+           quadrant searches into ~280 jobs) */
+        for (int task_lo = 0; search_stage && task_lo < ME_SLOTS;) {
+#ifdef ME_HME_TRACE
+            tr_mark = clock64();
+#endif
+            if (warp == 0) {
+                const HmPlan pl = sm.plan[lane];
+                const int    nj = lane >= task_lo && pl.new_path ? (int)pl.nxb * (int)pl.nyb : 0;
+                int          inclj = nj;
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int vj = __shfl_up_sync(0xffffffffu, inclj, o);
+                    if (lane >= o)
+                        inclj += vj;
+                }
+                const bool     over = inclj > HM_MAXJOBS; /* job table full: this task and the ones after it wait for the next round */
+                const unsigned ovm  = __ballot_sync(0xffffffffu, over);
+                const int      kept = __reduce_max_sync(0xffffffffu, over ? 0 : inclj);
+                /* warps per job in this round: the largest team any of its window jobs needs */
+                const int team = __reduce_max_sync(0xffffffffu, nj > 0 && !over ? (int)pl.team : 1);
+                sm.job_first[lane + 1] = (uint16_t)(over ? kept : inclj);
+                if (lane == 0) {
+                    sm.job_first[0] = 0;
+                    sm.team         = team;
+                    sm.next_lo      = ovm ? __ffs(ovm) - 1 : ME_SLOTS;
+                }
+            }
+            __syncthreads();
+            const int njobs = sm.job_first[ME_SLOTS];
+            task_lo         = sm.next_lo;
+#ifdef ME_HME_TRACE
+            tr_round += clock64() - tr_mark;
+            tr_mark = clock64();
+#endif
+            if (njobs == 0)
+                break;
+            for (int jb = tid; jb < njobs; jb += HM_THREADS) hm_job_decode(sm.t, sm.plan, sm.job_first, j, jb, sm.jobs[jb]);
+            __syncthreads();
+#ifdef ME_HME_TRACE
+            tr_decode += clock64() - tr_mark;
+            tr_mark = clock64();
+#endif
+            fetched = 0;
+            if (producer) {
+                if (lane == 0) { /* ring placement, in job order (FIFO): depends on the sizes only, never on timing */
+                    { /* job 0 sits at the start of the ring whatever follows: its window is requested before the others are placed */
+                        HmJobD &J0 = sm.jobs[0];
+                        J0.off128  = 0;
+                        J0.dep     = -1;
+                        const uint32_t bar = hm_smem(&sm.mbar[seq % HM_NBAR]);
+                        const int      pitch = hm_map_width(J0.map), br = hm_map_rows(J0.map);
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); /* generic-proxy accesses to the ring come first */
+                        hm_mbar_expect(bar, (uint32_t)((int)J0.nrows * pitch));
+                        for (int y = 0; y < (int)J0.nrows; y += br)
+                            hm_tma_box(hm_smem(raw0) + (uint32_t)(y * pitch), maps.m[J0.map], J0.xt, J0.y0 + y, sm.t[J0.task].ref_slot, bar);
+                        fetched = 1;
+                    }
+                    int cur = 0;
+                    if (sm.team < HM_WARPS) {
+                        /* the jobs of a batch are searched together: batches alternate between the ring halves when they
+                           fit one, else every batch starts at 0 (then the next batch is fetched after this one) */
+                        const int per = HM_WARPS / sm.team;
+                        for (int jb0 = 0; jb0 < njobs; jb0 += per) {
+                            int bytes = 0;
+                            for (int jb = jb0; jb < min(njobs, jb0 + per); jb++)
+                                bytes += (int)sm.jobs[jb].nrows * hm_map_width(sm.jobs[jb].map);
+                            cur = (bytes <= HM_RING_BYTES / 2 && ((jb0 / per) & 1)) ? HM_RING_BYTES / 2 : 0;
+                            for (int jb = jb0; jb < min(njobs, jb0 + per); jb++) {
+                                sm.jobs[jb].off128 = (uint16_t)(cur >> 7);
+                                cur += (int)sm.jobs[jb].nrows * hm_map_width(sm.jobs[jb].map);
+                            }
+                        }
+                    } else
+                        for (int jb = 0; jb < njobs; jb++) {
+                            const int size = (int)sm.jobs[jb].nrows * hm_map_width(sm.jobs[jb].map);
+                            if (cur + size > HM_RING_BYTES)
+                                cur = 0;
+                            sm.jobs[jb].off128 = (uint16_t)(cur >> 7);
+                            cur += size;
+                        }
+                }
+                __syncwarp();
+                for (int n = lane; n < njobs; n += 32) { /* ring dependencies (at most HM_NBAR jobs are in flight) */
+                    const int off = (int)sm.jobs[n].off128 * 128, size = (int)sm.jobs[n].nrows * hm_map_width(sm.jobs[n].map);
+                    int       dep = -1;
+                    for (int k = max(0, n - (HM_NBAR - 1)); k < n; k++) {
+                        const int offk = (int)sm.jobs[k].off128 * 128, sizek = (int)sm.jobs[k].nrows * hm_map_width(sm.jobs[k].map);
+                        if (off < offk + sizek && offk < off + size)
+                            dep = k;
+                    }
+                    sm.jobs[n].dep = (int8_t)dep;
+                }
+                __syncwarp();
+            }
+            /* searched while the TMA transfers of the following jobs are in flight: large jobs by the whole CTA one after
+               the other, small ones by one warp each, four at a time */
+            const uint32_t seq0 = seq;
+            const int      team = sm.team, per_iter = HM_WARPS / team;
+            for (int jb0 = 0; jb0 < njobs; jb0 += per_iter) {
+                if (producer) {
+                    if (lane == 0) {
+                        if (jb0 == 0) /* generic-proxy accesses to the ring (per-warp path of earlier stages) come first */
+                            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                        hm_fetch_ahead(maps, sm.t, sm.jobs, sm.mbar, hm_smem(raw0), njobs, seq0, jb0, fetched);
+                    }
+                    __syncthreads();
+                    continue;
+                }
+                const int jb = jb0 + warp / team;
+                if (jb < njobs) {
+                    const uint32_t    slot = (seq0 + (uint32_t)jb) % HM_NBAR, par = ((seq0 + (uint32_t)jb) / HM_NBAR) & 1;
+                    __syncwarp();
+#ifdef ME_HME_TRACE
+                    const long long tw0 = clock64();
+#endif
+                    hm_mbar_wait(hm_smem(&sm.mbar[slot]), par); /* also orders the producer's ring placement before the read */
+#ifdef ME_HME_TRACE
+                    const long long tw1 = clock64();
+                    if (jb0 == 0)
+                        tr_first += tw1 - tr_mark;
+#endif
+                    const HmJobD      J    = sm.jobs[jb];
+                    const SearchTask &t    = sm.t[J.task];
+                    const HmPlan     &pl   = sm.plan[J.task];
+                    const uint32_t   *raw  = reinterpret_cast<const uint32_t *>(raw0 + (size_t)J.off128 * 128);
+                    const uint32_t   *srcb = t.level == 2 ? sm.src2 : t.level == 1 ? sm.src1 : sm.src0;
+                    const int sp4 = (t.level == 2 ? HM_SRC2_PITCH : t.level == 1 ? HM_SRC1_PITCH : HM_SRC0_PITCH) / 4;
+                    const int widx = team == HM_WARPS ? (warp + jb) & (HM_WARPS - 1) : warp % team, nthr = 32 * team;
+                    unsigned long long key;
+                    if (pl.kx == 8)
+                        key = hm_job_search8(J, t, raw, srcb, sp4, widx, nthr, lane);
+                    else if (pl.kx == 1)
+                        key = hm_job_search_tall(J, t, raw, srcb, sp4, widx, nthr, lane);
+                    else if (pl.kx == 4)
+                        key = hm_job_search<4>(J, t, pl.g_log2, raw, srcb, sp4, widx, nthr, lane);
+                    else
+                        key = hm_job_search<2>(J, t, pl.g_log2, raw, srcb, sp4, widx, nthr, lane);
+                    if (lane == 0)
+                        atomicMin(&sm.tkey[J.task], key);
+#ifdef ME_HME_TRACE
+                    tr_wait += tw1 - tw0;
+                    tr_search += clock64() - tw1;
+                    tr_jobs++;
+#endif
+                }
+#ifdef ME_HME_TRACE
+                const long long tb0 = clock64();
+#endif
+                __syncthreads(); /* the windows' ring bytes are free again */
+#ifdef ME_HME_TRACE
+                tr_bar += clock64() - tb0;
+#endif
+            }
+            seq += (uint32_t)njobs;
         }
+#ifdef ME_HME_TRACE
+        long long tr2 = clock64();
+#endif
+        const int total = sm.item_first[ME_SLOTS];
+        for (; !producer;) {
+            int it = 0;
+            if (lane == 0)
+                it = atomicAdd(&sm.next_item, 1);
+            it = __shfl_sync(0xffffffffu, it, 0);
+            if (it >= total)
+                break;
+            const unsigned hit  = __ballot_sync(0xffffffffu, sm.item_first[lane] <= it && it < sm.item_first[lane + 1]);
+            const int      task = __ffs(hit) - 1;
+            const int      rows_per = sm.item_rows[task];
+            const int      lo = (it - sm.item_first[task]) * rows_per;
+            if (search_stage) {
+                const SearchTask &t = sm.t[task];
+                const bool skip  = t.bw == 16 && t.rows <= 16 && t.skip_line;
+                const int  erows = skip ? (t.sa_h >> 1) : t.sa_h;
+                const unsigned long long key =
+                    search_item(t, lo, min(erows, lo + rows_per), j, pool, sm.buf[warp], &list->overflow, lane);
+                if (lane == 0)
+                    atomicMin(&sm.tkey[task], key);
+            } else {
+                const FsTask &f = sm.f[task];
+                if (sub)
+                    fullsearch_item<true>(f, lo, min((int)f.h, lo + rows_per), j, pool, sm.buf[warp], keys + task * ME_NPU,
+                                          c.org_x, c.org_y, lane, sm.src0);
+                else
+                    fullsearch_item<false>(f, lo, min((int)f.h, lo + rows_per), j, pool, sm.buf[warp], keys + task * ME_NPU,
+                                           c.org_x, c.org_y, lane, sm.src0);
+            }
+        }
+        if (!search_stage)
+            __threadfence(); /* the probe keys are read (at L2) by thread 0 in the next stage */
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); /* warp buffers written here are TMA targets later */
+#ifdef ME_HME_TRACE
+        long long tr3w = clock64();
+#endif
+        __syncthreads();
+#ifdef ME_HME_TRACE
+        long long tr3 = clock64();
+        tr[st][0] = tr1 - tr0; tr[st][1] = tr2 - tr1; tr[st][2] = tr3 - tr2; tr[st][3] = tr3w - tr2;
+        tr[st][4] = tr_wait; tr[st][5] = tr_search; tr[st][6] = tr_bar; tr[st][7] = tr_jobs;
+        tr[st][8] = tr_round; tr[st][9] = tr_decode; tr[st][10] = tr_first; tr[st][11] = tr_pa - tr1; tr[st][3] = tr_pb - tr_pa;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_stage[st]));
+#endif
+        if (search_stage && tid < ME_SLOTS && sm.t[tid].valid) {
+            /* key -> what the callers of svt_sad_loop_kernel see */
+            const SearchTask &t   = sm.t[tid];
+            const unsigned long long key = sm.tkey[tid];
+            SearchResult      r;
+            r.sad   = (uint32_t)(key >> 32);
+            r.found = r.sad < ME_SAD_LOOP_INIT;
+            r.x = r.y = 0;
+            r.pad_[0] = r.pad_[1] = r.pad_[2] = 0;
+            if (r.found) {
+                const bool     skip = t.bw == 16 && t.rows <= 16 && t.skip_line;
+                const uint32_t idx = (uint32_t)key, ee = idx / (uint32_t)t.sa_w;
+                r.x                = (int16_t)(idx - ee * (uint32_t)t.sa_w);
+                r.y                = (int16_t)(skip ? 2 * ee + 1 : ee);
+            }
+            sm.r[tid] = r;
+        }
+        __syncthreads();
     }
-#undef HM_RUN
-    TR_PHASE(TR_MAIN);
-    __syncthreads();
-    TR_PHASE(TR_END);
-    TR_ADD(TR_WARPS, 1);
-    TR_ADD(TR_TOTAL, TR_T() - t_begin);
+#ifdef ME_HME_TRACE
+    if (blockIdx.y == 0 && b == 100 && tid == 0) {
+        for (int st = 0; st < ST_COUNT; st++)
+            printf("b %d tid %d stage %d: ctrl %lld plan+jobs %lld items+barrier %lld (own items %lld) cycles; warp 0's window jobs: %lld "
+                   "of them, TMA wait %lld, SAD loop %lld, barrier %lld; round planning %lld, decode %lld, decode -> first window there %lld; task planning %lld (+ barrier %lld)\n", b, tid, st, tr[st][0], tr[st][1], tr[st][2], tr[st][3],
+                   tr[st][7], tr[st][4], tr[st][5], tr[st][6], tr[st][8], tr[st][9], tr[st][10], tr[st][11], tr[st][3]);
+        printf("b %d tid %d total %lld cycles\n", b, tid, clock64() - t_begin);
+    }
+    if (tid == 0) { /* print only once every CTA of the launch is past its last stage (bounded wait): printf stalls the SM */
+        const unsigned old = atomicAdd(&g_trace_cnt, 1u), target = (old / gridDim.x + 1u) * gridDim.x;
+        for (int spin = 0; spin < 4000000 && *(volatile unsigned *)&g_trace_cnt < target; spin++) __nanosleep(100);
+    }
+    if (tid == 0)
+        printf("CTA %d sm %u t0 %llu st %llu %llu %llu %llu %llu %llu %llu %llu %llu\n", b, smid, gt_begin, gt_stage[0] - gt_begin,
+               gt_stage[1] - gt_begin, gt_stage[2] - gt_begin, gt_stage[3] - gt_begin, gt_stage[4] - gt_begin, gt_stage[5] - gt_begin,
+               gt_stage[6] - gt_begin, gt_stage[7] - gt_begin, gt_stage[8] - gt_begin);
+#endif
     /* the epilogue (after the tiled searches) continues from the state in HBM */
     {
         const uint32_t *src = reinterpret_cast<const uint32_t *>(&sm.s);
         uint32_t       *dst = reinterpret_cast<uint32_t *>(&j->state[b]);
-        for (int i = tid; i < (int)(sizeof(B64State) / 4); i += nthr) dst[i] = src[i];
+        for (int i = tid; i < (int)(sizeof(B64State) / 4); i += HM_THREADS) dst[i] = src[i];
     }
 }
 
-#ifdef ME_HME_TRACE
-extern "C" int me_hme_trace_read(unsigned long long *out, int reset) {
-    cudaDeviceSynchronize();
-    cudaMemcpyFromSymbol(out, g_trace, sizeof(unsigned long long) * TR_N);
-    if (reset) {
-        unsigned long long z[TR_N] = {0};
-        cudaMemcpyToSymbol(g_trace, z, sizeof(z));
-    }
-    return TR_N;
-}
-#endif
 static unsigned long long g_hme_launches = 0;
 unsigned long long me_hme_launch_count(void) { return g_hme_launches; }
 
-cudaError_t me_hme_setup(void) { return cudaFuncSetAttribute(k_hme, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); }
+cudaError_t me_hme_setup(void) { return cudaFuncSetAttribute(k_hme, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HmeShared)); }
 
 /* tensor maps of the pool's planes for pictures of geometry g (TMA: rank 3 = byte column, row, pool slot) */
 int me_hme_make_maps(HmeMaps *maps, const uint8_t *pool, const MePicGeom *g, int nslots) {
@@ -1192,30 +1239,10 @@ int me_hme_make_maps(HmeMaps *maps, const uint8_t *pool, const MePicGeom *g, int
     return 0;
 }
 
-/* Shared memory of a CTA of `nwarps` search warps: the fixed part + a window ring per warp. The ring is what is left of
- * the SM's 227 KB when `target` CTAs are resident - as many as the registers allow (HM_MAXREG) - never above 32 KB (the
- * in-job keys of hm_job_search8 index positions with 16 bits) nor below the largest single window (128 x 72 bytes). */
-int me_hme_ring_bytes(int nwarps) {
-    int target = (65536 / HM_MAXREG) / (32 * nwarps);
-    if (target > 8)
-        target = 8;
-    if (target < 1)
-        target = 1;
-    for (;; target--) {
-        const int budget = (227 * 1024) / target - 1024 /* per-CTA reservation */ - (int)HM_FIXED_BYTES - (int)HM_WARP_BYTES(nwarps) - 128 /* over-read slack */;
-        int       ring   = (budget / nwarps) & ~127;
-        if (ring > 32768)
-            ring = 32768;
-        if (ring >= 7168 || target == 1) /* 96 x 72: the whole window of an HME level 2 / centre search */
-            return ring < 9216 && target == 1 ? 9216 : ring;
-    }
-}
-
 void me_launch_hme(MeJob *jobs, int njobs, int max_b64, int nwarps, FsTileList *list, const uint8_t *pool, const HmeMaps *maps,
                    cudaStream_t st) {
-    dim3         grid(max_b64, njobs);
-    const int    ring = me_hme_ring_bytes(nwarps);
-    const size_t smem = HM_FIXED_BYTES + HM_WARP_BYTES(nwarps) + (size_t)nwarps * (size_t)ring + 128;
-    k_hme<<<grid, 32 * nwarps, smem, st>>>(jobs, list, pool, *maps, ring);
+    (void)nwarps;
+    dim3 grid(max_b64, njobs);
+    k_hme<<<grid, HM_ALL_THREADS, sizeof(HmeShared), st>>>(jobs, list, pool, *maps);
     g_hme_launches++;
 }

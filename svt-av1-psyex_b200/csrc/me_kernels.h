@@ -84,7 +84,6 @@ int    me_hme_make_maps(HmeMaps *maps, const uint8_t *pool, const MePicGeom *g, 
 /* nwarps = searched references of the picture (one warp each) */
 void   me_launch_hme(MeJob *jobs, int njobs, int max_b64, int nwarps, FsTileList *list, const uint8_t *pool, const HmeMaps *maps,
                      cudaStream_t st);
-int    me_hme_ring_bytes(int nwarps);
 /* me_dg.cu: dynamic-GOP detector HME level 0 of one (source, reference) pair, summed into *acc (device memory, zeroed
  * by the caller on the same stream) */
 unsigned long long me_dg_launch_count(void);
