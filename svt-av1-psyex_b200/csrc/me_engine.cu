@@ -931,7 +931,7 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
 #endif
         pbegin(3);
         if (!(skip & 1))
-            me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, d.sms * FS_CTAS_PER_SM, st);
+            me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, maps, d.sms, st);
         pend();
     }
     if (jc->tail != st) {

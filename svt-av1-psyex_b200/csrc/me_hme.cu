@@ -353,7 +353,8 @@ __device__ __forceinline__ void hm_tma_prefetch_l2(const void *map, int x, int y
     asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(map), "r"(x), "r"(y), "r"(z) : "memory");
 }
 
-/* box widths of the tensor maps, by plane: sixteenth {48, 80, 224}, quarter {80}, full {96, 128} */
+/* box widths of the tensor maps, by plane: sixteenth {48, 80, 224}, quarter {80}, full {96, 128}; map 6 (full plane,
+ * 128 x 96) is the window of a k_fullsearch tile (me_kernels.cu) */
 __host__ __device__ __forceinline__ int hm_map_width(int m) {
     return m == 0 ? 48 : m == 1 ? 80 : m == 2 ? 224 : m == 3 ? 80 : m == 4 ? 96 : 128;
 }
@@ -361,7 +362,7 @@ __host__ __device__ __forceinline__ int hm_map_level(int m) { return m < 3 ? 2 :
 /* rows per box: the usual window of the stage that uses the map in ONE box (the TMA unit takes a box every ~35 cycles
  * per SM whatever its size: tools/tma_bench.cu); taller windows stack boxes */
 __host__ __device__ __forceinline__ int hm_map_rows(int m) {
-    return m == 0 ? 64 : m == 1 ? 56 : m == 2 ? 24 : m == 3 ? 40 : 72;
+    return m == 0 ? 64 : m == 1 ? 56 : m == 2 ? 24 : m == 3 ? 40 : m == 6 ? 96 : 72;
 }
 
 /* cut one task into window jobs (or leave it to the per-warp path: picture-edge blocks) */

@@ -106,7 +106,6 @@ __global__ void __launch_bounds__(256) k_pad_full(uint8_t *pool, size_t slot_off
 #define FS_KEY_SHIFT 10 /* 32 x 32 tile positions */
 #define FS_BIAS (1u << 17) /* added to the 8x8 SADs of positions outside the tile: they can never win */
 #define FS_SBEST 96 /* words per warp: best (sad << 10 | tile position) of the 85 PUs over the warp's 8 search rows */
-#define FS_SMEM_BYTES ((4 * FS_ROWS * FS_PW + 64 * 16 + 4 * FS_SBEST) * 4)
 
 /* a tile visits every PU once per warp and sbest has a row per warp: no atomic is needed */
 #ifndef FS_STORE_MODE
@@ -227,24 +226,103 @@ __device__ __forceinline__ void fs_compute(const uint32_t *__restrict__ wc, cons
     }
 }
 
-__global__ void __launch_bounds__(FS_THREADS, FS_CTAS_PER_SM) k_fullsearch(MeJob *jobs, FsTileList *list, const uint8_t *pool) {
-    extern __shared__ __align__(16) uint32_t fs_smem[];
-    uint32_t *win   = fs_smem; /* [4][FS_ROWS][FS_PW] */
-    uint32_t *srcw  = fs_smem + 4 * FS_ROWS * FS_PW; /* [64][16] (32 rows used for sub-sampled SAD) */
+/* ---- TMA / mbarrier / cp.async helpers of k_fullsearch ---- */
+__device__ __forceinline__ uint32_t fs_smem(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void fs_mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fs_mbar_expect(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void fs_mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    while (!done)
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(done)
+                     : "r"(bar), "r"(parity), "r"(1000u)
+                     : "memory");
+}
+__device__ __forceinline__ void fs_tma_box(uint32_t dst, const void *map, int x, int y, int z, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(z), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void fs_cp_async4(uint32_t dst, const void *src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+
+#define FS_RAW_PITCH 128 /* bytes per row of the TMA box: 15 (alignment) + 31 (positions) + 64 (block) <= 128 */
+#define FS_RAW_ROWS 96 /* FS_TH + 63 window rows, in one box */
+#define FS_RAW_BYTES (FS_RAW_PITCH * FS_RAW_ROWS)
+/* shared memory: raw[2] (TMA double buffer) | win[4][FS_ROWS][FS_PW] (the four byte-shifted copies) | srcw[64][16] | sbest[4][FS_SBEST] */
+#define FS_SMEM_BYTES (2 * FS_RAW_BYTES + (4 * FS_ROWS * FS_PW + 64 * 16 + 4 * FS_SBEST) * 4)
+
+/* One tile per iteration, software-pipelined over a double buffer: while the CTA searches tile i, the window of tile i + 1
+ * is in flight (ONE TMA box of 128 x 96 bytes on the (x, row, slot) tensor map of the pool, 16-byte-aligned column, completion
+ * on an mbarrier) and the work-list index of tile i + 2 is being fetched. TMA cannot shift bytes, so the four byte-shifted
+ * copies the SAD loop reads with LDS.128 are made shared -> shared from the raw window (3 LDS + 4 funnel shifts + 4 STS per
+ * word, a uniform switch on the alignment instead of per-word selects and divisions); the source block comes in by
+ * cp.async while that pass runs. */
+__global__ void __launch_bounds__(FS_THREADS, FS_CTAS_PER_SM)
+    k_fullsearch(MeJob *jobs, FsTileList *list, const uint8_t *pool, const __grid_constant__ HmeMaps maps) {
+    extern __shared__ __align__(1024) uint8_t fs_dyn[];
+    uint8_t  *raw   = fs_dyn; /* [2][FS_RAW_ROWS][FS_RAW_PITCH] */
+    uint32_t *win   = reinterpret_cast<uint32_t *>(fs_dyn + 2 * FS_RAW_BYTES); /* [4][FS_ROWS][FS_PW] */
+    uint32_t *srcw  = win + 4 * FS_ROWS * FS_PW; /* [64][16] (32 rows used for sub-sampled SAD) */
     uint32_t *sbest = srcw + 64 * 16; /* [4 warps][FS_SBEST] packed (sad << 10 | tile position): a tile visits every PU once per warp, so plain stores */
-    __shared__ uint32_t s_tile;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __shared__ __align__(8) unsigned long long s_bar[2];
+    __shared__ FsTile   s_desc[2];
+    __shared__ uint32_t s_idx[2]; /* work-list index of the tile in s_desc[b]; >= total: none */
+    const int      tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t total = list->count > list->cap ? 0u : list->count;
 
-    for (;;) {
-        __syncthreads();
-        if (tid == 0)
-            s_tile = atomicAdd(&list->next, 1u);
-        __syncthreads();
-        const uint32_t ti = s_tile;
+    /* thread 0 runs the tile pipeline: index of tile i + 2 (atomic), descriptor of tile i + 1, TMA of tile i + 1 */
+    uint32_t idx_next = 0xFFFFFFFFu, idx_next2 = 0xFFFFFFFFu;
+    FsTile   d_next;
+    if (tid == 0) {
+        fs_mbar_init(fs_smem(&s_bar[0]), 1);
+        fs_mbar_init(fs_smem(&s_bar[1]), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        const uint32_t i0 = atomicAdd(&list->next, 1u);
+        s_idx[0] = i0;
+        s_idx[1] = 0xFFFFFFFFu;
+        if (i0 < total) {
+            const FsTile t0 = list->tiles[i0];
+            s_desc[0]       = t0;
+            const MeJob *j0 = &jobs[t0.job];
+            const MePlaneGeom &pl = j0->g.plane[0];
+            const int b = (int)(t0.task / ME_NREF);
+            const int gx = (b % j0->g.b64_cols) * 64 + t0.x0 + (int)t0.tx, gy = (b / j0->g.b64_cols) * 64 + t0.y0 + (int)t0.ty;
+            fs_mbar_expect(fs_smem(&s_bar[0]), FS_RAW_BYTES);
+            fs_tma_box(fs_smem(raw), maps.m[FS_MAP], (pl.pad + gx) & ~15, pl.pad + gy, t0.ref_slot, fs_smem(&s_bar[0]));
+            idx_next = atomicAdd(&list->next, 1u);
+            if (idx_next < total)
+                d_next = list->tiles[idx_next];
+        }
+    }
+    for (uint32_t it = 0;; it++) {
+        const int buf = (int)(it & 1);
+        __syncthreads(); /* the previous tile is done with win / srcw / sbest and with raw[buf ^ 1]; s_idx / s_desc[buf] are visible */
+        const uint32_t ti = s_idx[buf];
         if (ti >= total)
             break;
-        const FsTile  tile = list->tiles[ti];
+        const FsTile tile = s_desc[buf];
+        if (tid == 0) { /* tile it + 1: its window goes into the other buffer while this one is searched */
+            s_idx[buf ^ 1] = idx_next;
+            if (idx_next < total) {
+                s_desc[buf ^ 1] = d_next;
+                const MeJob *jn = &jobs[d_next.job];
+                const MePlaneGeom &pl = jn->g.plane[0];
+                const int b = (int)(d_next.task / ME_NREF);
+                const int gx = (b % jn->g.b64_cols) * 64 + d_next.x0 + (int)d_next.tx, gy = (b / jn->g.b64_cols) * 64 + d_next.y0 + (int)d_next.ty;
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); /* the shift pass read raw[buf ^ 1] through the generic proxy */
+                fs_mbar_expect(fs_smem(&s_bar[buf ^ 1]), FS_RAW_BYTES);
+                fs_tma_box(fs_smem(raw + (buf ^ 1) * FS_RAW_BYTES), maps.m[FS_MAP], (pl.pad + gx) & ~15, pl.pad + gy, d_next.ref_slot,
+                           fs_smem(&s_bar[buf ^ 1]));
+                idx_next2 = atomicAdd(&list->next, 1u); /* consumed at the end of this iteration: the latency hides behind the search */
+            } else
+                idx_next2 = 0xFFFFFFFFu;
+        }
         MeJob        *j    = &jobs[tile.job];
         FsTask        f;
         f.valid = 1; f.probe = tile.probe; f.ref_slot = tile.ref_slot;
@@ -256,39 +334,47 @@ __global__ void __launch_bounds__(FS_THREADS, FS_CTAS_PER_SM) k_fullsearch(MeJob
         const int kx = tile.kx;
         const int wvalid = min(4 * kx, f.w - (int)tile.tx), hvalid = min(FS_TH, f.h - (int)tile.ty);
 
-        /* stage: source block rows (every other row for sub-sampled SAD) */
+        /* source block rows (every other row for sub-sampled SAD): asynchronous, lands while the shift pass runs */
         {
             const uint8_t *sp = plane_ptr(pool, j->g, j->src_slot, 0) + (size_t)(pl.pad + org_y) * pl.stride + pl.pad + org_x;
             const int      nrows = sub ? 32 : 64, rstep = sub ? 2 : 1;
-#pragma unroll 4
-            for (int i = tid; i < nrows * 16; i += FS_THREADS) {
-                const int r = i >> 4, cw = i & 15;
-                srcw[i]     = *(const uint32_t *)(sp + (size_t)(r * rstep) * pl.stride + cw * 4);
-            }
+            for (int i = tid; i < nrows * 16; i += FS_THREADS)
+                fs_cp_async4(fs_smem(srcw + i), sp + (size_t)((i >> 4) * rstep) * pl.stride + (i & 15) * 4);
+            asm volatile("cp.async.commit_group;" ::: "memory");
             for (int i = tid; i < 4 * FS_SBEST; i += FS_THREADS) sbest[i] = 0xFFFFFFFFu; /* warps without positions leave it so */
         }
-        /* stage: reference window, four copies shifted by 0..3 bytes */
+        /* the four byte-shifted copies of the window: copy s, word cw of row r = raw bytes a + s + 4 cw .. of that row */
         {
-            const int      gx = org_x + f.x0 + (int)tile.tx, gy = org_y + f.y0 + (int)tile.ty;
-            const uint8_t *w00 = plane_ptr(pool, j->g, f.ref_slot, 0) + (size_t)(pl.pad + gy) * pl.stride + pl.pad + gx;
-            const int      a   = (int)((uintptr_t)w00 & 3);
-            const uint32_t *g0 = (const uint32_t *)(w00 - a);
-            const int      nrows = hvalid + (sub ? 62 : 63) + 1;
-#pragma unroll 4 /* the loads of four iterations in flight: the staging phase is L2-latency bound */
-            for (int i = tid; i < nrows * FS_PW; i += FS_THREADS) {
-                const int       r = i / FS_PW, cw = i - r * FS_PW;
-                const uint32_t *g = g0 + (size_t)r * (pl.stride >> 2) + cw;
-                const uint32_t  w0 = g[0], w1 = g[1], w2 = g[2];
-#pragma unroll
-                for (int s = 0; s < 4; s++) {
-                    const int t = a + s;
-                    win[(s * FS_ROWS + r) * FS_PW + cw] =
-                        t < 4 ? __funnelshift_r(w0, w1, 8 * t) : __funnelshift_r(w1, w2, 8 * (t - 4));
+            const int gx = org_x + f.x0 + (int)tile.tx;
+            const int a  = (pl.pad + gx) & 15; /* byte of search position 0 in a raw row (the box starts on a 16-byte column) */
+            const int nrows = hvalid + (sub ? 62 : 63) + 1;
+            fs_mbar_wait(fs_smem(&s_bar[buf]), (it >> 1) & 1);
+            const uint32_t *rw0 = reinterpret_cast<const uint32_t *>(raw + buf * FS_RAW_BYTES) + (a >> 2);
+            const int a3 = a & 3;
+            if (lane < FS_PW) {
+#define FS_SHIFT_ROWS(E0, E1, E2, E3)                                                          \
+    for (int r = warp; r < nrows; r += FS_THREADS / 32) {                                      \
+        const uint32_t *q  = rw0 + r * (FS_RAW_PITCH / 4) + lane;                              \
+        const uint32_t  w0 = q[0], w1 = q[1], w2 = q[2];                                       \
+        (void)w2;                                                                              \
+        uint32_t *o = win + r * FS_PW + lane;                                                  \
+        o[0]                     = E0;                                                         \
+        o[FS_ROWS * FS_PW]       = E1;                                                         \
+        o[2 * FS_ROWS * FS_PW]   = E2;                                                         \
+        o[3 * FS_ROWS * FS_PW]   = E3;                                                         \
+    }
+                switch (a3) { /* uniform over the CTA */
+                case 0: FS_SHIFT_ROWS(w0, __funnelshift_r(w0, w1, 8), __funnelshift_r(w0, w1, 16), __funnelshift_r(w0, w1, 24)) break;
+                case 1: FS_SHIFT_ROWS(__funnelshift_r(w0, w1, 8), __funnelshift_r(w0, w1, 16), __funnelshift_r(w0, w1, 24), w1) break;
+                case 2: FS_SHIFT_ROWS(__funnelshift_r(w0, w1, 16), __funnelshift_r(w0, w1, 24), w1, __funnelshift_r(w1, w2, 8)) break;
+                default: FS_SHIFT_ROWS(__funnelshift_r(w0, w1, 24), w1, __funnelshift_r(w1, w2, 8), __funnelshift_r(w1, w2, 16)) break;
                 }
+#undef FS_SHIFT_ROWS
             }
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncthreads();
-        /* compute: warp -> 32 x 8 positions, lane -> (byte shift s, row), 8 positions x = s + 4k per thread */
+        /* compute: warp -> 32 x 8 positions, lane -> (byte shift s, row), KX positions x = s + 4k per thread */
         {
             /* the warp -> quarter-tile assignment rotates with the tile number: partly filled tiles leave different
                SM sub-partitions idle */
@@ -306,14 +392,19 @@ __global__ void __launch_bounds__(FS_THREADS, FS_CTAS_PER_SM) k_fullsearch(MeJob
 #undef FS_CALL
             }
         }
+        if (tid == 0) { /* the descriptor of tile it + 2, for the top of the next iteration */
+            idx_next = idx_next2;
+            if (idx_next < total)
+                d_next = list->tiles[idx_next];
+        }
         __syncthreads();
         /* merge the tile's best keys into the task's 64-bit (sad, scan order) keys */
         if (tid < ME_NPU) {
             const uint32_t key = min(min(sbest[tid], sbest[FS_SBEST + tid]), min(sbest[2 * FS_SBEST + tid], sbest[3 * FS_SBEST + tid]));
             if (key != 0xFFFFFFFFu) {
-                const uint32_t raw = key >> FS_KEY_SHIFT, pos = key & ((1u << FS_KEY_SHIFT) - 1u);
+                const uint32_t rawk = key >> FS_KEY_SHIFT, pos = key & ((1u << FS_KEY_SHIFT) - 1u);
                 const uint32_t lx = pos & (FS_TW - 1), ly = pos / FS_TW;
-                const uint32_t sad = sub ? raw << 1 : raw;
+                const uint32_t sad = sub ? rawk << 1 : rawk;
                 const uint32_t ord = f.probe ? 0u : 1u + (tile.ty + ly) * (uint32_t)f.w + tile.tx + lx;
                 atomicMin(&j->keys[(size_t)tile.task * ME_NPU + tid], ((unsigned long long)sad << 32) | ord);
             }
@@ -452,8 +543,8 @@ void me_launch_downsample(uint8_t *pool, size_t slot_off, const MePlaneGeom *src
     g_launches++;
 }
 
-void me_launch_fullsearch(MeJob *jobs, FsTileList *list, const uint8_t *pool, int ctas, cudaStream_t st) {
-    k_fullsearch<<<ctas, FS_THREADS, FS_SMEM_BYTES, st>>>(jobs, list, pool);
+void me_launch_fullsearch(MeJob *jobs, FsTileList *list, const uint8_t *pool, const HmeMaps *maps, int sms, cudaStream_t st) {
+    k_fullsearch<<<sms * FS_CTAS_PER_SM, FS_THREADS, FS_SMEM_BYTES, st>>>(jobs, list, pool, *maps);
     g_launches++;
 }
 

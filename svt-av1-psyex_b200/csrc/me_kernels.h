@@ -13,7 +13,7 @@
 #define FS_TH 32
 #endif
 #define FS_THREADS (FS_TH * 4)
-#define FS_CTAS_PER_SM (512 / FS_THREADS) /* 128 registers per thread */
+#define FS_CTAS_PER_SM 3 /* 73 KB of shared memory each (TMA double buffer + the four shifted copies): 170 registers per thread */
 
 /* positions per thread (x = s + 4k, k < KX) of the tiles of a search area `w` positions wide: a warp covers 4 * KX
  * columns; the KX in 5..8 that wastes the fewest columns wins (104 -> 7: 4 x 28 = 112 instead of 4 x 32 = 128) */
@@ -67,16 +67,17 @@ unsigned long long me_launch_count(void);
 void   me_launch_pad_full(uint8_t *pool, size_t slot_off, const MePlaneGeom *pl, cudaStream_t st);
 void   me_launch_repitch(const uint8_t *src, int src_pitch, uint8_t *dst, int dst_pitch, int row_bytes, int rows, cudaStream_t st);
 void   me_launch_downsample(uint8_t *pool, size_t slot_off, const MePlaneGeom *src, const MePlaneGeom *dst, cudaStream_t st);
-void   me_launch_fullsearch(MeJob *jobs, FsTileList *list, const uint8_t *pool, int ctas, cudaStream_t st);
 void   me_launch_epilogue(MeJob *jobs, int njobs, int max_b64, cudaStream_t st);
 double me_measure_sad_peak(cudaStream_t st);
 /* me_hme.cu */
-#define HM_NMAPS 6
+#define HM_NMAPS 7
+#define FS_MAP 6 /* tensor map of a k_fullsearch tile's window: full plane, 128 bytes x 96 rows */
 /* TMA descriptors (CUtensorMap, 128 bytes each) of the three planes of the pool as (x, row, slot) byte tensors, one per
  * box width that k_hme stages search windows with; passed to the kernel by value (__grid_constant__) */
 typedef struct HmeMaps {
     alignas(64) unsigned char m[HM_NMAPS][128];
 } HmeMaps;
+void   me_launch_fullsearch(MeJob *jobs, FsTileList *list, const uint8_t *pool, const HmeMaps *maps, int sms, cudaStream_t st);
 cudaError_t        me_hme_setup(void);
 unsigned long long me_hme_launch_count(void);
 /* 0 on success; -1 when the driver has no cuTensorMapEncodeTiled, else the CUresult of the failed encode */
