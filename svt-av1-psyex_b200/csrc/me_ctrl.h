@@ -32,6 +32,7 @@ enum MeStage {
     ST_PREHME0, /* emit pre-HME tasks of list 0 (and list 1 unless l1_early_exit) */
     ST_PREHME1, /* emit pre-HME tasks of list 1 (l1_early_exit only) */
     ST_HME_L0,
+    ST_HME_L0B, /* HME level 0 of the references other than (0, 0), where their search area depends on (0, 0)'s result (ME:1810-1825) */
     ST_HME_L1,
     ST_HME_L2,
     ST_CENTRE, /* final centre, HME prune, search-area derivation, emit check_00_center SADs */
@@ -58,7 +59,18 @@ typedef struct CtrlCtx {
      * the steps that look across references are run by lane 0 alone, with a warp barrier between steps. One thread
      * (host emulation, legacy kernel): only = -1, lane = 0, nlanes = 1. */
     int32_t             only, lane, nlanes;
+    /* integer-search stages (ST_PROBE / ST_MAIN): 0 = every reference; 1 = reference (0, 0) only, 2 = all the others. With
+     * enable_me_sr_adjustment == 2 the search area of the other references depends on the FINISHED search of (0, 0)
+     * (ME:1355-1364), so the picture takes the two stages twice, with the tiled searches of (0, 0) in between. */
+    int32_t             fs_which;
 } CtrlCtx;
+
+#define MC_FS_MINE(c, li, ri) ((c)->fs_which == 0 || ((c)->fs_which == 1) == (!(li) && !(ri)))
+/* the references other than (0, 0) size their HME level 0 area by (0, 0)'s level 0 centre (low delay, ME:1810-1825) */
+ME_HD int mc_l0_two_phase(const MeGpuParams *p) {
+    return p->enable_me_sr_adjustment && p->distance_based_hme_resizing && p->reduce_hme_l0_sr_th_min && p->reduce_hme_l0_sr_th_max;
+}
+ME_HD int mc_fs_two_pass(const MeGpuParams *p) { return p->enable_me_sr_adjustment == 2 && !p->me_early_exit_th; }
 
 #define MC_MINE(c, li, ri) ((c)->only < 0 || (c)->only == (li) * ME_NR + (ri))
 /* loop bounds over lists / references / task slots: everything for only < 0, else exactly this thread's reference, so that
@@ -379,13 +391,15 @@ ME_HD void mc_hme_l0_area(const CtrlCtx *c, int li, int ri, uint16_t dist, int16
 }
 
 /* ME:1906-2036 hme_level0_b64 (decisions + task emission); ME:820-920 hme_level_0 */
-ME_HD void mc_l0_emit(CtrlCtx *c) {
+ME_HD void mc_l0_emit(CtrlCtx *c, int which /* 0 all, 1 reference (0, 0) only, 2 the others */) {
     const MeGpuParams *p  = c->p;
     B64State          *s  = c->s;
     const MePlaneGeom *pl = &c->j->g.plane[2];
     const int          ox = (int16_t)c->org_x >> 2, oy = (int16_t)c->org_y >> 2;
     for (int li = MC_L0(c); li < MC_L1(c, p->num_of_list_to_search); li++)
         for (int ri = MC_R0(c); ri < MC_R1(c, p->num_of_ref_pic_to_search[li]); ri++) {
+            if (which && (which == 1) != (!li && !ri))
+                continue;
             if (p->me_early_exit_th && s->zz_sad[li][ri] < (p->me_early_exit_th >> 2)) {
                 mc_fill_quadrants(s->l0x[li][ri], s->l0y[li][ri], s->l0sad[li][ri], 0, 0, 0);
                 continue;
@@ -700,9 +714,11 @@ ME_HD void mc_probe_emit(CtrlCtx *c) {
     for (int k = MC_K0(c, 1); k < MC_K1(c, 1); k++) c->f[k].valid = 0;
     for (int li = MC_L0(c); li < MC_L1(c, p->num_of_list_to_search); li++)
         for (int ri = MC_R0(c); ri < MC_R1(c, p->num_of_ref_pic_to_search[li]); ri++) {
-            if (!s->do_ref[li][ri])
+            if (!s->do_ref[li][ri] || !MC_FS_MINE(c, li, ri))
                 continue;
-            int16_t w = s->sw[li][ri], h = s->sh[li][ri];
+            int16_t  w = s->sw[li][ri], h = s->sh[li][ri];
+            int      hme_accurate = 1;
+            uint64_t best_hme_sad = ~(uint64_t)0;
             if (s->pend00[li][ri]) {
                 const int k  = (li * ME_NR + ri) * 2;
                 int16_t   dx = 0, dy = 0;
@@ -713,6 +729,21 @@ ME_HD void mc_probe_emit(CtrlCtx *c) {
                 if ((uint64_t)zero_sad <= (uint64_t)hme_sad)
                     s->cx[li][ri] = s->cy[li][ri] = 0;
                 s->pend00[li][ri] = 0;
+                best_hme_sad      = hme_sad; /* check_00_center returns the SAD at the HME centre (ME:1205) */
+                if (s->cx[li][ri] == 0 && s->cy[li][ri] == 0)
+                    hme_accurate = 0;
+            }
+            if (p->enable_me_sr_adjustment == 2 && !p->me_early_exit_th) { /* ME:1349-1364 */
+                const int16_t w_before = w, h_before = h;
+                if ((hme_accurate && best_hme_sad < 24 * 24) || (p->is_ref && s->hme_sad[li][ri] < 24 * 24))
+                    h = (int16_t)(h / 2);
+                /* p_sb_best_sad[0][0][0]: the 64x64 result of reference (0, 0), whose whole search precedes this one */
+                if ((li || ri) && (uint32_t)(MC_KEY_LOAD(&c->keys[0]) >> 32) < 5000 && h == h_before && w == w_before) {
+                    h = (int16_t)(h >> 1);
+                    w = (int16_t)(w >> 1);
+                }
+                s->sw[li][ri] = w;
+                s->sh[li][ri] = h;
             }
             if (p->me_8x8_var_enabled && (w * h > 24)) {
                 s->probed[li][ri]   = 1;
@@ -730,7 +761,7 @@ ME_HD void mc_main_emit_after_probe(CtrlCtx *c) {
     for (int k = MC_K0(c, 1); k < MC_K1(c, 1); k++) c->f[k].valid = 0;
     for (int li = MC_L0(c); li < MC_L1(c, p->num_of_list_to_search); li++)
         for (int ri = MC_R0(c); ri < MC_R1(c, p->num_of_ref_pic_to_search[li]); ri++) {
-            if (!s->do_ref[li][ri] || !s->probed[li][ri])
+            if (!s->do_ref[li][ri] || !s->probed[li][ri] || !MC_FS_MINE(c, li, ri))
                 continue;
             const unsigned long long *key = &c->keys[(li * ME_NR + ri) * ME_NPU];
             const uint32_t            mean = (uint32_t)(MC_KEY_LOAD(&key[0]) >> 32) / 64;
@@ -833,7 +864,17 @@ ME_HD void mc_run_stage(CtrlCtx *c, int stage) {
         mc_clear_tasks(c);
         MC_SYNC(c);
         if (p->enable_hme_flag && p->enable_hme_level0_flag) {
-            mc_l0_emit(c);
+            mc_l0_emit(c, mc_l0_two_phase(p) ? 1 : 0);
+            if (c->lane == 0)
+                c->s->pending = PEND_L0;
+        }
+        break;
+    case ST_HME_L0B:
+        if (p->enable_hme_flag && p->enable_hme_level0_flag && mc_l0_two_phase(p)) {
+            mc_consume_pending(c); /* (0, 0)'s level 0 centres, pre-HME replacement included */
+            mc_clear_tasks(c);
+            MC_SYNC(c);
+            mc_l0_emit(c, 2);
             if (c->lane == 0)
                 c->s->pending = PEND_L0;
         }

@@ -765,12 +765,6 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
     if (p.num_of_list_to_search < 1 || p.num_of_list_to_search > ME_NL || p.num_of_ref_pic_to_search[0] < 1 ||
         p.num_of_ref_pic_to_search[0] > ME_NR || p.num_of_ref_pic_to_search[1] > ME_NR)
         return fail(ME_GPU_ERR_BAD_ARG, "bad reference counts");
-    if (p.enable_me_sr_adjustment == 2)
-        return fail(ME_GPU_ERR_UNSUPPORTED,
-                    "me_sr_adjustment level 4/5 (screen content) makes later references depend on reference (0,0)'s "
-                    "search result; not implemented");
-    if (p.distance_based_hme_resizing && p.reduce_hme_l0_sr_th_min && p.reduce_hme_l0_sr_th_max)
-        return fail(ME_GPU_ERR_UNSUPPORTED, "low-delay HME-L0 resizing from reference (0,0)'s centre is not implemented");
     if (p.max_number_of_pus_per_sb != ME_NPU)
         return fail(ME_GPU_ERR_UNSUPPORTED, "max_number_of_pus_per_sb must be 85");
     if (p.me_type != ME_GPU_ME_OPEN_LOOP && p.me_type != ME_GPU_ME_MCTF)
@@ -825,8 +819,23 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
     const OutLayout L = output_layout(nb, j.pu_count, p.max_cand, p.max_refs);
     if (L.total > jc->out_cap)
         return fail(ME_GPU_ERR_BAD_ARG, "max_cand / max_refs exceed what me_gpu_init allocated");
-    if (max_tiles_per_b64(&p) * nb > jc->tile_cap)
-        return fail(ME_GPU_ERR_UNSUPPORTED, "search area too large for the tile list");
+    if (max_tiles_per_b64(&p) * nb > jc->tile_cap) {
+        /* screen-content presets search up to 750 x 750 (x2 by MV) positions per reference: the job's tile list grows on
+           demand (the context is idle: its last job has been retired). Rare, and the one place a submit allocates. */
+        const uint64_t want = max_tiles_per_b64(&p) * nb;
+        if (want > (1ull << 28))
+            return fail(ME_GPU_ERR_UNSUPPORTED, "search area too large for the tile list");
+        CU(cudaSetDevice(d.id));
+        CU(cudaStreamSynchronize(jc->tail));
+        cudaFree(jc->tiles);
+        jc->tiles    = nullptr;
+        jc->tile_cap = 0;
+        if (dalloc(&jc->tiles, (size_t)want) != cudaSuccess) {
+            cudaGetLastError();
+            return fail(ME_GPU_ERR_NO_MEMORY, "no device memory for the full-search tile list of this search area");
+        }
+        jc->tile_cap = (uint32_t)want;
+    }
     if (out && out->b64_count < nb)
         return fail(ME_GPU_ERR_BAD_ARG, "MeGpuOutputs.b64_count is smaller than the picture's b64 count");
     j.state = jc->state; j.tasks = jc->tasks; j.results = jc->results; j.fs_tasks = jc->fs_tasks; j.keys = jc->keys;
@@ -914,9 +923,9 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
             d.mapsets.push_back(ms);
             maps = &d.mapsets.back().maps;
         }
+        const bool two_pass = mc_fs_two_pass(&p) != 0;
         pbegin(1);
-        me_launch_hme(jc->d_job, 1, nbi, (int)p.num_of_ref_pic_to_search[0] + (p.num_of_list_to_search > 1 ? (int)p.num_of_ref_pic_to_search[1] : 0),
-                      jc->d_list, d.pool, maps, st);
+        me_launch_hme(jc->d_job, 1, nbi, two_pass ? 1 : 0, jc->d_list, d.pool, maps, st);
         pend();
         if (prof) CU(cudaEventRecord(jc->ev[1], st));
         if (jc->tail != st) { /* the rest of the picture goes to the higher-priority stream */
@@ -933,6 +942,17 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
         if (!(skip & 1))
             me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, maps, d.sms, st);
         pend();
+        if (two_pass) {
+            /* enable_me_sr_adjustment == 2 (ME:1355-1364): the other references' search areas depend on the finished
+               search of reference (0, 0), tiles included: their integer-search stages run now, then their tiles */
+            CU(cudaMemsetAsync(jc->d_list, 0, 2 * sizeof(unsigned int), st)); /* count = next = 0 */
+            pbegin(1);
+            me_launch_hme(jc->d_job, 1, nbi, 2, jc->d_list, d.pool, maps, st);
+            pend();
+            pbegin(3);
+            me_launch_fullsearch(jc->d_job, jc->d_list, d.pool, maps, d.sms, st);
+            pend();
+        }
     }
     if (jc->tail != st) {
         CU(cudaEventRecord(jc->ev_mid, st));

@@ -809,7 +809,7 @@ __device__ void fullsearch_item(const FsTask &f, int y_lo, int y_hi, const MeJob
  * k_hme
  * ---------------------------------------------------------------------------------------------- */
 __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
-    k_hme(MeJob *jobs, FsTileList *list, const uint8_t *pool, const __grid_constant__ HmeMaps maps) {
+    k_hme(MeJob *jobs, FsTileList *list, const uint8_t *pool, const __grid_constant__ HmeMaps maps, int phase) {
     extern __shared__ __align__(1024) unsigned char hm_raw[];
     HmeShared     &sm  = *reinterpret_cast<HmeShared *>(hm_raw);
     MeJob         *j   = &jobs[blockIdx.y];
@@ -837,16 +837,30 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
     c.only = min(lane, ME_NREF); /* warp 0 runs the control stages: lane = (list, reference) slot, lanes >= ME_NREF only help clearing */
     c.lane = lane;
     c.nlanes = 32;
+    /* phase 0: the whole chain. With enable_me_sr_adjustment == 2 the picture takes two launches around the tiled searches of
+       reference (0, 0): phase 1 = the whole chain with the integer search of (0, 0) only, phase 2 = the integer-search stages
+       of the other references, continuing from the state phase 1 left in HBM (me_ctrl.h, CtrlCtx.fs_which) */
+    c.fs_which = phase;
     const bool sub = j->p.me_search_method == ME_GPU_SUB_SAD_SEARCH;
 
     for (int i = tid; i < (int)(sizeof(MeGpuParams) / 4); i += HM_THREADS)
         reinterpret_cast<uint32_t *>(&sm.p)[i] = reinterpret_cast<const uint32_t *>(&j->p)[i];
-    mc_init_keys(keys, tid, HM_THREADS);
-    for (int i = tid; i < ME_SLOTS; i += HM_THREADS) {
-        sm.t[i].valid = 0;
-        sm.r[i].sad   = 0;
-        sm.r[i].found = 0;
-        sm.r[i].x = sm.r[i].y = 0;
+    if (phase != 2) {
+        mc_init_keys(keys, tid, HM_THREADS);
+        for (int i = tid; i < ME_SLOTS; i += HM_THREADS) {
+            sm.t[i].valid = 0;
+            sm.r[i].sad   = 0;
+            sm.r[i].found = 0;
+            sm.r[i].x = sm.r[i].y = 0;
+        }
+    } else { /* the block's state, and the check_00_center tasks and results the probe stage reads, as phase 1 left them */
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(&j->state[b]);
+        uint32_t       *dst = reinterpret_cast<uint32_t *>(&sm.s);
+        for (int i = tid; i < (int)(sizeof(B64State) / 4); i += HM_THREADS) dst[i] = src[i];
+        for (int i = tid; i < ME_SLOTS; i += HM_THREADS) {
+            sm.t[i] = j->tasks[(size_t)b * ME_SLOTS + i];
+            sm.r[i] = j->results[(size_t)b * ME_SLOTS + i];
+        }
     }
     if (tid == 0) {
         for (int i = 0; i < HM_NBAR; i++) hm_mbar_init(hm_smem(&sm.mbar[i]), 1);
@@ -893,7 +907,16 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_begin));
     asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
 #endif
-    for (int st = 0; st < ST_COUNT; st++) {
+    for (int st = phase == 2 ? ST_PROBE : 0; st < ST_COUNT; st++) {
+        { /* stages without work for this picture's controls cost a round of CTA barriers: skipped (uniform over the grid).
+             What they would have consumed stays pending for the next stage that runs (mc_consume_pending). */
+            const MeGpuParams &pp = sm.p;
+            const bool hme = pp.enable_hme_flag != 0;
+            if ((st == ST_PREHME1 && !(pp.prehme_enable && pp.prehme_l1_early_exit)) || (st == ST_HME_L0B && !mc_l0_two_phase(&pp)) ||
+                (st == ST_HME_L1 && !(hme && pp.enable_hme_level1_flag)) || (st == ST_HME_L2 && !(hme && pp.enable_hme_level2_flag)) ||
+                (st == ST_MAIN && !pp.me_8x8_var_enabled))
+                continue;
+        }
 #ifdef ME_HME_TRACE
         long long tr0 = clock64();
         long long tr_wait = 0, tr_search = 0, tr_bar = 0, tr_round = 0, tr_decode = 0, tr_first = 0, tr_mark = 0;
@@ -1207,6 +1230,11 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
         const uint32_t *src = reinterpret_cast<const uint32_t *>(&sm.s);
         uint32_t       *dst = reinterpret_cast<uint32_t *>(&j->state[b]);
         for (int i = tid; i < (int)(sizeof(B64State) / 4); i += HM_THREADS) dst[i] = src[i];
+        if (phase == 1) /* ... and so does phase 2 */
+            for (int i = tid; i < ME_SLOTS; i += HM_THREADS) {
+                j->tasks[(size_t)b * ME_SLOTS + i]   = sm.t[i];
+                j->results[(size_t)b * ME_SLOTS + i] = sm.r[i];
+            }
     }
 }
 
@@ -1240,10 +1268,9 @@ int me_hme_make_maps(HmeMaps *maps, const uint8_t *pool, const MePicGeom *g, int
     return 0;
 }
 
-void me_launch_hme(MeJob *jobs, int njobs, int max_b64, int nwarps, FsTileList *list, const uint8_t *pool, const HmeMaps *maps,
+void me_launch_hme(MeJob *jobs, int njobs, int max_b64, int phase, FsTileList *list, const uint8_t *pool, const HmeMaps *maps,
                    cudaStream_t st) {
-    (void)nwarps;
     dim3 grid(max_b64, njobs);
-    k_hme<<<grid, HM_ALL_THREADS, sizeof(HmeShared), st>>>(jobs, list, pool, *maps);
+    k_hme<<<grid, HM_ALL_THREADS, sizeof(HmeShared), st>>>(jobs, list, pool, *maps, phase);
     g_hme_launches++;
 }

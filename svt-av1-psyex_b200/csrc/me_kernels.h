@@ -82,8 +82,8 @@ cudaError_t        me_hme_setup(void);
 unsigned long long me_hme_launch_count(void);
 /* 0 on success; -1 when the driver has no cuTensorMapEncodeTiled, else the CUresult of the failed encode */
 int    me_hme_make_maps(HmeMaps *maps, const uint8_t *pool, const MePicGeom *g, int nslots);
-/* nwarps = searched references of the picture (one warp each) */
-void   me_launch_hme(MeJob *jobs, int njobs, int max_b64, int nwarps, FsTileList *list, const uint8_t *pool, const HmeMaps *maps,
+/* phase: 0 = the whole per-b64 chain; 1 / 2 = its two halves around the tiled searches of reference (0, 0) (me_hme.cu) */
+void   me_launch_hme(MeJob *jobs, int njobs, int max_b64, int phase, FsTileList *list, const uint8_t *pool, const HmeMaps *maps,
                      cudaStream_t st);
 /* me_dg.cu: dynamic-GOP detector HME level 0 of one (source, reference) pair, summed into *acc (device memory, zeroed
  * by the caller on the same stream) */

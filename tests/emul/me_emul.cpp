@@ -121,7 +121,7 @@ extern "C" int emul_me_picture(const OraclePicture *src, const OraclePicture *co
     j.me_mv_array              = out->me_mv_array;
     j.dbg_best_sad = out->p_sb_best_sad; j.dbg_best_mv = out->p_sb_best_mv; j.dbg_centre = out->hme_search_centre;
     j.dbg_hme_sad = (uint64_t *)out->hme_sad; j.dbg_do_ref = out->do_ref; j.dbg_area = out->search_area;
-    unsigned long long totals[4] = {0, 0, 0, 0};
+    unsigned long long totals[5] = {0, 0, 0, 0, 0};
     j.ops_total = totals;
     j.tf_best_sad = out->tf_best_sad; j.tf_best_mv = out->tf_best_mv; j.tf_hme_centre = out->tf_hme_centre;
     j.tf_hme_sad = out->tf_hme_sad; j.tf_early_exit = out->tf_early_exit;
@@ -136,12 +136,19 @@ extern "C" int emul_me_picture(const OraclePicture *src, const OraclePicture *co
         c.b64_w = (uint32_t)MC_MIN(64, j.g.width - c.org_x); c.b64_h = (uint32_t)MC_MIN(64, j.g.height - c.org_y);
         c.pic_w = j.g.width; c.pic_h = j.g.height;
         c.only = -1; c.lane = 0; c.nlanes = 1;
+        c.fs_which = 0;
         return c;
     };
-    /* the same stage sequence the engine launches (me_engine.cu, run_job) */
-    for (int stage = 0; stage < ST_COUNT; stage++) {
+    /* the same stage sequence the engine runs (me_engine.cu, k_hme): with enable_me_sr_adjustment == 2 the integer-search
+       stages are taken twice, reference (0, 0) first and the others after its search has finished */
+    const bool two_pass = mc_fs_two_pass(params) != 0;
+    const int  nseq = ST_COUNT + (two_pass ? 2 : 0);
+    for (int seq = 0; seq < nseq; seq++) {
+        const int stage = seq < ST_COUNT ? seq : ST_PROBE + (seq - ST_COUNT);
+        const int fs_which = two_pass ? (seq < ST_COUNT ? 1 : 2) : 0;
         for (int b = 0; b < nb; b++) {
             CtrlCtx c = ctx_of(b);
+            c.fs_which = fs_which;
             if (stage == ST_INIT)
                 mc_init_keys(c.keys, 0, 1);
             mc_run_stage(&c, stage);

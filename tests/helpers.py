@@ -118,3 +118,10 @@ TF_CASES = [(320, 192, 0, "motion", 8, 7, 0), (320, 192, 1, "motion", 8, 11, 400
             (320, 192, 3, "motion", 8, 9, 6000), (320, 192, 4, "iid", 8, 6, 0), (264, 200, 0, "iid", 4, 5, 20000),
             (264, 200, 1, "motion", 8, 5, 3000), (264, 200, 2, "motion", 8, 11, 400), (200, 136, 3, "iid", 8, 11, 400),
             (136, 72, 1, "motion", 2, 3, 1000)]
+
+
+# Cases whose controls make a reference's searches depend on reference (0, 0)'s results (screen content: enable_me_sr_adjustment
+# == 2, motion_estimation.c:1349-1364; low delay: reduce_hme_l0_sr_th_*, :1810-1825): (preset, poc, kind, encoder-config extras)
+_SC, _RTC, _BOTH = dict(sc_class1=1), dict(rtc_tune=1), dict(rtc_tune=1, sc_class1=1)
+DEP_CASES = [(0, 1, "motion", _SC), (2, 4, "motion", _SC), (4, 7, "iid", _SC), (2, 16, "iid", _SC), (8, 4, "motion", _RTC),
+             (9, 1, "iid", _RTC), (10, 8, "motion", _RTC), (6, 4, "motion", _BOTH), (8, 7, "iid", _BOTH), (4, 1, "motion", _RTC)]

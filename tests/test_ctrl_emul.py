@@ -56,3 +56,36 @@ def test_tf_control_logic_matches_oracle(tools, case):
     bad = planes.compare_outputs(a, b, fields=planes.TF_FIELDS + planes.DEBUG_FIELDS, used_refs=[1, 0])
     assert not bad, bad
     assert a.tf_blocks == b.tf_blocks and a.byte_sad_ops == b.byte_sad_ops
+
+
+def _dep_id(c):
+    return f"m{c[0]}_poc{c[1]}_{c[2]}_" + "_".join(sorted(c[3]))
+
+
+@pytest.mark.parametrize("case", __import__("helpers").DEP_CASES, ids=_dep_id)
+def test_searches_that_depend_on_reference_00(tools, case):
+    """screen-content / low-delay controls: later references read reference (0, 0)'s HME level 0 centre and its finished
+    integer search (two-phase stages in me_ctrl.h)"""
+    oracle, emul = tools
+    preset, poc, kind, kw = case
+    w, h, n = 200, 136, 33
+    ps = PictureSet(w, h, n, kind, oracle)
+    cfg, p, l0, l1 = derive(preset, w, h, poc, n, **kw)
+    refs = [[ps.get(k) for k in l0], [ps.get(k) for k in l1]]
+    a = oracle.me_picture(ps.get(poc), refs, p)
+    b = emul.me_picture(ps.get(poc), refs, p)
+    bad = planes.compare_outputs(a, b, used_refs=used_refs(l0, l1))
+    assert not bad, bad
+    assert a.byte_sad_ops == b.byte_sad_ops
+
+
+def test_dependent_cases_reach_both_branches():
+    from helpers import DEP_CASES
+    from me_b200 import abi  # noqa: F401
+    hits = [0, 0]
+    for preset, poc, kind, kw in DEP_CASES:
+        _, p, l0, l1 = derive(preset, 200, 136, poc, 33, **kw)
+        multi = len(l0) + len(l1) > 1
+        hits[0] += bool(multi and p.enable_me_sr_adjustment == 2 and not p.me_early_exit_th)
+        hits[1] += bool(multi and p.enable_me_sr_adjustment and p.distance_based_hme_resizing and p.reduce_hme_l0_sr_th_min)
+    assert hits[0] >= 2 and hits[1] >= 3, hits

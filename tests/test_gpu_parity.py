@@ -74,6 +74,28 @@ def test_me_parity_small(engine, oracle, size, preset, poc, kind):
     assert exp.byte_sad_ops == got.byte_sad_ops
 
 
+@pytest.mark.parametrize("size", [(320, 192), (200, 136)])
+@pytest.mark.parametrize("case", __import__("helpers").DEP_CASES, ids=lambda c: f"m{c[0]}_poc{c[1]}_{c[2]}_" + "_".join(sorted(c[3])))
+def test_me_parity_dependent_references(engine, oracle, size, case):
+    """screen-content / low-delay controls: references that read reference (0, 0)'s HME level 0 centre (an extra stage inside
+    k_hme) and its finished integer search (two k_hme + k_fullsearch passes per picture)"""
+    preset, poc, kind, kw = case
+    w, h = size
+    n = 33
+    ps = PictureSet(w, h, n, kind, oracle)
+    cfg, p, l0, l1 = derive(preset, w, h, poc, n, **kw)
+    pocs = sorted(set([poc] + l0 + l1))
+    _register(engine, ps, pocs)
+    try:
+        got = engine.me_picture(poc, w, h, p, [l0, l1])
+    finally:
+        _release(engine, pocs)
+    exp = oracle.me_picture(ps.get(poc), [[ps.get(k) for k in l0], [ps.get(k) for k in l1]], p)
+    bad = planes.compare_outputs(exp, got, used_refs=used_refs(l0, l1))
+    assert not bad, bad
+    assert exp.byte_sad_ops == got.byte_sad_ops
+
+
 @pytest.mark.parametrize("preset,poc,kind,first,count", [(8, 4, "motion", 0, 510), (4, 8, "motion", 200, 40),
                                                          (4, 1, "iid", 490, 20), (2, 2, "motion", 29, 3)])
 def test_me_parity_1080p_sample(engine, oracle, preset, poc, kind, first, count):
@@ -373,3 +395,28 @@ def test_wait_protocol_with_several_threads(engine, oracle):
         assert not planes.compare_outputs(exp_tf, tf, fields=planes.TF_FIELDS)
     finally:
         _release(engine, pocs)
+
+
+@pytest.mark.parametrize("preset,poc,kind,kw,first,count", [(2, 4, "motion", dict(sc_class1=1), 215, 24), (0, 1, "iid", dict(sc_class1=1), 29, 1),
+                                                            (9, 1, "motion", dict(rtc_tune=1), 0, 510)])
+def test_me_parity_1080p_dependent_references(engine, oracle, preset, poc, kind, kw, first, count):
+    """the same at 1080p, where the integer searches are tiled: with enable_me_sr_adjustment == 2 reference (0, 0)'s tiles run
+    in a k_fullsearch launch of their own before the other references' areas are decided"""
+    w, h, n = 1920, 1080, 17
+    ps = PictureSet(w, h, n, kind, oracle)
+    cfg, p, l0, l1 = derive(preset, w, h, poc, n, **kw)
+    pocs = sorted(set([poc] + l0 + l1))
+    _register(engine, ps, pocs)
+    try:
+        got = engine.me_picture(poc, w, h, p, [l0, l1])
+    finally:
+        _release(engine, pocs)
+    exp = oracle.me_picture(ps.get(poc), [[ps.get(k) for k in l0], [ps.get(k) for k in l1]], p, first, count)
+    for name in exp.arrays:
+        a, b = exp.arrays[name][first:first + count], got.arrays[name][first:first + count]
+        if name in planes.DEBUG_FIELDS:
+            mask = np.zeros((2, 4), dtype=bool)
+            mask[0, :len(l0)] = True
+            mask[1, :len(l1)] = True
+            a, b = a[:, mask], b[:, mask]
+        assert np.array_equal(a, b), name

@@ -131,6 +131,26 @@ def test_oracle_matches_reference_me(oracle, size, preset, poc, kind):
 
 
 @have_ref
+@pytest.mark.parametrize("case", __import__("helpers").DEP_CASES, ids=lambda c: f"m{c[0]}_poc{c[1]}_{c[2]}_" + "_".join(sorted(c[3])))
+def test_oracle_matches_reference_me_dependent_references(oracle, case):
+    """screen-content / low-delay controls (enable_me_sr_adjustment == 2, reduce_hme_l0_sr_th_*): the restatement against
+    the reference's own svt_aom_motion_estimation_b64, C and AVX2"""
+    ref = Reference()
+    preset, poc, kind, kw = case
+    w, h = 264, 200
+    ps = PictureSet(w, h, 33, kind, ref)
+    cfg, p, l0, l1 = derive(preset, w, h, poc, 33, **kw)
+    refs = [[ps.get(k) for k in l0], [ps.get(k) for k in l1]]
+    a = oracle.me_picture(ps.get(poc), refs, p)
+    b = ref.me_picture(ps.get(poc), refs, p)
+    fields = [f for f in a.arrays if f != "search_area"]
+    bad = planes.compare_outputs(a, b, fields=fields, used_refs=used_refs(l0, l1))
+    assert not bad, bad
+    c = ref.me_picture(ps.get(poc), refs, p, simd=1)
+    assert not planes.compare_outputs(b, c, fields=planes.PRODUCT_FIELDS)
+
+
+@have_ref
 def test_reference_simd_equals_reference_c():
     """The timed CPU baseline (AVX2 kernels behind the RTCD pointers) gives the same results as the C path."""
     ref = Reference()
