@@ -234,6 +234,10 @@ int me_gpu_register_picture_unpadded(uint64_t picture_number, const uint8_t *y8b
 int  me_gpu_release_picture(uint64_t picture_number);
 /* copy the device pyramids back (parity tests): planes are full padded images; any pointer may be NULL */
 int me_gpu_read_pyramid(uint64_t picture_number, uint8_t *full, uint8_t *quarter, uint8_t *sixteenth);
+/* one level into a caller-owned padded plane with the caller's stride (>= plane width + 2 * pad): what picture analysis
+ * needs to take the device-built 1/4 and 1/16 planes instead of running svt_aom_downsample_filtering_input_picture
+ * (pic_analysis_process.c:2139-2196; its histograms read the 1/16 plane, :1560-1570) - SURVEY 8(f)-4 */
+int me_gpu_read_plane(uint64_t picture_number, int level, uint8_t *dst, int dst_stride);
 /* plane geometry helper: level 0 = full (pad 68), 1 = quarter (pad 32), 2 = sixteenth (pad 16) */
 int me_gpu_plane_geometry(int width, int height, int level, int *plane_w, int *plane_h, int *pad, int *stride,
                           int *rows);

@@ -15,6 +15,7 @@ int (*svt_me_picture_submit)(uint64_t, const MeGpuParams *, const uint64_t[ME_GP
 int (*svt_me_picture_wait)(uint64_t, MeGpuOutputs *)                                                                 = NULL;
 int (*svt_me_picture_release)(uint64_t)                                                                              = NULL;
 static int (*hook_cancel)(uint64_t) = NULL;
+static int (*hook_read_plane)(uint64_t, int, uint8_t *, int) = NULL;
 static const char *(*hook_last_error)(void) = NULL;
 static void (*hook_shutdown)(void) = NULL;
 static int (*hook_dg)(uint64_t, uint64_t, uint8_t, MeGpuDgMetrics *) = NULL;
@@ -43,6 +44,7 @@ EbErrorType svt_me_gpu_hook_init(const char *library_path, int max_width, int ma
     svt_me_picture_wait     = (int (*)(uint64_t, MeGpuOutputs *))dlsym(h, "me_gpu_wait");
     svt_me_picture_release  = (int (*)(uint64_t))dlsym(h, "me_gpu_release_picture");
     hook_cancel             = (int (*)(uint64_t))dlsym(h, "me_gpu_cancel");
+    hook_read_plane         = (int (*)(uint64_t, int, uint8_t *, int))dlsym(h, "me_gpu_read_plane");
     hook_last_error         = (const char *(*)(void))dlsym(h, "me_gpu_last_error");
     hook_shutdown           = (void (*)(void))dlsym(h, "me_gpu_shutdown");
     hook_dg                 = (int (*)(uint64_t, uint64_t, uint8_t, MeGpuDgMetrics *))dlsym(h, "me_gpu_dg_detector");
@@ -63,6 +65,7 @@ void svt_me_gpu_hook_shutdown(void) {
     svt_me_picture_release  = NULL;
     hook_shutdown           = NULL;
     hook_cancel             = NULL;
+    hook_read_plane         = NULL;
     hook_dg                 = NULL;
     if (hook_lib)
         dlclose(hook_lib);
@@ -152,6 +155,20 @@ EbErrorType svt_me_gpu_register_picture(const PictureParentControlSet *pcs, cons
     const EbPictureBufferDesc *d = input_padded_pic; /* y8b luma with its 68-pixel border, reference_object.c:251-253 */
     return map_error(svt_me_picture_register(pcs->picture_number, d->buffer_y, d->stride_y, d->org_x, d->org_y,
                                              pcs->aligned_width, pcs->aligned_height));
+}
+
+EbErrorType svt_me_gpu_pyramid_for_analysis(const PictureParentControlSet *pcs, const EbPictureBufferDesc *input_padded_pic,
+                                            EbPictureBufferDesc *quarter_pic, EbPictureBufferDesc *sixteenth_pic) {
+    if (!hook_read_plane)
+        return EB_ErrorUndefined;
+    EbErrorType rc = svt_me_gpu_register_picture(pcs, input_padded_pic);
+    if (rc != EB_ErrorNone)
+        return rc;
+    /* the descriptors' buffers start at the first padded byte; org_x = org_y = the plane's padding (32 / 16) */
+    int e = hook_read_plane(pcs->picture_number, 1, quarter_pic->buffer_y, quarter_pic->stride_y);
+    if (e == ME_GPU_OK)
+        e = hook_read_plane(pcs->picture_number, 2, sixteenth_pic->buffer_y, sixteenth_pic->stride_y);
+    return map_error(e);
 }
 
 EbErrorType svt_me_gpu_release_picture(uint64_t picture_number) {

@@ -65,6 +65,15 @@ int svt_me_gpu_live(void);
 /* pictures the hook has registered / released so far (diagnostics) */
 void svt_me_gpu_stats(uint64_t *registered, uint64_t *released, uint64_t *pictures);
 
+/* ---- picture analysis takes the device-built pyramid --------------------------------------------- */
+/* in svt_aom_picture_analysis_kernel, in place of svt_aom_downsample_filtering_input_picture (pic_analysis_process.c:2345):
+ * uploads the padded y8b luma (as svt_me_gpu_register_picture does) and fills the PA reference object's quarter and
+ * sixteenth planes, padding included, from the device: byte for byte what downsample_2d + svt_aom_generate_padding leave
+ * there, so svt_aom_gathering_picture_statistics (:2356) and every later CPU reader see the same planes. The picture
+ * stays registered under pcs->picture_number. */
+EbErrorType svt_me_gpu_pyramid_for_analysis(const PictureParentControlSet *pcs, const EbPictureBufferDesc *input_padded_pic,
+                                            EbPictureBufferDesc *quarter_pic, EbPictureBufferDesc *sixteenth_pic);
+
 /* ---- temporal filter (ME_MCTF, temporal_filtering.c:3144-3187) ------------------------------------------------ */
 /* ME results of one (centre, neighbour) pair over all blocks: what the block loop of produce_temporally_filtered_pic
  * reads from the MeContext after its svt_aom_motion_estimation_b64 call. Arrays are caller-owned, b64_count long. */

@@ -749,6 +749,42 @@ REF_API int ref_hook_dg_detector(const OraclePicture *src, const OraclePicture *
     return rc;
 }
 
+/* picture analysis takes the device-built pyramid through the binding. `pic`: full plane filled, quarter and
+ * sixteenth planes to be written (padding included). hist_cpu / hist_gpu[256]: the reference's own calculate_histogram
+ * (pic_analysis_process.c:166, the statistic picture analysis computes on the 1/16 plane at :1495) over the interior of
+ * the sixteenth plane, once on the reference's CPU-built plane (`cpu`) and once on the fetched one. GPU tests only. */
+void calculate_histogram(uint8_t *input_samples, uint32_t input_area_width, uint32_t input_area_height, uint32_t stride,
+                         uint8_t decim_step, uint32_t *histogram, uint64_t *sum);
+REF_API int ref_hook_pyramid_for_analysis(const OraclePicture *pic, const OraclePicture *cpu, uint32_t *hist_cpu, uint32_t *hist_gpu,
+                                          const char *gpu_library_path) {
+    const int pic_w = (pic->full.width + 7) & ~7, pic_h = (pic->full.height + 7) & ~7;
+    PictureParentControlSet *pcs = calloc(1, sizeof *pcs);
+    if (!pcs)
+        return -1;
+    pcs->picture_number = pic->picture_number;
+    pcs->aligned_width  = (uint16_t)pic_w;
+    pcs->aligned_height = (uint16_t)pic_h;
+    EbPictureBufferDesc f, q, s16;
+    desc_from_plane(&f, &pic->full);
+    desc_from_plane(&q, &pic->quarter);
+    desc_from_plane(&s16, &pic->sixteenth);
+    int rc = svt_me_gpu_hook_init(gpu_library_path, pic_w, pic_h, 4, 3, 4) == EB_ErrorNone ? 0 : -10;
+    if (!rc && svt_me_gpu_pyramid_for_analysis(pcs, &f, &q, &s16) != EB_ErrorNone)
+        rc = -13;
+    if (!rc) {
+        uint64_t sum = 0;
+        memset(hist_cpu, 0, 256 * sizeof(uint32_t));
+        memset(hist_gpu, 0, 256 * sizeof(uint32_t));
+        calculate_histogram((uint8_t *)cpu->sixteenth.buf + cpu->sixteenth.org_y * cpu->sixteenth.stride + cpu->sixteenth.org_x,
+                            (uint32_t)cpu->sixteenth.width, (uint32_t)cpu->sixteenth.height, (uint32_t)cpu->sixteenth.stride, 1, hist_cpu, &sum);
+        calculate_histogram(s16.buffer_y + s16.org_y * s16.stride_y + s16.org_x, s16.width, s16.height, s16.stride_y, 1, hist_gpu, &sum);
+        svt_me_gpu_release_picture(pic->picture_number);
+    }
+    svt_me_gpu_hook_shutdown();
+    free(pcs);
+    return rc;
+}
+
 /* static in the reference (temporal_filtering.c:2760): level 0 copies hme_l0_sa_default_tf into hme_l0_sa */
 static void harness_set_hme_search_params_mctf0(MeContext *m) { m->hme_l0_sa = m->hme_l0_sa_default_tf; }
 

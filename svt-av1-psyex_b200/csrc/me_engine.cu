@@ -541,6 +541,43 @@ int me_gpu_release_picture(uint64_t picture_number) {
     return ME_GPU_OK;
 }
 
+/* one level of a registered picture's pyramid into a caller-owned padded plane (picture analysis reads the
+ * device-built sixteenth plane for its histograms, pic_analysis_process.c:1560-1570, instead of building its own) */
+int me_gpu_read_plane(uint64_t picture_number, int level, uint8_t *dst, int dst_stride) {
+    std::unique_lock<std::mutex> lk(g.mu);
+    if (!g.initialised)
+        return fail(ME_GPU_ERR_STATE, "not initialised");
+    auto it = g.by_number.find(picture_number);
+    if (it == g.by_number.end())
+        return fail(ME_GPU_ERR_NOT_FOUND, "picture not registered");
+    if (level < 0 || level > 2 || !dst)
+        return fail(ME_GPU_ERR_BAD_ARG, "level must be 0 (full), 1 (quarter) or 2 (sixteenth)");
+    const int s = it->second;
+    MePicGeom gm;
+    me_make_geom(&gm, g.slots[s].width, g.slots[s].height);
+    const MePlaneGeom &pl = gm.plane[level];
+    const int          pw = pl.width + 2 * pl.pad;
+    if (dst_stride < pw)
+        return fail(ME_GPU_ERR_BAD_ARG, "destination stride smaller than the padded plane's row");
+    Device &d = g.dev[0];
+    CU(cudaSetDevice(d.id));
+    g.slots[s].refcount++; /* the slot stays while the copy runs outside the lock */
+    cudaEvent_t ready = g.slots[s].ready[0];
+    const uint8_t *src = d.pool + (size_t)s * g.gmax.slot_bytes + pl.offset;
+    lk.unlock();
+    cudaError_t e = cudaEventSynchronize(ready);
+    if (e == cudaSuccess)
+        e = cudaMemcpy2D(dst, (size_t)dst_stride, src, pl.stride, pw, pl.rows, cudaMemcpyDeviceToHost);
+    lk.lock();
+    g.slots[s].refcount--;
+    free_slot_if_idle(s);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(ME_GPU_ERR_CUDA, std::string("me_gpu_read_plane: ") + cudaGetErrorString(e));
+    }
+    return ME_GPU_OK;
+}
+
 /* ---- one process per GPU: pyramids travel between the processes' pools over NVLink (CUDA IPC), no collective ---------- */
 int me_gpu_ipc_export_pool(unsigned char handle[64], uint64_t *slot_bytes) {
     std::lock_guard<std::mutex> lk(g.mu);

@@ -158,7 +158,7 @@ GPU_SYMBOLS = [
     "me_gpu_register_picture_unpadded", "me_gpu_release_picture", "me_gpu_read_pyramid", "me_gpu_plane_geometry",
     "me_gpu_submit", "me_gpu_wait", "me_gpu_derive_params", "me_gpu_get_timings", "me_gpu_measure_sad_peak", "me_gpu_set_profiling", "me_gpu_submit_out", "me_gpu_output_layout",
     "me_gpu_dg_detector", "me_gpu_derive_params_tf",
-    "me_gpu_wait_pair", "me_gpu_cancel", "me_gpu_wait_done",
+    "me_gpu_wait_pair", "me_gpu_cancel", "me_gpu_wait_done", "me_gpu_read_plane",
     "me_gpu_ipc_export_pool", "me_gpu_ipc_open_peer", "me_gpu_ipc_picture", "me_gpu_register_picture_from_peer",
     "me_gpu_ipc_bytes_pulled",
     "me_gpu_dg_detector_noalloc", "me_gpu_dg_detector_noalloc_setup", "me_gpu_dg_detector_noalloc_error",
@@ -181,6 +181,7 @@ def load_gpu_lib():
     lib.me_gpu_wait.argtypes = [u64, C.POINTER(MeGpuOutputs)]
     lib.me_gpu_wait_pair.argtypes = [u64, u8, u64, C.POINTER(MeGpuOutputs)]
     lib.me_gpu_cancel.argtypes = [u64]
+    lib.me_gpu_read_plane.argtypes = [u64, C.c_int, C.c_void_p, C.c_int]
     lib.me_gpu_ipc_export_pool.argtypes = [C.c_char_p, C.POINTER(u64)]
     lib.me_gpu_ipc_open_peer.argtypes = [C.c_int, C.c_char_p, u64]
     lib.me_gpu_ipc_picture.argtypes = [u64, C.POINTER(C.c_int), C.c_char_p]

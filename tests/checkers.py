@@ -165,6 +165,19 @@ class Reference:
             raise RuntimeError(f"ref_hook_dg_detector failed: {rc}")
         return m.as_tuple()
 
+    def hook_pyramid_for_analysis(self, pic: Picture, cpu: Picture, gpu_library_path):
+        """svt_me_gpu_pyramid_for_analysis of the binding: fills pic's quarter / sixteenth planes from the device; returns the
+        reference's calculate_histogram of the sixteenth plane of `cpu` (CPU-built) and of the fetched one"""
+        import numpy as np
+        self.lib.ref_hook_pyramid_for_analysis.argtypes = [C.POINTER(abi.OraclePicture), C.POINTER(abi.OraclePicture), C.c_void_p,
+                                                           C.c_void_p, C.c_char_p]
+        a, b = pic.c_struct(), cpu.c_struct()
+        h0, h1 = np.zeros(256, dtype=np.uint32), np.zeros(256, dtype=np.uint32)
+        rc = self.lib.ref_hook_pyramid_for_analysis(C.byref(a), C.byref(b), h0.ctypes.data, h1.ctypes.data, gpu_library_path.encode())
+        if rc != 0:
+            raise RuntimeError(f"ref_hook_pyramid_for_analysis failed: {rc}")
+        return h0, h1
+
     def derive_params_tf(self, cfg):
         p = abi.MeGpuParams()
         self.lib.ref_derive_params_tf.argtypes = [C.POINTER(abi.MeGpuTfConfig), C.POINTER(abi.MeGpuParams)]

@@ -128,3 +128,22 @@ def test_reference_side_hook_temporal_filter_and_dg_detector():
     for w, h, res, kind, a, b in [(320, 192, 4, "motion", 4, 3), (640, 360, 2, "motion", 8, 0), (320, 192, 4, "blocks", 2, 1)]:
         ps = DgPictures(w, h, kind, ref)
         assert ref.hook_dg_detector(ps.get(a), ps.get(b), res, abi.GPU_LIB) == ref.dg_detector(ps.get(a), ps.get(b), res)
+
+
+@pytest.mark.parametrize("w,h", [(320, 192), (1920, 1080), (200, 136)])
+def test_reference_side_hook_pyramid_for_picture_analysis(w, h):
+    """picture analysis takes the device-built quarter / sixteenth planes through the binding
+    (svt_me_gpu_pyramid_for_analysis) instead of svt_aom_downsample_filtering_input_picture: the planes it gets, padding
+    included, and the reference's own histogram of the sixteenth plane (pic_analysis_process.c:166, :1495) equal the CPU ones."""
+    from me_b200 import abi
+    from checkers import Reference
+    if not Reference.available():
+        pytest.skip("oracle/_ref/libme_ref.so is built where /root/reference exists and travels prebuilt")
+    ref = Reference()
+    cpu = PictureSet(w, h, 3, "motion", ref).get(2)  # pyramid by the reference's own downsampler
+    dev = planes.Picture(w, h, 2)
+    dev.planes[0][...] = cpu.planes[0]
+    h_cpu, h_gpu = ref.hook_pyramid_for_analysis(dev, cpu, abi.GPU_LIB)
+    for lvl in (1, 2):
+        assert np.array_equal(dev.planes[lvl], cpu.planes[lvl]), lvl
+    assert np.array_equal(h_cpu, h_gpu) and int(h_cpu.sum()) == (w // 4) * (h // 4)
