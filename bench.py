@@ -322,13 +322,16 @@ def init_dist(torch, dist, local_rank, world):
 def measure(args, kind, mode, steps, warmup, torch, dist, ctl, with_cpu):
     """One measurement of the current workload (set_workload) on this rank's GPU.
     mode "replicas": every rank runs the whole step on its own copy of the stream (weak scaling; configs[3]).
-    mode "sharded":  ONE stream; the pictures of the step are dealt round-robin in decode order over the ranks; a picture
+    mode "sharded":  ONE stream; the pictures of the step are dealt over the ranks by measured cost (shard.owners); a picture
                      is uploaded by its owner only and reaches the ranks that reference it GPU to GPU (CUDA IPC mapping of
                      the owner's pool, device-to-device copy over NVLink); strong scaling; no collective on the data path."""
     from me_b200 import shard
     from me_b200.engine import Engine
+    global NSETS
     rank, local_rank, world = rank_info()
     sharded = mode == "sharded" and world > 1
+    if sharded:
+        NSETS = max(NSETS, 3)  # the pipelined e2e step below needs a set to rest for two steps before its slots are reused
 
     def barrier():
         torch.cuda.synchronize()
@@ -336,12 +339,47 @@ def measure(args, kind, mode, steps, warmup, torch, dist, ctl, with_cpu):
             dist.barrier()
 
     pics = make_pictures(kind, pinned=True, padded=False)
-    owner = shard.owners(synth.decode_order(NPIC), world) if sharded else {poc: rank for poc in range(NPIC)}
+    all_jobs = {poc: derive(poc) for poc in STEP_POCS}
+
+    # Sharded: pictures are dealt by COST, the device time each one took the last time its position of the mini-GOP was
+    # searched (what an encoder-side scheduler knows from the previous mini-GOP; here: one untimed pass on rank 0, every
+    # rank gets the same table). A base-layer picture with 3 references and small scaled areas and a layer-3 picture with
+    # 7 differ several times in work; dealing the decode order round-robin leaves GPUs idle.
+    cost_ms = None
+    if sharded:
+        box = [None]
+        if rank == 0:
+            cal = Engine(W, H, 4, 3, pictures_in_flight=NPIC + 4, devices=[local_rank])
+            for poc in range(NPIC):
+                a, _ = pics[poc]
+                cal.register_picture_unpadded_ptr(poc, a.ctypes.data, a.strides[0], W, H)
+            cal.set_profiling(True)
+            box[0] = {}
+            for poc in STEP_POCS:
+                _, p, l0, l1 = all_jobs[poc]
+                out = planes.Outputs(W, H, p, debug=False)
+                cal.submit(poc, p, [l0, l1])
+                cal.wait(poc, out)
+                box[0][poc] = cal.timings().total_ms
+            cal.close()
+        dist.broadcast_object_list(box, src=0, group=ctl)
+        cost_ms = box[0]
+    # the decode order starts with the key frame: mini-GOPs are [1:17], [17:33] of it; mini-GOP 1 and the key frame are only read
+    order = synth.decode_order(NPIC)
+    owner = ({**shard.owners(order[:17], world), **shard.owners(order[17:], world, cost=lambda poc: cost_ms[poc])} if sharded
+             else {poc: rank for poc in range(NPIC)})
     my_pocs = [poc for poc in STEP_POCS if owner[poc] == rank]
-    jobs = {poc: derive(poc) for poc in my_pocs}
+    jobs = {poc: all_jobs[poc] for poc in my_pocs}
     needed = shard.pyramids_needed(my_pocs, lambda poc: jobs[poc][2:])  # what this rank's pictures read
     eng = Engine(W, H, 4, 3, pictures_in_flight=NSETS * NPIC + 4, devices=[local_rank])
-    outs = {poc: pinned_outputs(jobs[poc][1], eng) for poc in my_pocs}
+    # pinned result buffers: one per picture of a step; a rank that has few pictures per step (sharded, N = 8: two) gets one
+    # per (picture, resident set) so that as many pictures can be in flight as with a whole step per rank
+    osets = NSETS if sharded and len(my_pocs) < 8 else 1
+    outs_all = {(poc, o): pinned_outputs(jobs[poc][1], eng) for poc in my_pocs for o in range(osets)}
+    outs = {poc: outs_all[(poc, 0)] for poc in my_pocs}
+
+    def out_of(poc, st):
+        return outs_all[(poc, st % osets)]
     state = {"k": 0}
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # profiling pass only
     num = lambda poc, st: poc + SET_STRIDE * st  # noqa: E731  picture numbers of a set are offset by a constant: distances are unchanged
@@ -374,24 +412,29 @@ def measure(args, kind, mode, steps, warmup, torch, dist, ctl, with_cpu):
         _, p, l0, l1 = jobs[poc]
         q = abi.MeGpuParams.from_buffer_copy(p)
         q.picture_number = num(poc, st)
-        eng.submit_out(num(poc, st), q, [[num(k, st) for k in l0], [num(k, st) for k in l1]], outs[poc])
+        eng.submit_out(num(poc, st), q, [[num(k, st) for k in l0], [num(k, st) for k in l1]], out_of(poc, st))
 
     # Pictures stream through the engine the way they stream through the encoder's ME stage: up to WINDOW pictures
     # are in flight, the oldest one is waited for (its results copied back) before the next is submitted, and a step
     # does not drain the pipeline; drain() (inside the timed region) waits for whatever is left.
     # < 16: the engine's job contexts, and the pinned result buffer of a POC is reused every 16 pictures
-    WINDOW = int(os.environ.get("BENCH_WINDOW", 12))
+    # ... and a (picture, set) has one result buffer and one identity: never two of the same in flight
+    WINDOW = min(int(os.environ.get("BENCH_WINDOW", 12)), len(my_pocs) * osets)
     in_flight = collections.deque()
 
     def retire_oldest():
-        poc, st = in_flight.popleft()
-        eng.wait(num(poc, st), outs[poc])
+        poc, st, _ = in_flight.popleft()
+        eng.wait(num(poc, st), out_of(poc, st))
 
     def enqueue(poc, st):
         while len(in_flight) >= WINDOW:
             retire_oldest()
         submit(poc, st)
-        in_flight.append((poc, st))
+        in_flight.append((poc, st, state["k"]))
+
+    def retire_before(k):
+        while in_flight and in_flight[0][2] < k:
+            retire_oldest()
 
     def drain():
         while in_flight:
@@ -414,7 +457,11 @@ def measure(args, kind, mode, steps, warmup, torch, dist, ctl, with_cpu):
                     eng.release_picture(num(poc, st))
         uploaded.add(st)
         if sharded:
-            drain()  # result buffers of this rank's pictures are reused; and the pulls below need the pool slots
+            # Three resident sets: the slots released above were filled three steps ago. Every rank retires its jobs of two
+            # steps ago before this step's rendezvous (the ticket exchange), so when a rank passes the NEXT rendezvous nobody
+            # reads or pulls those slots any more - while the jobs of the previous step still run under this step's uploads
+            # and pulls.
+            retire_before(state["k"] - 1)  # tags are the counter after its increment: keeps only the previous step in flight
             for poc in my_pocs:
                 reg(poc, st)
             exchange(STEP_POCS, st)
@@ -486,7 +533,7 @@ def measure(args, kind, mode, steps, warmup, torch, dist, ctl, with_cpu):
             flush_buf.zero_()
             torch.cuda.synchronize()
             submit(poc, rep)
-            eng.wait(num(poc, rep), outs[poc])
+            eng.wait(num(poc, rep), out_of(poc, rep))
             t = eng.timings()
             for k in ("k_search_ms", "k_fullsearch_ms", "k_fullsearch_main_ms", "k_ctrl_ms", "k_epilogue_ms", "total_ms"):
                 prof[k] += getattr(t, k)
@@ -514,16 +561,17 @@ def measure(args, kind, mode, steps, warmup, torch, dist, ctl, with_cpu):
     wrong = [poc for poc in my_pocs if have and workloads.picture_hashes(outs[poc]) != gold[keys[poc]]]
     checked = len(my_pocs) if have else 0
     nvlink = [bytes1 - bytes0, bytes2 - bytes1]
+    d2h = sum(sum(a.nbytes for a in outs[p].arrays.values()) for p in my_pocs)  # this rank's result bytes per step
+    d2h_all = d2h
     if world > 1:
-        t = torch.tensor([len(wrong), checked, nvlink[0], nvlink[1]], dtype=torch.int64, device="cuda")
+        t = torch.tensor([len(wrong), checked, nvlink[0], nvlink[1], d2h], dtype=torch.int64, device="cuda")
         dist.all_reduce(t)
-        n_wrong, checked, nvlink = int(t[0]), int(t[1]), [int(t[2]), int(t[3])]
+        n_wrong, checked, nvlink, d2h_all = int(t[0]), int(t[1]), [int(t[2]), int(t[3])], int(t[4])
     else:
         n_wrong = len(wrong)
     parity = {"pictures": checked, "equal": (n_wrong == 0) if checked else None, "mismatched_pocs_rank0": wrong,
               "against": "tests/golden/picture_hashes.json (reference svt_aom_motion_estimation_b64 + AVX2 kernels, all b64s, "
                          "every product array)" if checked else "no golden digests for this workload"}
-    d2h = sum(sum(a.nbytes for a in outs[p].arrays.values()) for p in my_pocs)
     eng.close()
 
     n_frames = 16 * steps * (1 if sharded else world)
@@ -578,7 +626,7 @@ def measure(args, kind, mode, steps, warmup, torch, dist, ctl, with_cpu):
         cpu_baseline["parity_equal"] = arm.parity(kind)
         cpu_baseline["host"] = host_info()
     cfg = workload_config(kind)
-    cfg["mode"] = ("sharded: one stream, the step's pictures dealt round-robin in decode order over the ranks; owners upload, "
+    cfg["mode"] = ("sharded: one stream, the step's pictures dealt over the ranks by measured cost (`dealing`); owners upload, "
                    "the others pull pyramids GPU to GPU (CUDA IPC + device-to-device copy over NVLink), no collective on the data path"
                    if sharded else "replicas: every rank runs the whole step on its own copy of the stream" if world > 1 else "one GPU")
     line = {
@@ -586,7 +634,7 @@ def measure(args, kind, mode, steps, warmup, torch, dist, ctl, with_cpu):
         "warmup": warmup, "ms_per_step": 1e3 * dt_res / steps, "higher_is_better": True,
         "scaling": "strong" if sharded else "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": cfg,
         "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": 16 * W * H * (1 if sharded else world),
-                "d2h_bytes_per_step": d2h * (world if not sharded else 1), "ms_per_step": 1e3 * dt_e2e / steps,
+                "d2h_bytes_per_step": d2h_all, "ms_per_step": 1e3 * dt_e2e / steps,
                 "h2d_gbs_per_rank": h2d / (dt_e2e / steps) / 1e9, "d2h_gbs_per_rank": d2h / (dt_e2e / steps) / 1e9},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline, "parity": parity,
         "host": {"cpus": os.cpu_count()},
@@ -595,6 +643,9 @@ def measure(args, kind, mode, steps, warmup, torch, dist, ctl, with_cpu):
         line["nvlink_bytes_per_step"] = nvlink[1] / (steps + warmup)  # all ranks, e2e arm, warm-up steps counted on both sides
         line["peer_copy_verified"] = peer_verified
         line["pictures_per_rank_per_step"] = len(my_pocs)
+        line["dealing"] = {"rule": "per mini-GOP, most expensive picture first to the least loaded rank (me_b200/shard.py owners)",
+                           "cost": "device ms of the picture's ME, measured once on rank 0 before the clock starts",
+                           "ms_per_rank": [round(sum(cost_ms[p] for p in STEP_POCS if owner[p] == r), 3) for r in range(world)]}
     return line
 
 
@@ -619,7 +670,7 @@ def gpu_main(args):
         sh = measure(args, "motion", "sharded", max(3, args.steps), args.warmup, torch, dist, ctl, with_cpu=False)
         set_workload(main_wl)
         line["sharded_4k"] = {k: sh[k] for k in ("value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "scaling", "config", "e2e",
-                                                  "parity", "nvlink_bytes_per_step", "peer_copy_verified", "pictures_per_rank_per_step",
+                                                  "parity", "nvlink_bytes_per_step", "peer_copy_verified", "pictures_per_rank_per_step", "dealing",
                                                   "clocks")}
         ok = ok and sh["parity"]["equal"] is not False
     extra = None

@@ -10,6 +10,9 @@ What it changes (the same edits integration/encoder_me_gpu.patch shows as a unif
                                      pointers, once; svt_av1_enc_deinit: svt_me_gpu_hook_shutdown
   Source/Lib/Codec/me_process.c      svt_aom_motion_estimation_kernel, TASK_PAME: the b64 loop is replaced by
                                      svt_me_gpu_segment (whole picture on the device, once per picture) when the hook is live
+  Source/Lib/Codec/pic_analysis_process.c  svt_aom_downsample_filtering_input_picture (picture analysis, the temporal filter's
+                                     re-decimation, the overlay picture): svt_me_gpu_downsample - upload once, pyramid on the
+                                     device, the quarter / sixteenth planes read back for the CPU stages that still use them
   Source/Lib/Codec/CMakeLists.txt    lists the new files; Source/Lib/CMakeLists.txt links libdl
 Every edit is an exact-match replacement: the script fails if the tree is not the one it was written against.
 """
@@ -120,6 +123,37 @@ def main():
     first_inc = s.index("#include")
     s = s[:first_inc] + '#include "svt_me_gpu_hook.h"\n#include "svt_log.h"\n' + s[first_inc:]
     open(mp, "w").write(s)
+
+    # ---- the pyramid: every caller of the downsample takes the device's planes -------------------------------------
+    pa = os.path.join(codec, "pic_analysis_process.c")
+    replace_once(pa, '''                                                EbPictureBufferDesc *sixteenth_picture_ptr) {
+    // Downsample input picture for HME L0 and L1
+    if (pcs->enable_hme_flag || pcs->tf_enable_hme_flag) {''',
+                 '''                                                EbPictureBufferDesc *sixteenth_picture_ptr) {
+    if (svt_me_gpu_live() && pcs->pa_ref_pic_wrapper && (pcs->enable_hme_flag || pcs->tf_enable_hme_flag) &&
+        (pcs->enable_hme_level0_flag || pcs->tf_enable_hme_level0_flag) &&
+        (pcs->enable_hme_level1_flag || pcs->tf_enable_hme_level1_flag)) {
+        /* B200 path: the device builds the pyramid ME will search (once per picture version) and hands the two planes
+           back; only for the pcs's own PA reference object at the picture's own size (not the rescaled copies of
+           super-res / resize, which stay on the CPU like their ME does) */
+        const EbPaReferenceObject *own = (const EbPaReferenceObject *)pcs->pa_ref_pic_wrapper->object_ptr;
+        if (quarter_picture_ptr == own->quarter_downsampled_picture_ptr &&
+            sixteenth_picture_ptr == own->sixteenth_downsampled_picture_ptr && input_padded_pic->width == pcs->aligned_width &&
+            input_padded_pic->height == pcs->aligned_height && !(pcs->aligned_width & 7) && !(pcs->aligned_height & 7)) {
+            if (svt_me_gpu_downsample(pcs, input_padded_pic, quarter_picture_ptr, sixteenth_picture_ptr) != EB_ErrorNone) {
+                SVT_ERROR("B200 ME engine failed to build the pyramid of picture %llu (no CPU fallback)\\n",
+                          (unsigned long long)pcs->picture_number);
+                abort();
+            }
+            return;
+        }
+    }
+    // Downsample input picture for HME L0 and L1
+    if (pcs->enable_hme_flag || pcs->tf_enable_hme_flag) {''')
+    s = open(pa).read()
+    first_inc = s.index("#include")
+    s = s[:first_inc] + '#include "svt_me_gpu_hook.h"\n#include "svt_log.h"\n' + s[first_inc:]
+    open(pa, "w").write(s)
 
     # ---- the new source joins the CODEC object library ----
     replace_once(os.path.join(codec, "CMakeLists.txt"), "set(all_files\n        adaptive_mv_pred.c\n",

@@ -57,8 +57,14 @@ EbErrorType svt_me_gpu_hook_init(const char *library_path, int max_width, int ma
 }
 
 void svt_me_gpu_hook_shutdown(void) {
-    if (hook_shutdown)
+    if (hook_shutdown) {
+        uint64_t reg, rel, pics;
+        svt_me_gpu_stats(&reg, &rel, &pics);
+        fprintf(stderr, "svt_me_gpu_hook: %llu pictures searched, %llu pyramids built on the device (%llu for picture analysis / "
+                        "the temporal filter / overlays), %llu released\n", (unsigned long long)pics, (unsigned long long)reg,
+                (unsigned long long)svt_me_gpu_downsample_count(), (unsigned long long)rel);
         hook_shutdown();
+    }
     svt_me_picture_register = NULL;
     svt_me_picture_submit   = NULL;
     svt_me_picture_wait     = NULL;
@@ -247,6 +253,9 @@ typedef struct HookReg {
                        picture and its overlay share a picture number but not their pixels: identities must not collide, and
                        ME only ever reads 16-bit differences of the numbers */
     int         used;
+    int         by_downsample; /* registered by svt_me_gpu_downsample: current by construction (every version of the object's
+                                  picture passes through it), whatever obj->picture_number says - the overlay path never
+                                  sets it (pd_process.c:2691-2740) */
 } HookReg;
 typedef struct HookPic {
     const void *pcs; /* the picture's control set: an alt-ref and its overlay are two pictures with one number */
@@ -260,7 +269,7 @@ static HookReg         hook_regs[HOOK_MAX_REGS];
 static HookPic         hook_pics[HOOK_MAX_PICS];
 static pthread_mutex_t hook_mu = PTHREAD_MUTEX_INITIALIZER;
 static pthread_cond_t  hook_cv = PTHREAD_COND_INITIALIZER;
-static uint64_t        hook_n_reg, hook_n_rel, hook_n_pic;
+static uint64_t        hook_n_reg, hook_n_rel, hook_n_pic, hook_n_ds;
 
 int svt_me_gpu_live(void) { return svt_me_picture_submit != NULL; }
 
@@ -281,7 +290,7 @@ static EbErrorType hook_ensure_registered(const PictureParentControlSet *pcs, co
         else if (!hook_regs[i].used && !free_slot)
             free_slot = &hook_regs[i];
     }
-    if (slot && slot->number == obj->picture_number) {
+    if (slot && (slot->by_downsample || slot->number == obj->picture_number)) {
         *id = slot->id;
         return EB_ErrorNone;
     }
@@ -303,9 +312,66 @@ static EbErrorType hook_ensure_registered(const PictureParentControlSet *pcs, co
     free_slot->number = obj->picture_number;
     free_slot->id     = nid;
     free_slot->used   = 1;
+    free_slot->by_downsample = 0;
     hook_n_reg++;
     *id = nid;
     return EB_ErrorNone;
+}
+
+/* Every caller of svt_aom_downsample_filtering_input_picture (picture analysis, pic_analysis_process.c:2345; the temporal
+ * filter once it has rewritten the centre picture, temporal_filtering.c:3956; the overlay picture, pd_process.c:2735)
+ * lands here when the hook is live: the device gets the luma plane as it is NOW, under a fresh identity (an earlier
+ * version of the same object, or the picture the pool object held before, is released), builds the pyramid, and the two
+ * CPU planes are filled from it. svt_me_gpu_segment finds the object registered and uploads nothing. */
+EbErrorType svt_me_gpu_downsample(const PictureParentControlSet *pcs, const EbPictureBufferDesc *pic, EbPictureBufferDesc *quarter_pic,
+                                  EbPictureBufferDesc *sixteenth_pic) {
+    if (!svt_me_gpu_live() || !hook_read_plane)
+        return EB_ErrorUndefined;
+    const EbPaReferenceObject *obj  = (const EbPaReferenceObject *)pcs->pa_ref_pic_wrapper->object_ptr;
+    HookReg                   *slot = NULL, *free_slot = NULL;
+    pthread_mutex_lock(&hook_mu);
+    for (int i = 0; i < HOOK_MAX_REGS; i++) {
+        if (hook_regs[i].used && hook_regs[i].obj == (const void *)obj)
+            slot = &hook_regs[i];
+        else if (!hook_regs[i].used && !free_slot)
+            free_slot = &hook_regs[i];
+    }
+    if (slot) {
+        svt_me_picture_release(slot->id);
+        hook_n_rel++;
+        slot->used = 0;
+    } else
+        slot = free_slot;
+    if (!slot) {
+        pthread_mutex_unlock(&hook_mu);
+        return EB_ErrorInsufficientResources;
+    }
+    const uint64_t nid = ((hook_n_reg + 1) << 32) | (pcs->picture_number & 0xFFFFFFFFull);
+    int            e   = svt_me_picture_register(nid, pic->buffer_y, pic->stride_y, pic->org_x, pic->org_y, pcs->aligned_width,
+                                                 pcs->aligned_height);
+    if (e == ME_GPU_OK) {
+        slot->obj    = obj;
+        slot->number = pcs->picture_number;
+        slot->id     = nid;
+        slot->used   = 1;
+        slot->by_downsample = 1;
+        hook_n_reg++;
+        hook_n_ds++;
+    }
+    pthread_mutex_unlock(&hook_mu);
+    /* the read-backs wait for the upload and the pyramid kernel on the device; other pictures' calls are not held up */
+    if (e == ME_GPU_OK)
+        e = hook_read_plane(nid, 1, quarter_pic->buffer_y, quarter_pic->stride_y);
+    if (e == ME_GPU_OK)
+        e = hook_read_plane(nid, 2, sixteenth_pic->buffer_y, sixteenth_pic->stride_y);
+    return map_error(e);
+}
+
+uint64_t svt_me_gpu_downsample_count(void) {
+    pthread_mutex_lock(&hook_mu);
+    const uint64_t n = hook_n_ds;
+    pthread_mutex_unlock(&hook_mu);
+    return n;
 }
 
 EbErrorType svt_me_gpu_segment(PictureParentControlSet *pcs, MeContext *me_ctx) {

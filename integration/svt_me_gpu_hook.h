@@ -74,6 +74,15 @@ void svt_me_gpu_stats(uint64_t *registered, uint64_t *released, uint64_t *pictur
 EbErrorType svt_me_gpu_pyramid_for_analysis(const PictureParentControlSet *pcs, const EbPictureBufferDesc *input_padded_pic,
                                             EbPictureBufferDesc *quarter_pic, EbPictureBufferDesc *sixteenth_pic);
 
+/* the same, for the encoder itself: called at the top of svt_aom_downsample_filtering_input_picture
+ * (pic_analysis_process.c:2139), so picture analysis, the temporal filter's pad_and_decimate_filtered_pic
+ * (temporal_filtering.c:3956) and the overlay path (pd_process.c:2735) all take the device's planes. Keyed by the pcs's
+ * PA reference object like svt_me_gpu_segment's lazy registration, which then finds the picture already on the device;
+ * a second call for the same object (the temporal filter rewrote the picture) replaces the first version. */
+EbErrorType svt_me_gpu_downsample(const PictureParentControlSet *pcs, const EbPictureBufferDesc *pic, EbPictureBufferDesc *quarter_pic,
+                                  EbPictureBufferDesc *sixteenth_pic);
+uint64_t    svt_me_gpu_downsample_count(void);
+
 /* ---- temporal filter (ME_MCTF, temporal_filtering.c:3144-3187) ------------------------------------------------ */
 /* ME results of one (centre, neighbour) pair over all blocks: what the block loop of produce_temporally_filtered_pic
  * reads from the MeContext after its svt_aom_motion_estimation_b64 call. Arrays are caller-owned, b64_count long. */

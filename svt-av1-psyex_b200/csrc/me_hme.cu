@@ -1241,7 +1241,12 @@ __global__ void __launch_bounds__(HM_ALL_THREADS, 5)
 static unsigned long long g_hme_launches = 0;
 unsigned long long me_hme_launch_count(void) { return g_hme_launches; }
 
-cudaError_t me_hme_setup(void) { return cudaFuncSetAttribute(k_hme, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HmeShared)); }
+#ifndef HM_EXTRA_SMEM /* experiments only (tools/exp/mkvariant.sh): unused shared memory that lowers the CTAs per SM */
+#define HM_EXTRA_SMEM 0
+#endif
+cudaError_t me_hme_setup(void) {
+    return cudaFuncSetAttribute(k_hme, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HmeShared) + HM_EXTRA_SMEM);
+}
 
 /* tensor maps of the pool's planes for pictures of geometry g (TMA: rank 3 = byte column, row, pool slot) */
 int me_hme_make_maps(HmeMaps *maps, const uint8_t *pool, const MePicGeom *g, int nslots) {
@@ -1271,6 +1276,6 @@ int me_hme_make_maps(HmeMaps *maps, const uint8_t *pool, const MePicGeom *g, int
 void me_launch_hme(MeJob *jobs, int njobs, int max_b64, int phase, FsTileList *list, const uint8_t *pool, const HmeMaps *maps,
                    cudaStream_t st) {
     dim3 grid(max_b64, njobs);
-    k_hme<<<grid, HM_ALL_THREADS, sizeof(HmeShared), st>>>(jobs, list, pool, *maps, phase);
+    k_hme<<<grid, HM_ALL_THREADS, sizeof(HmeShared) + HM_EXTRA_SMEM, st>>>(jobs, list, pool, *maps, phase);
     g_hme_launches++;
 }

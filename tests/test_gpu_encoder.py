@@ -30,6 +30,11 @@ def test_bitstream_identical_with_me_on_the_gpu(workdir, name):
     got, log = ec.encode(ec.GPU, name, workdir, env={"SVT_ME_GPU_LIB": abi.GPU_LIB})
     assert "open-loop ME on the B200 engine" in log, log[-1500:]
     assert got == gold[name], (name, got, gold[name])
+    # the pyramid too came from the device: every picture searched had its planes built there for picture analysis
+    m = re.search(r"(\d+) pictures searched, (\d+) pyramids built on the device \((\d+) for picture analysis", log)
+    assert m, log[-1500:]
+    searched, built, for_analysis = (int(x) for x in m.groups())
+    assert searched > 0 and for_analysis == built >= searched, (searched, built, for_analysis)
     if ec.CASES[name][3] >= 6:  # quick: the stock encoder on this box too
         live, _ = ec.encode(ec.STOCK, name, workdir)
         assert live == gold[name], ("stock encoder differs from its golden on this box", name)

@@ -1,4 +1,4 @@
-"""Runs a few pictures of a bench workload (for ncu / launch lists). Usage: profile_step.py [npictures] [kind] [workload]"""
+"""Runs a few pictures of a bench workload (for ncu / launch lists). Usage: profile_step.py [npictures] [kind] [workload | w:h:preset:refs0:refs1]"""
 import os
 import sys
 
@@ -10,7 +10,12 @@ from me_b200.engine import Engine  # noqa: E402
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 4
 kind = sys.argv[2] if len(sys.argv) > 2 else "motion"
-bench.set_workload(sys.argv[3] if len(sys.argv) > 3 else "1080p-m4")
+wl = sys.argv[3] if len(sys.argv) > 3 else "1080p-m4"
+if ":" in wl:  # experiments: width:height:preset:refs0:refs1 (e.g. 3840:2160:4:2:2 = the 1080p workload's controls on 4x the b64s)
+    w_, h_, pr_, r0_, r1_ = (int(x) for x in wl.split(":"))
+    bench.WORKLOAD, bench.W, bench.H, bench.PRESET, bench.FORCE_REFS = wl, w_, h_, pr_, (r0_, r1_)
+else:
+    bench.set_workload(wl)
 pics = bench.make_pictures(kind, pinned=False)
 eng = Engine(bench.W, bench.H, 4, 3, pictures_in_flight=40, devices=[0])
 for poc in range(bench.NPIC):
