@@ -77,4 +77,6 @@ for f in sorted(os.listdir(O)):
         open(os.path.join(P, f"ncu_{TAG}_{name}_details.txt"), "w").write(det)
         lines = subprocess.run([sys.executable, os.path.join(REPO, "tools", "ncu_lines.py"), rep, "40"], capture_output=True, text=True).stdout
         open(os.path.join(P, f"ncu_{TAG}_{name}_lines.txt"), "w").write(lines)
+        ops = subprocess.run([sys.executable, os.path.join(REPO, "tools", "ncu_opcodes.py"), rep, "40"], capture_output=True, text=True).stdout
+        open(os.path.join(P, f"ncu_{TAG}_{name}_opcodes.txt"), "w").write(ops)
 print("\n".join(sorted(f for f in os.listdir(P) if TAG in f)))
