@@ -635,7 +635,9 @@ def measure(args, kind, mode, steps, warmup, torch, dist, ctl, with_cpu):
         "scaling": "strong" if sharded else "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": cfg,
         "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": 16 * W * H * (1 if sharded else world),
                 "d2h_bytes_per_step": d2h_all, "ms_per_step": 1e3 * dt_e2e / steps,
-                "h2d_gbs_per_rank": h2d / (dt_e2e / steps) / 1e9, "d2h_gbs_per_rank": d2h / (dt_e2e / steps) / 1e9},
+                "h2d_gbs_per_rank": h2d / (dt_e2e / steps) / 1e9, "d2h_gbs_per_rank": d2h / (dt_e2e / steps) / 1e9,
+                "note": "can exceed `value`: the resident arm rotates L2-busting copies of the sequence, this arm searches planes "
+                        "it has just uploaded (warm in L2); uploads and result copies overlap the searches of other pictures"},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline, "parity": parity,
         "host": {"cpus": os.cpu_count()},
     }

@@ -48,6 +48,24 @@ def test_two_ranks_cover_the_mini_gop_once():
     assert set(a) <= set(need) and all(0 <= k < N for k in need)
 
 
+def test_cost_aware_dealing_balances_every_mini_gop():
+    """shard.owners with a cost: every picture owned exactly once, every rank computes the same map, and within a mini-GOP no
+    rank carries more than the lightest one plus one picture's cost (longest-processing-time-first bound)"""
+    order = synth.decode_order(N)
+    cost = {poc: 3.0 + (poc * 7 % 5) for poc in order}  # 3..7 "references"
+    for world in (2, 3, 4, 8):
+        own = shard.owners(order[1:], world, cost=lambda poc: cost[poc])
+        assert sorted(own) == sorted(order[1:]) and set(own.values()) <= set(range(world))
+        assert own == shard.owners(order[1:], world, cost=lambda poc: cost[poc])
+        load = [0.0] * world
+        for g0 in range(0, len(order) - 1, 16):
+            for poc in order[1 + g0:1 + g0 + 16]:
+                load[own[poc]] += cost[poc]
+            assert max(load) - min(load) <= max(cost.values()), (world, load)
+    # without a cost: the decode order dealt round-robin
+    assert shard.owners(order, 4) == {poc: i % 4 for i, poc in enumerate(order)}
+
+
 def test_gloo_world2_matches_single_process():
     ps, emul = PictureSet(W, H, N, "motion", Oracle()), Emulator()
     expect = [_checksum(poc, ps, emul) for poc in POCS]
