@@ -13,6 +13,7 @@ if [[ $STAGES == *1* ]]; then
   for a in "1080p-m4 iid" "1080p-m8 motion" "4k-m2 motion" "4k-m2 iid" "4k-m0 motion" "4k-m0 iid"; do
     set -- $a
     timeout 900 python bench.py --workload $1 --kind $2 --no-extra --no-cpu > $O/r2_bench_$1_$2.json 2> $O/r2_bench_$1_$2.err
+    timeout 600 python bench.py --impl reference --workload $1 --kind $2 --steps 3 --warmup 1 > $O/r2_bench_reference_arm_$1_$2.json 2> $O/r2_bench_reference_arm_$1_$2.err
   done
   for f in $O/r2_bench_*.json; do python - $f <<'PY'
 import json, sys
