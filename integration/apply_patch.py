@@ -13,6 +13,8 @@ What it changes (the same edits integration/encoder_me_gpu.patch shows as a unif
   Source/Lib/Codec/pic_analysis_process.c  svt_aom_downsample_filtering_input_picture (picture analysis, the temporal filter's
                                      re-decimation, the overlay picture): svt_me_gpu_downsample - upload once, pyramid on the
                                      device, the quarter / sixteenth planes read back for the CPU stages that still use them
+  Source/Lib/Codec/pd_process.c      early_hme (dynamic-GOP detector): svt_me_gpu_dg_detector in place of the TASK_DG_DETECTOR_HME
+                                     segments and the semaphore wait, when the device holds both pyramids
   Source/Lib/Codec/CMakeLists.txt    lists the new files; Source/Lib/CMakeLists.txt links libdl
 Every edit is an exact-match replacement: the script fails if the tree is not the one it was written against.
 """
@@ -154,6 +156,31 @@ def main():
     first_inc = s.index("#include")
     s = s[:first_inc] + '#include "svt_me_gpu_hook.h"\n#include "svt_log.h"\n' + s[first_inc:]
     open(pa, "w").write(s)
+
+    # ---- dynamic-GOP detector: one device call instead of the TASK_DG_DETECTOR_HME segments -------------------------
+    pd = os.path.join(codec, "pd_process.c")
+    replace_once(pd, '''    // create segments for the dg detector and send them to the motion estimation kernel
+    for (uint16_t seg_idx = 0; seg_idx < dg_detector_seg_total_count; ++seg_idx) {
+''', '''    if (svt_me_gpu_live() && svt_me_gpu_dg_ready(src_pcs, ref_pcs)) {
+        /* B200 path: HME level 0 of the whole picture pair in one launch over the two device-resident sixteenth planes */
+        if (svt_me_gpu_dg_detector(src_pcs) != EB_ErrorNone) {
+            SVT_ERROR("B200 ME engine failed in the dynamic-GOP detector (no CPU fallback)\\n");
+            abort();
+        }
+    } else {
+    // create segments for the dg detector and send them to the motion estimation kernel
+    for (uint16_t seg_idx = 0; seg_idx < dg_detector_seg_total_count; ++seg_idx) {
+''')
+    replace_once(pd, '''    // wait for all segments to complete before the frame based calculations can be performed using the dg metrics
+    svt_block_on_semaphore(src_pcs->dg_detector->frame_done_sem);
+''', '''    // wait for all segments to complete before the frame based calculations can be performed using the dg metrics
+    svt_block_on_semaphore(src_pcs->dg_detector->frame_done_sem);
+    }
+''')
+    s = open(pd).read()
+    first_inc = s.index("#include")
+    s = s[:first_inc] + '#include "svt_me_gpu_hook.h"\n#include "svt_log.h"\n' + s[first_inc:]
+    open(pd, "w").write(s)
 
     # ---- the new source joins the CODEC object library ----
     replace_once(os.path.join(codec, "CMakeLists.txt"), "set(all_files\n        adaptive_mv_pred.c\n",

@@ -20,6 +20,7 @@ static const char *(*hook_last_error)(void) = NULL;
 static void (*hook_shutdown)(void) = NULL;
 static int (*hook_dg)(uint64_t, uint64_t, uint8_t, MeGpuDgMetrics *) = NULL;
 static void *hook_lib              = NULL;
+static uint64_t hook_n_dg_read(void);
 
 #include <stdio.h>
 static EbErrorType map_error(int rc) {
@@ -61,8 +62,9 @@ void svt_me_gpu_hook_shutdown(void) {
         uint64_t reg, rel, pics;
         svt_me_gpu_stats(&reg, &rel, &pics);
         fprintf(stderr, "svt_me_gpu_hook: %llu pictures searched, %llu pyramids built on the device (%llu for picture analysis / "
-                        "the temporal filter / overlays), %llu released\n", (unsigned long long)pics, (unsigned long long)reg,
-                (unsigned long long)svt_me_gpu_downsample_count(), (unsigned long long)rel);
+                        "the temporal filter / overlays), %llu released, %llu dynamic-GOP detector calls\n", (unsigned long long)pics,
+                (unsigned long long)reg, (unsigned long long)svt_me_gpu_downsample_count(), (unsigned long long)rel,
+                (unsigned long long)hook_n_dg_read());
         hook_shutdown();
     }
     svt_me_picture_register = NULL;
@@ -269,7 +271,7 @@ static HookReg         hook_regs[HOOK_MAX_REGS];
 static HookPic         hook_pics[HOOK_MAX_PICS];
 static pthread_mutex_t hook_mu = PTHREAD_MUTEX_INITIALIZER;
 static pthread_cond_t  hook_cv = PTHREAD_COND_INITIALIZER;
-static uint64_t        hook_n_reg, hook_n_rel, hook_n_pic, hook_n_ds;
+static uint64_t        hook_n_reg, hook_n_rel, hook_n_pic, hook_n_ds, hook_n_dg;
 
 int svt_me_gpu_live(void) { return svt_me_picture_submit != NULL; }
 
@@ -461,17 +463,56 @@ void svt_me_gpu_tf_load_block(MeContext *me_ctx, const SvtMeGpuTfPair *pair, uin
         me_ctx->tf_use_pred_64x64_only_th = (uint8_t)~0; /* motion_estimation.c:3111 */
 }
 
+static uint64_t hook_n_dg_read(void) {
+    pthread_mutex_lock(&hook_mu);
+    const uint64_t n = hook_n_dg;
+    pthread_mutex_unlock(&hook_mu);
+    return n;
+}
+
+/* hook_mu NOT held. The engine identity of the pyramid registered for `obj` (svt_me_gpu_downsample / svt_me_gpu_segment), or 0 */
+static int hook_id_of(const void *obj, uint64_t *id) {
+    int found = 0;
+    pthread_mutex_lock(&hook_mu);
+    for (int i = 0; i < HOOK_MAX_REGS && !found; i++)
+        if (hook_regs[i].used && hook_regs[i].obj == obj) {
+            *id   = hook_regs[i].id;
+            found = 1;
+        }
+    pthread_mutex_unlock(&hook_mu);
+    return found;
+}
+
+int svt_me_gpu_dg_ready(const PictureParentControlSet *src_pcs, const PictureParentControlSet *ref_pcs) {
+    uint64_t a, b;
+    return hook_dg && src_pcs->pa_ref_pic_wrapper && ref_pcs->pa_ref_pic_wrapper && hook_id_of(src_pcs->pa_ref_pic_wrapper->object_ptr, &a) &&
+           hook_id_of(ref_pcs->pa_ref_pic_wrapper->object_ptr, &b);
+}
+
 EbErrorType svt_me_gpu_dg_detector(PictureParentControlSet *src_pcs) {
     if (!hook_dg)
         return EB_ErrorUndefined;
-    MeGpuDgMetrics m;
-    const int      rc = hook_dg(src_pcs->picture_number, src_pcs->dg_detector->ref_pic->picture_number,
-                                (uint8_t)src_pcs->input_resolution, &m);
+    MeGpuDgMetrics                 m;
+    const PictureParentControlSet *ref_pcs = src_pcs->dg_detector->ref_pic;
+    /* inside the encoder the pictures are known to the engine by the identities the hook registered them under (keyed by
+       their PA reference objects); a host that registered them itself (svt_me_gpu_register_picture) uses the picture numbers */
+    uint64_t a = src_pcs->picture_number, b = ref_pcs->picture_number;
+    if (src_pcs->pa_ref_pic_wrapper && ref_pcs->pa_ref_pic_wrapper) {
+        uint64_t ia, ib;
+        if (hook_id_of(src_pcs->pa_ref_pic_wrapper->object_ptr, &ia) && hook_id_of(ref_pcs->pa_ref_pic_wrapper->object_ptr, &ib)) {
+            a = ia;
+            b = ib;
+        }
+    }
+    const int rc = hook_dg(a, b, (uint8_t)src_pcs->input_resolution, &m);
     if (rc != ME_GPU_OK)
         return map_error(rc);
     src_pcs->dg_detector->metrics.tot_dist       = m.tot_dist; /* then pd_process.c:595-603 unchanged */
     src_pcs->dg_detector->metrics.tot_cplx       = m.tot_cplx;
     src_pcs->dg_detector->metrics.tot_active     = m.tot_active;
     src_pcs->dg_detector->metrics.sum_in_vectors = m.sum_in_vectors;
+    pthread_mutex_lock(&hook_mu);
+    hook_n_dg++;
+    pthread_mutex_unlock(&hook_mu);
     return EB_ErrorNone;
 }

@@ -106,6 +106,9 @@ void svt_me_gpu_tf_load_block(MeContext *me_ctx, const SvtMeGpuTfPair *pair, uin
 /* replaces the TASK_DG_DETECTOR_HME segment dispatch + semaphore wait: fills src_pcs->dg_detector->metrics for
  * (src_pcs, src_pcs->dg_detector->ref_pic); both pictures registered */
 EbErrorType svt_me_gpu_dg_detector(PictureParentControlSet *src_pcs);
+/* non-zero when the hook is live and the device holds the pyramids of both pictures (they passed through
+ * svt_me_gpu_downsample): early_hme then calls svt_me_gpu_dg_detector instead of posting its segments */
+int svt_me_gpu_dg_ready(const PictureParentControlSet *src_pcs, const PictureParentControlSet *ref_pcs);
 
 #ifdef __cplusplus
 }

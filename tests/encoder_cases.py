@@ -26,6 +26,8 @@ CASES = {
     "320x192_m0": (320, 192, 9, 0, ["--lp", "4"]),
     "640x360_m8_scene": (640, 360, 25, 8, ["--lp", "1", "--keyint", "12", "--enable-overlays", "1"]),
     "640x360_m4_scene": (640, 360, 17, 4, ["--lp", "4", "--keyint", "8", "--enable-overlays", "1"]),
+    # 65 pictures in mini-GOPs of 32 (six hierarchical layers): the dynamic-GOP detector (early_hme) decides 6L vs 5L
+    "320x192_m6_6L": (320, 192, 65, 6, ["--lp", "1", "--hierarchical-levels", "5"]),
 }
 
 

@@ -3,7 +3,7 @@ integration/ applied (integration/build_encoder.sh; the binaries travel prebuilt
 ME on the B200; the bitstream must be byte-identical (md5 of the .ivf) to the one of the unmodified encoder, frozen in
 tests/golden/encoder_md5.json by tests/golden/make_encoder_md5.py and, for the quick cases, re-encoded here by the stock
 binary on this box as well. Presets 0, 2, 4, 6, 8; I slices, a scene change, overlay pictures and short mini-GOPs in the
-"scene" clips; ME runs on every non-I picture of every case."""
+"scene" clips; a 65-picture clip in mini-GOPs of 32 for the dynamic-GOP detector; ME runs on every non-I picture of every case."""
 import json
 import os
 import re
@@ -35,6 +35,9 @@ def test_bitstream_identical_with_me_on_the_gpu(workdir, name):
     assert m, log[-1500:]
     searched, built, for_analysis = (int(x) for x in m.groups())
     assert searched > 0 and for_analysis == built >= searched, (searched, built, for_analysis)
+    # mini-GOPs of 32: the dynamic-GOP detector's three picture pairs per decision went to the device too
+    dg = int(re.search(r"(\d+) dynamic-GOP detector calls", log).group(1))
+    assert dg > 0 if "6L" in name else dg >= 0, dg
     if ec.CASES[name][3] >= 6:  # quick: the stock encoder on this box too
         live, _ = ec.encode(ec.STOCK, name, workdir)
         assert live == gold[name], ("stock encoder differs from its golden on this box", name)
