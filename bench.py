@@ -56,7 +56,9 @@ STEP_POCS = workloads.STEP_POCS  # decode order of mini-GOP 2 (POC 17..32)
 
 
 def derive(poc):
-    from helpers import derive as _d
+    if WORKLOAD in WORKLOADS:  # the encoder's own reference lists at the workload's preset (tests/golden/encoder_lists.json)
+        return workloads.derive_for(WORKLOAD, poc)
+    from helpers import derive as _d  # experiments on other sizes (tools/profile_step.py w:h:preset:r0:r1): synth's table
     return _d(PRESET, W, H, poc, NPIC, force_refs=FORCE_REFS)
 
 

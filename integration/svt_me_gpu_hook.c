@@ -20,6 +20,7 @@ static const char *(*hook_last_error)(void) = NULL;
 static void (*hook_shutdown)(void) = NULL;
 static int (*hook_dg)(uint64_t, uint64_t, uint8_t, MeGpuDgMetrics *) = NULL;
 static void *hook_lib              = NULL;
+static int   hook_log_lists        = 0;
 static uint64_t hook_n_dg_read(void);
 
 #include <stdio.h>
@@ -40,6 +41,7 @@ EbErrorType svt_me_gpu_hook_init(const char *library_path, int max_width, int ma
         dlclose(h);
         return EB_ErrorInsufficientResources;
     }
+    hook_log_lists          = getenv("SVT_ME_GPU_LOG_LISTS") != NULL; /* diagnostics only: changes nothing that is computed */
     svt_me_picture_register = (int (*)(uint64_t, const uint8_t *, int, int, int, int, int))dlsym(h, "me_gpu_register_picture");
     svt_me_picture_submit   = (int (*)(uint64_t, const MeGpuParams *, const uint64_t[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS]))dlsym(h, "me_gpu_submit");
     svt_me_picture_wait     = (int (*)(uint64_t, MeGpuOutputs *))dlsym(h, "me_gpu_wait");
@@ -196,6 +198,17 @@ static EbErrorType hook_picture(PictureParentControlSet *pcs, const MeContext *m
     for (int l = 0; l < me_ctx->num_of_list_to_search; l++)
         for (int r = 0; r < me_ctx->num_of_ref_pic_to_search[l]; r++)
             refs[l][r] = ref_ids ? ref_ids[l][r] : me_ctx->me_ds_ref_array[l][r].picture_number; /* me_process.c:248-262 */
+    if (hook_log_lists) { /* SVT_ME_GPU_LOG_LISTS: the reference lists the encoder's own prediction structure gives (pd_process.c:3675-3693) */
+        char line[256];
+        int  n = snprintf(line, sizeof line, "svt_me_gpu_hook: lists poc %llu tl %u:", (unsigned long long)pcs->picture_number,
+                          (unsigned)pcs->temporal_layer_index);
+        for (int l = 0; l < me_ctx->num_of_list_to_search; l++) {
+            n += snprintf(line + n, sizeof line - (size_t)n, " L%d", l);
+            for (int r = 0; r < me_ctx->num_of_ref_pic_to_search[l]; r++)
+                n += snprintf(line + n, sizeof line - (size_t)n, " %llu", (unsigned long long)me_ctx->me_ds_ref_array[l][r].picture_number);
+        }
+        fprintf(stderr, "%s\n", line);
+    }
     const uint64_t job = src_id;
     const int rc = svt_me_picture_submit(job, &gp, refs);
     if (rc != ME_GPU_OK)

@@ -12,9 +12,10 @@ def host_lib():
     return abi.load_host_lib()
 
 
-def derive(preset, width, height, poc, n_pictures, force_refs=None, qp=35, **kw):
-    """MeGpuParams + reference lists of picture `poc` in a random-access 5-layer sequence."""
-    tl = synth.RA5_RPS[poc % 16][0]
+def derive(preset, width, height, poc, n_pictures, force_refs=None, qp=35, lists=None, **kw):
+    """MeGpuParams + reference lists of picture `poc` in a random-access 5-layer sequence. `lists` = (temporal layer, list 0,
+    list 1) given by the caller (the bench workloads: the encoder's own lists, workloads.lists_for); else synth's table."""
+    tl = lists[0] if lists else synth.RA5_RPS[poc % 16][0]
     cfg = abi.MeGpuEncoderConfig(enc_mode=preset, qp=qp, hierarchical_levels=4, width=width, height=height,
                                  picture_number=poc, temporal_layer_index=tl, is_ref=1 if tl < 4 else 0, **kw)
     if force_refs:
@@ -22,7 +23,10 @@ def derive(preset, width, height, poc, n_pictures, force_refs=None, qp=35, **kw)
     p = abi.MeGpuParams()
     rc = host_lib().me_gpu_derive_params(C.byref(cfg), C.byref(p))
     assert rc == 0
-    _, l0, l1 = synth.ref_lists(poc, n_pictures, p.num_of_ref_pic_to_search[0], p.num_of_ref_pic_to_search[1])
+    if lists:
+        l0, l1 = list(lists[1])[:p.num_of_ref_pic_to_search[0]], list(lists[2])[:p.num_of_ref_pic_to_search[1]]
+    else:
+        _, l0, l1 = synth.ref_lists(poc, n_pictures, p.num_of_ref_pic_to_search[0], p.num_of_ref_pic_to_search[1])
     p.num_of_ref_pic_to_search[0] = len(l0)
     p.num_of_ref_pic_to_search[1] = len(l1)
     if not l1:

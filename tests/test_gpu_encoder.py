@@ -48,3 +48,32 @@ def test_encoder_fails_loudly_when_the_engine_library_is_missing(workdir):
         pytest.skip("integration/_build/SvtAv1EncApp_gpu missing")
     with pytest.raises(RuntimeError, match="could not be brought up"):
         ec.encode(ec.GPU, "320x192_m8", workdir, env={"SVT_ME_GPU_LIB": "/nonexistent/libme_gpu.so"})
+
+
+def test_bench_reference_lists_are_the_encoders_own(workdir):
+    """VERDICT missing #8: the bench workloads take their reference lists from tests/golden/encoder_lists.json. That file must be
+    what the encoder's own prediction structure (pd_process.c:3675-3693) hands to the ME stage: the patched encoder prints
+    the lists it receives (SVT_ME_GPU_LOG_LISTS) for the generator's clip at presets 4 and 8, compared picture by picture."""
+    if not os.path.exists(ec.GPU):
+        pytest.skip("integration/_build/SvtAv1EncApp_gpu missing")
+    import workloads
+    frozen = json.load(open(workloads.LISTS_FILE))["lists"]
+    for preset in (4, 8):
+        name = f"lists_m{preset}"
+        ec.CASES[name] = (320, 192, 49, preset, ["--lp", "1", "--enable-tf", "0", "--hierarchical-levels", "4"])
+        try:
+            _, log = ec.encode(ec.GPU, name, workdir, env={"SVT_ME_GPU_LIB": abi.GPU_LIB, "SVT_ME_GPU_LOG_LISTS": "1"})
+        finally:
+            del ec.CASES[name]
+        seen = {}
+        for m in re.finditer(r"lists poc (\d+) tl (\d+):(.*)", log):
+            lists = [[int(x) for x in part.split()[1:]] for part in re.findall(r"L\d[ \d]*", m.group(3))]
+            seen[m.group(1)] = ([int(m.group(2))] + lists + [[]])[:3]
+        assert len(seen) == 48, len(seen)  # every picture but the key frame went through ME
+        assert seen == frozen[str(preset)], {k: (seen.get(k), v) for k, v in frozen[str(preset)].items() if seen.get(k) != v}
+    # and the workloads use them: 1080p-m4 = preset 4 cut to 2 + 2, the 4K ones = presets 2 / 0 whole
+    for wl, poc in (("1080p-m4", 24), ("4k-m2", 20), ("4k-m0", 31), ("1080p-m8", 28)):
+        tl, l0, l1 = workloads.lists_for(wl, poc)
+        f = frozen[str(workloads.WORKLOADS[wl]["preset"])][str(poc)]
+        r = workloads.WORKLOADS[wl]["refs"] or (9, 9)
+        assert (tl, l0, l1) == (f[0], f[1][:r[0]], f[2][:r[1]])

@@ -32,11 +32,29 @@ STEP_POCS = [32 if g == 0 else 16 + g for g in synth.RA5_DECODE_ORDER]
 HASH_FILE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "picture_hashes.json")
 
 
+LISTS_FILE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "encoder_lists.json")
+_LISTS = None
+
+
+def lists_for(name, poc):
+    """(temporal layer, list0 pocs, list1 pocs) of picture `poc` of workload `name`: the lists the ENCODER's own prediction
+    structure gives at the workload's preset (tests/golden/encoder_lists.json, frozen from a run of the encoder), cut to
+    the workload's forced reference counts where BASELINE.json states them (configs[1]: "2 refs/list")."""
+    global _LISTS
+    if _LISTS is None:
+        _LISTS = json.load(open(LISTS_FILE))["lists"]
+    wl = WORKLOADS[name]
+    tl, l0, l1 = _LISTS[str(wl["preset"])][str(poc)]
+    if wl["refs"]:
+        l0, l1 = l0[:wl["refs"][0]], l1[:wl["refs"][1]]
+    return tl, list(l0), list(l1)
+
+
 def derive_for(name, poc):
     """(cfg, MeGpuParams, list0 pocs, list1 pocs) of picture `poc` of workload `name`"""
     from helpers import derive
     wl = WORKLOADS[name]
-    return derive(wl["preset"], wl["w"], wl["h"], poc, NPIC, force_refs=wl["refs"])
+    return derive(wl["preset"], wl["w"], wl["h"], poc, NPIC, force_refs=wl["refs"], lists=lists_for(name, poc))
 
 
 def picture_hashes(out):
@@ -70,11 +88,10 @@ def reference_params(name, poc, ref):
     from me_b200 import abi
     wl = WORKLOADS[name]
     l0max, l1max, nref, zz, only_l_bwd = MRP[name]
-    tl = synth.RA5_RPS[poc % 16][0]
+    tl, l0, l1 = lists_for(name, poc)
     cfg = abi.MeGpuEncoderConfig(enc_mode=wl["preset"], qp=35, hierarchical_levels=4, width=wl["w"], height=wl["h"],
                                  picture_number=poc, temporal_layer_index=tl, is_ref=1 if tl < 4 else 0)
     p = ref.derive_params(cfg, nref, zz)
-    _, l0, l1 = synth.ref_lists(poc, NPIC, l0max, l1max)
     p.only_l_bwd = only_l_bwd
     p.max_l0, p.max_refs = l0max, l0max + l1max
     p.max_cand = l0max + l1max + l0max * l1max + (l0max - 1) + (1 if l1max == 3 else 0)  # pcs.c:91-96
