@@ -259,6 +259,17 @@ int me_gpu_register_picture_from_peer(uint64_t picture_number, int peer, int pee
                                       int width, int height);
 uint64_t me_gpu_ipc_bytes_pulled(void); /* bytes copied from peers' pools so far */
 
+/* more than one engine per process ------------------------------------------------------------
+ * The reference library serves several encoder instances in one process (EbComponentType handles, enc_handle.c:1405);
+ * so does this one. Every me_gpu_* call goes to the engine BOUND TO THE CALLING THREAD: the process-wide default engine
+ * unless the thread has called me_gpu_engine_bind. An instance creates its engine once, and each of its threads binds it
+ * before its first call (a thread-local pointer: free). Engines share nothing (pool, jobs, streams, errors are per engine
+ * / per thread); the static scratch of me_gpu_dg_detector_noalloc is the one thing every caller of a process shares. */
+typedef struct MeGpuEngine MeGpuEngine;
+int  me_gpu_engine_create(MeGpuEngine **engine); /* not initialised yet: bind it, then me_gpu_init */
+void me_gpu_engine_bind(MeGpuEngine *engine); /* NULL = back to the default engine */
+int  me_gpu_engine_destroy(MeGpuEngine *engine); /* after me_gpu_shutdown on it: ME_GPU_ERR_STATE otherwise */
+
 /* motion estimation ----------------------------------------------------------------------- */
 int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
                   const uint64_t ref_picture_numbers[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS]);

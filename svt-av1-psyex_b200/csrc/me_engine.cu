@@ -19,6 +19,7 @@
 #include <cstring>
 #include <map>
 #include <mutex>
+#include <new>
 #include <string>
 #include <vector>
 
@@ -163,7 +164,11 @@ struct Engine {
     unsigned            done_next = 0;
 };
 
-Engine g;
+/* The engine the me_gpu_* calls of the calling thread go to: the process-wide default engine unless the thread has bound
+ * another one (me_gpu_engine_bind): several encoder instances in one process each get their own pool, jobs and streams. */
+static Engine               g_default;
+static thread_local Engine *t_eng = &g_default;
+static inline Engine &E() { return *t_eng; }
 thread_local std::string t_err; /* every calling thread reads back its own last error */
 
 int fail(int code, const std::string &msg) {
@@ -277,9 +282,9 @@ void free_job(JobCtx &jc) {
 }
 
 void free_slot_if_idle(int s) {
-    Slot &sl = g.slots[s];
+    Slot &sl = E().slots[s];
     if (sl.used && sl.release_pending && sl.refcount == 0) {
-        g.by_number.erase(sl.picture_number);
+        E().by_number.erase(sl.picture_number);
         sl.used = false;
         sl.release_pending = false;
     }
@@ -287,41 +292,41 @@ void free_slot_if_idle(int s) {
 
 /* builds the pyramid of slot s on its owner device and replicates the slot to the other devices */
 int build_and_replicate(int s, int owner, const MePicGeom &gm, bool pad_full) {
-    Device      &d   = g.dev[owner];
-    const size_t off = (size_t)s * g.gmax.slot_bytes;
+    Device      &d   = E().dev[owner];
+    const size_t off = (size_t)s * E().gmax.slot_bytes;
     CU(cudaSetDevice(d.id));
     if (pad_full)
         me_launch_pad_full(d.pool, off, &gm.plane[0], d.upload);
     me_launch_downsample(d.pool, off, &gm.plane[0], &gm.plane[1], d.upload);
     me_launch_downsample(d.pool, off, &gm.plane[1], &gm.plane[2], d.upload);
     CU(cudaGetLastError());
-    CU(cudaEventRecord(g.slots[s].ready[owner], d.upload));
-    for (size_t o = 0; o < g.dev.size(); o++) {
+    CU(cudaEventRecord(E().slots[s].ready[owner], d.upload));
+    for (size_t o = 0; o < E().dev.size(); o++) {
         if ((int)o == owner)
             continue;
-        Device &p = g.dev[o];
+        Device &p = E().dev[o];
         /* the copy runs on the destination's upload stream, after the owner finished the pyramid */
         CU(cudaSetDevice(p.id));
-        CU(cudaStreamWaitEvent(p.upload, g.slots[s].ready[owner], 0));
-        CU(cudaMemcpyPeerAsync(p.pool + off, p.id, d.pool + off, d.id, g.gmax.slot_bytes, p.upload));
-        CU(cudaEventRecord(g.slots[s].ready[o], p.upload));
+        CU(cudaStreamWaitEvent(p.upload, E().slots[s].ready[owner], 0));
+        CU(cudaMemcpyPeerAsync(p.pool + off, p.id, d.pool + off, d.id, E().gmax.slot_bytes, p.upload));
+        CU(cudaEventRecord(E().slots[s].ready[o], p.upload));
     }
     return ME_GPU_OK;
 }
 
 int register_common(uint64_t picture_number, const uint8_t *src, int stride, int org_x, int org_y, int width, int height,
                     bool padded) {
-    if (!g.initialised)
+    if (!E().initialised)
         return fail(ME_GPU_ERR_STATE, "me_gpu_init has not been called");
-    if (!src || width <= 0 || height <= 0 || (width & 7) || (height & 7) || width > g.gmax.width || height > g.gmax.height)
+    if (!src || width <= 0 || height <= 0 || (width & 7) || (height & 7) || width > E().gmax.width || height > E().gmax.height)
         return fail(ME_GPU_ERR_BAD_ARG, "bad picture geometry (luma size must be a multiple of 8 and within the init maximum)");
     if (padded && (org_x < ME_PAD_FULL || org_y < ME_PAD_FULL || stride < width + org_x + ME_PAD_FULL))
         return fail(ME_GPU_ERR_BAD_ARG, "padded plane needs at least 68 pixels of border on every side");
-    if (g.by_number.count(picture_number))
+    if (E().by_number.count(picture_number))
         return fail(ME_GPU_ERR_STATE, "picture already registered");
     int s = -1;
-    for (int i = 0; i < g.nslots; i++)
-        if (!g.slots[i].used) {
+    for (int i = 0; i < E().nslots; i++)
+        if (!E().slots[i].used) {
             s = i;
             break;
         }
@@ -329,9 +334,9 @@ int register_common(uint64_t picture_number, const uint8_t *src, int stride, int
         return fail(ME_GPU_ERR_NO_MEMORY, "picture pool is full (raise pictures_in_flight or release pictures)");
     MePicGeom gm;
     me_make_geom(&gm, width, height);
-    const int    owner = (int)(g.register_counter++ % g.dev.size());
-    Device      &d     = g.dev[owner];
-    const size_t off   = (size_t)s * g.gmax.slot_bytes + gm.plane[0].offset;
+    const int    owner = (int)(E().register_counter++ % E().dev.size());
+    Device      &d     = E().dev[owner];
+    const size_t off   = (size_t)s * E().gmax.slot_bytes + gm.plane[0].offset;
     CU(cudaSetDevice(d.id));
     /* rows of the source to their place in the pool. When the source rows are (nearly) contiguous and 4-byte granular, one
        contiguous copy into the landing buffer plus a re-pitch kernel: a pitched copy of 2 KB rows reaches a third of the
@@ -346,7 +351,7 @@ int register_common(uint64_t picture_number, const uint8_t *src, int stride, int
         me_launch_repitch(d.stage, stride, dst, gm.plane[0].stride, row_bytes, rows, d.upload);
     } else
         CU(cudaMemcpy2DAsync(dst, gm.plane[0].stride, first, stride, row_bytes, rows, cudaMemcpyHostToDevice, d.upload));
-    Slot &sl          = g.slots[s];
+    Slot &sl          = E().slots[s];
     sl.used           = true;
     sl.picture_number = picture_number;
     sl.width          = width;
@@ -354,7 +359,7 @@ int register_common(uint64_t picture_number, const uint8_t *src, int stride, int
     sl.refcount       = 0;
     sl.release_pending = false;
     for (auto &v : sl.ready_seen) v = false;
-    g.by_number[picture_number] = s;
+    E().by_number[picture_number] = s;
     return build_and_replicate(s, owner, gm, !padded);
 }
 
@@ -372,10 +377,10 @@ int me_gpu_device_count(void) {
 }
 
 void me_gpu_shutdown(void) {
-    std::lock_guard<std::mutex> lk(g.mu);
-    if (!g.initialised)
+    std::lock_guard<std::mutex> lk(E().mu);
+    if (!E().initialised)
         return;
-    for (auto &d : g.dev) {
+    for (auto &d : E().dev) {
         cudaSetDevice(d.id);
         cudaDeviceSynchronize();
         for (auto &jc : d.jobs) free_job(jc);
@@ -386,28 +391,28 @@ void me_gpu_shutdown(void) {
         cudaFree(d.pool);
         cudaFree(d.stage);
     }
-    for (auto &pr : g.peers) {
+    for (auto &pr : E().peers) {
         for (auto &kv : pr.ev) cudaEventDestroy(kv.second);
         pr.ev.clear();
         if (pr.open) cudaIpcCloseMemHandle(pr.base);
         pr = Engine::Peer();
     }
-    for (auto &s : g.slots) {
+    for (auto &s : E().slots) {
         for (auto &e : s.ready)
             if (e) cudaEventDestroy(e);
         if (s.ipc_ready) cudaEventDestroy(s.ipc_ready);
     }
-    g.dev.clear();
-    g.slots.clear();
-    g.by_number.clear();
-    g.initialised = false;
-    g.cv.notify_all();
+    E().dev.clear();
+    E().slots.clear();
+    E().by_number.clear();
+    E().initialised = false;
+    E().cv.notify_all();
 }
 
 int me_gpu_init(int device_count, const int *device_ids, int max_width, int max_height, int max_refs_l0, int max_refs_l1,
                 int pictures_in_flight) {
-    std::lock_guard<std::mutex> lk(g.mu);
-    if (g.initialised)
+    std::lock_guard<std::mutex> lk(E().mu);
+    if (E().initialised)
         return fail(ME_GPU_ERR_STATE, "already initialised");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
@@ -425,15 +430,15 @@ int me_gpu_init(int device_count, const int *device_ids, int max_width, int max_
     for (int id : ids)
         if (id < 0 || id >= ndev)
             return fail(ME_GPU_ERR_BAD_ARG, "device id out of range");
-    me_make_geom(&g.gmax, (max_width + 7) & ~7, (max_height + 7) & ~7);
-    g.nslots = pictures_in_flight;
-    g.max_l0 = max_refs_l0;
-    g.max_l1 = max_refs_l1;
-    g.slots.assign((size_t)g.nslots, Slot());
-    g.dev.resize(ids.size());
+    me_make_geom(&E().gmax, (max_width + 7) & ~7, (max_height + 7) & ~7);
+    E().nslots = pictures_in_flight;
+    E().max_l0 = max_refs_l0;
+    E().max_l1 = max_refs_l1;
+    E().slots.assign((size_t)E().nslots, Slot());
+    E().dev.resize(ids.size());
     const int njobs = pictures_in_flight < kMaxJobs ? pictures_in_flight : kMaxJobs;
     for (size_t i = 0; i < ids.size(); i++) {
-        Device &d = g.dev[i];
+        Device &d = E().dev[i];
         d.id      = ids[i];
         CU(cudaSetDevice(d.id));
         cudaDeviceProp prop;
@@ -444,16 +449,16 @@ int me_gpu_init(int device_count, const int *device_ids, int max_width, int max_
         CU(me_kernels_setup());
         CU(me_hme_setup());
         CU(cudaStreamCreateWithFlags(&d.upload, cudaStreamNonBlocking));
-        CU(cudaMalloc((void **)&d.pool, (size_t)g.nslots * g.gmax.slot_bytes + 65536));
-        CU(cudaMemset(d.pool, 0, (size_t)g.nslots * g.gmax.slot_bytes + 65536));
-        d.stage_bytes = (size_t)(g.gmax.width + 2 * ME_PAD_FULL) * (size_t)(g.gmax.height + 2 * ME_PAD_FULL) * 5 / 4;
+        CU(cudaMalloc((void **)&d.pool, (size_t)E().nslots * E().gmax.slot_bytes + 65536));
+        CU(cudaMemset(d.pool, 0, (size_t)E().nslots * E().gmax.slot_bytes + 65536));
+        d.stage_bytes = (size_t)(E().gmax.width + 2 * ME_PAD_FULL) * (size_t)(E().gmax.height + 2 * ME_PAD_FULL) * 5 / 4;
         CU(cudaMalloc((void **)&d.stage, d.stage_bytes));
         CU(cudaStreamCreateWithFlags(&d.dg_stream, cudaStreamNonBlocking));
         CU(cudaMalloc((void **)&d.dg_acc, sizeof(MeGpuDgMetrics)));
         CU(cudaMallocHost((void **)&d.dg_host, sizeof(MeGpuDgMetrics)));
         d.jobs.resize((size_t)njobs);
         for (auto &jc : d.jobs) {
-            int rc = alloc_job(d, jc, g.gmax, max_refs_l0, max_refs_l1);
+            int rc = alloc_job(d, jc, E().gmax, max_refs_l0, max_refs_l1);
             if (rc)
                 return rc;
         }
@@ -470,12 +475,12 @@ int me_gpu_init(int device_count, const int *device_ids, int max_width, int max_
             }
         CU(cudaDeviceSynchronize());
     }
-    for (auto &s : g.slots)
+    for (auto &s : E().slots)
         for (size_t i = 0; i < ids.size(); i++) {
             CU(cudaSetDevice(ids[i]));
             CU(cudaEventCreateWithFlags(&s.ready[i], cudaEventDisableTiming));
         }
-    g.initialised = true;
+    E().initialised = true;
     return ME_GPU_OK;
 }
 
@@ -494,7 +499,7 @@ int me_gpu_plane_geometry(int width, int height, int level, int *plane_w, int *p
 
 int me_gpu_register_picture(uint64_t picture_number, const uint8_t *y8b_padded, int stride, int org_x, int org_y, int width,
                             int height) {
-    std::lock_guard<std::mutex> lk(g.mu);
+    std::lock_guard<std::mutex> lk(E().mu);
     if (!y8b_padded)
         return fail(ME_GPU_ERR_BAD_ARG, "null plane");
     /* y8b_padded points at the first byte of the padded buffer: the interior starts at (org_x, org_y) */
@@ -502,18 +507,18 @@ int me_gpu_register_picture(uint64_t picture_number, const uint8_t *y8b_padded, 
 }
 
 int me_gpu_register_picture_unpadded(uint64_t picture_number, const uint8_t *y8b, int stride, int width, int height) {
-    std::lock_guard<std::mutex> lk(g.mu);
+    std::lock_guard<std::mutex> lk(E().mu);
     if (stride < width)
         return fail(ME_GPU_ERR_BAD_ARG, "stride < width");
     return register_common(picture_number, y8b, stride, 0, 0, width, height, false);
 }
 
 int me_gpu_release_picture(uint64_t picture_number) {
-    std::unique_lock<std::mutex> lk(g.mu);
-    if (!g.initialised)
+    std::unique_lock<std::mutex> lk(E().mu);
+    if (!E().initialised)
         return fail(ME_GPU_ERR_STATE, "not initialised");
-    auto it = g.by_number.find(picture_number);
-    if (it == g.by_number.end())
+    auto it = E().by_number.find(picture_number);
+    if (it == E().by_number.end())
         return fail(ME_GPU_ERR_NOT_FOUND, "picture not registered");
     const int s = it->second;
     /* uploads / peer copies into this slot must finish before the slot can be handed out again; the wait happens outside
@@ -522,10 +527,10 @@ int me_gpu_release_picture(uint64_t picture_number) {
     cudaEvent_t ev[8];
     int         ids[8];
     size_t      n = 0;
-    for (size_t i = 0; i < g.dev.size(); i++)
-        if (!g.slots[s].ready_seen[i]) {
-            ev[n]    = g.slots[s].ready[i];
-            ids[n++] = g.dev[i].id;
+    for (size_t i = 0; i < E().dev.size(); i++)
+        if (!E().slots[s].ready_seen[i]) {
+            ev[n]    = E().slots[s].ready[i];
+            ids[n++] = E().dev[i].id;
         }
     lk.unlock();
     for (size_t i = 0; i < n; i++) {
@@ -533,10 +538,10 @@ int me_gpu_release_picture(uint64_t picture_number) {
         cudaEventSynchronize(ev[i]);
     }
     lk.lock();
-    it = g.by_number.find(picture_number);
-    if (!g.initialised || it == g.by_number.end() || it->second != s)
+    it = E().by_number.find(picture_number);
+    if (!E().initialised || it == E().by_number.end() || it->second != s)
         return fail(ME_GPU_ERR_NOT_FOUND, "picture released twice");
-    g.slots[s].release_pending = true;
+    E().slots[s].release_pending = true;
     free_slot_if_idle(s);
     return ME_GPU_OK;
 }
@@ -544,32 +549,32 @@ int me_gpu_release_picture(uint64_t picture_number) {
 /* one level of a registered picture's pyramid into a caller-owned padded plane (picture analysis reads the
  * device-built sixteenth plane for its histograms, pic_analysis_process.c:1560-1570, instead of building its own) */
 int me_gpu_read_plane(uint64_t picture_number, int level, uint8_t *dst, int dst_stride) {
-    std::unique_lock<std::mutex> lk(g.mu);
-    if (!g.initialised)
+    std::unique_lock<std::mutex> lk(E().mu);
+    if (!E().initialised)
         return fail(ME_GPU_ERR_STATE, "not initialised");
-    auto it = g.by_number.find(picture_number);
-    if (it == g.by_number.end())
+    auto it = E().by_number.find(picture_number);
+    if (it == E().by_number.end())
         return fail(ME_GPU_ERR_NOT_FOUND, "picture not registered");
     if (level < 0 || level > 2 || !dst)
         return fail(ME_GPU_ERR_BAD_ARG, "level must be 0 (full), 1 (quarter) or 2 (sixteenth)");
     const int s = it->second;
     MePicGeom gm;
-    me_make_geom(&gm, g.slots[s].width, g.slots[s].height);
+    me_make_geom(&gm, E().slots[s].width, E().slots[s].height);
     const MePlaneGeom &pl = gm.plane[level];
     const int          pw = pl.width + 2 * pl.pad;
     if (dst_stride < pw)
         return fail(ME_GPU_ERR_BAD_ARG, "destination stride smaller than the padded plane's row");
-    Device &d = g.dev[0];
+    Device &d = E().dev[0];
     CU(cudaSetDevice(d.id));
-    g.slots[s].refcount++; /* the slot stays while the copy runs outside the lock */
-    cudaEvent_t ready = g.slots[s].ready[0];
-    const uint8_t *src = d.pool + (size_t)s * g.gmax.slot_bytes + pl.offset;
+    E().slots[s].refcount++; /* the slot stays while the copy runs outside the lock */
+    cudaEvent_t ready = E().slots[s].ready[0];
+    const uint8_t *src = d.pool + (size_t)s * E().gmax.slot_bytes + pl.offset;
     lk.unlock();
     cudaError_t e = cudaEventSynchronize(ready);
     if (e == cudaSuccess)
         e = cudaMemcpy2D(dst, (size_t)dst_stride, src, pl.stride, pw, pl.rows, cudaMemcpyDeviceToHost);
     lk.lock();
-    g.slots[s].refcount--;
+    E().slots[s].refcount--;
     free_slot_if_idle(s);
     if (e != cudaSuccess) {
         cudaGetLastError();
@@ -580,54 +585,54 @@ int me_gpu_read_plane(uint64_t picture_number, int level, uint8_t *dst, int dst_
 
 /* ---- one process per GPU: pyramids travel between the processes' pools over NVLink (CUDA IPC), no collective ---------- */
 int me_gpu_ipc_export_pool(unsigned char handle[64], uint64_t *slot_bytes) {
-    std::lock_guard<std::mutex> lk(g.mu);
-    if (!g.initialised)
+    std::lock_guard<std::mutex> lk(E().mu);
+    if (!E().initialised)
         return fail(ME_GPU_ERR_STATE, "not initialised");
     if (!handle || !slot_bytes)
         return fail(ME_GPU_ERR_BAD_ARG, "null argument");
     static_assert(sizeof(cudaIpcMemHandle_t) == 64 && sizeof(cudaIpcEventHandle_t) == 64, "IPC handles are 64 bytes");
-    CU(cudaSetDevice(g.dev[0].id));
+    CU(cudaSetDevice(E().dev[0].id));
     cudaIpcMemHandle_t h;
-    CU(cudaIpcGetMemHandle(&h, g.dev[0].pool));
+    CU(cudaIpcGetMemHandle(&h, E().dev[0].pool));
     memcpy(handle, &h, 64);
-    *slot_bytes = g.gmax.slot_bytes;
+    *slot_bytes = E().gmax.slot_bytes;
     return ME_GPU_OK;
 }
 
 int me_gpu_ipc_open_peer(int peer, const unsigned char handle[64], uint64_t slot_bytes) {
-    std::lock_guard<std::mutex> lk(g.mu);
-    if (!g.initialised)
+    std::lock_guard<std::mutex> lk(E().mu);
+    if (!E().initialised)
         return fail(ME_GPU_ERR_STATE, "not initialised");
     if (peer < 0 || peer >= 16 || !handle)
         return fail(ME_GPU_ERR_BAD_ARG, "peer index out of range");
-    if (slot_bytes != g.gmax.slot_bytes)
+    if (slot_bytes != E().gmax.slot_bytes)
         return fail(ME_GPU_ERR_BAD_ARG, "the peer's pool was sized for another maximum picture size");
-    if (g.peers[peer].open)
+    if (E().peers[peer].open)
         return fail(ME_GPU_ERR_STATE, "peer already open");
-    CU(cudaSetDevice(g.dev[0].id));
+    CU(cudaSetDevice(E().dev[0].id));
     cudaIpcMemHandle_t h;
     memcpy(&h, handle, 64);
     void *base = nullptr;
     CU(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
-    g.peers[peer].open       = true;
-    g.peers[peer].base       = (uint8_t *)base;
-    g.peers[peer].slot_bytes = slot_bytes;
+    E().peers[peer].open       = true;
+    E().peers[peer].base       = (uint8_t *)base;
+    E().peers[peer].slot_bytes = slot_bytes;
     return ME_GPU_OK;
 }
 
 int me_gpu_ipc_picture(uint64_t picture_number, int *slot, unsigned char event_handle[64]) {
-    std::lock_guard<std::mutex> lk(g.mu);
-    if (!g.initialised)
+    std::lock_guard<std::mutex> lk(E().mu);
+    if (!E().initialised)
         return fail(ME_GPU_ERR_STATE, "not initialised");
-    auto it = g.by_number.find(picture_number);
-    if (it == g.by_number.end() || !slot || !event_handle)
+    auto it = E().by_number.find(picture_number);
+    if (it == E().by_number.end() || !slot || !event_handle)
         return fail(ME_GPU_ERR_NOT_FOUND, "picture not registered");
-    CU(cudaSetDevice(g.dev[0].id));
-    Slot &sl = g.slots[it->second];
+    CU(cudaSetDevice(E().dev[0].id));
+    Slot &sl = E().slots[it->second];
     if (!sl.ipc_ready)
         CU(cudaEventCreateWithFlags(&sl.ipc_ready, cudaEventDisableTiming | cudaEventInterprocess));
     /* everything that fills this device's copy of the slot went through the upload stream: a marker behind it */
-    CU(cudaEventRecord(sl.ipc_ready, g.dev[0].upload));
+    CU(cudaEventRecord(sl.ipc_ready, E().dev[0].upload));
     cudaIpcEventHandle_t h;
     CU(cudaIpcGetEventHandle(&h, sl.ipc_ready));
     memcpy(event_handle, &h, 64);
@@ -637,25 +642,25 @@ int me_gpu_ipc_picture(uint64_t picture_number, int *slot, unsigned char event_h
 
 int me_gpu_register_picture_from_peer(uint64_t picture_number, int peer, int peer_slot, const unsigned char event_handle[64],
                                       int width, int height) {
-    std::lock_guard<std::mutex> lk(g.mu);
-    if (!g.initialised)
+    std::lock_guard<std::mutex> lk(E().mu);
+    if (!E().initialised)
         return fail(ME_GPU_ERR_STATE, "not initialised");
-    if (peer < 0 || peer >= 16 || !g.peers[peer].open || peer_slot < 0 || !event_handle)
+    if (peer < 0 || peer >= 16 || !E().peers[peer].open || peer_slot < 0 || !event_handle)
         return fail(ME_GPU_ERR_BAD_ARG, "peer not open");
-    if (width <= 0 || height <= 0 || (width & 7) || (height & 7) || width > g.gmax.width || height > g.gmax.height)
+    if (width <= 0 || height <= 0 || (width & 7) || (height & 7) || width > E().gmax.width || height > E().gmax.height)
         return fail(ME_GPU_ERR_BAD_ARG, "bad picture geometry");
-    if (g.by_number.count(picture_number))
+    if (E().by_number.count(picture_number))
         return fail(ME_GPU_ERR_STATE, "picture already registered");
     int s = -1;
-    for (int i = 0; i < g.nslots; i++)
-        if (!g.slots[i].used) {
+    for (int i = 0; i < E().nslots; i++)
+        if (!E().slots[i].used) {
             s = i;
             break;
         }
     if (s < 0)
         return fail(ME_GPU_ERR_NO_MEMORY, "picture pool is full (raise pictures_in_flight or release pictures)");
-    Engine::Peer &pr = g.peers[peer];
-    Device       &d  = g.dev[0];
+    Engine::Peer &pr = E().peers[peer];
+    Device       &d  = E().dev[0];
     CU(cudaSetDevice(d.id));
     cudaEvent_t ev = nullptr;
     auto        f  = pr.ev.find(peer_slot);
@@ -670,10 +675,10 @@ int me_gpu_register_picture_from_peer(uint64_t picture_number, int peer, int pee
     me_make_geom(&gm, width, height);
     /* the owner recorded the event behind its pyramid kernels before it handed out the handle: the copy starts after them */
     CU(cudaStreamWaitEvent(d.upload, ev, 0));
-    CU(cudaMemcpyAsync(d.pool + (size_t)s * g.gmax.slot_bytes, pr.base + (size_t)peer_slot * pr.slot_bytes, gm.slot_bytes,
+    CU(cudaMemcpyAsync(d.pool + (size_t)s * E().gmax.slot_bytes, pr.base + (size_t)peer_slot * pr.slot_bytes, gm.slot_bytes,
                        cudaMemcpyDeviceToDevice, d.upload));
-    g.peer_bytes += gm.slot_bytes;
-    Slot &sl          = g.slots[s];
+    E().peer_bytes += gm.slot_bytes;
+    Slot &sl          = E().slots[s];
     sl.used           = true;
     sl.picture_number = picture_number;
     sl.width          = width;
@@ -681,46 +686,46 @@ int me_gpu_register_picture_from_peer(uint64_t picture_number, int peer, int pee
     sl.refcount       = 0;
     sl.release_pending = false;
     for (auto &v : sl.ready_seen) v = false;
-    g.by_number[picture_number] = s;
+    E().by_number[picture_number] = s;
     CU(cudaEventRecord(sl.ready[0], d.upload));
-    for (size_t o = 1; o < g.dev.size(); o++) { /* several devices in this process as well: replicate as usual */
-        Device &p2 = g.dev[o];
+    for (size_t o = 1; o < E().dev.size(); o++) { /* several devices in this process as well: replicate as usual */
+        Device &p2 = E().dev[o];
         CU(cudaSetDevice(p2.id));
         CU(cudaStreamWaitEvent(p2.upload, sl.ready[0], 0));
-        CU(cudaMemcpyPeerAsync(p2.pool + (size_t)s * g.gmax.slot_bytes, p2.id, d.pool + (size_t)s * g.gmax.slot_bytes, d.id,
-                               g.gmax.slot_bytes, p2.upload));
+        CU(cudaMemcpyPeerAsync(p2.pool + (size_t)s * E().gmax.slot_bytes, p2.id, d.pool + (size_t)s * E().gmax.slot_bytes, d.id,
+                               E().gmax.slot_bytes, p2.upload));
         CU(cudaEventRecord(sl.ready[o], p2.upload));
     }
     return ME_GPU_OK;
 }
 
 uint64_t me_gpu_ipc_bytes_pulled(void) {
-    std::lock_guard<std::mutex> lk(g.mu);
-    return g.peer_bytes;
+    std::lock_guard<std::mutex> lk(E().mu);
+    return E().peer_bytes;
 }
 
 int me_gpu_read_pyramid(uint64_t picture_number, uint8_t *full, uint8_t *quarter, uint8_t *sixteenth) {
-    std::lock_guard<std::mutex> lk(g.mu);
-    if (!g.initialised)
+    std::lock_guard<std::mutex> lk(E().mu);
+    if (!E().initialised)
         return fail(ME_GPU_ERR_STATE, "not initialised");
-    auto it = g.by_number.find(picture_number);
-    if (it == g.by_number.end())
+    auto it = E().by_number.find(picture_number);
+    if (it == E().by_number.end())
         return fail(ME_GPU_ERR_NOT_FOUND, "picture not registered");
     const int s = it->second;
     MePicGeom gm;
-    me_make_geom(&gm, g.slots[s].width, g.slots[s].height);
+    me_make_geom(&gm, E().slots[s].width, E().slots[s].height);
     /* read from the last device: proves the replication as well when there are several */
-    const size_t di = g.dev.size() - 1;
-    Device      &d  = g.dev[di];
+    const size_t di = E().dev.size() - 1;
+    Device      &d  = E().dev[di];
     CU(cudaSetDevice(d.id));
-    CU(cudaEventSynchronize(g.slots[s].ready[di]));
+    CU(cudaEventSynchronize(E().slots[s].ready[di]));
     uint8_t *dst[3] = {full, quarter, sixteenth};
     for (int l = 0; l < 3; l++) {
         if (!dst[l])
             continue;
         const MePlaneGeom &pl = gm.plane[l];
         const int          pw = pl.width + 2 * pl.pad;
-        CU(cudaMemcpy2D(dst[l], pw, d.pool + (size_t)s * g.gmax.slot_bytes + pl.offset, pl.stride, pw, pl.rows,
+        CU(cudaMemcpy2D(dst[l], pw, d.pool + (size_t)s * E().gmax.slot_bytes + pl.offset, pl.stride, pw, pl.rows,
                         cudaMemcpyDeviceToHost));
     }
     return ME_GPU_OK;
@@ -792,7 +797,7 @@ static int enqueue_d2h(JobCtx *jc, const MeGpuOutputs *out) {
 
 static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
                          const uint64_t ref_picture_numbers[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS], const MeGpuOutputs *out) {
-    if (!g.initialised)
+    if (!E().initialised)
         return fail(ME_GPU_ERR_STATE, "not initialised");
     if (!params || !ref_picture_numbers)
         return fail(ME_GPU_ERR_BAD_ARG, "null argument");
@@ -808,14 +813,14 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
         return fail(ME_GPU_ERR_BAD_ARG, "me_type must be ME_GPU_ME_OPEN_LOOP or ME_GPU_ME_MCTF");
     if (p.me_type == ME_GPU_ME_MCTF && (p.num_of_list_to_search != 1 || p.num_of_ref_pic_to_search[0] != 1))
         return fail(ME_GPU_ERR_BAD_ARG, "temporal-filter ME takes one list with one reference");
-    auto it = g.by_number.find(picture_number);
-    if (it == g.by_number.end())
+    auto it = E().by_number.find(picture_number);
+    if (it == E().by_number.end())
         return fail(ME_GPU_ERR_NOT_FOUND, "source picture not registered");
     const int   src_slot = it->second;
-    const Slot &src      = g.slots[src_slot];
+    const Slot &src      = E().slots[src_slot];
     /* device: pictures are dealt round-robin */
-    const size_t di = (size_t)(g.submit_counter % g.dev.size());
-    Device      &d  = g.dev[di];
+    const size_t di = (size_t)(E().submit_counter % E().dev.size());
+    Device      &d  = E().dev[di];
     JobCtx      *jc = nullptr;
     for (auto &c : d.jobs)
         if (!c.busy) {
@@ -824,7 +829,7 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
         }
     if (!jc)
         return fail(ME_GPU_ERR_STATE, "too many pictures in flight: call me_gpu_wait first");
-    for (auto &dv : g.dev)
+    for (auto &dv : E().dev)
         for (auto &c : dv.jobs)
             if (c.busy && c.picture_number == picture_number && c.me_type == p.me_type && c.ref00 == ref_picture_numbers[0][0])
                 return fail(ME_GPU_ERR_STATE, "picture already submitted (same me_type and first reference)");
@@ -833,16 +838,16 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
     memset(jc->h_head, 0, sizeof(JobHead));
     j.p = p;
     me_make_geom(&j.g, src.width, src.height);
-    j.g.slot_bytes = g.gmax.slot_bytes;
+    j.g.slot_bytes = E().gmax.slot_bytes;
     j.src_slot     = (uint16_t)src_slot;
     jc->slots_used.clear();
     jc->slots_used.push_back(src_slot);
     for (int li = 0; li < p.num_of_list_to_search; li++)
         for (int ri = 0; ri < p.num_of_ref_pic_to_search[li]; ri++) {
-            auto r = g.by_number.find(ref_picture_numbers[li][ri]);
-            if (r == g.by_number.end())
+            auto r = E().by_number.find(ref_picture_numbers[li][ri]);
+            if (r == E().by_number.end())
                 return fail(ME_GPU_ERR_NOT_FOUND, "reference picture not registered");
-            const Slot &rs = g.slots[r->second];
+            const Slot &rs = E().slots[r->second];
             if (rs.width != src.width || rs.height != src.height)
                 return fail(ME_GPU_ERR_BAD_ARG, "reference picture size differs from the source (get_me_reference warns and skips)");
             j.ref_slot[li][ri]           = (uint16_t)r->second;
@@ -911,7 +916,7 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
     CU(cudaSetDevice(d.id));
     cudaStream_t st = jc->stream;
     for (int s : jc->slots_used) {
-        Slot &sl = g.slots[s];
+        Slot &sl = E().slots[s];
         if (sl.ready_seen[di])
             continue;
         if (cudaEventQuery(sl.ready[di]) == cudaSuccess)
@@ -928,7 +933,7 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
 
     const int nbi = (int)nb;
     jc->npairs = 0;
-    const bool prof = g.profiling;
+    const bool prof = E().profiling;
     /* profiling mode: a (begin, end) event pair around each launch, tagged with its kernel class */
     auto pbegin = [&](int kind) {
         if (prof && jc->npairs < 32) {
@@ -952,7 +957,7 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
             Device::MapSet ms;
             ms.width  = j.g.width;
             ms.height = j.g.height;
-            const int rc = me_hme_make_maps(&ms.maps, d.pool, &j.g, g.nslots);
+            const int rc = me_hme_make_maps(&ms.maps, d.pool, &j.g, E().nslots);
             if (rc)
                 return fail(ME_GPU_ERR_CUDA, rc < 0 ? "the driver does not export cuTensorMapEncodeTiled"
                                                     : "cuTensorMapEncodeTiled failed (CUresult " + std::to_string(rc) + ")");
@@ -1020,21 +1025,21 @@ static int submit_locked(uint64_t picture_number, const MeGpuParams *params,
     jc->picture_number = picture_number;
     jc->me_type        = p.me_type;
     jc->ref00          = ref_picture_numbers[0][0];
-    jc->ticket         = ++g.ticket;
-    for (int s : jc->slots_used) g.slots[s].refcount++;
-    g.submit_counter++;
+    jc->ticket         = ++E().ticket;
+    for (int s : jc->slots_used) E().slots[s].refcount++;
+    E().submit_counter++;
     return ME_GPU_OK;
 }
 
 int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
                   const uint64_t ref_picture_numbers[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS]) {
-    std::lock_guard<std::mutex> lk(g.mu);
+    std::lock_guard<std::mutex> lk(E().mu);
     return submit_locked(picture_number, params, ref_picture_numbers, nullptr);
 }
 
 int me_gpu_submit_out(uint64_t picture_number, const MeGpuParams *params,
                       const uint64_t ref_picture_numbers[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS], MeGpuOutputs *out) {
-    std::lock_guard<std::mutex> lk(g.mu);
+    std::lock_guard<std::mutex> lk(E().mu);
     if (!out)
         return fail(ME_GPU_ERR_BAD_ARG, "null outputs");
     return submit_locked(picture_number, params, ref_picture_numbers, out);
@@ -1053,7 +1058,7 @@ int me_gpu_output_layout(int width, int height, const MeGpuParams *params, size_
 /* the oldest job in flight of a picture (any me_type / reference when !exact) */
 static JobCtx *find_job(uint64_t picture_number, bool exact, uint8_t me_type, uint64_t ref00, Device **dv) {
     JobCtx *jc = nullptr;
-    for (auto &d : g.dev)
+    for (auto &d : E().dev)
         for (auto &c : d.jobs)
             if (c.busy && c.picture_number == picture_number && (!exact || (c.me_type == me_type && c.ref00 == ref00)) &&
                 (!jc || c.ticket < jc->ticket)) {
@@ -1068,19 +1073,19 @@ static void retire_locked(JobCtx *jc) {
     jc->busy     = false;
     jc->retiring = false;
     for (int s : jc->slots_used) {
-        g.slots[s].refcount--;
+        E().slots[s].refcount--;
         free_slot_if_idle(s);
     }
-    g.done_ring[g.done_next % 64]  = jc->picture_number;
-    g.done_valid[g.done_next % 64] = true;
-    g.done_next++;
-    g.cv.notify_all();
+    E().done_ring[E().done_next % 64]  = jc->picture_number;
+    E().done_valid[E().done_next % 64] = true;
+    E().done_next++;
+    E().cv.notify_all();
 }
 
 /* out == nullptr: cancel (wait for the device to be done with the job, deliver nothing) */
 static int wait_impl(uint64_t picture_number, bool exact, uint8_t me_type, uint64_t ref00, MeGpuOutputs *out) {
-    std::unique_lock<std::mutex> lk(g.mu);
-    if (!g.initialised)
+    std::unique_lock<std::mutex> lk(E().mu);
+    if (!E().initialised)
         return fail(ME_GPU_ERR_STATE, "not initialised");
     Device *dv = nullptr;
     JobCtx *jc = find_job(picture_number, exact, me_type, ref00, &dv);
@@ -1137,7 +1142,7 @@ static int wait_impl(uint64_t picture_number, bool exact, uint8_t me_type, uint6
     t.byte_sad_ops    = jc->h_tail->ops[0];
     t.byte_sad_ops_fullsearch = jc->h_tail->ops[1];
     t.byte_sad_ops_fullsearch_inline = jc->h_tail->ops[4];
-    g.last            = t;
+    E().last            = t;
     out->b64_count    = (uint32_t)nb;
     out->pu_count     = j.pu_count;
     if (j.p.me_type == ME_GPU_ME_MCTF) {
@@ -1166,19 +1171,19 @@ int me_gpu_wait_pair(uint64_t picture_number, uint8_t me_type, uint64_t first_re
 int me_gpu_cancel(uint64_t picture_number) { return wait_impl(picture_number, false, 0, 0, nullptr); }
 
 int me_gpu_wait_done(uint64_t picture_number) {
-    std::unique_lock<std::mutex> lk(g.mu);
-    if (!g.initialised)
+    std::unique_lock<std::mutex> lk(E().mu);
+    if (!E().initialised)
         return fail(ME_GPU_ERR_STATE, "not initialised");
     Device *dv   = nullptr;
     JobCtx *jc   = find_job(picture_number, false, 0, 0, &dv);
     if (!jc) {
         for (int i = 0; i < 64; i++)
-            if (g.done_valid[i] && g.done_ring[i] == picture_number)
+            if (E().done_valid[i] && E().done_ring[i] == picture_number)
                 return ME_GPU_OK;
         return fail(ME_GPU_ERR_NOT_FOUND, "picture was not submitted (or was retired more than 64 jobs ago)");
     }
     const uint64_t ticket = jc->ticket;
-    g.cv.wait(lk, [&] { return !g.initialised || !jc->busy || jc->ticket != ticket; });
+    E().cv.wait(lk, [&] { return !E().initialised || !jc->busy || jc->ticket != ticket; });
     return ME_GPU_OK;
 }
 
@@ -1186,28 +1191,28 @@ int me_gpu_wait_done(uint64_t picture_number) {
  * sums come back in one 24-byte copy. Calls alternate between the devices (every device holds every picture). */
 int me_gpu_dg_detector(uint64_t src_picture_number, uint64_t ref_picture_number, uint8_t input_resolution,
                        MeGpuDgMetrics *metrics) {
-    std::lock_guard<std::mutex>  dg(g.dg_mu);
-    std::unique_lock<std::mutex> lk(g.mu);
-    if (!g.initialised)
+    std::lock_guard<std::mutex>  dg(E().dg_mu);
+    std::unique_lock<std::mutex> lk(E().mu);
+    if (!E().initialised)
         return fail(ME_GPU_ERR_STATE, "not initialised");
     if (!metrics)
         return fail(ME_GPU_ERR_BAD_ARG, "null metrics");
-    auto si = g.by_number.find(src_picture_number), ri = g.by_number.find(ref_picture_number);
-    if (si == g.by_number.end() || ri == g.by_number.end())
+    auto si = E().by_number.find(src_picture_number), ri = E().by_number.find(ref_picture_number);
+    if (si == E().by_number.end() || ri == E().by_number.end())
         return fail(ME_GPU_ERR_NOT_FOUND, "picture not registered");
     const int ss = si->second, rs = ri->second;
-    if (g.slots[ss].width != g.slots[rs].width || g.slots[ss].height != g.slots[rs].height)
+    if (E().slots[ss].width != E().slots[rs].width || E().slots[ss].height != E().slots[rs].height)
         return fail(ME_GPU_ERR_BAD_ARG, "source and reference picture sizes differ");
-    const size_t di = (size_t)(g.dg_counter++ % g.dev.size());
-    Device      &d  = g.dev[di];
+    const size_t di = (size_t)(E().dg_counter++ % E().dev.size());
+    Device      &d  = E().dev[di];
     MePicGeom    gm;
-    me_make_geom(&gm, g.slots[ss].width, g.slots[ss].height);
-    gm.slot_bytes = g.gmax.slot_bytes;
+    me_make_geom(&gm, E().slots[ss].width, E().slots[ss].height);
+    gm.slot_bytes = E().gmax.slot_bytes;
     /* pd_process.c:497-498: 16 up to 360p, 64 up to 480p, else 128 (EbInputResolution, definitions.h:2079) */
     const int sa = input_resolution <= 1 ? 16 : input_resolution <= 2 ? 64 : 128;
     CU(cudaSetDevice(d.id));
     for (int s : {ss, rs}) {
-        Slot &sl = g.slots[s];
+        Slot &sl = E().slots[s];
         if (!sl.ready_seen[di])
             CU(cudaStreamWaitEvent(d.dg_stream, sl.ready[di], 0));
         sl.refcount++;
@@ -1224,7 +1229,7 @@ int me_gpu_dg_detector(uint64_t src_picture_number, uint64_t ref_picture_number,
         e = cudaStreamSynchronize(d.dg_stream);
     lk.lock();
     for (int s : {ss, rs}) {
-        g.slots[s].refcount--;
+        E().slots[s].refcount--;
         free_slot_if_idle(s);
     }
     if (e != cudaSuccess)
@@ -1234,27 +1239,49 @@ int me_gpu_dg_detector(uint64_t src_picture_number, uint64_t ref_picture_number,
 }
 
 int me_gpu_get_timings(MeGpuTimings *t) {
-    std::lock_guard<std::mutex> lk(g.mu);
+    std::lock_guard<std::mutex> lk(E().mu);
     if (!t)
         return ME_GPU_ERR_BAD_ARG;
-    *t                 = g.last;
+    *t                 = E().last;
     t->kernel_launches = me_launch_count() + me_hme_launch_count() + me_dg_launch_count();
     return ME_GPU_OK;
 }
 
 void me_gpu_set_profiling(int on) {
-    std::lock_guard<std::mutex> lk(g.mu);
-    g.profiling = on != 0;
+    std::lock_guard<std::mutex> lk(E().mu);
+    E().profiling = on != 0;
 }
 
 /* VABSDIFF4 lane-operations per second of device 0 of the engine (x4 = byte-SADs per second): the measured
  * denominator of the integer-SAD roofline */
 double me_gpu_measure_sad_peak(void) {
-    std::lock_guard<std::mutex> lk(g.mu);
-    if (!g.initialised)
+    std::lock_guard<std::mutex> lk(E().mu);
+    if (!E().initialised)
         return 0.0;
-    cudaSetDevice(g.dev[0].id);
-    return me_measure_sad_peak(g.dev[0].upload);
+    cudaSetDevice(E().dev[0].id);
+    return me_measure_sad_peak(E().dev[0].upload);
 }
 
 } /* extern "C" */
+
+/* ---- more than one engine per process -------------------------------------------------------------------------- */
+extern "C" int me_gpu_engine_create(MeGpuEngine **out) {
+    if (!out)
+        return fail(ME_GPU_ERR_BAD_ARG, "me_gpu_engine_create: null argument");
+    *out = reinterpret_cast<MeGpuEngine *>(new (std::nothrow) Engine());
+    return *out ? ME_GPU_OK : fail(ME_GPU_ERR_NO_MEMORY, "me_gpu_engine_create: out of host memory");
+}
+
+extern "C" void me_gpu_engine_bind(MeGpuEngine *e) { t_eng = e ? reinterpret_cast<Engine *>(e) : &g_default; }
+
+extern "C" int me_gpu_engine_destroy(MeGpuEngine *e) {
+    Engine *en = reinterpret_cast<Engine *>(e);
+    if (!en)
+        return ME_GPU_OK;
+    if (en->initialised)
+        return fail(ME_GPU_ERR_STATE, "me_gpu_engine_destroy: the engine is still initialised (bind it and call me_gpu_shutdown first)");
+    if (t_eng == en)
+        t_eng = &g_default;
+    delete en;
+    return ME_GPU_OK;
+}

@@ -162,6 +162,7 @@ GPU_SYMBOLS = [
     "me_gpu_ipc_export_pool", "me_gpu_ipc_open_peer", "me_gpu_ipc_picture", "me_gpu_register_picture_from_peer",
     "me_gpu_ipc_bytes_pulled",
     "me_gpu_dg_detector_noalloc", "me_gpu_dg_detector_noalloc_setup", "me_gpu_dg_detector_noalloc_error",
+    "me_gpu_engine_create", "me_gpu_engine_bind", "me_gpu_engine_destroy",
 ]
 
 
@@ -199,6 +200,9 @@ def load_gpu_lib():
     lib.me_gpu_dg_detector_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, u8,
                                                C.POINTER(MeGpuDgMetrics)]
     lib.me_gpu_dg_detector_noalloc_error.restype = C.c_char_p
+    lib.me_gpu_engine_create.argtypes = [C.POINTER(C.c_void_p)]
+    lib.me_gpu_engine_bind.argtypes = [C.c_void_p]
+    lib.me_gpu_engine_destroy.argtypes = [C.c_void_p]
     return lib
 
 
