@@ -15,6 +15,8 @@ What it changes (the same edits integration/encoder_me_gpu.patch shows as a unif
                                      device, the quarter / sixteenth planes read back for the CPU stages that still use them
   Source/Lib/Codec/pd_process.c      early_hme (dynamic-GOP detector): svt_me_gpu_dg_detector in place of the TASK_DG_DETECTOR_HME
                                      segments and the semaphore wait, when the device holds both pyramids
+  Source/Lib/Codec/temporal_filtering.c  produce_temporally_filtered_pic: svt_me_gpu_tf_block in place of the per-block
+                                     svt_aom_motion_estimation_b64 call (one ME_MCTF job per (centre, neighbour) pair)
   Source/Lib/Codec/CMakeLists.txt    lists the new files; Source/Lib/CMakeLists.txt links libdl
 Every edit is an exact-match replacement: the script fails if the tree is not the one it was written against.
 """
@@ -181,6 +183,41 @@ def main():
     first_inc = s.index("#include")
     s = s[:first_inc] + '#include "svt_me_gpu_hook.h"\n#include "svt_log.h"\n' + s[first_inc:]
     open(pd, "w").write(s)
+
+    # ---- temporal filter: the ME of a (centre, neighbour) pair on the device, once, for all blocks -------------------
+    tf = os.path.join(codec, "temporal_filtering.c")
+    replace_once(tf, '''                    svt_aom_motion_estimation_b64(centre_pcs,
+                        (uint32_t)blk_row * blk_cols + blk_col,
+                        (uint32_t)blk_col * BW, // x block
+                        (uint32_t)blk_row * BH, // y block
+                        ctx,
+                        input_picture_ptr_central); // source picture
+''', '''                    if (svt_me_gpu_tf_ready(centre_pcs, pcs_list[frame_index])) { /* 8- and 10-bit alike: ME reads the 8-bit y8b planes */
+                        /* B200 path: the first segment thread that needs this (centre, neighbour) pair runs its ME for all
+                           blocks in one job; this block's results are loaded where the filter reads them */
+                        if (svt_me_gpu_tf_block(centre_pcs, ctx, pcs_list[frame_index], frame_index, blk_rows * blk_cols,
+                                                (uint32_t)blk_row * blk_cols + blk_col) != EB_ErrorNone) {
+                            SVT_ERROR("B200 ME engine failed in the temporal filter (no CPU fallback)\\n");
+                            abort();
+                        }
+                    } else
+                    svt_aom_motion_estimation_b64(centre_pcs,
+                        (uint32_t)blk_row * blk_cols + blk_col,
+                        (uint32_t)blk_col * BW, // x block
+                        (uint32_t)blk_row * BH, // y block
+                        ctx,
+                        input_picture_ptr_central); // source picture
+''')
+    replace_once(tf, '''    svt_block_on_mutex(centre_pcs->temp_filt_mutex);
+    centre_pcs->temp_filt_seg_acc++;
+''', '''    svt_me_gpu_tf_centre_done(centre_pcs); /* the last segment frees the pairs' results */
+    svt_block_on_mutex(centre_pcs->temp_filt_mutex);
+    centre_pcs->temp_filt_seg_acc++;
+''')
+    s = open(tf).read()
+    first_inc = s.index("#include")
+    s = s[:first_inc] + '#include "svt_me_gpu_hook.h"\n#include "svt_log.h"\n' + s[first_inc:]
+    open(tf, "w").write(s)
 
     # ---- the new source joins the CODEC object library ----
     replace_once(os.path.join(codec, "CMakeLists.txt"), "set(all_files\n        adaptive_mv_pred.c\n",

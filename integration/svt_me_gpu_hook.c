@@ -16,12 +16,15 @@ int (*svt_me_picture_wait)(uint64_t, MeGpuOutputs *)                            
 int (*svt_me_picture_release)(uint64_t)                                                                              = NULL;
 static int (*hook_cancel)(uint64_t) = NULL;
 static int (*hook_read_plane)(uint64_t, int, uint8_t *, int) = NULL;
+static int (*hook_wait_pair)(uint64_t, uint8_t, uint64_t, MeGpuOutputs *) = NULL;
 static const char *(*hook_last_error)(void) = NULL;
 static void (*hook_shutdown)(void) = NULL;
 static int (*hook_dg)(uint64_t, uint64_t, uint8_t, MeGpuDgMetrics *) = NULL;
 static void *hook_lib              = NULL;
 static int   hook_log_lists        = 0;
 static uint64_t hook_n_dg_read(void);
+static uint64_t hook_n_tf_read(void);
+static int      hook_id_of(const void *obj, uint64_t *id);
 
 #include <stdio.h>
 static EbErrorType map_error(int rc) {
@@ -48,6 +51,7 @@ EbErrorType svt_me_gpu_hook_init(const char *library_path, int max_width, int ma
     svt_me_picture_release  = (int (*)(uint64_t))dlsym(h, "me_gpu_release_picture");
     hook_cancel             = (int (*)(uint64_t))dlsym(h, "me_gpu_cancel");
     hook_read_plane         = (int (*)(uint64_t, int, uint8_t *, int))dlsym(h, "me_gpu_read_plane");
+    hook_wait_pair          = (int (*)(uint64_t, uint8_t, uint64_t, MeGpuOutputs *))dlsym(h, "me_gpu_wait_pair");
     hook_last_error         = (const char *(*)(void))dlsym(h, "me_gpu_last_error");
     hook_shutdown           = (void (*)(void))dlsym(h, "me_gpu_shutdown");
     hook_dg                 = (int (*)(uint64_t, uint64_t, uint8_t, MeGpuDgMetrics *))dlsym(h, "me_gpu_dg_detector");
@@ -64,9 +68,9 @@ void svt_me_gpu_hook_shutdown(void) {
         uint64_t reg, rel, pics;
         svt_me_gpu_stats(&reg, &rel, &pics);
         fprintf(stderr, "svt_me_gpu_hook: %llu pictures searched, %llu pyramids built on the device (%llu for picture analysis / "
-                        "the temporal filter / overlays), %llu released, %llu dynamic-GOP detector calls\n", (unsigned long long)pics,
-                (unsigned long long)reg, (unsigned long long)svt_me_gpu_downsample_count(), (unsigned long long)rel,
-                (unsigned long long)hook_n_dg_read());
+                        "the temporal filter / overlays), %llu released, %llu dynamic-GOP detector calls, %llu temporal-filter pairs\n",
+                (unsigned long long)pics, (unsigned long long)reg, (unsigned long long)svt_me_gpu_downsample_count(),
+                (unsigned long long)rel, (unsigned long long)hook_n_dg_read(), (unsigned long long)hook_n_tf_read());
         hook_shutdown();
     }
     svt_me_picture_register = NULL;
@@ -76,6 +80,7 @@ void svt_me_gpu_hook_shutdown(void) {
     hook_shutdown           = NULL;
     hook_cancel             = NULL;
     hook_read_plane         = NULL;
+    hook_wait_pair          = NULL;
     hook_dg                 = NULL;
     if (hook_lib)
         dlclose(hook_lib);
@@ -146,9 +151,10 @@ void svt_me_gpu_params_from_ctx(MeGpuParams *p, const PictureParentControlSet *p
     p->pcs_temporal_layer_index        = pcs->temporal_layer_index;
     p->similar_brightness_refs         = pcs->similar_brightness_refs;
     p->only_l_bwd                      = scs->mrp_ctrls.only_l_bwd;
-    p->max_cand                        = pcs->pa_me_data->max_cand;
-    p->max_refs                        = pcs->pa_me_data->max_refs;
-    p->max_l0                          = pcs->pa_me_data->max_l0;
+    /* the temporal filter runs before the picture's pa_me_data is attached; its job writes none of the candidate arrays */
+    p->max_cand                        = pcs->pa_me_data ? pcs->pa_me_data->max_cand : 1;
+    p->max_refs                        = pcs->pa_me_data ? pcs->pa_me_data->max_refs : 1;
+    p->max_l0                          = pcs->pa_me_data ? pcs->pa_me_data->max_l0 : 1;
     /* per-call MeContext fields, me_process.c:215-262 */
     p->me_type                     = (uint8_t)m->me_type;
     p->tf_me_exit_th               = m->tf_me_exit_th;
@@ -469,11 +475,178 @@ EbErrorType svt_me_gpu_tf_pair(const PictureParentControlSet *centre_pcs, MeCont
 void svt_me_gpu_tf_load_block(MeContext *me_ctx, const SvtMeGpuTfPair *pair, uint32_t b) {
     memcpy(me_ctx->p_sb_best_sad[0][0], pair->best_sad + (size_t)SQUARE_PU_COUNT * b, SQUARE_PU_COUNT * sizeof(uint32_t));
     memcpy(me_ctx->p_sb_best_mv[0][0], pair->best_mv + (size_t)SQUARE_PU_COUNT * b, SQUARE_PU_COUNT * sizeof(uint32_t));
+    /* the per-size views the integer search leaves pointing into slot (0, 0) (motion_estimation.c:1368-1384): a thread that never
+       ran the CPU search has them unset */
+    me_ctx->p_best_sad_64x64 = &me_ctx->p_sb_best_sad[0][0][ME_TIER_ZERO_PU_64x64];
+    me_ctx->p_best_sad_32x32 = &me_ctx->p_sb_best_sad[0][0][ME_TIER_ZERO_PU_32x32_0];
+    me_ctx->p_best_sad_16x16 = &me_ctx->p_sb_best_sad[0][0][ME_TIER_ZERO_PU_16x16_0];
+    me_ctx->p_best_sad_8x8   = &me_ctx->p_sb_best_sad[0][0][ME_TIER_ZERO_PU_8x8_0];
+    me_ctx->p_best_mv64x64   = &me_ctx->p_sb_best_mv[0][0][ME_TIER_ZERO_PU_64x64];
+    me_ctx->p_best_mv32x32   = &me_ctx->p_sb_best_mv[0][0][ME_TIER_ZERO_PU_32x32_0];
+    me_ctx->p_best_mv16x16   = &me_ctx->p_sb_best_mv[0][0][ME_TIER_ZERO_PU_16x16_0];
+    me_ctx->p_best_mv8x8     = &me_ctx->p_sb_best_mv[0][0][ME_TIER_ZERO_PU_8x8_0];
     me_ctx->search_results[0][0].hme_sc_x = pair->hme_centre[2 * b];
     me_ctx->search_results[0][0].hme_sc_y = pair->hme_centre[2 * b + 1];
     me_ctx->search_results[0][0].hme_sad  = pair->hme_sad[b];
     if (pair->early_exit[b])
         me_ctx->tf_use_pred_64x64_only_th = (uint8_t)~0; /* motion_estimation.c:3111 */
+}
+
+/* ---- the temporal filter inside the encoder ---------------------------------------------------------------------- */
+/* produce_temporally_filtered_pic walks blocks outside and neighbour pictures inside, on several segment threads per
+ * centre picture. The first thread that needs the ME of a (centre, neighbour) pair runs it for ALL blocks on the device
+ * (one ME_MCTF job) while the other threads that need the same pair wait; every later block of any segment loads its
+ * results from the pair's arrays. The arrays live until every segment of the centre has called svt_me_gpu_tf_centre_done. */
+#define HOOK_MAX_TF 64
+typedef struct HookTf {
+    const void    *centre;
+    uint64_t       number;
+    int            frame_index, state; /* 0 free, 1 running, 2 done */
+    EbErrorType    rc;
+    SvtMeGpuTfPair pair;
+    uint32_t       horz, vert; /* the pair's tf_tot_horz/vert_blks, handed to the thread that ran it */
+} HookTf;
+typedef struct HookTfCentre {
+    const void *centre;
+    uint64_t    number;
+    uint32_t    arrivals;
+    int         used;
+} HookTfCentre;
+static HookTf       hook_tf[HOOK_MAX_TF];
+static HookTfCentre hook_tfc[16];
+static uint64_t     hook_n_tf;
+
+int svt_me_gpu_tf_ready(const PictureParentControlSet *centre_pcs, const PictureParentControlSet *neighbour_pcs) {
+    uint64_t  a, b;
+    const int live = svt_me_gpu_live() && hook_wait_pair && centre_pcs->pa_ref_pic_wrapper && neighbour_pcs->pa_ref_pic_wrapper;
+    const int ca = live && hook_id_of(centre_pcs->pa_ref_pic_wrapper->object_ptr, &a);
+    const int nb = live && hook_id_of(neighbour_pcs->pa_ref_pic_wrapper->object_ptr, &b);
+    if (hook_log_lists && !(ca && nb))
+        fprintf(stderr, "svt_me_gpu_hook: tf pair (%llu, %llu) stays on the CPU: live %d wait_pair %d centre on device %d neighbour on device %d\n",
+                (unsigned long long)centre_pcs->picture_number, (unsigned long long)neighbour_pcs->picture_number, svt_me_gpu_live(),
+                hook_wait_pair != NULL, ca, nb);
+    return ca && nb;
+}
+
+static EbErrorType hook_tf_run(const PictureParentControlSet *centre_pcs, MeContext *me_ctx, const PictureParentControlSet *neighbour_pcs,
+                               HookTf *e, uint32_t b64_count) {
+    uint64_t cid, nid;
+    if (!hook_id_of(centre_pcs->pa_ref_pic_wrapper->object_ptr, &cid) || !hook_id_of(neighbour_pcs->pa_ref_pic_wrapper->object_ptr, &nid))
+        return EB_ErrorUndefined;
+    SvtMeGpuTfPair *pr = &e->pair;
+    pr->b64_count  = b64_count;
+    pr->best_sad   = (uint32_t *)malloc((size_t)b64_count * SQUARE_PU_COUNT * sizeof(uint32_t));
+    pr->best_mv    = (uint32_t *)malloc((size_t)b64_count * SQUARE_PU_COUNT * sizeof(uint32_t));
+    pr->hme_centre = (int16_t *)malloc((size_t)b64_count * 2 * sizeof(int16_t));
+    pr->hme_sad    = (uint32_t *)malloc((size_t)b64_count * sizeof(uint32_t));
+    pr->early_exit = (uint8_t *)malloc((size_t)b64_count);
+    if (!pr->best_sad || !pr->best_mv || !pr->hme_centre || !pr->hme_sad || !pr->early_exit)
+        return EB_ErrorInsufficientResources;
+    MeGpuParams gp;
+    uint64_t    refs[ME_GPU_MAX_LISTS][ME_GPU_MAX_REFS] = {{0}};
+    svt_me_gpu_params_from_ctx(&gp, centre_pcs, me_ctx);
+    gp.picture_number              = cid; /* distances are not used by ME_MCTF beyond the 16-bit difference of the low bits */
+    gp.me_type                     = ME_GPU_ME_MCTF;
+    gp.num_of_list_to_search       = 1;
+    gp.num_of_ref_pic_to_search[0] = 1;
+    gp.num_of_ref_pic_to_search[1] = 0;
+    refs[0][0]                     = nid;
+    int rc = svt_me_picture_submit(cid, &gp, refs);
+    if (rc != ME_GPU_OK)
+        return map_error(rc);
+    MeGpuOutputs out;
+    memset(&out, 0, sizeof out);
+    out.b64_count     = b64_count;
+    out.tf_best_sad   = pr->best_sad;
+    out.tf_best_mv    = pr->best_mv;
+    out.tf_hme_centre = pr->hme_centre;
+    out.tf_hme_sad    = pr->hme_sad;
+    out.tf_early_exit = pr->early_exit;
+    rc = hook_wait_pair(cid, ME_GPU_ME_MCTF, nid, &out);
+    if (rc != ME_GPU_OK)
+        return map_error(rc);
+    e->horz = out.tf_tot_horz_blks;
+    e->vert = out.tf_tot_vert_blks;
+    return EB_ErrorNone;
+}
+
+EbErrorType svt_me_gpu_tf_block(const PictureParentControlSet *centre_pcs, MeContext *me_ctx, const PictureParentControlSet *neighbour_pcs,
+                                int frame_index, uint32_t b64_count, uint32_t b) {
+    HookTf *e = NULL, *free_e = NULL;
+    int     runner = 0;
+    pthread_mutex_lock(&hook_mu);
+    for (int i = 0; i < HOOK_MAX_TF; i++) {
+        if (hook_tf[i].state && hook_tf[i].centre == (const void *)centre_pcs && hook_tf[i].number == centre_pcs->picture_number &&
+            hook_tf[i].frame_index == frame_index)
+            e = &hook_tf[i];
+        else if (!hook_tf[i].state && !free_e)
+            free_e = &hook_tf[i];
+    }
+    if (!e) {
+        if (!free_e) {
+            pthread_mutex_unlock(&hook_mu);
+            return EB_ErrorInsufficientResources;
+        }
+        e = free_e;
+        memset(e, 0, sizeof *e);
+        e->centre = centre_pcs; e->number = centre_pcs->picture_number; e->frame_index = frame_index; e->state = 1;
+        runner = 1;
+        hook_n_tf++;
+    }
+    pthread_mutex_unlock(&hook_mu);
+    if (runner) {
+        const EbErrorType rc = hook_tf_run(centre_pcs, me_ctx, neighbour_pcs, e, b64_count);
+        if (rc == EB_ErrorNone) { /* motion_estimation.c:2469-2474, summed over the segment threads at temporal_filtering.c:4259 */
+            me_ctx->tf_tot_horz_blks += e->horz;
+            me_ctx->tf_tot_vert_blks += e->vert;
+        }
+        pthread_mutex_lock(&hook_mu);
+        e->rc    = rc;
+        e->state = 2;
+        pthread_cond_broadcast(&hook_cv);
+    } else {
+        pthread_mutex_lock(&hook_mu);
+        while (e->state != 2) pthread_cond_wait(&hook_cv, &hook_mu);
+    }
+    const EbErrorType rc = e->rc;
+    pthread_mutex_unlock(&hook_mu);
+    if (rc == EB_ErrorNone)
+        svt_me_gpu_tf_load_block(me_ctx, &e->pair, b);
+    return rc;
+}
+
+void svt_me_gpu_tf_centre_done(const PictureParentControlSet *centre_pcs) {
+    if (!svt_me_gpu_live())
+        return;
+    pthread_mutex_lock(&hook_mu);
+    HookTfCentre *c = NULL, *free_c = NULL;
+    for (int i = 0; i < 16; i++) {
+        if (hook_tfc[i].used && hook_tfc[i].centre == (const void *)centre_pcs && hook_tfc[i].number == centre_pcs->picture_number)
+            c = &hook_tfc[i];
+        else if (!hook_tfc[i].used && !free_c)
+            free_c = &hook_tfc[i];
+    }
+    if (!c && free_c) {
+        c = free_c;
+        c->centre = centre_pcs; c->number = centre_pcs->picture_number; c->arrivals = 0; c->used = 1;
+    }
+    if (c && ++c->arrivals == (uint32_t)centre_pcs->tf_segments_total_count) {
+        c->used = 0;
+        for (int i = 0; i < HOOK_MAX_TF; i++)
+            if (hook_tf[i].state && hook_tf[i].centre == (const void *)centre_pcs && hook_tf[i].number == centre_pcs->picture_number) {
+                free(hook_tf[i].pair.best_sad); free(hook_tf[i].pair.best_mv); free(hook_tf[i].pair.hme_centre);
+                free(hook_tf[i].pair.hme_sad); free(hook_tf[i].pair.early_exit);
+                hook_tf[i].state = 0;
+            }
+    }
+    pthread_mutex_unlock(&hook_mu);
+}
+
+static uint64_t hook_n_tf_read(void) {
+    pthread_mutex_lock(&hook_mu);
+    const uint64_t n = hook_n_tf;
+    pthread_mutex_unlock(&hook_mu);
+    return n;
 }
 
 static uint64_t hook_n_dg_read(void) {

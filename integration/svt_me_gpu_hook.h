@@ -102,6 +102,15 @@ EbErrorType svt_me_gpu_tf_pair(const PictureParentControlSet *centre_pcs, MeCont
  * filter's readers expect them (p_sb_best_sad/mv[0][0], search_results[0][0], the 64x64-only switch) */
 void svt_me_gpu_tf_load_block(MeContext *me_ctx, const SvtMeGpuTfPair *pair, uint32_t b);
 
+/* inside the encoder: at the svt_aom_motion_estimation_b64 call of produce_temporally_filtered_pic (temporal_filtering.c:3182),
+ * on whichever segment thread gets there first for a (centre, neighbour) pair: ME_MCTF of ALL blocks of the pair on the
+ * device, once; every block of every segment then loads its own results (svt_me_gpu_tf_load_block). me_ctx set up as at
+ * :3144-3181. svt_me_gpu_tf_centre_done: once per segment thread after the block loop; the last one frees the pairs. */
+int         svt_me_gpu_tf_ready(const PictureParentControlSet *centre_pcs, const PictureParentControlSet *neighbour_pcs);
+EbErrorType svt_me_gpu_tf_block(const PictureParentControlSet *centre_pcs, MeContext *me_ctx, const PictureParentControlSet *neighbour_pcs,
+                                int frame_index, uint32_t b64_count, uint32_t b);
+void        svt_me_gpu_tf_centre_done(const PictureParentControlSet *centre_pcs);
+
 /* ---- dynamic-GOP detector (early_hme, pd_process.c:561-625) ---------------------------------------------------- */
 /* replaces the TASK_DG_DETECTOR_HME segment dispatch + semaphore wait: fills src_pcs->dg_detector->metrics for
  * (src_pcs, src_pcs->dg_detector->ref_pic); both pictures registered */

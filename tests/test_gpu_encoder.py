@@ -38,6 +38,8 @@ def test_bitstream_identical_with_me_on_the_gpu(workdir, name):
     # mini-GOPs of 32: the dynamic-GOP detector's three picture pairs per decision went to the device too
     dg = int(re.search(r"(\d+) dynamic-GOP detector calls", log).group(1))
     assert dg > 0 if "6L" in name else dg >= 0, dg
+    # the temporal filter's ME (key frames and base-layer pictures are filtered in every case) ran on the device as well
+    assert int(re.search(r"(\d+) temporal-filter pairs", log).group(1)) > 0, log[-800:]
     if ec.CASES[name][3] >= 6:  # quick: the stock encoder on this box too
         live, _ = ec.encode(ec.STOCK, name, workdir)
         assert live == gold[name], ("stock encoder differs from its golden on this box", name)
