@@ -268,7 +268,8 @@ uint64_t me_gpu_ipc_bytes_pulled(void); /* bytes copied from peers' pools so far
 typedef struct MeGpuEngine MeGpuEngine;
 int  me_gpu_engine_create(MeGpuEngine **engine); /* not initialised yet: bind it, then me_gpu_init */
 void me_gpu_engine_bind(MeGpuEngine *engine); /* NULL = back to the default engine */
-int  me_gpu_engine_destroy(MeGpuEngine *engine); /* after me_gpu_shutdown on it: ME_GPU_ERR_STATE otherwise */
+int  me_gpu_engine_destroy(MeGpuEngine *engine); /* after me_gpu_shutdown on it (ME_GPU_ERR_STATE otherwise); the caller's binding
+                                                    goes back to the default engine, no OTHER thread may still be bound to it */
 
 /* motion estimation ----------------------------------------------------------------------- */
 int me_gpu_submit(uint64_t picture_number, const MeGpuParams *params,
