@@ -16,7 +16,8 @@ for v in stock gpu; do
     (cd "$REF" && tar --exclude=.git --exclude=Bin -cf - .) | tar -xf - -C "$WORK/src_$v"
 done
 python "$HERE/apply_patch.py" "$WORK/src_gpu"
-(cd "$WORK" && diff -urN src_stock/Source src_gpu/Source | grep -v '^Only in' > "$HERE/encoder_me_gpu.patch" || true)
+# (the files' timestamps are cut from the diff headers: the patch changes only when its content does)
+(cd "$WORK" && diff -urN src_stock/Source src_gpu/Source | grep -v '^Only in' | sed -E 's/^(--- |\+\+\+ )([^\t]+)\t.*/\1\2/' > "$HERE/encoder_me_gpu.patch" || true)
 for v in stock gpu; do
     mkdir -p "$WORK/build_$v"
     (cd "$WORK/build_$v" && cmake "$WORK/src_$v" -G Ninja -DCMAKE_BUILD_TYPE=Release -DCOMPILE_C_ONLY=ON -DBUILD_TESTING=OFF \
