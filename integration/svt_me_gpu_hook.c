@@ -23,6 +23,7 @@ static int (*hook_dg)(uint64_t, uint64_t, uint8_t, MeGpuDgMetrics *) = NULL;
 static void *hook_lib              = NULL;
 static int   hook_log_lists        = 0;
 static uint64_t hook_n_dg_read(void);
+static void     hook_reset_tables(void);
 static uint64_t hook_n_tf_read(void);
 static int      hook_id_of(const void *obj, uint64_t *id);
 
@@ -72,6 +73,7 @@ void svt_me_gpu_hook_shutdown(void) {
                 (unsigned long long)pics, (unsigned long long)reg, (unsigned long long)svt_me_gpu_downsample_count(),
                 (unsigned long long)rel, (unsigned long long)hook_n_dg_read(), (unsigned long long)hook_n_tf_read());
         hook_shutdown();
+        hook_reset_tables(); /* a later svt_me_gpu_hook_init (another encoder instance of the process) starts clean */
     }
     svt_me_picture_register = NULL;
     svt_me_picture_submit   = NULL;
@@ -639,6 +641,21 @@ void svt_me_gpu_tf_centre_done(const PictureParentControlSet *centre_pcs) {
                 hook_tf[i].state = 0;
             }
     }
+    pthread_mutex_unlock(&hook_mu);
+}
+
+static void hook_reset_tables(void) {
+    pthread_mutex_lock(&hook_mu);
+    for (int i = 0; i < HOOK_MAX_TF; i++)
+        if (hook_tf[i].state) {
+            free(hook_tf[i].pair.best_sad); free(hook_tf[i].pair.best_mv); free(hook_tf[i].pair.hme_centre);
+            free(hook_tf[i].pair.hme_sad); free(hook_tf[i].pair.early_exit);
+        }
+    memset(hook_tf, 0, sizeof hook_tf);
+    memset(hook_tfc, 0, sizeof hook_tfc);
+    memset(hook_regs, 0, sizeof hook_regs);
+    memset(hook_pics, 0, sizeof hook_pics);
+    hook_n_reg = hook_n_rel = hook_n_pic = hook_n_ds = hook_n_dg = hook_n_tf = 0;
     pthread_mutex_unlock(&hook_mu);
 }
 

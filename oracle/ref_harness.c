@@ -442,6 +442,7 @@ REF_API int ref_me_b64_range(const OraclePicture *src, const OraclePicture *cons
  * state is built once per picture per step, outside the b64 loop. every > 1: only every `every`-th segment of a picture
  * is run (a bounded sample for the slow configurations); *b64_done = blocks actually searched.
  * ---------------------------------------------------------------------------------------------- */
+#include <dlfcn.h>
 #include <pthread.h>
 typedef struct RefStepJob {
     const OraclePicture *src;
@@ -873,4 +874,136 @@ REF_API int ref_dg_detector(const OraclePicture *src, const OraclePicture *ref, 
     svt_destroy_semaphore(dg->frame_done_sem);
     free(ro); free(so); free(rw); free(sw); free(dg); free(scs); free(rpcs); free(pcs);
     return 0;
+}
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * Host logic of the binding on the CPU (tests/test_hook_host_logic.py): the hook bound to tests/emul/libme_fake_engine.so.
+ * Returns 0, or the (negative) number of the first step whose expectation failed. report[0..7] = the fake engine's counters
+ * at the end, report[8] = pictures it still holds.
+ * ------------------------------------------------------------------------------------------------------------------ */
+typedef struct HostLogicPic {
+    PictureParentControlSet pcs;
+    EbObjectWrapper         wrap;
+    EbPictureBufferDesc     full, quarter, sixteenth;
+    uint8_t                 luma[64], q[64], s[64];
+} HostLogicPic;
+
+static void host_logic_pic(HostLogicPic *p, EbPaReferenceObject *obj, SequenceControlSet *scs, uint64_t poc) {
+    memset(p, 0, sizeof *p);
+    p->wrap.object_ptr         = obj;
+    p->pcs.pa_ref_pic_wrapper  = &p->wrap;
+    p->pcs.scs                 = scs;
+    p->pcs.picture_number      = poc;
+    p->pcs.aligned_width       = 128;
+    p->pcs.aligned_height      = 64;
+    p->pcs.tf_segments_total_count = 8;
+    obj->picture_number        = poc;
+    p->full.buffer_y = p->luma; p->full.stride_y = 8;
+    p->quarter.buffer_y = p->q; p->quarter.stride_y = 8;
+    p->sixteenth.buffer_y = p->s; p->sixteenth.stride_y = 8;
+    obj->input_padded_pic                  = &p->full;
+    obj->quarter_downsampled_picture_ptr   = &p->quarter;
+    obj->sixteenth_downsampled_picture_ptr = &p->sixteenth;
+}
+
+typedef struct HostLogicTf {
+    HostLogicPic *centre, *nb[2];
+    int           tid, bad;
+    uint32_t      horz, vert;
+} HostLogicTf;
+
+static void *host_logic_tf_thread(void *arg) {
+    HostLogicTf *a = (HostLogicTf *)arg;
+    MeContext   *m = calloc(1, sizeof *m);
+    const uint32_t nb64 = 2; /* 128 x 64 */
+    for (uint32_t b = 0; b < nb64; b++)
+        for (int f = 0; f < 2; f++) {
+            if (!svt_me_gpu_tf_ready(&a->centre->pcs, &a->nb[f]->pcs)) { a->bad = 1; continue; }
+            m->tf_use_pred_64x64_only_th = 1;
+            if (svt_me_gpu_tf_block(&a->centre->pcs, m, &a->nb[f]->pcs, 2 * f, nb64, b) != EB_ErrorNone) { a->bad = 2; continue; }
+            /* the fake engine's pattern: (registration count of the neighbour) * 100000 + block * 100 + PU */
+            const uint32_t v = m->p_sb_best_sad[0][0][3];
+            if (v % 100000u != b * 100u + 3u || v / 100000u == 0) a->bad = 3;
+            if (m->p_best_sad_32x32 != &m->p_sb_best_sad[0][0][1] || m->search_results[0][0].hme_sc_x != (int16_t)b) a->bad = 4;
+            if ((m->tf_use_pred_64x64_only_th == (uint8_t)~0) != (int)(b & 1)) a->bad = 5;
+        }
+    a->horz = m->tf_tot_horz_blks;
+    a->vert = m->tf_tot_vert_blks;
+    svt_me_gpu_tf_centre_done(&a->centre->pcs);
+    free(m);
+    return NULL;
+}
+
+REF_API int ref_hook_host_logic(const char *fake_library_path, uint64_t *report) {
+    typedef int (*CountsFn)(uint64_t *);
+    uint64_t            c[8];
+    SequenceControlSet *scs = calloc(1, sizeof *scs);
+    EbPaReferenceObject obj[3];
+    HostLogicPic       *p = calloc(5, sizeof *p);
+    DGDetectorSeg       dg;
+    int                 rc = 0;
+    memset(obj, 0, sizeof obj);
+    memset(&dg, 0, sizeof dg);
+    if (svt_me_gpu_hook_init(fake_library_path, 128, 64, 4, 3, 8) != EB_ErrorNone)
+        return -1;
+    void    *h = dlopen(fake_library_path, RTLD_NOW | RTLD_NOLOAD);
+    CountsFn counts = h ? (CountsFn)dlsym(h, "fake_engine_counts") : NULL;
+    if (!counts)
+        return -2;
+#define STEP(n, cond) do { if (!rc && !(cond)) rc = -(n); } while (0)
+    /* 10: picture analysis registers a picture by its PA reference object and gets the two planes back */
+    host_logic_pic(&p[0], &obj[0], scs, 0);
+    STEP(10, svt_me_gpu_downsample(&p[0].pcs, &p[0].full, &p[0].quarter, &p[0].sixteenth) == EB_ErrorNone);
+    counts(c);
+    STEP(11, c[0] == 1 && c[1] == 0 && c[5] == 2 && p[0].q[0] == 1 * 16 + 1 && p[0].s[0] == 1 * 16 + 2);
+    /* 20: the temporal filter rewrote the picture: same object again -> the first version is released, a new identity */
+    STEP(20, svt_me_gpu_downsample(&p[0].pcs, &p[0].full, &p[0].quarter, &p[0].sixteenth) == EB_ErrorNone);
+    counts(c);
+    STEP(21, c[0] == 2 && c[1] == 1 && p[0].q[0] == 2 * 16 + 1 && svt_me_gpu_downsample_count() == 2);
+    /* 30: two more pictures; then the pool hands object 0 to a new picture (POC 7): the old pyramid goes */
+    host_logic_pic(&p[1], &obj[1], scs, 1);
+    host_logic_pic(&p[2], &obj[2], scs, 2);
+    STEP(30, svt_me_gpu_downsample(&p[1].pcs, &p[1].full, &p[1].quarter, &p[1].sixteenth) == EB_ErrorNone);
+    STEP(31, svt_me_gpu_downsample(&p[2].pcs, &p[2].full, &p[2].quarter, &p[2].sixteenth) == EB_ErrorNone);
+    host_logic_pic(&p[3], &obj[0], scs, 7);
+    STEP(32, svt_me_gpu_downsample(&p[3].pcs, &p[3].full, &p[3].quarter, &p[3].sixteenth) == EB_ErrorNone);
+    STEP(33, counts(c) == 3 && c[0] == 5 && c[1] == 2);
+    /* 40: the detector gets the identities of the two OBJECTS (registration counts 3 and 4), not the picture numbers */
+    EbPaReferenceObject stranger;
+    memset(&stranger, 0, sizeof stranger);
+    host_logic_pic(&p[4], &stranger, scs, 9); /* never downsampled */
+    STEP(40, svt_me_gpu_dg_ready(&p[1].pcs, &p[2].pcs) && !svt_me_gpu_dg_ready(&p[1].pcs, &p[4].pcs));
+    p[1].pcs.dg_detector = &dg;
+    dg.ref_pic           = &p[2].pcs;
+    STEP(41, svt_me_gpu_dg_detector(&p[1].pcs) == EB_ErrorNone && dg.metrics.tot_dist == 3 && dg.metrics.tot_cplx == 4 &&
+                 dg.metrics.tot_active == 1 && dg.metrics.sum_in_vectors == 2);
+    /* 50: temporal filter of centre 1 with neighbours 2 and 7 (object 0): eight segment threads, two blocks, two pairs ->
+       exactly two jobs; every thread sees the pair's results; the totals are handed out once per pair */
+    pthread_t   th[8];
+    HostLogicTf a[8];
+    for (int i = 0; i < 8; i++) {
+        a[i] = (HostLogicTf){&p[1], {&p[2], &p[3]}, i, 0, 0, 0};
+        pthread_create(&th[i], NULL, host_logic_tf_thread, &a[i]);
+    }
+    uint32_t horz = 0, vert = 0;
+    int      bad  = 0;
+    for (int i = 0; i < 8; i++) {
+        pthread_join(th[i], NULL);
+        horz += a[i].horz; vert += a[i].vert; bad |= a[i].bad;
+    }
+    counts(c);
+    STEP(50, !bad);
+    STEP(51, c[2] == 2 && c[4] == 2 && horz == 10 && vert == 14);
+    /* 60: all eight segments are through: the pairs are gone, the same pair asked again is a new job */
+    a[0] = (HostLogicTf){&p[1], {&p[2], &p[3]}, 0, 0, 0, 0};
+    p[1].pcs.tf_segments_total_count = 1;
+    host_logic_tf_thread(&a[0]);
+    counts(c);
+    STEP(60, !a[0].bad && c[2] == 4 && c[4] == 4);
+    STEP(61, c[7] == 0); /* nothing the engine had to reject */
+#undef STEP
+    report[8] = (uint64_t)counts(report);
+    svt_me_gpu_hook_shutdown();
+    free(p); free(scs);
+    return rc;
 }
