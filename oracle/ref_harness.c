@@ -934,6 +934,24 @@ static void *host_logic_tf_thread(void *arg) {
     return NULL;
 }
 
+typedef struct HostLogicSeg {
+    PictureParentControlSet *pcs;
+    EbErrorType              rc;
+} HostLogicSeg;
+
+static void *host_logic_seg_thread(void *arg) { /* one TASK_PAME segment item of me_process.c:215-262 */
+    HostLogicSeg *a = (HostLogicSeg *)arg;
+    MeContext    *m = calloc(1, sizeof *m);
+    m->me_type                     = ME_OPEN_LOOP;
+    m->num_of_list_to_search       = 2;
+    m->num_of_ref_pic_to_search[0] = m->num_of_ref_pic_to_search[1] = 1;
+    for (int l = 0; l < 2; l++)
+        m->me_ds_ref_array[l][0].picture_number = ((EbPaReferenceObject *)a->pcs->ref_pa_pic_ptr_array[l][0]->object_ptr)->picture_number;
+    a->rc = svt_me_gpu_segment(a->pcs, m);
+    free(m);
+    return NULL;
+}
+
 REF_API int ref_hook_host_logic(const char *fake_library_path, uint64_t *report) {
     typedef int (*CountsFn)(uint64_t *);
     uint64_t            c[8];
@@ -1000,6 +1018,50 @@ REF_API int ref_hook_host_logic(const char *fake_library_path, uint64_t *report)
     host_logic_tf_thread(&a[0]);
     counts(c);
     STEP(60, !a[0].bad && c[2] == 4 && c[4] == 4);
+    /* 70: open-loop ME of picture 1 with references 2 (list 0) and 7 (list 1): its six segment items arrive on six threads;
+       ONE submit and ONE wait, every thread returns after the results are in the pcs; nothing is uploaded again */
+    {
+        PictureParentControlSet *pcs = &p[1].pcs;
+        MotionEstimationData     md;
+        MeSbResults              res[2], *rp[2] = {&res[0], &res[1]};
+        uint8_t                  idx[2][85], cand[2][85 * 3 * sizeof(MeCandidate)];
+        MvCandidate              mv[2][85 * 2];
+        uint32_t                 arr[6][2];
+        uint8_t                  flags[2][2];
+        memset(&md, 0, sizeof md);
+        for (int b = 0; b < 2; b++) {
+            res[b].total_me_candidate_index = idx[b];
+            res[b].me_candidate_array       = (MeCandidate *)cand[b];
+            res[b].me_mv_array              = mv[b];
+        }
+        md.me_results = rp; md.max_cand = 3; md.max_refs = 2; md.max_l0 = 1;
+        pcs->pa_me_data = &md;
+        pcs->enable_me_8x8 = pcs->enable_me_16x16 = 1;
+        pcs->max_number_of_pus_per_sb = 85;
+        pcs->me_64x64_distortion = arr[0]; pcs->me_32x32_distortion = arr[1]; pcs->me_16x16_distortion = arr[2];
+        pcs->me_8x8_distortion = arr[3]; pcs->me_8x8_cost_variance = arr[4]; pcs->rc_me_distortion = arr[5];
+        pcs->stationary_block_present_sb = flags[0]; pcs->rc_me_allow_gm = flags[1];
+        pcs->me_segments_total_count = 6;
+        pcs->ref_pa_pic_ptr_array[0][0] = &p[2].wrap;
+        pcs->ref_pa_pic_ptr_array[1][0] = &p[3].wrap;
+        uint64_t     before[8];
+        pthread_t    ts[6];
+        HostLogicSeg sa[6];
+        counts(before);
+        for (int i = 0; i < 6; i++) {
+            sa[i].pcs = pcs; sa[i].rc = EB_ErrorUndefined;
+            pthread_create(&ts[i], NULL, host_logic_seg_thread, &sa[i]);
+        }
+        int ok = 1;
+        for (int i = 0; i < 6; i++) {
+            pthread_join(ts[i], NULL);
+            ok &= sa[i].rc == EB_ErrorNone;
+        }
+        counts(c);
+        STEP(70, ok);
+        STEP(71, c[2] == before[2] + 1 && c[3] == before[3] + 1 && c[0] == before[0]);
+        STEP(72, idx[1][84] == (uint8_t)(85 + 84) && idx[0][3] == 3); /* scattered into the per-b64 MeSbResults */
+    }
     STEP(61, c[7] == 0); /* nothing the engine had to reject */
 #undef STEP
     report[8] = (uint64_t)counts(report);

@@ -103,6 +103,10 @@ static int retire(uint64_t id, int exact, uint8_t type, uint64_t ref, MeGpuOutpu
                     out->tf_hme_sad[b] = b + 1; out->tf_early_exit[b] = (uint8_t)(b & 1);
                 }
             if (out) { out->tf_tot_horz_blks = 5; out->tf_tot_vert_blks = 7; }
+            if (out && out->total_me_candidate_index) { /* open-loop pattern: 85 PUs per b64, the index names (b64, PU) */
+                out->pu_count = 85;
+                for (uint32_t k = 0; k < out->b64_count * 85u; k++) out->total_me_candidate_index[k] = (uint8_t)k;
+            }
             break;
         }
     if (rc != ME_GPU_OK) cnt[7]++;
