@@ -28,3 +28,20 @@ def test_binding_host_logic_against_a_stand_in_engine():
     assert (registers, releases, held) == (5, 2, 3)
     assert (submits, wait_pairs, waits, dg_calls, rejected) == (5, 4, 1, 1, 0)
     assert read_planes == 2 * registers  # a quarter and a sixteenth plane per pyramid
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/Source"), reason="builds against the reference's headers")
+def test_binding_host_logic_is_race_free_under_threadsanitizer():
+    """the same scenario as a stand-alone program with the hook, the harness and the stand-in engine built with
+    -fsanitize=thread (make -C oracle tsan): the once-per-picture / once-per-pair protocols under a race detector"""
+    import subprocess
+    oracle = os.path.join(HERE, "..", "oracle")
+    b = subprocess.run(["make", "-C", oracle, "tsan"], capture_output=True, text=True)
+    if b.returncode != 0:
+        pytest.skip("no ThreadSanitizer runtime for this compiler: " + b.stderr[-300:])
+    exe, fake = os.path.join(oracle, "_ref", "host_logic_tsan"), os.path.join(oracle, "_ref", "libme_fake_engine_tsan.so")
+    r = subprocess.run([exe, os.path.abspath(fake)], capture_output=True, text=True, timeout=300,
+                       env=dict(os.environ, TSAN_OPTIONS="halt_on_error=0 exitcode=66"))
+    out = r.stdout + r.stderr
+    assert "ThreadSanitizer" not in out, out[-3000:]
+    assert r.returncode == 0 and "ref_hook_host_logic rc 0" in out, out[-1000:]
